@@ -1,0 +1,3 @@
+// TEST INFRASTRUCTURE ONLY (oracle/): see opencv2/core/mat.hpp in this directory.
+#pragma once
+#include "core/mat.hpp"
