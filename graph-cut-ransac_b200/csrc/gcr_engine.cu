@@ -1,0 +1,525 @@
+// Host side of libgcr_b200.so: buffer management, launch sequence and the extern "C" ABI declared in
+// include/gcr_b200.h.  Compiled for sm_100a only, with -fmad=false (see gcr_exact.cuh).
+#include "gcr_kernels.cuh"
+#include "../../include/gcr_b200.h"
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+#include <algorithm>
+#include <new>
+
+namespace
+{
+using namespace gcr;
+
+static_assert(sizeof(Record) == sizeof(gcr_record), "record layout");
+static_assert(sizeof(Model4) == 32, "model layout");
+
+template <typename T>
+struct DevBuf
+{
+    T* p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t n)
+    {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        const size_t want = n + n / 4 + 64;
+        cudaError_t e = cudaMalloc(&p, want * sizeof(T));
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release()
+    {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+} // namespace
+
+struct gcr_engine_s
+{
+    int device = 0;
+    int n_sm = 148;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, evk0 = nullptr, evk1 = nullptr;
+    std::string err;
+
+    // features
+    int ns = 0, no = 0, ncs = 0, nco = 0;
+    DevBuf<double> d_scale, d_orient;
+    const double* scale_ptr = nullptr; // adopted or owned
+    const double* orient_ptr = nullptr;
+    DevBuf<float> d_fs, d_fo;
+    DevBuf<unsigned int> d_irr_s, d_irr_o;
+    DevBuf<Scene> d_scene;
+
+    // hypotheses
+    int n_hyp = 0;
+    unsigned long long first_hyp = 0;
+    bool have_masks = false, have_run = false;
+    DevBuf<int> d_samples;
+    DevBuf<Model4> d_models;
+    DevBuf<unsigned char> d_flags;
+    DevBuf<double> d_sums, d_score;
+    DevBuf<unsigned int> d_cnts, d_ninl, d_masks, d_fast_hyp, d_hard_hyp;
+    DevBuf<float4> d_pf0, d_pf1;
+    DevBuf<uint2> d_worklist;
+    DevBuf<unsigned int> d_cand_hyp, d_cand_cnt, d_cand_masks, d_best_masks;
+    DevBuf<Model4> d_cand_model;
+    DevBuf<double> d_cand_score;
+    DevBuf<Counters> d_ctr;
+    DevBuf<Record> d_record;
+    DevBuf<double> d_dbg_in, d_dbg_out;
+
+    int fail(int code, const std::string& msg)
+    {
+        err = msg;
+        return code;
+    }
+    int cuda_fail(cudaError_t e, const char* what)
+    {
+        err = std::string(what) + ": " + cudaGetErrorString(e);
+        return GCR_ERR_CUDA;
+    }
+};
+
+#define GCR_CUDA(call)                                             \
+    do                                                             \
+    {                                                              \
+        cudaError_t e_ = (call);                                   \
+        if (e_ != cudaSuccess) return h->cuda_fail(e_, #call);     \
+    } while (0)
+
+namespace
+{
+
+// r^2 = z P(z), z = tan^2: degree-3 interpolation of P(z) = (atan(sqrt z)/sqrt z)^2 at Chebyshev nodes of
+// [0, zmax]; returns the maximum relative error of z P(z) against atan^2 on a dense grid.
+double fit_atan2_poly(double zmax, float pc[4])
+{
+    auto P = [](double z) {
+        if (z < 1e-12) return 1.0 - 2.0 * z / 3.0;
+        const double s = std::sqrt(z), a = std::atan(s) / s;
+        return a * a;
+    };
+    double x[4], y[4];
+    for (int i = 0; i < 4; i++)
+    {
+        x[i] = 0.5 * zmax * (1.0 + std::cos(M_PI * (2.0 * i + 1.0) / 8.0));
+        y[i] = P(x[i]);
+    }
+    // Newton divided differences -> monomial coefficients
+    double dd[4] = {y[0], y[1], y[2], y[3]};
+    for (int j = 1; j < 4; j++)
+        for (int i = 3; i >= j; i--) dd[i] = (dd[i] - dd[i - 1]) / (x[i] - x[i - j]);
+    double c[4] = {dd[3], 0, 0, 0}; // Horner expansion of the Newton form
+    int deg = 0;
+    for (int k = 2; k >= 0; k--)
+    {
+        // c(z) <- c(z) * (z - x[k]) + dd[k]
+        double nc[4] = {0, 0, 0, 0};
+        for (int i = 0; i <= deg; i++)
+        {
+            nc[i + 1] += c[i];
+            nc[i] -= c[i] * x[k];
+        }
+        nc[0] += dd[k];
+        deg++;
+        for (int i = 0; i <= deg; i++) c[i] = nc[i];
+    }
+    for (int i = 0; i < 4; i++) pc[i] = static_cast<float>(c[i]);
+    double worst = 0.0;
+    for (int i = 1; i <= 2000; i++)
+    {
+        const double z = zmax * i / 2000.0;
+        const double approx = ((static_cast<double>(pc[3]) * z + pc[2]) * z + pc[1]) * z + pc[0];
+        worst = std::max(worst, std::fabs(approx - P(z)) / P(z));
+    }
+    return worst;
+}
+
+Thresholds make_thresholds(const double thr[2])
+{
+    Thresholds T;
+    std::memset(&T, 0, sizeof(T));
+    T.tsq[0] = (2.25 * thr[0]) * thr[0]; // S1: MSAC_scoring_function.hpp:64
+    T.tsq[1] = (2.25 * thr[1]) * thr[1];
+    const double tr0 = std::sqrt(T.tsq[0]), tr1 = std::sqrt(T.tsq[1]);
+    T.Tp = static_cast<float>(tr0 / (3.0 * kLn2));
+    T.scale_unit = static_cast<float>((3.0 * kLn2) * (3.0 * kLn2));
+    T.orient_all_exact = 0;
+    if (!(tr1 < 0.6)) // beyond ~34 degrees the tan-domain test loses its margin: exact path
+    {
+        T.orient_all_exact = 1;
+        T.tanT = 0.5f;
+    }
+    else
+    {
+        const double tt = std::tan(tr1);
+        T.tanT = static_cast<float>(tt);
+        const double zmax = (tt * 1.01 + 1e-6) * (tt * 1.01 + 1e-6);
+        const double fit_err = fit_atan2_poly(zmax, T.pc);
+        if (fit_err > 5e-7) T.orient_all_exact = 1;
+    }
+    // rounding of tanT to float + rcp (1 ulp) + two multiplies + polynomial-free compare
+    T.t_band0 = static_cast<float>(26.0 * kU + 4.0 * kU * T.tanT);
+    return T;
+}
+
+Buffers make_buffers(gcr_engine_s* h, unsigned long long seed, bool have_samples, void* record_user)
+{
+    Buffers B;
+    std::memset(&B, 0, sizeof(B));
+    B.scale = h->scale_ptr;
+    B.orient = h->orient_ptr;
+    B.ns = h->ns;
+    B.no = h->no;
+    B.fs = h->d_fs.p;
+    B.fo = h->d_fo.p;
+    B.ncs = h->ncs;
+    B.nco = h->nco;
+    B.scene = h->d_scene.p;
+    B.irr_s = h->d_irr_s.p;
+    B.irr_o = h->d_irr_o.p;
+    B.n_hyp = h->n_hyp;
+    B.first_hyp = h->first_hyp;
+    B.seed = seed;
+    B.samples = h->d_samples.p;
+    B.have_samples = have_samples ? 1 : 0;
+    B.models = h->d_models.p;
+    B.flags = h->d_flags.p;
+    B.sums = h->d_sums.p;
+    B.cnts = h->d_cnts.p;
+    B.score = h->d_score.p;
+    B.n_inl = h->d_ninl.p;
+    B.masks = h->have_masks ? h->d_masks.p : nullptr;
+    B.ws = (h->ns + 31) / 32;
+    B.wmask = B.ws + (h->no + 31) / 32;
+    B.pf0 = h->d_pf0.p;
+    B.pf1 = h->d_pf1.p;
+    B.fast_hyp = h->d_fast_hyp.p;
+    B.hard_hyp = h->d_hard_hyp.p;
+    B.worklist = h->d_worklist.p;
+    B.worklist_cap = static_cast<unsigned int>(std::min<size_t>(h->d_worklist.cap, 0x7fffffffu));
+    B.cand_hyp = h->d_cand_hyp.p;
+    B.cand_model = h->d_cand_model.p;
+    B.cand_score = h->d_cand_score.p;
+    B.cand_cnt = h->d_cand_cnt.p;
+    B.cand_masks = h->d_cand_masks.p;
+    B.ctr = h->d_ctr.p;
+    B.record = h->d_record.p;
+    B.record_user = record_user;
+    B.best_masks = h->d_best_masks.p;
+    return B;
+}
+
+int ensure_common(gcr_engine_s* h)
+{
+    const size_t W = static_cast<size_t>((h->ns + 31) / 32 + (h->no + 31) / 32);
+    GCR_CUDA(h->d_ctr.ensure(1));
+    GCR_CUDA(h->d_record.ensure(1));
+    GCR_CUDA(h->d_cand_hyp.ensure(kCandCap));
+    GCR_CUDA(h->d_cand_model.ensure(kCandCap));
+    GCR_CUDA(h->d_cand_score.ensure(kCandCap));
+    GCR_CUDA(h->d_cand_cnt.ensure(2 * kCandCap));
+    GCR_CUDA(h->d_cand_masks.ensure(W * kCandCap));
+    GCR_CUDA(h->d_best_masks.ensure(W));
+    return GCR_OK;
+}
+
+} // namespace
+
+extern "C"
+{
+
+const char* gcr_version(void) { return "gcr_b200 0.1 sm_100a"; }
+
+int gcr_create(int device, gcr_handle* out)
+{
+    if (!out) return GCR_ERR_INVALID;
+    *out = nullptr;
+    gcr_engine_s* h = new (std::nothrow) gcr_engine_s();
+    if (!h) return GCR_ERR_NOMEM;
+    h->device = device;
+    cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreate(&h->ev0);
+    if (e == cudaSuccess) e = cudaEventCreate(&h->ev1);
+    if (e == cudaSuccess) e = cudaEventCreate(&h->evk0);
+    if (e == cudaSuccess) e = cudaEventCreate(&h->evk1);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&h->n_sm, cudaDevAttrMultiProcessorCount, device);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(k_score_fast<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ScoreSmem));
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(k_score_fast<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ScoreSmem));
+    if (e != cudaSuccess)
+    {
+        // keep the handle so that gcr_last_error can be read; every later call fails with GCR_ERR_CUDA
+        h->cuda_fail(e, "gcr_create");
+        *out = h;
+        return GCR_ERR_CUDA;
+    }
+    h->stream = h->own_stream;
+    *out = h;
+    return GCR_OK;
+}
+
+int gcr_destroy(gcr_handle h)
+{
+    if (!h) return GCR_ERR_INVALID;
+    cudaSetDevice(h->device);
+    if (h->own_stream) cudaStreamSynchronize(h->own_stream);
+    h->d_scale.release(); h->d_orient.release(); h->d_fs.release(); h->d_fo.release();
+    h->d_irr_s.release(); h->d_irr_o.release(); h->d_scene.release(); h->d_samples.release();
+    h->d_models.release(); h->d_flags.release(); h->d_sums.release(); h->d_score.release();
+    h->d_cnts.release(); h->d_ninl.release(); h->d_masks.release(); h->d_fast_hyp.release();
+    h->d_hard_hyp.release(); h->d_pf0.release(); h->d_pf1.release(); h->d_worklist.release();
+    h->d_cand_hyp.release(); h->d_cand_cnt.release(); h->d_cand_masks.release(); h->d_best_masks.release();
+    h->d_cand_model.release(); h->d_cand_score.release(); h->d_ctr.release(); h->d_record.release();
+    h->d_dbg_in.release(); h->d_dbg_out.release();
+    if (h->ev0) cudaEventDestroy(h->ev0);
+    if (h->ev1) cudaEventDestroy(h->ev1);
+    if (h->evk0) cudaEventDestroy(h->evk0);
+    if (h->evk1) cudaEventDestroy(h->evk1);
+    if (h->own_stream) cudaStreamDestroy(h->own_stream);
+    delete h;
+    return GCR_OK;
+}
+
+const char* gcr_last_error(gcr_handle h) { return h ? h->err.c_str() : "null handle"; }
+
+int gcr_set_stream(gcr_handle h, void* cuda_stream)
+{
+    if (!h) return GCR_ERR_INVALID;
+    h->stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : h->own_stream;
+    return GCR_OK;
+}
+
+int gcr_set_features(gcr_handle h, const double* scale, int64_t ns, const double* orient, int64_t no, int on_device)
+{
+    if (!h) return GCR_ERR_INVALID;
+    if (!h->stream) return h->fail(GCR_ERR_STATE, "engine was not created successfully");
+    if (!scale || !orient) return h->fail(GCR_ERR_INVALID, "null feature pointer");
+    // bindings.cpp:206-224: at least 2 rows per class (the minimal sample size)
+    if (ns < 2 || no < 2) return h->fail(GCR_ERR_INVALID, "each feature class needs at least 2 rows of 3 columns");
+    if (ns > (1ll << 30) || no > (1ll << 30)) return h->fail(GCR_ERR_INVALID, "feature count too large");
+    GCR_CUDA(cudaSetDevice(h->device));
+    h->ns = static_cast<int>(ns);
+    h->no = static_cast<int>(no);
+    h->ncs = (h->ns + kChunk - 1) / kChunk;
+    h->nco = (h->no + kChunk - 1) / kChunk;
+    h->have_run = false;
+    if (on_device)
+    {
+        h->scale_ptr = scale;
+        h->orient_ptr = orient;
+    }
+    else
+    {
+        GCR_CUDA(h->d_scale.ensure(3 * static_cast<size_t>(ns)));
+        GCR_CUDA(h->d_orient.ensure(3 * static_cast<size_t>(no)));
+        GCR_CUDA(cudaMemcpyAsync(h->d_scale.p, scale, sizeof(double) * 3 * ns, cudaMemcpyHostToDevice, h->stream));
+        GCR_CUDA(cudaMemcpyAsync(h->d_orient.p, orient, sizeof(double) * 3 * no, cudaMemcpyHostToDevice, h->stream));
+        h->scale_ptr = h->d_scale.p;
+        h->orient_ptr = h->d_orient.p;
+    }
+    GCR_CUDA(h->d_fs.ensure(static_cast<size_t>(h->ncs) * kChunkFloats));
+    GCR_CUDA(h->d_fo.ensure(static_cast<size_t>(h->nco) * kChunkFloats));
+    GCR_CUDA(h->d_irr_s.ensure(kIrrCap));
+    GCR_CUDA(h->d_irr_o.ensure(kIrrCap));
+    GCR_CUDA(h->d_scene.ensure(1));
+    GCR_CUDA(cudaMemsetAsync(h->d_scene.p, 0, sizeof(Scene), h->stream));
+    const int n = std::max(h->ncs, h->nco) * kChunk;
+    k_prep_features<<<(n + 255) / 256, 256, 0, h->stream>>>(h->scale_ptr, h->ns, h->orient_ptr, h->no, h->d_fs.p,
+                                                           h->d_fo.p, h->ncs, h->nco, h->d_scene.p, h->d_irr_s.p,
+                                                           h->d_irr_o.p);
+    GCR_CUDA(cudaGetLastError());
+    return ensure_common(h);
+}
+
+int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, const int32_t* samples,
+            const double thr[2], uint32_t flags, void* d_record, gcr_result* out)
+{
+    if (!h) return GCR_ERR_INVALID;
+    if (h->ns < 2) return h->fail(GCR_ERR_STATE, "gcr_run before gcr_set_features");
+    if (n_hyp < 1 || n_hyp > (1ll << 30)) return h->fail(GCR_ERR_INVALID, "n_hyp out of range");
+    if (!thr || !(thr[0] >= 0.0) || !(thr[1] >= 0.0) || !std::isfinite(thr[0]) || !std::isfinite(thr[1]))
+        return h->fail(GCR_ERR_INVALID, "thresholds must be finite and non-negative");
+    GCR_CUDA(cudaSetDevice(h->device));
+    const size_t H = static_cast<size_t>(n_hyp);
+    const size_t W = static_cast<size_t>((h->ns + 31) / 32 + (h->no + 31) / 32);
+    h->n_hyp = static_cast<int>(n_hyp);
+    h->first_hyp = first_hyp;
+    h->have_masks = (flags & GCR_RUN_EMIT_MASKS) != 0;
+    GCR_CUDA(h->d_samples.ensure(4 * H));
+    GCR_CUDA(h->d_models.ensure(H));
+    GCR_CUDA(h->d_flags.ensure(H));
+    GCR_CUDA(h->d_sums.ensure(2 * H));
+    GCR_CUDA(h->d_cnts.ensure(2 * H));
+    GCR_CUDA(h->d_score.ensure(H));
+    GCR_CUDA(h->d_ninl.ensure(2 * H));
+    GCR_CUDA(h->d_fast_hyp.ensure(H));
+    GCR_CUDA(h->d_hard_hyp.ensure(H));
+    GCR_CUDA(h->d_pf0.ensure(H));
+    GCR_CUDA(h->d_pf1.ensure(H));
+    GCR_CUDA(h->d_worklist.ensure(std::max<size_t>(1u << 16, 4 * H)));
+    if (h->have_masks) GCR_CUDA(h->d_masks.ensure(H * W));
+    int rc = ensure_common(h);
+    if (rc != GCR_OK) return rc;
+
+    cudaStream_t s = h->stream;
+    if (samples)
+    {
+        if (flags & GCR_RUN_SAMPLES_ON_DEVICE)
+            GCR_CUDA(cudaMemcpyAsync(h->d_samples.p, samples, sizeof(int) * 4 * H, cudaMemcpyDeviceToDevice, s));
+        else
+            GCR_CUDA(cudaMemcpyAsync(h->d_samples.p, samples, sizeof(int) * 4 * H, cudaMemcpyHostToDevice, s));
+    }
+    const Thresholds T = make_thresholds(thr);
+    const Buffers B = make_buffers(h, seed, samples != nullptr, d_record);
+    const int all_exact = (flags & GCR_RUN_ALL_EXACT) ? 1 : 0;
+
+    GCR_CUDA(cudaEventRecord(h->ev0, s));
+    GCR_CUDA(cudaMemsetAsync(h->d_ctr.p, 0, sizeof(Counters), s));
+    if (h->have_masks) GCR_CUDA(cudaMemsetAsync(h->d_masks.p, 0, sizeof(unsigned int) * H * W, s));
+    const int hb = static_cast<int>((H + 127) / 128);
+    k_sample_solve<<<hb, 128, 0, s>>>(B, T, all_exact);
+    {
+        const int max_tiles = static_cast<int>((H + kTileHyps - 1) / kTileHyps);
+        const int grid = std::max(1, std::min(max_tiles * (h->ncs + h->nco), h->n_sm * 8));
+        GCR_CUDA(cudaEventRecord(h->evk0, s));
+        if (h->have_masks)
+            k_score_fast<true><<<grid, kScoreThreads, sizeof(ScoreSmem), s>>>(B, T);
+        else
+            k_score_fast<false><<<grid, kScoreThreads, sizeof(ScoreSmem), s>>>(B, T);
+        GCR_CUDA(cudaEventRecord(h->evk1, s));
+    }
+    k_fixup<<<h->n_sm * 2, 256, 0, s>>>(B, T);
+    k_exact_items<<<h->n_sm * 4, kExactThreads, 0, s>>>(B, T, 0);
+    k_finalize<<<hb, 128, 0, s>>>(B, T);
+    k_collect<<<hb, 128, 0, s>>>(B, 4e-5);
+    k_exact_items<<<64, kExactThreads, 0, s>>>(B, T, 1);
+    k_select<<<1, 128, 0, s>>>(B);
+    GCR_CUDA(cudaEventRecord(h->ev1, s));
+    GCR_CUDA(cudaGetLastError());
+    h->have_run = true;
+
+    if (out)
+    {
+        GCR_CUDA(cudaStreamSynchronize(s));
+        Counters c;
+        Record r;
+        GCR_CUDA(cudaMemcpy(&c, h->d_ctr.p, sizeof(c), cudaMemcpyDeviceToHost));
+        GCR_CUDA(cudaMemcpy(&r, h->d_record.p, sizeof(r), cudaMemcpyDeviceToHost));
+        std::memset(out, 0, sizeof(*out));
+        out->best_index = r.index;
+        out->best_score = r.score;
+        for (int i = 0; i < 4; i++) out->best_model[i] = r.model[i];
+        out->best_n_inl[0] = r.n_inl[0];
+        out->best_n_inl[1] = r.n_inl[1];
+        out->n_hyp = n_hyp;
+        out->n_sample_valid = c.n_sample_valid;
+        out->n_solved = c.n_solved;
+        out->n_rechecked = c.n_worklist;
+        out->n_exact_hyp = c.n_hard;
+        out->n_candidates = c.n_candidates;
+        GCR_CUDA(cudaEventElapsedTime(&out->device_ms, h->ev0, h->ev1));
+        GCR_CUDA(cudaEventElapsedTime(&out->score_kernel_ms, h->evk0, h->evk1));
+        if (c.n_bad_sample) return h->fail(GCR_ERR_INVALID, "replayed sample indices out of range");
+        if (c.n_worklist_overflow) return h->fail(GCR_ERR_STATE, "guard-band worklist overflow");
+    }
+    return GCR_OK;
+}
+
+int gcr_best(gcr_handle h, double model[4], double* score, uint32_t n_inl[2], uint32_t* scale_mask_words,
+             uint32_t* orient_mask_words, int64_t* hyp_index)
+{
+    if (!h) return GCR_ERR_INVALID;
+    if (!h->have_run) return h->fail(GCR_ERR_STATE, "gcr_best before gcr_run");
+    GCR_CUDA(cudaSetDevice(h->device));
+    GCR_CUDA(cudaStreamSynchronize(h->stream));
+    Record r;
+    GCR_CUDA(cudaMemcpy(&r, h->d_record.p, sizeof(r), cudaMemcpyDeviceToHost));
+    if (model) for (int i = 0; i < 4; i++) model[i] = r.model[i];
+    if (score) *score = r.score;
+    if (n_inl) { n_inl[0] = r.n_inl[0]; n_inl[1] = r.n_inl[1]; }
+    if (hyp_index) *hyp_index = r.index;
+    const size_t ws = (h->ns + 31) / 32, wo = (h->no + 31) / 32;
+    if (scale_mask_words) GCR_CUDA(cudaMemcpy(scale_mask_words, h->d_best_masks.p, 4 * ws, cudaMemcpyDeviceToHost));
+    if (orient_mask_words) GCR_CUDA(cudaMemcpy(orient_mask_words, h->d_best_masks.p + ws, 4 * wo, cudaMemcpyDeviceToHost));
+    return GCR_OK;
+}
+
+int gcr_fetch(gcr_handle h, uint8_t* flags, double* models, double* score, uint32_t* n_inl, uint32_t* masks,
+              int32_t* samples)
+{
+    if (!h) return GCR_ERR_INVALID;
+    if (!h->have_run) return h->fail(GCR_ERR_STATE, "gcr_fetch before gcr_run");
+    GCR_CUDA(cudaSetDevice(h->device));
+    GCR_CUDA(cudaStreamSynchronize(h->stream));
+    const size_t H = static_cast<size_t>(h->n_hyp);
+    const size_t W = static_cast<size_t>((h->ns + 31) / 32 + (h->no + 31) / 32);
+    if (flags) GCR_CUDA(cudaMemcpy(flags, h->d_flags.p, H, cudaMemcpyDeviceToHost));
+    if (models) GCR_CUDA(cudaMemcpy(models, h->d_models.p, H * sizeof(Model4), cudaMemcpyDeviceToHost));
+    if (score) GCR_CUDA(cudaMemcpy(score, h->d_score.p, H * sizeof(double), cudaMemcpyDeviceToHost));
+    if (n_inl) GCR_CUDA(cudaMemcpy(n_inl, h->d_ninl.p, 2 * H * sizeof(unsigned int), cudaMemcpyDeviceToHost));
+    if (samples) GCR_CUDA(cudaMemcpy(samples, h->d_samples.p, 4 * H * sizeof(int), cudaMemcpyDeviceToHost));
+    if (masks)
+    {
+        if (!h->have_masks) return h->fail(GCR_ERR_STATE, "masks were not kept: run with GCR_RUN_EMIT_MASKS");
+        GCR_CUDA(cudaMemcpy(masks, h->d_masks.p, H * W * sizeof(unsigned int), cudaMemcpyDeviceToHost));
+    }
+    return GCR_OK;
+}
+
+int gcr_score_model(gcr_handle h, const double model[4], const double thr[2], double* score, uint32_t n_inl[2],
+                    uint32_t* scale_mask_words, uint32_t* orient_mask_words)
+{
+    if (!h || !model || !thr) return GCR_ERR_INVALID;
+    if (h->ns < 2) return h->fail(GCR_ERR_STATE, "gcr_score_model before gcr_set_features");
+    GCR_CUDA(cudaSetDevice(h->device));
+    int rc = ensure_common(h);
+    if (rc != GCR_OK) return rc;
+    const Thresholds T = make_thresholds(thr);
+    const Buffers B = make_buffers(h, 0, false, nullptr);
+    const Model4 m = {model[0], model[1], model[2], model[3]};
+    cudaStream_t s = h->stream;
+    k_set_model<<<1, 1, 0, s>>>(B, m);
+    k_exact_items<<<1, kExactThreads, 0, s>>>(B, T, 2);
+    GCR_CUDA(cudaGetLastError());
+    GCR_CUDA(cudaStreamSynchronize(s));
+    const size_t ws = (h->ns + 31) / 32, wo = (h->no + 31) / 32;
+    if (score) GCR_CUDA(cudaMemcpy(score, h->d_cand_score.p, sizeof(double), cudaMemcpyDeviceToHost));
+    if (n_inl) GCR_CUDA(cudaMemcpy(n_inl, h->d_cand_cnt.p, 2 * sizeof(unsigned int), cudaMemcpyDeviceToHost));
+    if (scale_mask_words) GCR_CUDA(cudaMemcpy(scale_mask_words, h->d_cand_masks.p, 4 * ws, cudaMemcpyDeviceToHost));
+    if (orient_mask_words) GCR_CUDA(cudaMemcpy(orient_mask_words, h->d_cand_masks.p + ws, 4 * wo, cudaMemcpyDeviceToHost));
+    return GCR_OK;
+}
+
+int gcr_debug_eval(gcr_handle h, int which, const double* in, int64_t n, const double model[4], double* out)
+{
+    if (!h || !in || !out || n < 1 || which < 0 || which > 4) return GCR_ERR_INVALID;
+    if (!h->stream) return h->fail(GCR_ERR_STATE, "engine was not created successfully");
+    GCR_CUDA(cudaSetDevice(h->device));
+    GCR_CUDA(h->d_dbg_in.ensure(3 * static_cast<size_t>(n)));
+    GCR_CUDA(h->d_dbg_out.ensure(static_cast<size_t>(n)));
+    Model4 m = {0, 0, 1, 0};
+    if (model) m = Model4{model[0], model[1], model[2], model[3]};
+    GCR_CUDA(cudaMemcpyAsync(h->d_dbg_in.p, in, sizeof(double) * 3 * n, cudaMemcpyHostToDevice, h->stream));
+    k_debug_eval<<<static_cast<int>((n + 127) / 128), 128, 0, h->stream>>>(which, h->d_dbg_in.p, static_cast<int>(n), m,
+                                                                           h->d_dbg_out.p);
+    GCR_CUDA(cudaGetLastError());
+    GCR_CUDA(cudaMemcpyAsync(out, h->d_dbg_out.p, sizeof(double) * n, cudaMemcpyDeviceToHost, h->stream));
+    GCR_CUDA(cudaStreamSynchronize(h->stream));
+    return GCR_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,184 @@
+"""ctypes view of the C ABI in include/gcr_b200.h (libgcr_b200.so).
+
+This is what tests/ (``-m gpu``) and bench.py call: plain pointers and sizes straight into the shared
+library, no torch types.  The product has no CPU fallback: if the library is missing or was not built
+for this GPU, construction fails loudly.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(PKG_DIR, "libgcr_b200.so")
+
+FLAG_SAMPLE_VALID, FLAG_SOLVED, FLAG_MODEL_VALID, FLAG_EXACT = 1, 2, 4, 8
+RUN_EMIT_MASKS, RUN_SAMPLES_ON_DEVICE, RUN_KEEP_PER_HYP, RUN_ALL_EXACT = 1, 2, 4, 8
+
+EXPORTS = [
+    "gcr_create", "gcr_destroy", "gcr_last_error", "gcr_set_stream", "gcr_set_features", "gcr_run", "gcr_best",
+    "gcr_fetch", "gcr_score_model", "gcr_debug_eval", "gcr_version",
+]
+
+
+class GcrResult(C.Structure):
+    _fields_ = [
+        ("best_index", C.c_int64), ("best_score", C.c_double), ("best_model", C.c_double * 4),
+        ("best_n_inl", C.c_uint32 * 2), ("pad_", C.c_uint32 * 2), ("n_hyp", C.c_int64),
+        ("n_sample_valid", C.c_int64), ("n_solved", C.c_int64), ("n_rechecked", C.c_int64),
+        ("n_exact_hyp", C.c_int64), ("n_candidates", C.c_int64), ("device_ms", C.c_float),
+        ("score_kernel_ms", C.c_float),
+    ]
+
+
+RECORD_DTYPE = np.dtype([("score", "<f8"), ("index", "<i8"), ("model", "<f8", 4), ("n_inl", "<u4", 2),
+                         ("reserved", "<u8")])
+assert RECORD_DTYPE.itemsize == 64
+
+
+class GcrError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"gcr_b200 error {code}: {msg}")
+        self.code = code
+
+
+def load_library() -> C.CDLL:
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "(nvcc, sm_100a). There is no CPU fallback.")
+    lib = C.CDLL(LIB_PATH)
+    vp, i64, u64, u32 = C.c_void_p, C.c_int64, C.c_uint64, C.c_uint32
+    lib.gcr_create.argtypes = [C.c_int, C.POINTER(vp)]
+    lib.gcr_destroy.argtypes = [vp]
+    lib.gcr_last_error.argtypes = [vp]
+    lib.gcr_last_error.restype = C.c_char_p
+    lib.gcr_set_stream.argtypes = [vp, vp]
+    lib.gcr_set_features.argtypes = [vp, vp, i64, vp, i64, C.c_int]
+    lib.gcr_run.argtypes = [vp, i64, u64, u64, vp, C.POINTER(C.c_double), u32, vp, C.POINTER(GcrResult)]
+    lib.gcr_best.argtypes = [vp, vp, vp, vp, vp, vp, vp]
+    lib.gcr_fetch.argtypes = [vp, vp, vp, vp, vp, vp, vp]
+    lib.gcr_score_model.argtypes = [vp, vp, vp, vp, vp, vp, vp]
+    lib.gcr_debug_eval.argtypes = [vp, C.c_int, vp, i64, vp, vp]
+    lib.gcr_version.restype = C.c_char_p
+    for name in EXPORTS:
+        fn = getattr(lib, name)
+        if name not in ("gcr_last_error", "gcr_version"):
+            fn.restype = C.c_int
+    return lib
+
+
+def unpack_mask(words: np.ndarray, n: int) -> np.ndarray:
+    bits = np.unpackbits(np.ascontiguousarray(words, np.uint32).view(np.uint8), bitorder="little")
+    return bits[:n].astype(bool)
+
+
+class Engine:
+    """Thin RAII wrapper of a gcr_handle."""
+
+    def __init__(self, device: int = 0):
+        self.lib = load_library()
+        self.h = C.c_void_p()
+        rc = self.lib.gcr_create(device, C.byref(self.h))
+        if rc != 0:
+            msg = self.lib.gcr_last_error(self.h).decode() if self.h else "gcr_create failed"
+            raise GcrError(rc, msg)
+        self.ns = self.no = 0
+        self.n_hyp = 0
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.gcr_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != 0:
+            raise GcrError(rc, self.lib.gcr_last_error(self.h).decode())
+
+    def set_stream(self, cuda_stream: int):
+        self._check(self.lib.gcr_set_stream(self.h, C.c_void_p(cuda_stream)))
+
+    def set_features(self, scale: np.ndarray, orient: np.ndarray):
+        """Host float64 [N,3] arrays (copied to the device inside the call)."""
+        scale = np.ascontiguousarray(scale, np.float64)
+        orient = np.ascontiguousarray(orient, np.float64)
+        if scale.ndim != 2 or orient.ndim != 2 or scale.shape[1] != 3 or orient.shape[1] != 3:
+            raise ValueError("features must be [N,3] arrays")
+        self._keep = (scale, orient)
+        self.ns, self.no = len(scale), len(orient)
+        self._check(self.lib.gcr_set_features(self.h, scale.ctypes.data, self.ns, orient.ctypes.data, self.no, 0))
+
+    def set_features_device(self, scale_ptr: int, ns: int, orient_ptr: int, no: int):
+        """Device pointers to float64 [N,3] row-major arrays (zero-copy; caller keeps them alive)."""
+        self.ns, self.no = ns, no
+        self._check(self.lib.gcr_set_features(self.h, C.c_void_p(scale_ptr), ns, C.c_void_p(orient_ptr), no, 1))
+
+    def run(self, n_hyp, thr, seed=0, first_hyp=0, samples=None, flags=0, record_ptr=None, sync=True,
+            samples_ptr=None):
+        thr_c = (C.c_double * 2)(float(thr[0]), float(thr[1]))
+        sp = None
+        if samples is not None:
+            samples = np.ascontiguousarray(samples, np.int32)
+            if samples.shape != (n_hyp, 4):
+                raise ValueError("samples must be int32 [n_hyp,4]")
+            self._samples_keep = samples
+            sp = C.c_void_p(samples.ctypes.data)
+        elif samples_ptr is not None:
+            sp = C.c_void_p(samples_ptr)
+            flags |= RUN_SAMPLES_ON_DEVICE
+        res = GcrResult()
+        self.n_hyp = n_hyp
+        rc = self.lib.gcr_run(self.h, n_hyp, seed, first_hyp, sp, thr_c, flags,
+                              C.c_void_p(record_ptr) if record_ptr else None, C.byref(res) if sync else None)
+        self._check(rc)
+        return res if sync else None
+
+    def best(self):
+        model = np.zeros(4)
+        score = C.c_double()
+        n_inl = np.zeros(2, np.uint32)
+        sm = np.zeros((self.ns + 31) // 32, np.uint32)
+        om = np.zeros((self.no + 31) // 32, np.uint32)
+        idx = C.c_int64()
+        self._check(self.lib.gcr_best(self.h, model.ctypes.data, C.byref(score), n_inl.ctypes.data, sm.ctypes.data,
+                                      om.ctypes.data, C.byref(idx)))
+        return dict(model=model, score=score.value, n_inl=n_inl, scale_mask=unpack_mask(sm, self.ns),
+                    orient_mask=unpack_mask(om, self.no), index=idx.value, scale_words=sm, orient_words=om)
+
+    def fetch(self, masks=False, samples=False):
+        H = self.n_hyp
+        W = (self.ns + 31) // 32 + (self.no + 31) // 32
+        out = dict(flags=np.zeros(H, np.uint8), models=np.zeros((H, 4)), score=np.zeros(H),
+                   n_inl=np.zeros((H, 2), np.uint32))
+        out["masks"] = np.zeros((H, W), np.uint32) if masks else None
+        out["samples"] = np.zeros((H, 4), np.int32) if samples else None
+        self._check(self.lib.gcr_fetch(self.h, out["flags"].ctypes.data, out["models"].ctypes.data,
+                                       out["score"].ctypes.data, out["n_inl"].ctypes.data,
+                                       out["masks"].ctypes.data if masks else None,
+                                       out["samples"].ctypes.data if samples else None))
+        return out
+
+    def score_model(self, model, thr):
+        model = np.ascontiguousarray(model, np.float64)
+        thr = np.ascontiguousarray(thr, np.float64)
+        score = C.c_double()
+        n_inl = np.zeros(2, np.uint32)
+        sm = np.zeros((self.ns + 31) // 32, np.uint32)
+        om = np.zeros((self.no + 31) // 32, np.uint32)
+        self._check(self.lib.gcr_score_model(self.h, model.ctypes.data, thr.ctypes.data, C.byref(score),
+                                             n_inl.ctypes.data, sm.ctypes.data, om.ctypes.data))
+        return score.value, n_inl, unpack_mask(sm, self.ns), unpack_mask(om, self.no)
+
+    def debug_eval(self, which, abc, model=None):
+        abc = np.ascontiguousarray(abc, np.float64).reshape(-1, 3)
+        out = np.zeros(len(abc))
+        m = np.ascontiguousarray(model if model is not None else [0, 0, 1, 0], np.float64)
+        self._check(self.lib.gcr_debug_eval(self.h, which, abc.ctypes.data, len(abc), m.ctypes.data, out.ctypes.data))
+        return out

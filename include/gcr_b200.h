@@ -1,0 +1,139 @@
+/*
+ * gcr_b200.h -- C ABI of the B200-native hybrid-RANSAC hypothesis engine (libgcr_b200.so).
+ *
+ * One batched device call replaces the reference's per-iteration hypothesise/verify loop
+ *     sample -> isValidSample -> estimateModel -> getScore -> best-model update
+ * of yuvalnis/graph-cut-ransac, src/pygcransac/include/GCRANSAC.h:286-485, for the hybrid
+ * (scale-change + orientation-change) rectifying-homography problem:
+ *     sampler      GCRANSAC.h:53-80,160-189      (get_random_subset / GCRANSAC::sample)
+ *     degeneracy   estimators/solver_rectifying_homography_two_sift.hpp:141-215  (isValidSample)
+ *     solver       ...two_sift.hpp:261-344       (estimateMinimalModel), :45-61 (isValidModel)
+ *     residuals    ...two_sift.hpp:621-713, model.h:128-204, math_utils.hpp:78-102
+ *     MSAC         scoring_functions/MSAC_scoring_function.hpp:22-130, score.hpp:11-102
+ *     selection    GCRANSAC.h:440-462 (strict '<' on Score::value, earliest wins ties)
+ *
+ * Conventions: plain pointers and sizes, no C++/torch types; every call returns 0 (GCR_OK) or a
+ * negative gcr_status and never throws; the caller owns every buffer it passes, the handle owns
+ * all device memory; one CUDA stream per handle (replaceable with gcr_set_stream so the engine
+ * can be ordered against a caller's NCCL / PyTorch work).  Feature rows are the reference's:
+ * scale (x, y, s) and orientation (x, y, theta[rad]), float64, row-major [N,3]
+ * (bindings.cpp:181-250, gcransac_python.cpp:284-296).
+ *
+ * Packed masks: uint32 words, bit j of word w <-> feature 32*w + j, scale class first
+ * (ceil(Ns/32) words) then orientation class (ceil(No/32) words).
+ */
+#ifndef GCR_B200_H
+#define GCR_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct gcr_engine_s* gcr_handle;
+
+enum gcr_status
+{
+    GCR_OK = 0,
+    GCR_ERR_INVALID = -1, /* bad argument (the binding maps it to std::invalid_argument) */
+    GCR_ERR_CUDA = -2,    /* a CUDA call failed; see gcr_last_error */
+    GCR_ERR_STATE = -3,   /* call order violated (e.g. run before set_features) */
+    GCR_ERR_NOMEM = -4
+};
+
+/* per-hypothesis flag bits (gcr_fetch) */
+#define GCR_FLAG_SAMPLE_VALID 1u /* isValidSample accepted the minimal sample */
+#define GCR_FLAG_SOLVED 2u       /* estimateMinimalModel produced a model */
+#define GCR_FLAG_MODEL_VALID 4u  /* isValidModel (max(|h7|,|h8|) < 1e-3) */
+#define GCR_FLAG_EXACT 8u        /* scored entirely in FP64 (outside the FP32 fast path's proven range) */
+
+/* gcr_run flags */
+#define GCR_RUN_EMIT_MASKS 1u        /* keep the packed inlier mask of EVERY hypothesis (parity / replay mode) */
+#define GCR_RUN_SAMPLES_ON_DEVICE 2u /* `samples` is a device pointer */
+#define GCR_RUN_KEEP_PER_HYP 4u      /* keep per-hypothesis models/scores/counts for gcr_fetch (implied by EMIT_MASKS) */
+#define GCR_RUN_ALL_EXACT 8u         /* score every hypothesis with the FP64 reference-order kernel (validation) */
+
+typedef struct gcr_result
+{
+    int64_t best_index;    /* GLOBAL hypothesis index (first_hyp + local) of the selected model, -1 if none */
+    double best_score;     /* its MSAC score, FP64 reference-order evaluation */
+    double best_model[4];  /* h7, h8, alpha, phi; the vanishing line is (h7, h8, 1) */
+    uint32_t best_n_inl[2];
+    uint32_t pad_[2];
+    int64_t n_hyp;          /* hypothesis slots processed by this call */
+    int64_t n_sample_valid; /* ... that passed isValidSample */
+    int64_t n_solved;       /* ... that yielded a model (these are scored against every feature) */
+    int64_t n_rechecked;    /* (hypothesis, feature) pairs inside the FP32 guard band, re-evaluated in FP64 */
+    int64_t n_exact_hyp;    /* hypotheses scored entirely in FP64 */
+    int64_t n_candidates;   /* near-best hypotheses re-scored in FP64 before the final selection */
+    float device_ms;        /* CUDA-event time of the whole hypothesis stage on the engine stream */
+    float score_kernel_ms;  /* CUDA-event time of the dominant FP32 scoring kernel alone */
+} gcr_result;
+
+/* Winner record written to device memory by the last kernel of gcr_run when `d_record` is given:
+ * ready to be the send buffer of an NCCL all-gather (one 64-byte record per rank). */
+typedef struct gcr_record
+{
+    double score;        /* 0 when no model */
+    int64_t index;       /* global hypothesis index, -1 when no model */
+    double model[4];
+    uint32_t n_inl[2];
+    uint64_t reserved;
+} gcr_record;
+
+int gcr_create(int device, gcr_handle* out);
+int gcr_destroy(gcr_handle h);
+const char* gcr_last_error(gcr_handle h);
+
+/* Use `cuda_stream` (a cudaStream_t) for all subsequent work; NULL restores the engine's own stream. */
+int gcr_set_stream(gcr_handle h, void* cuda_stream);
+
+/* Upload (or adopt from device memory when on_device != 0) the two feature classes and build the
+ * FP32 structure-of-arrays working set.  Replaces the cv::Mat construction of
+ * gcransac_python.cpp:284-296.  Requires ns >= 2 and no >= 2 (bindings.cpp:199-224). */
+int gcr_set_features(gcr_handle h, const double* scale, int64_t ns, const double* orient, int64_t no, int on_device);
+
+/* The hypothesis stage over `n_hyp` hypothesis slots with global indices
+ * [first_hyp, first_hyp + n_hyp).
+ *   samples == NULL : draw minimal samples on the device, Philox4x32-10 keyed by `seed`, counter =
+ *                     global hypothesis index (results do not depend on how slots are sharded);
+ *   samples != NULL : replay int32[n_hyp,4] = (scale0, scale1, orient0, orient1) supplied by the caller.
+ *   thr             : the two residual thresholds (settings.threshold, gcransac_python.cpp:313-314).
+ *   d_record        : optional DEVICE pointer to a gcr_record the final kernel fills (NCCL send buffer).
+ * The call is asynchronous with respect to the host unless `out` is non-NULL, in which case it
+ * synchronises the stream and fills *out. */
+int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, const int32_t* samples,
+            const double thr[2], uint32_t flags, void* d_record, gcr_result* out);
+
+/* Selected model of the last gcr_run: model, score, counts and packed masks (any pointer may be NULL).
+ * Synchronises the stream.  *hyp_index = -1 and zeroed outputs when no model was found. */
+int gcr_best(gcr_handle h, double model[4], double* score, uint32_t n_inl[2], uint32_t* scale_mask_words,
+             uint32_t* orient_mask_words, int64_t* hyp_index);
+
+/* Per-hypothesis outputs of the last gcr_run (needs GCR_RUN_KEEP_PER_HYP / GCR_RUN_EMIT_MASKS), copied
+ * to HOST buffers; any pointer may be NULL.  flags u8[H]; models f64[H,4]; score f64[H]; n_inl u32[H,2]
+ * (after the MSAC zero-reset rule); masks u32[H, ceil(Ns/32)+ceil(No/32)]; samples i32[H,4]. */
+int gcr_fetch(gcr_handle h, uint8_t* flags, double* models, double* score, uint32_t* n_inl, uint32_t* masks,
+              int32_t* samples);
+
+/* Score ONE caller-supplied model (h7,h8,alpha,phi) against the resident features with the FP64
+ * reference-order kernel: MSACScoringFunction::getScore for a single model.  Used to materialise the
+ * global winner's masks on every rank after the multi-GPU combine, and by the host-side local
+ * optimisation.  Host output buffers, any may be NULL.  Synchronises. */
+int gcr_score_model(gcr_handle h, const double model[4], const double thr[2], double* score, uint32_t n_inl[2],
+                    uint32_t* scale_mask_words, uint32_t* orient_mask_words);
+
+/* Device-side helper math, evaluated on the GPU by the same __device__ functions the kernels use.
+ * which: 0 clipAngle(a) 1 minAngleDiff(a,b) 2 linesAnglesDiff(a,b)
+ *        3 scaleResidual(x=a,y=b,s=c; model) 4 orientationResidual(x=a,y=b,theta=c; model)
+ * in: f64[n,3] (a,b,c), model f64[4], out: f64[n].  Host buffers. */
+int gcr_debug_eval(gcr_handle h, int which, const double* in, int64_t n, const double model[4], double* out);
+
+/* Library / build identification, e.g. "gcr_b200 0.1 sm_100a". */
+const char* gcr_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GCR_B200_H */

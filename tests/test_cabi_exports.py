@@ -1,0 +1,52 @@
+"""CPU-side checks of the drop-in boundary: the shared library loads without a GPU and exports every
+symbol include/gcr_b200.h declares (no compute calls here)."""
+import ctypes
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    import __graft_entry__ as g
+    if not os.path.exists(g.LIB):
+        g.build()
+    import gcr_capi
+    return gcr_capi.load_library()
+
+
+def test_header_symbols_are_exported(lib):
+    hdr = open(os.path.join(ROOT, "include", "gcr_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(gcr_[a-z_]+)\s*\(", hdr))
+    assert {"gcr_create", "gcr_destroy", "gcr_set_features", "gcr_run", "gcr_best", "gcr_last_error"} <= declared
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in gcr_b200.h but not exported"
+    import gcr_capi
+    assert declared == set(gcr_capi.EXPORTS)
+
+
+def test_version_and_struct_layout(lib):
+    import gcr_capi
+    assert b"sm_100a" in lib.gcr_version()
+    assert ctypes.sizeof(gcr_capi.GcrResult) == 8 + 8 + 32 + 8 + 8 + 6 * 8 + 8
+    assert gcr_capi.RECORD_DTYPE.itemsize == 64
+
+
+def test_null_handle_is_an_error_not_a_crash(lib):
+    assert lib.gcr_destroy(None) == -1
+    assert lib.gcr_set_features(None, None, 0, None, 0, 0) == -1
+    assert lib.gcr_last_error(None) == b"null handle"
+
+
+def test_no_cpu_fallback_in_product_sources():
+    """The product path must not reach into oracle/ (BASELINE tier rule)."""
+    pkg = os.path.join(ROOT, "graph-cut-ransac_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h", ".hpp")):
+                text = open(os.path.join(dirpath, f), errors="ignore").read()
+                assert "oracle_lib" not in text and "libgcr_oracle" not in text and "libgcr_ref" not in text, f

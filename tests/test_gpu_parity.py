@@ -1,0 +1,238 @@
+"""GPU parity tests (run on the B200 box with ``-m gpu``): the CUDA hypothesis stage, called through the
+C ABI of libgcr_b200.so, against the CPU oracle on identical replayed minimal samples.
+
+Bars (BASELINE.json north_star): inlier masks and counts bit-exact, MSAC scores to 1e-5 relative,
+model / vanishing line (h7, h8, 1) to 1e-6 relative; flags and the selected hypothesis identical.
+"""
+import hashlib
+import math
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+SCORE_RTOL = 1e-5
+MODEL_RTOL = 1e-6
+
+
+@pytest.fixture(scope="module")
+def eng():
+    import gcr_capi
+    e = gcr_capi.Engine(0)
+    yield e
+    e.close()
+
+
+def _compare(dev, ora, ns, no, check_masks=True, label=""):
+    f_d, f_o = dev["flags"] & 7, ora["flags"] & 7
+    assert np.array_equal(f_d, f_o), f"{label}: flags differ at {np.nonzero(f_d != f_o)[0][:10]}"
+    solved = (f_o & 2) > 0
+    md, mo = dev["models"][solved], ora["models"][solved]
+    assert np.allclose(md, mo, rtol=MODEL_RTOL, atol=1e-300), f"{label}: models differ, max rel {np.max(np.abs(md - mo) / np.abs(mo))}"
+    assert np.array_equal(dev["n_inl"], ora["n_inl"]), (
+        f"{label}: inlier counts differ at {np.nonzero((dev['n_inl'] != ora['n_inl']).any(1))[0][:10]}")
+    assert np.allclose(dev["score"], ora["score"], rtol=SCORE_RTOL, atol=1e-9), (
+        f"{label}: scores differ, max rel {np.max(np.abs(dev['score'] - ora['score']) / np.maximum(ora['score'], 1e-9))}")
+    if check_masks:
+        assert np.array_equal(dev["masks"], ora["masks"]), (
+            f"{label}: masks differ in hypotheses {np.nonzero((dev['masks'] != ora['masks']).any(1))[0][:10]}")
+
+
+def _run_replay(eng, scale, orient, samples, thr, masks=True, extra_flags=0):
+    import gcr_capi
+    eng.set_features(scale, orient)
+    flags = (gcr_capi.RUN_EMIT_MASKS if masks else gcr_capi.RUN_KEEP_PER_HYP) | extra_flags
+    res = eng.run(len(samples), thr, samples=samples, flags=flags)
+    return res, eng.fetch(masks=masks)
+
+
+def test_device_helper_math(eng, port):
+    """The 16 known-answer cases of tests/unit_tests.cpp that concern angles, evaluated by the device functions."""
+    pi = math.pi
+    cases = [(-pi / 2, 1.5 * pi), (0.7861, 0.7861), (0.0, 0.0), (2.7 * pi, 0.7 * pi), (-pi, pi)]
+    out = eng.debug_eval(0, [(a, 0, 0) for a, _ in cases])
+    assert np.allclose(out, [e for _, e in cases], atol=1e-9)
+    cases = [(0.0, 0.0, 0.0), (-pi / 2, 0.0, pi / 2), (-3.48 * pi, 7.41 * pi, 0.89 * pi), (0.25 * pi, 1.25 * pi, pi)]
+    out = eng.debug_eval(1, [(a, b, 0) for a, b, _ in cases])
+    assert np.allclose(out, [e for _, _, e in cases], atol=1e-9)
+    cases = [(0.0, 0.0, 0.0), (-pi / 2, 0.0, pi / 2), (0.52 * pi, 1.49 * pi, 0.03 * pi), (1.49 * pi, 0.52 * pi, 0.03 * pi),
+             (-3.48 * pi, 5.60 * pi, 0.08 * pi), (0.25 * pi, 1.25 * pi, 0.0)]
+    out = eng.debug_eval(2, [(a, b, 0) for a, b, _ in cases])
+    assert np.allclose(out, [e for _, _, e in cases], atol=1e-9)
+    # random: the angle helpers use only exact operations (fmod, +, -, fabs, fmin): identical doubles
+    rng = np.random.default_rng(0)
+    ab = rng.uniform(-40, 40, size=(2000, 3))
+    for which, fn in ((0, lambda r: port.clip_angle(r[0])), (1, lambda r: port.min_angle_diff(r[0], r[1])),
+                      (2, lambda r: port.lines_angles_diff(r[0], r[1]))):
+        assert np.array_equal(eng.debug_eval(which, ab), np.array([fn(r) for r in ab]))
+
+
+def test_device_residuals_vs_golden_reference(eng, golden_dir):
+    """FP64 device residuals vs the reference's own residual tables (differences = libm last ulps)."""
+    g = np.load(os.path.join(golden_dir, "residuals_c1.npz"))
+    c1 = np.load(os.path.join(golden_dir, "hyp_stage_c1.npz"))
+    for m, rs, ro in zip(g["models"], g["rs"], g["ro"]):
+        ds = eng.debug_eval(3, c1["scale"], m)
+        do = eng.debug_eval(4, c1["orient"], m)
+        big = rs > 1e300  # DBL_MAX sentinel
+        assert np.array_equal(ds > 1e300, big)
+        assert np.allclose(ds[~big], rs[~big], rtol=1e-12, atol=1e-14)
+        assert np.allclose(do, ro, rtol=1e-12, atol=1e-14)
+
+
+@pytest.mark.parametrize("name", ["hyp_stage_small.npz", "hyp_stage_edge.npz"])
+def test_replay_matches_reference_golden(eng, golden_dir, name):
+    g = np.load(os.path.join(golden_dir, name))
+    res, dev = _run_replay(eng, g["scale"], g["orient"], g["samples"], g["thr"])
+    _compare(dev, g, len(g["scale"]), len(g["orient"]), label=name)
+    assert res.best_index == int(g["best"])
+
+
+def test_threshold_sweep_matches_reference_golden(eng, golden_dir):
+    g = np.load(os.path.join(golden_dir, "hyp_stage_sweep.npz"))
+    for p in (1, 2, 4, 8, 20):
+        ora = {k: g[f"p{p}_{k}"] for k in ("flags", "models", "score", "n_inl", "masks")}
+        _, dev = _run_replay(eng, g["scale"], g["orient"], g[f"p{p}_samples"], g[f"p{p}_thr"])
+        _compare(dev, ora, len(g["scale"]), len(g["orient"]), label=f"sweep p={p}")
+
+
+def test_config_c1_matches_reference_golden(eng, golden_dir):
+    """BASELINE config C1: 2000 + 500 features, 5000 replayed samples; mask digest of the reference."""
+    g = np.load(os.path.join(golden_dir, "hyp_stage_c1.npz"))
+    res, dev = _run_replay(eng, g["scale"], g["orient"], g["samples"], g["thr"])
+    _compare(dev, g, 2000, 500, check_masks=False, label="C1")
+    assert hashlib.sha256(np.ascontiguousarray(dev["masks"]).tobytes()).hexdigest() == str(g["masks_sha256"])
+    assert res.best_index == int(g["best"])
+    b = eng.best()
+    ws = (2000 + 31) // 32
+    assert np.array_equal(np.concatenate([b["scale_words"], b["orient_words"]]), g["best_masks"])
+    assert np.array_equal(b["n_inl"], g["n_inl"][int(g["best"])])
+    assert np.allclose(b["model"], g["models"][int(g["best"])], rtol=MODEL_RTOL)
+    assert abs(b["score"] - g["score"][int(g["best"])]) <= 1e-9 * g["score"][int(g["best"])]
+    # vanishing line (h7, h8, 1) of the winner vs the generating plane
+    assert np.allclose(b["model"][:2], g["truth"][:2], atol=5e-5)
+    assert res.n_solved == int(((g["flags"] & 2) > 0).sum())
+    assert ws == len(b["scale_words"])
+
+
+def test_config_c2_replay_vs_oracle(eng, port):
+    """BASELINE config C2: the C1 scene, 100k replayed hypotheses, all masks bit-exact vs the oracle."""
+    import gcr_scenes as gs
+    sc = gs.config_scene("C2")
+    smp = gs.draw_samples(100_000, 2000, 500, gs.SAMPLE_SEED)
+    ora = port.replay(sc.scale, sc.orient, smp, sc.thr, nthreads=0)
+    res, dev = _run_replay(eng, sc.scale, sc.orient, smp, sc.thr)
+    _compare(dev, ora, 2000, 500, label="C2")
+    assert res.best_index == port.select_best(ora["score"], ora["flags"])
+    # the fast path did the work: only a small share of pairs/hypotheses took the FP64 routes
+    assert res.n_exact_hyp < 0.02 * res.n_solved
+    assert res.n_rechecked < 1e-3 * res.n_solved * 2500
+
+
+def test_all_exact_mode_equals_fast_mode(eng, port):
+    import gcr_capi
+    import gcr_scenes as gs
+    sc = gs.make_scene(700, 333, 0.3, 21)
+    smp = gs.draw_samples(3000, 700, 333, 22)
+    _, fast = _run_replay(eng, sc.scale, sc.orient, smp, sc.thr)
+    _, exact = _run_replay(eng, sc.scale, sc.orient, smp, sc.thr, extra_flags=gcr_capi.RUN_ALL_EXACT)
+    assert np.array_equal(fast["masks"], exact["masks"])
+    assert np.array_equal(fast["n_inl"], exact["n_inl"])
+    assert np.allclose(fast["score"], exact["score"], rtol=SCORE_RTOL)
+    ora = port.replay(sc.scale, sc.orient, smp, sc.thr)
+    _compare(exact, ora, 700, 333, label="all-exact")
+    assert np.allclose(exact["score"], ora["score"], rtol=1e-11)
+
+
+def test_philox_sampler_matches_oracle_and_sharding_invariance(eng, port):
+    import gcr_capi
+    import gcr_scenes as gs
+    sc = gs.make_scene(1500, 400, 0.3, 5)
+    eng.set_features(sc.scale, sc.orient)
+    H, seed = 20_000, 0xC0FFEE1234
+    res = eng.run(H, sc.thr, seed=seed, flags=gcr_capi.RUN_EMIT_MASKS)
+    dev = eng.fetch(masks=True, samples=True)
+    smp = port.sample_philox(seed, 0, H, 1500, 400)
+    assert np.array_equal(dev["samples"], smp)
+    ora = port.replay(sc.scale, sc.orient, smp, sc.thr, nthreads=0)
+    _compare(dev, ora, 1500, 400, label="philox")
+    assert res.best_index == port.select_best(ora["score"], ora["flags"])
+    whole = eng.best()
+    # two shards with global counters reproduce the same hypotheses; the better shard winner is the global one
+    recs = []
+    for first in (0, H // 2):
+        r = eng.run(H // 2, sc.thr, seed=seed, first_hyp=first, flags=gcr_capi.RUN_KEEP_PER_HYP)
+        d = eng.fetch()
+        assert np.array_equal(d["flags"], dev["flags"][first:first + H // 2])
+        assert np.array_equal(d["n_inl"], dev["n_inl"][first:first + H // 2])
+        recs.append((r.best_score, -r.best_index, r.best_index))
+    assert max(recs)[2] == whole["index"]
+
+
+def test_large_scene_slice_and_properties(eng, port):
+    """C3-sized feature set (50k + 20k, 10 % inliers): oracle parity on a slice, then size-independent
+    properties on a bigger batch: winner masks == single-model scoring, popcount == counts, idempotence."""
+    import gcr_capi
+    import gcr_scenes as gs
+    sc = gs.config_scene("C3")
+    smp = gs.draw_samples(3000, 50_000, 20_000, 77)
+    ora = port.replay(sc.scale, sc.orient, smp, sc.thr, nthreads=0)
+    res, dev = _run_replay(eng, sc.scale, sc.orient, smp, sc.thr)
+    _compare(dev, ora, 50_000, 20_000, label="C3 slice")
+    assert res.best_index == port.select_best(ora["score"], ora["flags"])
+    # bigger batch, Philox, no per-hypothesis masks
+    r1 = eng.run(60_000, sc.thr, seed=9)
+    b1 = eng.best()
+    r2 = eng.run(60_000, sc.thr, seed=9)
+    b2 = eng.best()
+    assert r1.best_index == r2.best_index and b1["score"] == b2["score"]
+    assert np.array_equal(b1["scale_words"], b2["scale_words"])
+    s, n, sm, om = eng.score_model(b1["model"], sc.thr)
+    assert s == b1["score"] and np.array_equal(n, b1["n_inl"])
+    assert np.array_equal(sm, b1["scale_mask"]) and np.array_equal(om, b1["orient_mask"])
+    assert (sm.sum(), om.sum()) == tuple(b1["n_inl"])
+    # the winner explains the planted plane
+    assert np.allclose(b1["model"][:2], sc.model[:2], atol=5e-5)
+    assert (sm & sc.scale_is_inlier).sum() > 0.9 * sc.scale_is_inlier.sum()
+    # and matches the oracle's scoring of the same model bit-for-bit on masks
+    so, no_, smo, omo = port.score_model(sc.scale, sc.orient, b1["model"], sc.thr)
+    assert np.array_equal(sm, smo) and np.array_equal(om, omo) and abs(s - so) <= 1e-10 * so
+
+
+def test_minimal_and_ragged_inputs(eng, port):
+    import gcr_scenes as gs
+    rng = np.random.default_rng(3)
+    for ns, no in ((2, 2), (3, 5), (33, 31), (513, 511), (1025, 64)):
+        sc = gs.make_scene(ns, no, 0.5, 100 + ns)
+        smp = gs.draw_samples(257, ns, no, ns)
+        ora = port.replay(sc.scale, sc.orient, smp, sc.thr)
+        _, dev = _run_replay(eng, sc.scale, sc.orient, smp, sc.thr)
+        _compare(dev, ora, ns, no, label=f"ragged {ns}/{no}")
+    # zero thresholds: nothing but exact zeros can be an inlier
+    sc = gs.make_scene(100, 50, 0.5, 1)
+    smp = gs.draw_samples(64, 100, 50, 2)
+    thr = np.array([0.0, 0.0])
+    ora = port.replay(sc.scale, sc.orient, smp, thr)
+    _, dev = _run_replay(eng, sc.scale, sc.orient, smp, thr)
+    _compare(dev, ora, 100, 50, label="zero thr")
+    # very loose thresholds route the orientation class to the exact path
+    thr = np.array([2.0, 0.6])
+    ora = port.replay(sc.scale, sc.orient, smp, thr)
+    _, dev = _run_replay(eng, sc.scale, sc.orient, smp, thr)
+    _compare(dev, ora, 100, 50, label="loose thr")
+
+
+def test_error_conventions(eng):
+    import gcr_capi
+    with pytest.raises(gcr_capi.GcrError):
+        eng.set_features(np.zeros((1, 3)), np.zeros((5, 3)))  # < 2 rows (bindings.cpp:206-224)
+    import gcr_scenes as gs
+    sc = gs.make_scene(50, 20, 0.5, 1)
+    eng.set_features(sc.scale, sc.orient)
+    bad = np.array([[0, 1, 0, 99]], np.int32)
+    with pytest.raises(gcr_capi.GcrError):
+        eng.run(1, sc.thr, samples=bad, flags=gcr_capi.RUN_KEEP_PER_HYP)
+    with pytest.raises(gcr_capi.GcrError):
+        eng.run(10, [float("nan"), 0.1])
