@@ -1,0 +1,284 @@
+#!/usr/bin/env python
+"""bench.py -- hybrid-MSAC hypothesis stage throughput (BASELINE.json metric) on N B200s of one node.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config C2]
+
+A "step" is one pass of the hypothesis stage (replayed minimal samples -> degeneracy test -> minimal
+solver -> multi-class MSAC over every feature -> best-model selection) over one batch of hypotheses of
+the named configuration.  Metric: hypothesis x feature evaluations per second = H (Ns + No) / t, counted
+over ALL hypothesis slots as the reference's loop counts iterations (GCRANSAC.h:293,339), for both arms.
+
+`value`   device-resident inputs, CUDA-event timed on the engine stream, L2 flushed between steps.
+`e2e`     the same step through the C ABI with HOST buffers: features + samples copied host->device,
+          winner record + masks copied back, inside the timed region.
+`--impl reference` times the reference's own CPU implementation of the stage (oracle/_ref when it was
+built in the container, else the oracle port) on the host cores, on a bounded sample of the workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (os.path.join(ROOT, "graph-cut-ransac_b200"), os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import gcr_scenes as gs  # noqa: E402
+
+METRIC = "hypothesis-feature evals/sec (hybrid MSAC)"
+UNIT = "evals/s"
+# algorithmic FP32 work per evaluation (SURVEY.md 8d / DESIGN.md): scale 11 flop + 1 SFU, orientation 30 + 1
+FLOP_SCALE, FLOP_ORIENT = 11.0, 30.0
+FP32_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12  # nominal non-tensor FP32 peak at clocks.max.sm
+
+
+def workload(name: str, rank: int = 0):
+    c = gs.CONFIGS[name]
+    scene = gs.config_scene(name)
+    n_hyp = c["n_hyp"]
+    samples = gs.draw_samples(n_hyp, c["n_scale"], c["n_orient"], gs.SAMPLE_SEED + 1000 * rank)
+    return scene, samples, n_hyp
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 7 for n, v in zip(names, r[3:7]) if v.lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def cpu_reference_leg(name: str, budget_hyp: int, nthreads: int = 0):
+    """Times the reference's CPU hypothesis stage on a bounded sample of the workload."""
+    from oracle_lib import Oracle, have_reference
+    kind = "reference" if have_reference() else "port"
+    o = Oracle(kind)
+    scene, samples, n_hyp = workload(name)
+    smp = samples[:budget_hyp]
+    nfeat = len(scene.scale) + len(scene.orient)
+    o.replay(scene.scale, scene.orient, smp[:256], scene.thr, want_masks=False, nthreads=nthreads)  # warm
+    t0 = time.perf_counter()
+    r = o.replay(scene.scale, scene.orient, smp, scene.thr, want_masks=False, nthreads=nthreads)
+    dt = time.perf_counter() - t0
+    return {"value": len(smp) * nfeat / dt, "unit": UNIT, "cores": int(r["threads"]), "kind": kind,
+            "sample": f"first {len(smp)} of {n_hyp} replayed hypotheses of {name} x {nfeat} features, "
+                      f"{'unmodified reference headers on Eigen/OpenCV shims' if kind == 'reference' else 'C oracle port'}, "
+                      f"OpenMP over hypotheses, {dt:.2f} s"}, dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return  # the reference is single-process; other ranks exit without work
+    name = args.config
+    c = gs.CONFIGS[name]
+    nfeat = c["n_scale"] + c["n_orient"]
+    # bounded sample per step: ~2.5e8 evals of CPU work at most
+    budget = max(512, min(c["n_hyp"], int(2.5e8 / nfeat)))
+    for _ in range(args.warmup):
+        cpu_reference_leg(name, min(budget, 2048))
+    vals, times = [], []
+    for _ in range(args.steps):
+        leg, dt = cpu_reference_leg(name, budget)
+        vals.append(leg["value"])
+        times.append(dt)
+    value = float(np.mean(vals))
+    leg["value"] = value
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * float(np.mean(times)), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "impl": "reference",
+            "config": {"workload": f"{name}: {c['n_scale']} scale + {c['n_orient']} orientation features, "
+                                   f"{int(100 * c['inlier_ratio'])}% inliers, replayed samples, {budget} hypotheses per step (bounded sample)"},
+            "cpu_baseline": leg,
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import gcr_capi
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    name = args.config
+    scene, samples, n_hyp = workload(name, rank)
+    ns, no = len(scene.scale), len(scene.orient)
+    nfeat = ns + no
+    first_hyp = rank * n_hyp  # weak scaling: every rank owns its own block of hypothesis slots
+
+    eng = gcr_capi.Engine(local)
+    stream = torch.cuda.Stream()  # a real (non-null) stream shared by torch, NCCL and the engine
+    torch.cuda.set_stream(stream)
+    eng.set_stream(stream.cuda_stream)
+    d_scale = torch.from_numpy(scene.scale).cuda()
+    d_orient = torch.from_numpy(scene.orient).cuda()
+    d_samples = torch.from_numpy(samples).cuda()
+    d_record = torch.zeros(8, dtype=torch.float64, device="cuda")  # one 64-byte gcr_record: the NCCL send buffer
+    d_gather = torch.zeros(8 * world, dtype=torch.float64, device="cuda")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+    eng.set_features_device(d_scale.data_ptr(), ns, d_orient.data_ptr(), no)
+
+    def step():
+        eng.run(n_hyp, scene.thr, first_hyp=first_hyp, samples_ptr=d_samples.data_ptr(), record_ptr=d_record.data_ptr(),
+                sync=False)
+        if world > 1:  # the path's one exchange: 64-byte winner records, every rank then knows the global best
+            dist.all_gather_into_tensor(d_gather, d_record)
+
+    for _ in range(max(args.warmup, 3)):
+        flush.zero_()
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    torch.cuda.synchronize()
+    evs = []
+    for _ in range(args.steps):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        step()
+        e1.record(stream)
+        evs.append((e0, e1))
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    sampler.stop_flag = True
+    total_ms = sum(a.elapsed_time(b) for a, b in evs)
+    t = torch.tensor([total_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms = float(t.item())
+    ms_per_step = total_ms / args.steps
+    value = world * n_hyp * nfeat / (ms_per_step * 1e-3)
+
+    # ---- dominant kernel (FP32 MSAC scoring) timed alone, same launches, synchronous result read-back
+    res = eng.run(n_hyp, scene.thr, first_hyp=first_hyp, samples_ptr=d_samples.data_ptr(), sync=True)
+    k_ms = []
+    for _ in range(5):
+        flush.zero_()
+        r = eng.run(n_hyp, scene.thr, first_hyp=first_hyp, samples_ptr=d_samples.data_ptr(), sync=True)
+        k_ms.append(r.score_kernel_ms)
+    k_ms = float(np.median(k_ms))
+    n_fast = res.n_solved - res.n_exact_hyp
+    flops = n_fast * (ns * FLOP_SCALE + no * FLOP_ORIENT)
+    achieved = flops / (k_ms * 1e-3) / 1e12
+    alg_bytes = (res.n_solved * (32 + 32 + 4) + (ns + no) * 12)  # hypothesis parameters in/out + one pass over the features
+    roofline = {"bound": "fp32", "achieved": achieved, "peak": FP32_PEAK_TFLOPS, "unit": "TFLOP/s",
+                "frac": achieved / FP32_PEAK_TFLOPS, "traffic": None,
+                "note": "issue-bound FP32/SFU kernel (no dense contraction, HBM traffic negligible): peak = 148 SM x 128 lanes x 2 x "
+                        "1.965 GHz nominal (not in MEASURED_PEAKS.json, which holds HBM and bf16-tensor peaks only)",
+                "kernel": "k_score_fast", "kernel_ms": k_ms, "kernel_evals": int(n_fast) * nfeat,
+                "kernel_evals_per_s": n_fast * nfeat / (k_ms * 1e-3),
+                "hbm": {"algorithmic_bytes": int(alg_bytes), "achieved_gbs": alg_bytes / (k_ms * 1e-3) / 1e9}}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        roofline["hbm"]["peak_gbs_measured"] = peaks.get("hbm_gbs")
+    except Exception:
+        pass
+
+    # ---- end to end through the C ABI with HOST buffers (pinned), H2D + D2H inside the timed region
+    h_scale = torch.from_numpy(scene.scale).pin_memory()
+    h_orient = torch.from_numpy(scene.orient).pin_memory()
+    h_samples = torch.from_numpy(samples).pin_memory()
+    e2e_eng = gcr_capi.Engine(local)
+
+    def e2e_step():
+        e2e_eng.lib.gcr_set_features(e2e_eng.h, h_scale.data_ptr(), ns, h_orient.data_ptr(), no, 0)
+        e2e_eng.ns, e2e_eng.no = ns, no
+        thr_c = (gcr_capi.C.c_double * 2)(*scene.thr)
+        out = gcr_capi.GcrResult()
+        rc = e2e_eng.lib.gcr_run(e2e_eng.h, n_hyp, 0, first_hyp, gcr_capi.C.c_void_p(h_samples.data_ptr()), thr_c, 0, None,
+                                 gcr_capi.C.byref(out))
+        assert rc == 0, e2e_eng.lib.gcr_last_error(e2e_eng.h)
+        e2e_eng.n_hyp = n_hyp
+        return e2e_eng.best()
+
+    for _ in range(3):
+        best = e2e_step()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        best = e2e_step()
+    e2e_s = (time.perf_counter() - t0) / args.steps
+    t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_s = float(t.item())
+    h2d = scene.scale.nbytes + scene.orient.nbytes + samples.nbytes
+    d2h = 64 + 4 * ((ns + 31) // 32 + (no + 31) // 32) + 64
+    e2e = {"value": world * n_hyp * nfeat / e2e_s, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+           "ms_per_step": 1e3 * e2e_s, "api": "gcr_set_features + gcr_run + gcr_best (C ABI, pinned host buffers)"}
+
+    if rank == 0:
+        c = gs.CONFIGS[name]
+        cpu_leg, _ = cpu_reference_leg(name, max(512, min(n_hyp, int(2.5e8 / nfeat))))
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f32 (+f64 solver, guard-band and winner re-scoring)", "data": "synthetic",
+                "config": {"workload": f"{name}: {c['n_scale']} scale + {c['n_orient']} orientation features, "
+                                       f"{int(100 * c['inlier_ratio'])}% inliers, {n_hyp} replayed hypotheses per GPU per step",
+                           "l2": "flushed between timed steps (256 MiB write)", "hypotheses_scored_per_step": int(res.n_solved),
+                           "guard_band_pairs": int(res.n_rechecked), "exact_hypotheses": int(res.n_exact_hyp),
+                           "best_index": int(best["index"]), "best_score": float(best["score"])},
+                "clocks": sampler.summary(), "e2e": e2e, "gpu_launches": 8 * args.steps, "roofline": roofline,
+                "cpu_baseline": cpu_leg}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="C2", choices=sorted(gs.CONFIGS))
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -153,13 +153,13 @@ __device__ __forceinline__ void fence_barrier_init()
 __device__ __forceinline__ float lg2_approx(float x)
 {
     float r;
-    asm("lg2.approx.f32 %0, %1;" : "=f"(r) : "f"(x));
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
 }
 __device__ __forceinline__ float rcp_approx(float x)
 {
     float r;
-    asm("rcp.approx.f32 %0, %1;" : "=f"(r) : "f"(x));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
 }
 
@@ -347,7 +347,7 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
             const double kh = sc.k_max * (ah7 + ah8);
             const double dprime = 6.0 * kU * (2.0 + 3.0 * kh) * 1.0001;
             hard = all_exact || T.orient_all_exact || sc.irr_overflow || !isfinite(dv) || !isfinite(A) || !(v_lo > 4.0 * dv) ||
-                   !(v_hi * 1.01 < 1000.0) || !(drho < 0.25 * Tp) || !(kh < 1e6) || !isfinite(dprime) ||
+                   !(v_hi * 1.01 < 1000.0) || !(drho < 1e-3 * Tp) || !(kh < 1e6) || !isfinite(dprime) ||
                    !(ah7 < 1e6) || !(ah8 < 1e6);
             if (hard) f |= 8;
             double sphi, cphi;
@@ -395,7 +395,7 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
 struct ScaleEval
 {
     bool in, unc;
-    float d2;
+    float d;
 };
 // One (hypothesis, scale feature) evaluation.  rectified scale = v^-3, residual r = 3 ln2 |A - lg2 v|
 // (S4, two_sift.hpp:621-645).  `in`: certainly inside the truncated threshold (S1); `unc`: inside the
@@ -409,14 +409,14 @@ __device__ __forceinline__ ScaleEval eval_scale(float xq, float yq, float iq, fl
     ScaleEval e;
     e.in = fabsf(d) <= Tin;
     e.unc = (fabsf(d) <= Tout) && !e.in;
-    e.d2 = d * d;
+    e.d = d;
     return e;
 }
 
 struct OrientEval
 {
     bool in, unc;
-    float r2;
+    float z, p; // r^2 = z * p
 };
 // One (hypothesis, orientation feature) evaluation.  (denom, numer) of rectifiedAngle (model.h:156-165)
 // rotated by -phi; the residual (S5, two_sift.hpp:647-665) is the angle of that vector to the nearest
@@ -438,8 +438,8 @@ __device__ __forceinline__ OrientEval eval_orient(float k, float st, float ct, f
     OrientEval e;
     e.in = t <= T.tanT - band;
     e.unc = (t <= T.tanT + band) && !e.in;
-    const float z = t * t;
-    e.r2 = z * fmaf(z, fmaf(z, fmaf(z, T.pc[3], T.pc[2]), T.pc[1]), T.pc[0]);
+    e.z = t * t;
+    e.p = fmaf(e.z, fmaf(e.z, fmaf(e.z, T.pc[3], T.pc[2]), T.pc[1]), T.pc[0]);
     return e;
 }
 
@@ -532,9 +532,9 @@ __global__ void __launch_bounds__(kScoreThreads) k_score_fast(const __grid_const
             const float4* pa = reinterpret_cast<const float4*>(S.stage[st]);
             const float4* pb = reinterpret_cast<const float4*>(S.stage[st] + kChunk);
             const float4* pc = reinterpret_cast<const float4*>(S.stage[st] + 2 * kChunk);
-            float acc[kHB];
+            float acc[kHB], cntf[kHB]; // per-chunk FP32 partials (counts are exact integers < 2^24)
 #pragma unroll
-            for (int j = 0; j < kHB; j++) acc[j] = 0.f;
+            for (int j = 0; j < kHB; j++) acc[j] = cntf[j] = 0.f;
 
             if (chunk < B.ncs)
             {
@@ -557,8 +557,8 @@ __global__ void __launch_bounds__(kScoreThreads) k_score_fast(const __grid_const
                             const ScaleEval r = eval_scale(fa[e], fb[e], fc[e], nh7[j], nh8[j], A[j], Tin[j], Tout[j]);
                             if (r.in)
                             {
-                                acc[j] += r.d2;
-                                cnt_s[j]++;
+                                acc[j] = fmaf(r.d, r.d, acc[j]);
+                                cntf[j] += 1.0f;
                                 if (MASKS) mword[j] |= 1u << ((g * 4 + e) & 31);
                             }
                             any_unc |= r.unc;
@@ -596,7 +596,11 @@ __global__ void __launch_bounds__(kScoreThreads) k_score_fast(const __grid_const
                     }
                 }
 #pragma unroll
-                for (int j = 0; j < kHB; j++) sum_s[j] += static_cast<double>(acc[j]);
+                for (int j = 0; j < kHB; j++)
+                {
+                    sum_s[j] += static_cast<double>(acc[j]);
+                    cnt_s[j] += static_cast<unsigned int>(cntf[j]);
+                }
             }
             else
             {
@@ -620,8 +624,8 @@ __global__ void __launch_bounds__(kScoreThreads) k_score_fast(const __grid_const
                                 eval_orient(fa[e], fb[e], fc[e], nh7[j], nh8[j], cphi[j], sphi[j], dpr[j], T);
                             if (r.in)
                             {
-                                acc[j] += r.r2;
-                                cnt_o[j]++;
+                                acc[j] = fmaf(r.z, r.p, acc[j]);
+                                cntf[j] += 1.0f;
                                 if (MASKS) mword[j] |= 1u << ((g * 4 + e) & 31);
                             }
                             any_unc |= r.unc;
@@ -660,7 +664,11 @@ __global__ void __launch_bounds__(kScoreThreads) k_score_fast(const __grid_const
                     }
                 }
 #pragma unroll
-                for (int j = 0; j < kHB; j++) sum_o[j] += static_cast<double>(acc[j]);
+                for (int j = 0; j < kHB; j++)
+                {
+                    sum_o[j] += static_cast<double>(acc[j]);
+                    cnt_o[j] += static_cast<unsigned int>(cntf[j]);
+                }
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&S.empty[st]);
