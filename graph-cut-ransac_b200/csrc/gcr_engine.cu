@@ -58,6 +58,8 @@ struct gcr_engine_s
     const double* scale_ptr = nullptr; // adopted or owned
     const double* orient_ptr = nullptr;
     DevBuf<float> d_fs, d_fo;
+    DevBuf<double> d_fsd, d_fod; // FP64 SoA for the precise tiles
+    int ncsd = 0, ncod = 0;
     DevBuf<unsigned int> d_irr_s, d_irr_o;
     DevBuf<Scene> d_scene;
 
@@ -186,6 +188,10 @@ Buffers make_buffers(gcr_engine_s* h, unsigned long long seed, bool have_samples
     B.fo = h->d_fo.p;
     B.ncs = h->ncs;
     B.nco = h->nco;
+    B.fsd = h->d_fsd.p;
+    B.fod = h->d_fod.p;
+    B.ncsd = h->ncsd;
+    B.ncod = h->ncod;
     B.scene = h->d_scene.p;
     B.irr_s = h->d_irr_s.p;
     B.irr_o = h->d_irr_o.p;
@@ -277,7 +283,7 @@ int gcr_destroy(gcr_handle h)
     if (!h) return GCR_ERR_INVALID;
     cudaSetDevice(h->device);
     if (h->own_stream) cudaStreamSynchronize(h->own_stream);
-    h->d_scale.release(); h->d_orient.release(); h->d_fs.release(); h->d_fo.release();
+    h->d_scale.release(); h->d_orient.release(); h->d_fs.release(); h->d_fo.release(); h->d_fsd.release(); h->d_fod.release();
     h->d_irr_s.release(); h->d_irr_o.release(); h->d_scene.release(); h->d_samples.release();
     h->d_models.release(); h->d_flags.release(); h->d_sums.release(); h->d_score.release();
     h->d_cnts.release(); h->d_ninl.release(); h->d_masks.release(); h->d_fast_hyp.release();
@@ -333,13 +339,17 @@ int gcr_set_features(gcr_handle h, const double* scale, int64_t ns, const double
     }
     GCR_CUDA(h->d_fs.ensure(static_cast<size_t>(h->ncs) * kChunkFloats));
     GCR_CUDA(h->d_fo.ensure(static_cast<size_t>(h->nco) * kChunkFloats));
+    h->ncsd = (h->ns + kChunk / 2 - 1) / (kChunk / 2);
+    h->ncod = (h->no + kChunk / 2 - 1) / (kChunk / 2);
+    GCR_CUDA(h->d_fsd.ensure(static_cast<size_t>(h->ncsd) * (kChunkFloats / 2)));
+    GCR_CUDA(h->d_fod.ensure(static_cast<size_t>(h->ncod) * (kChunkFloats / 2)));
     GCR_CUDA(h->d_irr_s.ensure(kIrrCap));
     GCR_CUDA(h->d_irr_o.ensure(kIrrCap));
     GCR_CUDA(h->d_scene.ensure(1));
     GCR_CUDA(cudaMemsetAsync(h->d_scene.p, 0, sizeof(Scene), h->stream));
     const int n = std::max(h->ncs, h->nco) * kChunk;
     k_prep_features<<<(n + 255) / 256, 256, 0, h->stream>>>(h->scale_ptr, h->ns, h->orient_ptr, h->no, h->d_fs.p,
-                                                           h->d_fo.p, h->ncs, h->nco, h->d_scene.p, h->d_irr_s.p,
+                                                           h->d_fo.p, h->ncs, h->nco, h->d_fsd.p, h->d_fod.p, h->ncsd, h->ncod, h->d_scene.p, h->d_irr_s.p,
                                                            h->d_irr_o.p);
     GCR_CUDA(cudaGetLastError());
     return ensure_common(h);

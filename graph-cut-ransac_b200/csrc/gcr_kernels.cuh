@@ -15,164 +15,11 @@
 //
 // Reference semantics implemented are cited at each function.
 #pragma once
-#include <cuda_runtime.h>
-#include <cstdint>
-#include "gcr_exact.cuh"
+#include "gcr_kernels_common.cuh"
+#include "gcr_score.cuh"
 
 namespace gcr
 {
-
-constexpr int kChunk = 512;             // features per shared-memory stage
-constexpr int kChunkFloats = 3 * kChunk; // three SoA planes per chunk
-constexpr int kChunkBytes = kChunkFloats * 4;
-constexpr int kStages = 4;
-constexpr int kScoreThreads = 128;
-constexpr int kHB = 2; // hypotheses per thread in the fast kernel
-constexpr int kTileHyps = kScoreThreads * kHB;
-constexpr int kCandCap = 1024;
-constexpr int kIrrCap = 4096;
-constexpr double kLn2 = 0.693147180559945309417;
-constexpr double kU = 5.9604644775390625e-8; // 2^-24, FP32 unit round-off
-
-struct Counters
-{
-    unsigned int n_sample_valid, n_solved, n_fast, n_hard;
-    unsigned int n_worklist, n_worklist_overflow, n_candidates, n_cand_overflow;
-    unsigned int n_bad_sample, n_irregular_evals, blocks_done, pad0;
-    unsigned long long best_key; // ordered bits of the best fast score among model-valid hypotheses
-    unsigned long long pad1;
-};
-
-struct Scene // written by k_prep_features
-{
-    float xq_max, yq_max, iq_max, k_max; // maxima of |x/q|, |y/q|, |1/q| (scale class) and |k| (orientation class)
-    unsigned int n_irr_s, n_irr_o;       // irregular features (kept out of the FP32 arrays)
-    unsigned int irr_overflow, pad;
-};
-
-struct Thresholds
-{
-    double tsq[2];   // (2.25 t) t, S1
-    float Tp;        // sqrt(tsq0) / (3 ln 2): scale threshold in log2 units of v
-    float tanT;      // tan(sqrt(tsq1))
-    float t_band0;   // constant part of the orientation band in tan units
-    float pc[4];     // r^2 = z (pc0 + z (pc1 + z (pc2 + z pc3))), z = tan^2
-    float scale_unit; // (3 ln 2)^2: converts sum of d^2 (log2 units) into sum of r^2
-    int orient_all_exact; // orientation threshold outside the fast path's range -> every hypothesis exact
-};
-
-struct Buffers
-{
-    // features
-    const double* scale;
-    const double* orient;
-    int ns, no;
-    const float* fs; // chunked SoA, scale class: (x/q, y/q, 1/q)
-    const float* fo; // chunked SoA, orientation class: (k, sin, cos)
-    int ncs, nco;
-    const Scene* scene;
-    const unsigned int* irr_s;
-    const unsigned int* irr_o;
-    // hypotheses
-    int n_hyp;
-    unsigned long long first_hyp, seed;
-    int* samples;       // [H,4]
-    int have_samples;   // replay mode
-    Model4* models;     // [H]
-    unsigned char* flags; // [H]
-    double* sums;       // [H,2]  sum of r^2 over inliers per class
-    unsigned int* cnts; // [H,2]  raw inlier counts per class
-    double* score;      // [H]
-    unsigned int* n_inl; // [H,2] after zero-reset
-    unsigned int* masks; // [H,W] or null
-    int wmask, ws;       // words per hypothesis, words of the scale class
-    // compact lists
-    float4* pf0;         // (nh7, nh8, A, Tin)
-    float4* pf1;         // (Tout, cphi, sphi, dprime)
-    unsigned int* fast_hyp; // compact -> hypothesis
-    unsigned int* hard_hyp;
-    uint2* worklist;
-    unsigned int worklist_cap;
-    // candidates
-    unsigned int* cand_hyp;  // [kCandCap]
-    Model4* cand_model;
-    double* cand_score;
-    unsigned int* cand_cnt;  // [kCandCap,2]
-    unsigned int* cand_masks; // [kCandCap, W]
-    Counters* ctr;
-    void* record;  // gcr_record (device), engine-owned
-    void* record_user; // optional caller-owned copy target
-    unsigned int* best_masks; // [W]
-};
-
-// ------------------------------------------------------------------------------------------------
-// small PTX helpers (TMA bulk copy + mbarrier)
-
-__device__ __forceinline__ uint32_t smem_u32(const void* p)
-{
-    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
-}
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
-{
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes)
-{
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar)
-{
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
-{
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "WAIT_LOOP:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra DONE;\n"
-        "bra WAIT_LOOP;\n"
-        "DONE:\n"
-        "}\n" ::"r"(smem_u32(bar)),
-        "r"(parity)
-        : "memory");
-}
-// 1-D TMA bulk copy global -> shared, completion signalled on an mbarrier (SASS: UBLKCP)
-__device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar)
-{
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                     smem_u32(dst_smem)),
-                 "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
-                 : "memory");
-}
-__device__ __forceinline__ void fence_barrier_init()
-{
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ float lg2_approx(float x)
-{
-    float r;
-    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
-    return r;
-}
-__device__ __forceinline__ float rcp_approx(float x)
-{
-    float r;
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
-    return r;
-}
-
-__device__ __forceinline__ unsigned long long ordered_bits(double v)
-{
-    unsigned long long b = static_cast<unsigned long long>(__double_as_longlong(v));
-    return (b & 0x8000000000000000ull) ? ~b : (b | 0x8000000000000000ull);
-}
-__device__ __forceinline__ double from_ordered_bits(unsigned long long b)
-{
-    b = (b & 0x8000000000000000ull) ? (b & 0x7fffffffffffffffull) : ~b;
-    return __longlong_as_double(static_cast<long long>(b));
-}
 
 // ------------------------------------------------------------------------------------------------
 // K0: feature preparation.  Hoists what the reference recomputes per (model, feature):
@@ -183,14 +30,18 @@ __device__ __forceinline__ double from_ordered_bits(unsigned long long b)
 // Features whose prepared values are non-finite or absurdly large are "irregular": they are kept out of
 // the FP32 arrays (sentinel = never an inlier) and always evaluated in FP64 (k_fixup).
 __global__ void k_prep_features(const double* __restrict__ scale, int ns, const double* __restrict__ orient, int no,
-                                float* __restrict__ fs, float* __restrict__ fo, int ncs, int nco, Scene* scene,
+                                float* __restrict__ fs, float* __restrict__ fo, int ncs, int nco,
+                                double* __restrict__ fsd, double* __restrict__ fod, int ncsd, int ncod, Scene* scene,
                                 unsigned int* irr_s, unsigned int* irr_o)
 {
+    constexpr int kCD = kChunk / 2; // features per FP64 chunk (same byte size as an FP32 chunk)
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const float inf = __int_as_float(0x7f800000);
+    const double dinf = __longlong_as_double(0x7ff0000000000000ll), dnan = __longlong_as_double(0x7ff8000000000000ll);
     if (i < ncs * kChunk)
     {
         float a = 0.f, b = 0.f, c = inf; // pad: v = +inf -> never an inlier, never in the band
+        double ad = 0.0, bd = 0.0, cd = dinf;
         if (i < ns)
         {
             const double x = scale[3 * i], y = scale[3 * i + 1], s = scale[3 * i + 2];
@@ -203,6 +54,7 @@ __global__ void k_prep_features(const double* __restrict__ scale, int ns, const 
                 a = static_cast<float>(xa);
                 b = static_cast<float>(ya);
                 c = static_cast<float>(ia);
+                ad = xa; bd = ya; cd = ia;
                 atomicMax(reinterpret_cast<int*>(&scene->xq_max), __float_as_int(fabsf(a)));
                 atomicMax(reinterpret_cast<int*>(&scene->yq_max), __float_as_int(fabsf(b)));
                 atomicMax(reinterpret_cast<int*>(&scene->iq_max), __float_as_int(fabsf(c)));
@@ -217,10 +69,18 @@ __global__ void k_prep_features(const double* __restrict__ scale, int ns, const 
         base[0] = a;
         base[kChunk] = b;
         base[2 * kChunk] = c;
+        if (i < ncsd * kCD)
+        {
+            double* bd_ = fsd + static_cast<size_t>(i / kCD) * (3 * kCD) + (i % kCD);
+            bd_[0] = ad;
+            bd_[kCD] = bd;
+            bd_[2 * kCD] = cd;
+        }
     }
     if (i < nco * kChunk)
     {
         float a = 0.f, b = 0.f, c = 0.f;
+        double ad = 0.0, bd = dnan, cd = 0.0; // pad: NaN sine
         bool pad = true;
         if (i < no)
         {
@@ -234,6 +94,7 @@ __global__ void k_prep_features(const double* __restrict__ scale, int ns, const 
                 a = static_cast<float>(k);
                 b = static_cast<float>(st);
                 c = static_cast<float>(ct);
+                ad = k; bd = st; cd = ct;
                 pad = false;
                 atomicMax(reinterpret_cast<int*>(&scene->k_max), __float_as_int(fabsf(a)));
             }
@@ -254,6 +115,13 @@ __global__ void k_prep_features(const double* __restrict__ scale, int ns, const 
         base[0] = a;
         base[kChunk] = b;
         base[2 * kChunk] = c;
+        if (i < ncod * kCD)
+        {
+            double* bd_ = fod + static_cast<size_t>(i / kCD) * (3 * kCD) + (i % kCD);
+            bd_[0] = ad;
+            bd_[kCD] = bd;
+            bd_[2 * kCD] = cd;
+        }
     }
 }
 
@@ -288,7 +156,7 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
 {
     const int h = blockIdx.x * blockDim.x + threadIdx.x;
     const unsigned lane = threadIdx.x & 31;
-    bool solved = false, hard = false, sample_valid = false;
+    bool solved = false, hard = false, sample_valid = false, sens_s = false, sens_o = false;
     Model4 m = {0.0, 0.0, 0.0, 0.0};
     float4 p0 = make_float4(0.f, 0.f, 0.f, 0.f), p1 = make_float4(0.f, 1.f, 0.f, 0.f);
     if (h < B.n_hyp)
@@ -336,19 +204,38 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
         {
             f |= 2;
             if (is_valid_model(m)) f |= 4; // consulted at selection time, GCRANSAC.h:440-446
-            // ---- FP32 parameters and their error bands (DESIGN.md "error budget")
+            // ---- scoring-path parameters and their proven error bands (DESIGN.md "error budget")
             const Scene sc = *B.scene;
             const double ah7 = fabs(m.h7), ah8 = fabs(m.h8);
-            const double dv = 8.0 * kU * (ah7 * sc.xq_max + ah8 * sc.yq_max + sc.iq_max);
+            const double mag = ah7 * sc.xq_max + ah8 * sc.yq_max + sc.iq_max; // bound of the terms of v
             const double A = log2(m.alpha);
             const double Tp = T.Tp;
             const double v_lo = m.alpha * exp2(-Tp), v_hi = m.alpha * exp2(Tp);
-            double drho = 2.0 * (dv / ((v_lo - dv) * kLn2) + 2.384185791015625e-7 + 3.0 * kU * (fabs(A) + Tp + 1.0));
             const double kh = sc.k_max * (ah7 + ah8);
-            const double dprime = 6.0 * kU * (2.0 + 3.0 * kh) * 1.0001;
-            hard = all_exact || T.orient_all_exact || sc.irr_overflow || !isfinite(dv) || !isfinite(A) || !(v_lo > 4.0 * dv) ||
-                   !(v_hi * 1.01 < 1000.0) || !(drho < 1e-3 * Tp) || !(kh < 1e6) || !isfinite(dprime) ||
-                   !(ah7 < 1e6) || !(ah8 < 1e6);
+            const double eps_lg = 2.384185791015625e-7 + 3.0 * kU * (fabs(A) + Tp + 1.0); // MUFU.LG2 + roundings of A, d
+            // FP32 tiles: v, numer, denom from FP32 features and FP32 (h7, h8)
+            const double dv = 8.0 * kU * mag;
+            double drho = 2.0 * (dv / ((v_lo - dv) * kLn2) + eps_lg);
+            double dprime = 6.0 * kU * (2.0 + 3.0 * kh) * 1.0001;
+            const bool ok32 = isfinite(dv) && (v_lo > 4.0 * dv) && (drho < 1e-3 * Tp) && (dprime < 1e-3 * T.tanT);
+            // precise tiles: the same three FMAs in FP64, rounded once to FP32 (relative error u)
+            const double kU64 = 1.1102230246251565e-16;
+            const double dv64 = 8.0 * kU64 * mag;
+            const double drho64 = 2.0 * (dv64 / ((v_lo - dv64) * kLn2) + 1.5 * kU / kLn2 + eps_lg);
+            const bool ok64 = isfinite(dv64) && (v_lo > 4.0 * dv64) && (drho64 < 1e-3 * Tp);
+            const bool common_ok = !all_exact && !T.orient_all_exact && !sc.irr_overflow && isfinite(A) &&
+                                   (v_hi * 1.01 < 1000.0) && (kh < 1e6) && (ah7 < 1e6) && (ah8 < 1e6);
+            // The 1e-3 caps keep the FP32 residuals of the inliers within the 1e-5 score bar; hypotheses that
+            // miss them in FP32 (tiny alpha: cancellation in v; large |h|: angle noise) go to the precise tiles,
+            // the rest (out of any proven range) to the FP64 reference-order kernel.
+            if (common_ok && ok32) { }
+            else if (common_ok && ok64)
+            {
+                sens_s = true;
+                drho = drho64;
+                dprime = 6.0 * kU64 * (2.0 + 3.0 * kh) * 1.0001;
+            }
+            else hard = true;
             if (hard) f |= 8;
             double sphi, cphi;
             sincos(m.phi, &sphi, &cphi);
@@ -366,344 +253,34 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
     }
     // warp-aggregated compaction of solved hypotheses into the fast / exact lists
     const unsigned m_valid = __ballot_sync(0xffffffffu, sample_valid);
-    const unsigned m_fast = __ballot_sync(0xffffffffu, solved && !hard);
+    const bool sens = sens_s || sens_o;
+    const unsigned m_fast = __ballot_sync(0xffffffffu, solved && !hard && !sens);
+    const unsigned m_sens = __ballot_sync(0xffffffffu, solved && !hard && sens);
     const unsigned m_hard = __ballot_sync(0xffffffffu, solved && hard);
-    unsigned base_fast = 0, base_hard = 0;
+    unsigned base_fast = 0, base_hard = 0, base_sens = 0;
     if (lane == 0)
     {
         if (m_valid) atomicAdd(&B.ctr->n_sample_valid, __popc(m_valid));
-        if (m_fast | m_hard) atomicAdd(&B.ctr->n_solved, __popc(m_fast) + __popc(m_hard));
+        if (m_fast | m_hard | m_sens) atomicAdd(&B.ctr->n_solved, __popc(m_fast) + __popc(m_hard) + __popc(m_sens));
         if (m_fast) base_fast = atomicAdd(&B.ctr->n_fast, __popc(m_fast));
+        if (m_sens) base_sens = atomicAdd(&B.ctr->n_sens, __popc(m_sens));
         if (m_hard) base_hard = atomicAdd(&B.ctr->n_hard, __popc(m_hard));
     }
     base_fast = __shfl_sync(0xffffffffu, base_fast, 0);
+    base_sens = __shfl_sync(0xffffffffu, base_sens, 0);
     base_hard = __shfl_sync(0xffffffffu, base_hard, 0);
     const unsigned below = (1u << lane) - 1u;
     if (solved && !hard)
     {
-        const unsigned c = base_fast + __popc(m_fast & below);
+        // normal hypotheses fill the compact arrays from the front, score-sensitive ones from the back, so
+        // that the rare-path traffic of the latter stays in their own warps
+        const unsigned c = sens ? static_cast<unsigned>(B.n_hyp) - 1u - (base_sens + __popc(m_sens & below))
+                                : base_fast + __popc(m_fast & below);
         B.pf0[c] = p0;
         B.pf1[c] = p1;
         B.fast_hyp[c] = h;
     }
     if (solved && hard) B.hard_hyp[base_hard + __popc(m_hard & below)] = h;
-}
-
-// ------------------------------------------------------------------------------------------------
-// K3: the FP32 MSAC kernel.
-
-struct ScaleEval
-{
-    bool in, unc;
-    float d;
-};
-// One (hypothesis, scale feature) evaluation.  rectified scale = v^-3, residual r = 3 ln2 |A - lg2 v|
-// (S4, two_sift.hpp:621-645).  `in`: certainly inside the truncated threshold (S1); `unc`: inside the
-// proven FP32 error band around it -> decided in FP64 by k_fixup.  v <= 0 (beyond the horizon, DBL_MAX
-// residual in the reference) gives NaN/inf and fails both tests.
-__device__ __forceinline__ ScaleEval eval_scale(float xq, float yq, float iq, float nh7, float nh8, float A, float Tin,
-                                                float Tout)
-{
-    const float v = fmaf(nh8, yq, fmaf(nh7, xq, iq));
-    const float d = A - lg2_approx(v);
-    ScaleEval e;
-    e.in = fabsf(d) <= Tin;
-    e.unc = (fabsf(d) <= Tout) && !e.in;
-    e.d = d;
-    return e;
-}
-
-struct OrientEval
-{
-    bool in, unc;
-    float z, p; // r^2 = z * p
-};
-// One (hypothesis, orientation feature) evaluation.  (denom, numer) of rectifiedAngle (model.h:156-165)
-// rotated by -phi; the residual (S5, two_sift.hpp:647-665) is the angle of that vector to the nearest
-// multiple of pi/2 = atan(min/max) of its absolute components; r^2 by an even polynomial in tan.
-__device__ __forceinline__ OrientEval eval_orient(float k, float st, float ct, float nh7, float nh8, float cphi,
-                                                  float sphi, float dprime, const Thresholds& T)
-{
-    const float n = fmaf(k, nh7, st);  // sin - k h7
-    const float d = fmaf(-k, nh8, ct); // cos + k h8
-    const float c1 = fmaf(n, sphi, d * cphi);
-    const float s1 = fmaf(n, cphi, -(d * sphi));
-    const float a1 = fabsf(c1), a2 = fabsf(s1);
-    // the 1e-30 floor keeps an exact FP32 0/0 (numer = denom = 0, where the reference evaluates atan2 of
-    // round-off) finite: t = 0 with an enormous band -> guard band -> FP64
-    const float mn = fminf(a1, a2), mx = fmaxf(fmaxf(a1, a2), 1e-30f);
-    const float ri = rcp_approx(mx);
-    const float t = mn * ri;
-    const float band = fmaf(dprime, ri, T.t_band0);
-    OrientEval e;
-    e.in = t <= T.tanT - band;
-    e.unc = (t <= T.tanT + band) && !e.in;
-    e.z = t * t;
-    e.p = fmaf(e.z, fmaf(e.z, fmaf(e.z, T.pc[3], T.pc[2]), T.pc[1]), T.pc[0]);
-    return e;
-}
-
-struct __align__(16) ScoreSmem
-{
-    float stage[kStages][kChunkFloats];
-    uint64_t full[kStages];
-    uint64_t empty[kStages];
-};
-
-template <bool MASKS>
-__global__ void __launch_bounds__(kScoreThreads) k_score_fast(const __grid_constant__ Buffers B,
-                                                              const __grid_constant__ Thresholds T)
-{
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    ScoreSmem& S = *reinterpret_cast<ScoreSmem*>(smem_raw);
-    const int tid = threadIdx.x;
-    const int lane = tid & 31;
-    if (tid == 0)
-    {
-        for (int s = 0; s < kStages; s++)
-        {
-            mbar_init(&S.full[s], 1);
-            mbar_init(&S.empty[s], kScoreThreads / 32);
-        }
-        fence_barrier_init();
-    }
-    __syncthreads();
-
-    const int n_fast = static_cast<int>(B.ctr->n_fast);
-    const int n_tiles = (n_fast + kTileHyps - 1) / kTileHyps;
-    const int n_chunks = B.ncs + B.nco;
-    // work decomposition (identical in every CTA): split the feature chunks so that there are enough items
-    int splits = 1;
-    {
-        const int target = 4 * static_cast<int>(gridDim.x);
-        if (n_tiles > 0 && n_tiles < target) splits = min(n_chunks, (target + n_tiles - 1) / n_tiles);
-    }
-    const int cps = (n_chunks + splits - 1) / splits; // chunks per split
-    splits = (n_chunks + cps - 1) / cps;
-    const int n_items = n_tiles * splits;
-
-    uint32_t ring = 0; // chunks issued/consumed so far by this CTA (ring position)
-    for (int item = blockIdx.x; item < n_items; item += gridDim.x)
-    {
-        const int tile = item / splits, split = item - tile * splits;
-        const int c_begin = split * cps, c_end = min(n_chunks, c_begin + cps);
-        const int nch = c_end - c_begin;
-
-        auto issue = [&](uint32_t n, int chunk) {
-            if (tid == 0)
-            {
-                const uint32_t st = n % kStages;
-                if (n >= kStages) mbar_wait(&S.empty[st], ((n / kStages) - 1) & 1);
-                const float* src = chunk < B.ncs ? B.fs + static_cast<size_t>(chunk) * kChunkFloats
-                                                 : B.fo + static_cast<size_t>(chunk - B.ncs) * kChunkFloats;
-                mbar_expect_tx(&S.full[st], kChunkBytes);
-                tma_load_1d(S.stage[st], src, kChunkBytes, &S.full[st]);
-            }
-        };
-        for (int p = 0; p < min(kStages - 1, nch); p++) issue(ring + p, c_begin + p);
-
-        // per-thread hypotheses
-        float nh7[kHB], nh8[kHB], A[kHB], Tin[kHB], Tout[kHB], cphi[kHB], sphi[kHB], dpr[kHB];
-        unsigned int hyp[kHB];
-        bool active[kHB];
-        double sum_s[kHB], sum_o[kHB];
-        unsigned int cnt_s[kHB], cnt_o[kHB];
-#pragma unroll
-        for (int j = 0; j < kHB; j++)
-        {
-            const int c = tile * kTileHyps + j * kScoreThreads + tid;
-            active[j] = c < n_fast;
-            const float4 p0 = active[j] ? B.pf0[c] : make_float4(0.f, 0.f, 0.f, -1.f);
-            const float4 p1 = active[j] ? B.pf1[c] : make_float4(-1.f, __int_as_float(0x7fc00000), 0.f, 0.f);
-            hyp[j] = active[j] ? B.fast_hyp[c] : 0u;
-            nh7[j] = p0.x; nh8[j] = p0.y; A[j] = p0.z; Tin[j] = p0.w;
-            Tout[j] = p1.x; cphi[j] = p1.y; sphi[j] = p1.z; dpr[j] = p1.w;
-            sum_s[j] = sum_o[j] = 0.0;
-            cnt_s[j] = cnt_o[j] = 0u;
-        }
-
-        for (int i = 0; i < nch; i++)
-        {
-            if (i + kStages - 1 < nch) issue(ring + i + kStages - 1, c_begin + i + kStages - 1);
-            const uint32_t n = ring + i;
-            const uint32_t st = n % kStages;
-            mbar_wait(&S.full[st], (n / kStages) & 1);
-            const int chunk = c_begin + i;
-            const float4* pa = reinterpret_cast<const float4*>(S.stage[st]);
-            const float4* pb = reinterpret_cast<const float4*>(S.stage[st] + kChunk);
-            const float4* pc = reinterpret_cast<const float4*>(S.stage[st] + 2 * kChunk);
-            float acc[kHB], cntf[kHB]; // per-chunk FP32 partials (counts are exact integers < 2^24)
-#pragma unroll
-            for (int j = 0; j < kHB; j++) acc[j] = cntf[j] = 0.f;
-
-            if (chunk < B.ncs)
-            {
-                const int fbase = chunk * kChunk;
-                unsigned int mword[kHB];
-#pragma unroll
-                for (int j = 0; j < kHB; j++) mword[j] = 0u;
-#pragma unroll 2
-                for (int g = 0; g < kChunk / 4; g++)
-                {
-                    const float4 a = pa[g], b = pb[g], c = pc[g];
-                    const float fa[4] = {a.x, a.y, a.z, a.w}, fb[4] = {b.x, b.y, b.z, b.w}, fc[4] = {c.x, c.y, c.z, c.w};
-                    bool any_unc = false;
-#pragma unroll
-                    for (int j = 0; j < kHB; j++)
-                    {
-#pragma unroll
-                        for (int e = 0; e < 4; e++)
-                        {
-                            const ScaleEval r = eval_scale(fa[e], fb[e], fc[e], nh7[j], nh8[j], A[j], Tin[j], Tout[j]);
-                            if (r.in)
-                            {
-                                acc[j] = fmaf(r.d, r.d, acc[j]);
-                                cntf[j] += 1.0f;
-                                if (MASKS) mword[j] |= 1u << ((g * 4 + e) & 31);
-                            }
-                            any_unc |= r.unc;
-                        }
-                    }
-                    if (__any_sync(0xffffffffu, any_unc))
-                    {
-                        // rare: append the guard-band pairs of this group to the FP64 worklist
-#pragma unroll
-                        for (int j = 0; j < kHB; j++)
-#pragma unroll
-                            for (int e = 0; e < 4; e++)
-                            {
-                                const ScaleEval r =
-                                    eval_scale(fa[e], fb[e], fc[e], nh7[j], nh8[j], A[j], Tin[j], Tout[j]);
-                                if (r.unc && active[j])
-                                {
-                                    const unsigned int slot = atomicAdd(&B.ctr->n_worklist, 1u);
-                                    if (slot < B.worklist_cap)
-                                        B.worklist[slot] = make_uint2(hyp[j], static_cast<unsigned>(fbase + g * 4 + e));
-                                    else
-                                        atomicAdd(&B.ctr->n_worklist_overflow, 1u);
-                                }
-                            }
-                    }
-                    if (MASKS && (g & 7) == 7)
-                    {
-#pragma unroll
-                        for (int j = 0; j < kHB; j++)
-                        {
-                            if (active[j] && mword[j])
-                                atomicOr(&B.masks[static_cast<size_t>(hyp[j]) * B.wmask + (fbase >> 5) + (g >> 3)], mword[j]);
-                            mword[j] = 0u;
-                        }
-                    }
-                }
-#pragma unroll
-                for (int j = 0; j < kHB; j++)
-                {
-                    sum_s[j] += static_cast<double>(acc[j]);
-                    cnt_s[j] += static_cast<unsigned int>(cntf[j]);
-                }
-            }
-            else
-            {
-                const int fbase = (chunk - B.ncs) * kChunk;
-                unsigned int mword[kHB];
-#pragma unroll
-                for (int j = 0; j < kHB; j++) mword[j] = 0u;
-#pragma unroll 2
-                for (int g = 0; g < kChunk / 4; g++)
-                {
-                    const float4 a = pa[g], b = pb[g], c = pc[g];
-                    const float fa[4] = {a.x, a.y, a.z, a.w}, fb[4] = {b.x, b.y, b.z, b.w}, fc[4] = {c.x, c.y, c.z, c.w};
-                    bool any_unc = false;
-#pragma unroll
-                    for (int j = 0; j < kHB; j++)
-                    {
-#pragma unroll
-                        for (int e = 0; e < 4; e++)
-                        {
-                            const OrientEval r =
-                                eval_orient(fa[e], fb[e], fc[e], nh7[j], nh8[j], cphi[j], sphi[j], dpr[j], T);
-                            if (r.in)
-                            {
-                                acc[j] = fmaf(r.z, r.p, acc[j]);
-                                cntf[j] += 1.0f;
-                                if (MASKS) mword[j] |= 1u << ((g * 4 + e) & 31);
-                            }
-                            any_unc |= r.unc;
-                        }
-                    }
-                    if (__any_sync(0xffffffffu, any_unc))
-                    {
-#pragma unroll
-                        for (int j = 0; j < kHB; j++)
-#pragma unroll
-                            for (int e = 0; e < 4; e++)
-                            {
-                                const OrientEval r =
-                                    eval_orient(fa[e], fb[e], fc[e], nh7[j], nh8[j], cphi[j], sphi[j], dpr[j], T);
-                                const int f = fbase + g * 4 + e;
-                                if (r.unc && active[j] && f < B.no)
-                                {
-                                    const unsigned int slot = atomicAdd(&B.ctr->n_worklist, 1u);
-                                    if (slot < B.worklist_cap)
-                                        B.worklist[slot] = make_uint2(hyp[j], 0x80000000u | static_cast<unsigned>(f));
-                                    else
-                                        atomicAdd(&B.ctr->n_worklist_overflow, 1u);
-                                }
-                            }
-                    }
-                    if (MASKS && (g & 7) == 7)
-                    {
-#pragma unroll
-                        for (int j = 0; j < kHB; j++)
-                        {
-                            if (active[j] && mword[j])
-                                atomicOr(&B.masks[static_cast<size_t>(hyp[j]) * B.wmask + B.ws + (fbase >> 5) + (g >> 3)],
-                                         mword[j]);
-                            mword[j] = 0u;
-                        }
-                    }
-                }
-#pragma unroll
-                for (int j = 0; j < kHB; j++)
-                {
-                    sum_o[j] += static_cast<double>(acc[j]);
-                    cnt_o[j] += static_cast<unsigned int>(cntf[j]);
-                }
-            }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&S.empty[st]);
-        }
-        ring += nch;
-
-        // flush this item's partial sums
-#pragma unroll
-        for (int j = 0; j < kHB; j++)
-        {
-            if (!active[j]) continue;
-            const size_t h = hyp[j];
-            const double ss = sum_s[j] * static_cast<double>(T.scale_unit);
-            if (splits == 1)
-            {
-                B.sums[2 * h] = ss;
-                B.sums[2 * h + 1] = sum_o[j];
-                B.cnts[2 * h] = cnt_s[j];
-                B.cnts[2 * h + 1] = cnt_o[j];
-            }
-            else
-            {
-                if (cnt_s[j])
-                {
-                    atomicAdd(&B.sums[2 * h], ss);
-                    atomicAdd(&B.cnts[2 * h], cnt_s[j]);
-                }
-                if (cnt_o[j])
-                {
-                    atomicAdd(&B.sums[2 * h + 1], sum_o[j]);
-                    atomicAdd(&B.cnts[2 * h + 1], cnt_o[j]);
-                }
-            }
-        }
-    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -734,11 +311,12 @@ __global__ void k_fixup(Buffers B, Thresholds T)
     const unsigned int n_io = min(B.scene->n_irr_o, static_cast<unsigned>(kIrrCap));
     const unsigned int n_irr = n_is + n_io;
     if (n_irr == 0) return;
-    const unsigned long long total = static_cast<unsigned long long>(n_irr) * B.ctr->n_fast;
+    const unsigned int n_fast = B.ctr->n_fast, n_both = n_fast + B.ctr->n_sens;
+    const unsigned long long total = static_cast<unsigned long long>(n_irr) * n_both;
     for (unsigned long long i = t0; i < total; i += stride)
     {
         const unsigned int c = static_cast<unsigned int>(i / n_irr), k = static_cast<unsigned int>(i % n_irr);
-        const unsigned int h = B.fast_hyp[c];
+        const unsigned int h = B.fast_hyp[c < n_fast ? c : static_cast<unsigned>(B.n_hyp) - 1u - (c - n_fast)];
         const unsigned int cls = k >= n_is;
         const unsigned int f = cls ? B.irr_o[k - n_is] : B.irr_s[k];
         const Model4 m = B.models[h];

@@ -1,0 +1,167 @@
+// Shared declarations of the device code: constants, buffer descriptors, PTX helpers (TMA bulk copy, mbarrier,
+// MUFU approximations).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include "gcr_exact.cuh"
+
+namespace gcr
+{
+
+constexpr int kChunk = 512;             // features per shared-memory stage
+constexpr int kChunkFloats = 3 * kChunk; // three SoA planes per chunk
+constexpr int kChunkBytes = kChunkFloats * 4;
+constexpr int kStages = 4;
+constexpr int kScoreThreads = 128;
+constexpr int kHB = 2; // hypotheses per thread in the fast kernel
+constexpr int kTileHyps = kScoreThreads * kHB;
+constexpr int kCandCap = 1024;
+constexpr int kIrrCap = 4096;
+constexpr double kLn2 = 0.693147180559945309417;
+constexpr double kU = 5.9604644775390625e-8; // 2^-24, FP32 unit round-off
+
+struct Counters
+{
+    unsigned int n_sample_valid, n_solved, n_fast, n_hard;
+    unsigned int n_worklist, n_worklist_overflow, n_candidates, n_cand_overflow;
+    unsigned int n_bad_sample, n_irregular_evals, blocks_done, n_sens;
+    unsigned long long best_key; // ordered bits of the best fast score among model-valid hypotheses
+    unsigned long long pad1;
+};
+
+struct Scene // written by k_prep_features
+{
+    float xq_max, yq_max, iq_max, k_max; // maxima of |x/q|, |y/q|, |1/q| (scale class) and |k| (orientation class)
+    unsigned int n_irr_s, n_irr_o;       // irregular features (kept out of the FP32 arrays)
+    unsigned int irr_overflow, pad;
+};
+
+struct Thresholds
+{
+    double tsq[2];   // (2.25 t) t, S1
+    float Tp;        // sqrt(tsq0) / (3 ln 2): scale threshold in log2 units of v
+    float tanT;      // tan(sqrt(tsq1))
+    float t_band0;   // constant part of the orientation band in tan units
+    float pc[4];     // r^2 = z (pc0 + z (pc1 + z (pc2 + z pc3))), z = tan^2
+    float scale_unit; // (3 ln 2)^2: converts sum of d^2 (log2 units) into sum of r^2
+    int orient_all_exact; // orientation threshold outside the fast path's range -> every hypothesis exact
+};
+
+struct Buffers
+{
+    // features
+    const double* scale;
+    const double* orient;
+    int ns, no;
+    const float* fs; // chunked SoA, scale class: (x/q, y/q, 1/q)
+    const float* fo; // chunked SoA, orientation class: (k, sin, cos)
+    int ncs, nco;
+    const double* fsd; // FP64 chunked SoA (256 features per chunk) for the precise tiles: (x/q, y/q, 1/q)
+    const double* fod; // FP64 chunked SoA: (k, sin, cos)
+    int ncsd, ncod;
+    const Scene* scene;
+    const unsigned int* irr_s;
+    const unsigned int* irr_o;
+    // hypotheses
+    int n_hyp;
+    unsigned long long first_hyp, seed;
+    int* samples;       // [H,4]
+    int have_samples;   // replay mode
+    Model4* models;     // [H]
+    unsigned char* flags; // [H]
+    double* sums;       // [H,2]  sum of r^2 over inliers per class
+    unsigned int* cnts; // [H,2]  raw inlier counts per class
+    double* score;      // [H]
+    unsigned int* n_inl; // [H,2] after zero-reset
+    unsigned int* masks; // [H,W] or null
+    int wmask, ws;       // words per hypothesis, words of the scale class
+    // compact lists
+    float4* pf0;         // (nh7, nh8, A, Tin)
+    float4* pf1;         // (Tout, cphi, sphi, dprime)
+    unsigned int* fast_hyp; // compact -> hypothesis
+    unsigned int* hard_hyp;
+    uint2* worklist;
+    unsigned int worklist_cap;
+    // candidates
+    unsigned int* cand_hyp;  // [kCandCap]
+    Model4* cand_model;
+    double* cand_score;
+    unsigned int* cand_cnt;  // [kCandCap,2]
+    unsigned int* cand_masks; // [kCandCap, W]
+    Counters* ctr;
+    void* record;  // gcr_record (device), engine-owned
+    void* record_user; // optional caller-owned copy target
+    unsigned int* best_masks; // [W]
+};
+
+// ------------------------------------------------------------------------------------------------
+// small PTX helpers (TMA bulk copy + mbarrier)
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p)
+{
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+// 1-D TMA bulk copy global -> shared, completion signalled on an mbarrier (SASS: UBLKCP)
+__device__ __forceinline__ void tma_load_1d(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst_smem)),
+                 "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init()
+{
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ float lg2_approx(float x)
+{
+    float r;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float rcp_approx(float x)
+{
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+__device__ __forceinline__ unsigned long long ordered_bits(double v)
+{
+    unsigned long long b = static_cast<unsigned long long>(__double_as_longlong(v));
+    return (b & 0x8000000000000000ull) ? ~b : (b | 0x8000000000000000ull);
+}
+__device__ __forceinline__ double from_ordered_bits(unsigned long long b)
+{
+    b = (b & 0x8000000000000000ull) ? (b & 0x7fffffffffffffffull) : ~b;
+    return __longlong_as_double(static_cast<long long>(b));
+}
+
+
+} // namespace gcr

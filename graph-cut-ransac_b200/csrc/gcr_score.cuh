@@ -1,0 +1,350 @@
+// K3: the multi-class MSAC scoring kernel (the hot kernel of the engine).
+//
+// Work mapping: one thread <-> kHB hypotheses held in registers; the features of both classes stream
+// through a shared-memory ring filled by 1-D TMA bulk copies (cp.async.bulk + mbarrier full/empty pairs)
+// and are read as broadcast 128-bit loads.  No reductions: every thread owns its hypotheses' partial sums.
+// A work item is (tile of kTileHyps hypotheses) x (range of feature chunks); items are strided over a
+// persistent grid, the split is chosen on the device from the number of solved hypotheses.
+//
+// Two tile flavours share the code (template PRECISE):
+//   FP32 tiles     v, numer, denom from FP32 SoA features: the bulk of the hypotheses;
+//   precise tiles  the two FMAs that suffer cancellation (v = 1/q - h7 x/q - h8 y/q for tiny alpha,
+//                  numer/denom for large |h|) are done in FP64 from FP64 SoA features and rounded once,
+//                  everything after is FP32.  They hold the hypotheses whose FP32 band would be wide.
+// Both produce, per (hypothesis, feature): a certain inlier / certain outlier / "inside the proven error
+// band" verdict; the last kind is appended to a worklist and decided in FP64 by k_fixup.
+#pragma once
+#include "gcr_kernels_common.cuh"
+
+namespace gcr
+{
+
+struct HypRegs
+{
+    float nh7, nh8, A, Tin, Tout, cphi, sphi, dpr;
+    double h7d, h8d; // precise tiles only
+    unsigned int hyp;
+    bool active;
+    double sum_s, sum_o;
+    unsigned int cnt_s, cnt_o;
+};
+
+struct Verdict
+{
+    bool in, unc;
+};
+
+// rectified scale = v^-3, residual r = 3 ln2 |A - lg2 v|  (S4, two_sift.hpp:621-645).  v <= 0 (beyond the
+// horizon: DBL_MAX residual in the reference) gives NaN / inf and fails both tests.
+__device__ __forceinline__ Verdict scale_verdict(float v, const HypRegs& H, float& d)
+{
+    d = H.A - lg2_approx(v);
+    Verdict e;
+    e.in = fabsf(d) <= H.Tin;
+    e.unc = (fabsf(d) <= H.Tout) && !e.in;
+    return e;
+}
+
+// (denom, numer) of rectifiedAngle (model.h:156-165) rotated by -phi; the residual (S5, two_sift.hpp:647-665)
+// is the angle of that vector to the nearest multiple of pi/2 = atan(min/max) of its absolute components;
+// r^2 = z p(z), z = tan^2, by an even polynomial.
+__device__ __forceinline__ Verdict orient_verdict(float n, float d, const HypRegs& H, const Thresholds& T, float& z,
+                                                  float& p)
+{
+    const float c1 = fmaf(n, H.sphi, d * H.cphi);
+    const float s1 = fmaf(n, H.cphi, -(d * H.sphi));
+    const float a1 = fabsf(c1), a2 = fabsf(s1);
+    // the 1e-30 floor keeps an exact 0/0 (numer = denom = 0, where the reference evaluates atan2 of round-off)
+    // finite: t = 0 with an enormous band -> worklist
+    const float mn = fminf(a1, a2), mx = fmaxf(fmaxf(a1, a2), 1e-30f);
+    const float ri = rcp_approx(mx);
+    const float t = mn * ri;
+    const float band = fmaf(H.dpr, ri, T.t_band0);
+    Verdict e;
+    e.in = t <= T.tanT - band;
+    e.unc = (t <= T.tanT + band) && !e.in;
+    z = t * t;
+    p = fmaf(z, fmaf(z, fmaf(z, T.pc[3], T.pc[2]), T.pc[1]), T.pc[0]);
+    return e;
+}
+
+struct __align__(16) ScoreSmem
+{
+    float stage[kStages][kChunkFloats];
+    uint64_t full[kStages];
+    uint64_t empty[kStages];
+};
+
+__device__ __forceinline__ void worklist_push(const Buffers& B, unsigned int hyp, unsigned int feat_and_class)
+{
+    const unsigned int slot = atomicAdd(&B.ctr->n_worklist, 1u);
+    if (slot < B.worklist_cap) B.worklist[slot] = make_uint2(hyp, feat_and_class);
+    else atomicAdd(&B.ctr->n_worklist_overflow, 1u);
+}
+
+// One chunk of one class for the kHB hypotheses of this thread.  CLS 0 = scale, 1 = orientation.
+// FP32 chunk: 512 features, groups of 4 (float4 per plane).  Precise chunk: 256 features, groups of 2 (double2).
+template <bool MASKS, bool PRECISE, int CLS>
+__device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& T, const float* stage, int fbase,
+                                            HypRegs (&H)[kHB])
+{
+    constexpr int G = PRECISE ? 2 : 4;             // features per group
+    constexpr int NF = PRECISE ? kChunk / 2 : kChunk; // features per chunk
+    float acc[kHB], cntf[kHB]; // per-chunk FP32 partials; counts are exact integers (< 2^24)
+    unsigned int mword[kHB];
+#pragma unroll
+    for (int j = 0; j < kHB; j++)
+    {
+        acc[j] = cntf[j] = 0.f;
+        mword[j] = 0u;
+    }
+#pragma unroll 2
+    for (int g = 0; g < NF / G; g++)
+    {
+        float fa[G], fb[G], fc[G];   // FP32 planes
+        double da[G], db[G], dc[G];  // FP64 planes (precise tiles)
+        if constexpr (PRECISE)
+        {
+            const double2 a = reinterpret_cast<const double2*>(stage)[g];
+            const double2 b = reinterpret_cast<const double2*>(stage + 2 * NF)[g];
+            const double2 c = reinterpret_cast<const double2*>(stage + 4 * NF)[g];
+            da[0] = a.x; da[1] = a.y; db[0] = b.x; db[1] = b.y; dc[0] = c.x; dc[1] = c.y;
+        }
+        else
+        {
+            const float4 a = reinterpret_cast<const float4*>(stage)[g];
+            const float4 b = reinterpret_cast<const float4*>(stage + NF)[g];
+            const float4 c = reinterpret_cast<const float4*>(stage + 2 * NF)[g];
+            fa[0] = a.x; fa[1] = a.y; fa[2] = a.z; fa[3] = a.w;
+            fb[0] = b.x; fb[1] = b.y; fb[2] = b.z; fb[3] = b.w;
+            fc[0] = c.x; fc[1] = c.y; fc[2] = c.z; fc[3] = c.w;
+        }
+        auto verdict = [&](int j, int e, float& x0, float& x1) -> Verdict {
+            if constexpr (CLS == 0)
+            {
+                float v;
+                if constexpr (PRECISE) v = static_cast<float>(fma(-H[j].h8d, db[e], fma(-H[j].h7d, da[e], dc[e])));
+                else v = fmaf(H[j].nh8, fb[e], fmaf(H[j].nh7, fa[e], fc[e]));
+                x1 = 0.f;
+                return scale_verdict(v, H[j], x0);
+            }
+            else
+            {
+                float n, d;
+                if constexpr (PRECISE)
+                {
+                    n = static_cast<float>(fma(da[e], -H[j].h7d, db[e])); // sin - k h7
+                    d = static_cast<float>(fma(da[e], H[j].h8d, dc[e]));  // cos + k h8
+                }
+                else
+                {
+                    n = fmaf(fa[e], H[j].nh7, fb[e]);
+                    d = fmaf(-fa[e], H[j].nh8, fc[e]);
+                }
+                return orient_verdict(n, d, H[j], T, x0, x1);
+            }
+        };
+        bool any_unc = false;
+#pragma unroll
+        for (int j = 0; j < kHB; j++)
+        {
+#pragma unroll
+            for (int e = 0; e < G; e++)
+            {
+                float x0, x1;
+                const Verdict r = verdict(j, e, x0, x1);
+                if (r.in)
+                {
+                    acc[j] = CLS == 0 ? fmaf(x0, x0, acc[j]) : fmaf(x0, x1, acc[j]);
+                    cntf[j] += 1.0f;
+                    if (MASKS) mword[j] |= 1u << ((g * G + e) & 31);
+                }
+                any_unc |= r.unc;
+            }
+        }
+        if (__any_sync(0xffffffffu, any_unc))
+        {
+            // rare: re-derive which pairs of this group are inside the band (same instructions, same inputs)
+#pragma unroll
+            for (int j = 0; j < kHB; j++)
+#pragma unroll
+                for (int e = 0; e < G; e++)
+                {
+                    float x0, x1;
+                    const Verdict r = verdict(j, e, x0, x1);
+                    if (r.unc && H[j].active)
+                        worklist_push(B, H[j].hyp, (CLS ? 0x80000000u : 0u) | static_cast<unsigned>(fbase + g * G + e));
+                }
+        }
+        if (MASKS && ((g + 1) * G) % 32 == 0)
+        {
+#pragma unroll
+            for (int j = 0; j < kHB; j++)
+            {
+                if (H[j].active && mword[j])
+                    atomicOr(&B.masks[static_cast<size_t>(H[j].hyp) * B.wmask + (CLS ? B.ws : 0) + ((fbase + g * G) >> 5)],
+                             mword[j]);
+                mword[j] = 0u;
+            }
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < kHB; j++)
+    {
+        if (CLS == 0)
+        {
+            H[j].sum_s += static_cast<double>(acc[j]);
+            H[j].cnt_s += static_cast<unsigned int>(cntf[j]);
+        }
+        else
+        {
+            H[j].sum_o += static_cast<double>(acc[j]);
+            H[j].cnt_o += static_cast<unsigned int>(cntf[j]);
+        }
+    }
+}
+
+// One work item: all chunks [c_begin, c_end) of this tile flavour's chunk list, scale class first.
+template <bool MASKS, bool PRECISE>
+__device__ __forceinline__ void score_item(const Buffers& B, const Thresholds& T, ScoreSmem& S, uint32_t& ring,
+                                           int first_compact, int n_list, bool from_back, int c_begin, int c_end,
+                                           bool single_split)
+{
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int ncs = PRECISE ? B.ncsd : B.ncs;
+    const float* base_s = PRECISE ? reinterpret_cast<const float*>(B.fsd) : B.fs;
+    const float* base_o = PRECISE ? reinterpret_cast<const float*>(B.fod) : B.fo;
+    constexpr int NF = PRECISE ? kChunk / 2 : kChunk;
+    const int nch = c_end - c_begin;
+
+    auto issue = [&](uint32_t n, int chunk) {
+        if (tid == 0)
+        {
+            const uint32_t st = n % kStages;
+            if (n >= kStages) mbar_wait(&S.empty[st], ((n / kStages) - 1) & 1);
+            const float* src = chunk < ncs ? base_s + static_cast<size_t>(chunk) * kChunkFloats
+                                           : base_o + static_cast<size_t>(chunk - ncs) * kChunkFloats;
+            mbar_expect_tx(&S.full[st], kChunkBytes);
+            tma_load_1d(S.stage[st], src, kChunkBytes, &S.full[st]);
+        }
+    };
+    for (int p = 0; p < min(kStages - 1, nch); p++) issue(ring + p, c_begin + p);
+
+    HypRegs H[kHB];
+#pragma unroll
+    for (int j = 0; j < kHB; j++)
+    {
+        const int k = first_compact + j * kScoreThreads + tid;
+        H[j].active = k < n_list;
+        const int c = from_back ? B.n_hyp - 1 - k : k;
+        // inactive lanes: parameters for which every comparison is false
+        const float4 p0 = H[j].active ? B.pf0[c] : make_float4(0.f, 0.f, 0.f, -1.f);
+        const float4 p1 = H[j].active ? B.pf1[c] : make_float4(-1.f, __int_as_float(0x7fc00000), 0.f, 0.f);
+        H[j].hyp = H[j].active ? B.fast_hyp[c] : 0u;
+        H[j].nh7 = p0.x; H[j].nh8 = p0.y; H[j].A = p0.z; H[j].Tin = p0.w;
+        H[j].Tout = p1.x; H[j].cphi = p1.y; H[j].sphi = p1.z; H[j].dpr = p1.w;
+        H[j].h7d = H[j].h8d = 0.0;
+        if (PRECISE && H[j].active)
+        {
+            const Model4 m = B.models[H[j].hyp];
+            H[j].h7d = m.h7;
+            H[j].h8d = m.h8;
+        }
+        H[j].sum_s = H[j].sum_o = 0.0;
+        H[j].cnt_s = H[j].cnt_o = 0u;
+    }
+
+    for (int i = 0; i < nch; i++)
+    {
+        if (i + kStages - 1 < nch) issue(ring + i + kStages - 1, c_begin + i + kStages - 1);
+        const uint32_t n = ring + i;
+        const uint32_t st = n % kStages;
+        mbar_wait(&S.full[st], (n / kStages) & 1);
+        const int chunk = c_begin + i;
+        if (chunk < ncs) score_chunk<MASKS, PRECISE, 0>(B, T, S.stage[st], chunk * NF, H);
+        else score_chunk<MASKS, PRECISE, 1>(B, T, S.stage[st], (chunk - ncs) * NF, H);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&S.empty[st]);
+    }
+    ring += nch;
+
+#pragma unroll
+    for (int j = 0; j < kHB; j++)
+    {
+        if (!H[j].active) continue;
+        const size_t h = H[j].hyp;
+        const double ss = H[j].sum_s * static_cast<double>(T.scale_unit);
+        if (single_split)
+        {
+            B.sums[2 * h] = ss;
+            B.sums[2 * h + 1] = H[j].sum_o;
+            B.cnts[2 * h] = H[j].cnt_s;
+            B.cnts[2 * h + 1] = H[j].cnt_o;
+        }
+        else
+        {
+            if (H[j].cnt_s)
+            {
+                atomicAdd(&B.sums[2 * h], ss);
+                atomicAdd(&B.cnts[2 * h], H[j].cnt_s);
+            }
+            if (H[j].cnt_o)
+            {
+                atomicAdd(&B.sums[2 * h + 1], H[j].sum_o);
+                atomicAdd(&B.cnts[2 * h + 1], H[j].cnt_o);
+            }
+        }
+    }
+}
+
+template <bool MASKS>
+__global__ void __launch_bounds__(kScoreThreads) k_score_fast(const __grid_constant__ Buffers B,
+                                                              const __grid_constant__ Thresholds T)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    ScoreSmem& S = *reinterpret_cast<ScoreSmem*>(smem_raw);
+    if (threadIdx.x == 0)
+    {
+        for (int s = 0; s < kStages; s++)
+        {
+            mbar_init(&S.full[s], 1);
+            mbar_init(&S.empty[s], kScoreThreads / 32);
+        }
+        fence_barrier_init();
+    }
+    __syncthreads();
+
+    const int n_fast = static_cast<int>(B.ctr->n_fast), n_sens = static_cast<int>(B.ctr->n_sens);
+    const int tiles_a = (n_fast + kTileHyps - 1) / kTileHyps, tiles_b = (n_sens + kTileHyps - 1) / kTileHyps;
+    const int chunks_a = B.ncs + B.nco, chunks_b = B.ncsd + B.ncod;
+    // work decomposition, identical in every CTA: split the chunk lists so that the grid has ~4 items per CTA
+    const int target = 4 * static_cast<int>(gridDim.x);
+    const int tiles = tiles_a + 2 * tiles_b; // a precise tile has twice the chunks
+    int splits_a = 1;
+    if (tiles > 0 && tiles < target) splits_a = min(chunks_a, (target + tiles - 1) / tiles);
+    const int cps_a = (chunks_a + splits_a - 1) / splits_a;
+    splits_a = (chunks_a + cps_a - 1) / cps_a;
+    const int cps_b = min(chunks_b, 2 * cps_a);
+    const int splits_b = (chunks_b + cps_b - 1) / cps_b;
+    const int items_a = tiles_a * splits_a, n_items = items_a + tiles_b * splits_b;
+
+    uint32_t ring = 0; // chunks issued / consumed so far by this CTA (ring position, same in every thread)
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x)
+    {
+        if (item < items_a)
+        {
+            const int tile = item / splits_a, split = item - tile * splits_a;
+            score_item<MASKS, false>(B, T, S, ring, tile * kTileHyps, n_fast, false, split * cps_a,
+                                     min(chunks_a, (split + 1) * cps_a), splits_a == 1);
+        }
+        else
+        {
+            const int it = item - items_a;
+            const int tile = it / splits_b, split = it - tile * splits_b;
+            score_item<MASKS, true>(B, T, S, ring, tile * kTileHyps, n_sens, true, split * cps_b,
+                                    min(chunks_b, (split + 1) * cps_b), splits_b == 1);
+        }
+    }
+}
+
+} // namespace gcr
