@@ -48,6 +48,7 @@ struct gcr_engine_s
 {
     int device = 0;
     int n_sm = 148;
+    int score_grid[2] = {148, 148};
     cudaStream_t own_stream = nullptr, stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, evk0 = nullptr, evk1 = nullptr;
     std::string err;
@@ -266,6 +267,13 @@ int gcr_create(int device, gcr_handle* out)
         e = cudaFuncSetAttribute(k_score_fast<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ScoreSmem));
     if (e == cudaSuccess)
         e = cudaFuncSetAttribute(k_score_fast<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ScoreSmem));
+    for (int m = 0; m < 2 && e == cudaSuccess; m++)
+    {
+        int per_sm = 1;
+        e = m ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_score_fast<true>, kScoreThreads, sizeof(ScoreSmem))
+              : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_score_fast<false>, kScoreThreads, sizeof(ScoreSmem));
+        h->score_grid[m] = h->n_sm * std::max(1, per_sm);
+    }
     if (e != cudaSuccess)
     {
         // keep the handle so that gcr_last_error can be read; every later call fails with GCR_ERR_CUDA
@@ -403,8 +411,7 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
     const int hb = static_cast<int>((H + 127) / 128);
     k_sample_solve<<<hb, 128, 0, s>>>(B, T, all_exact);
     {
-        const int max_tiles = static_cast<int>((H + kTileHyps - 1) / kTileHyps);
-        const int grid = std::max(1, std::min(max_tiles * (h->ncs + h->nco), h->n_sm * 8));
+        const int grid = h->score_grid[h->have_masks ? 1 : 0]; // persistent: one CTA per resident slot
         GCR_CUDA(cudaEventRecord(h->evk0, s));
         if (h->have_masks)
             k_score_fast<true><<<grid, kScoreThreads, sizeof(ScoreSmem), s>>>(B, T);

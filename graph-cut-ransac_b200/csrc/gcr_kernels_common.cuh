@@ -8,10 +8,10 @@
 namespace gcr
 {
 
-constexpr int kChunk = 512;             // features per shared-memory stage
+constexpr int kChunk = 256;             // features per shared-memory stage
 constexpr int kChunkFloats = 3 * kChunk; // three SoA planes per chunk
 constexpr int kChunkBytes = kChunkFloats * 4;
-constexpr int kStages = 4;
+constexpr int kStages = 6;
 constexpr int kScoreThreads = 128;
 constexpr int kHB = 2; // hypotheses per thread in the fast kernel
 constexpr int kTileHyps = kScoreThreads * kHB;
@@ -24,7 +24,7 @@ struct Counters
 {
     unsigned int n_sample_valid, n_solved, n_fast, n_hard;
     unsigned int n_worklist, n_worklist_overflow, n_candidates, n_cand_overflow;
-    unsigned int n_bad_sample, n_irregular_evals, blocks_done, n_sens;
+    unsigned int n_bad_sample, next_item, blocks_done, n_sens;
     unsigned long long best_key; // ordered bits of the best fast score among model-valid hypotheses
     unsigned long long pad1;
 };

@@ -298,7 +298,7 @@ __device__ __forceinline__ void score_item(const Buffers& B, const Thresholds& T
 }
 
 template <bool MASKS>
-__global__ void __launch_bounds__(kScoreThreads) k_score_fast(const __grid_constant__ Buffers B,
+__global__ void __launch_bounds__(kScoreThreads, 6) k_score_fast(const __grid_constant__ Buffers B,
                                                               const __grid_constant__ Thresholds T)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -317,8 +317,10 @@ __global__ void __launch_bounds__(kScoreThreads) k_score_fast(const __grid_const
     const int n_fast = static_cast<int>(B.ctr->n_fast), n_sens = static_cast<int>(B.ctr->n_sens);
     const int tiles_a = (n_fast + kTileHyps - 1) / kTileHyps, tiles_b = (n_sens + kTileHyps - 1) / kTileHyps;
     const int chunks_a = B.ncs + B.nco, chunks_b = B.ncsd + B.ncod;
-    // work decomposition, identical in every CTA: split the chunk lists so that the grid has ~4 items per CTA
-    const int target = 4 * static_cast<int>(gridDim.x);
+    // Work decomposition, identical in every CTA: the chunk lists are cut so that there are ~8 items per resident
+    // CTA; items are handed out dynamically (atomic counter), costliest first: precise tiles, then FP32 tiles from
+    // the orientation end of the chunk list (an orientation evaluation costs about twice a scale evaluation).
+    const int target = 8 * static_cast<int>(gridDim.x);
     const int tiles = tiles_a + 2 * tiles_b; // a precise tile has twice the chunks
     int splits_a = 1;
     if (tiles > 0 && tiles < target) splits_a = min(chunks_a, (target + tiles - 1) / tiles);
@@ -326,21 +328,27 @@ __global__ void __launch_bounds__(kScoreThreads) k_score_fast(const __grid_const
     splits_a = (chunks_a + cps_a - 1) / cps_a;
     const int cps_b = min(chunks_b, 2 * cps_a);
     const int splits_b = (chunks_b + cps_b - 1) / cps_b;
-    const int items_a = tiles_a * splits_a, n_items = items_a + tiles_b * splits_b;
+    const int items_b = tiles_b * splits_b, n_items = items_b + tiles_a * splits_a;
 
+    __shared__ int s_item;
     uint32_t ring = 0; // chunks issued / consumed so far by this CTA (ring position, same in every thread)
-    for (int item = blockIdx.x; item < n_items; item += gridDim.x)
+    for (;;)
     {
-        if (item < items_a)
+        if (threadIdx.x == 0) s_item = static_cast<int>(atomicAdd(&B.ctr->next_item, 1u));
+        __syncthreads();
+        const int item = s_item;
+        __syncthreads();
+        if (item >= n_items) break;
+        if (item >= items_b)
         {
-            const int tile = item / splits_a, split = item - tile * splits_a;
+            const int k = item - items_b;
+            const int split = splits_a - 1 - k / tiles_a, tile = k % tiles_a;
             score_item<MASKS, false>(B, T, S, ring, tile * kTileHyps, n_fast, false, split * cps_a,
                                      min(chunks_a, (split + 1) * cps_a), splits_a == 1);
         }
         else
         {
-            const int it = item - items_a;
-            const int tile = it / splits_b, split = it - tile * splits_b;
+            const int split = splits_b - 1 - item / tiles_b, tile = item % tiles_b;
             score_item<MASKS, true>(B, T, S, ring, tile * kTileHyps, n_sens, true, split * cps_b,
                                     min(chunks_b, (split + 1) * cps_b), splits_b == 1);
         }
