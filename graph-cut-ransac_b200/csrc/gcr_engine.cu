@@ -106,39 +106,38 @@ namespace
 
 // r^2 = z P(z), z = tan^2: degree-3 interpolation of P(z) = (atan(sqrt z)/sqrt z)^2 at Chebyshev nodes of
 // [0, zmax]; returns the maximum relative error of z P(z) against atan^2 on a dense grid.
-double fit_atan2_poly(double zmax, float pc[4])
+double fit_atan2_poly(double zmax, float pc[4], int deg)
 {
     auto P = [](double z) {
         if (z < 1e-12) return 1.0 - 2.0 * z / 3.0;
         const double s = std::sqrt(z), a = std::atan(s) / s;
         return a * a;
     };
-    double x[4], y[4];
-    for (int i = 0; i < 4; i++)
+    const int n = deg + 1; // interpolation nodes
+    double x[4], dd[4];
+    for (int i = 0; i < n; i++)
     {
-        x[i] = 0.5 * zmax * (1.0 + std::cos(M_PI * (2.0 * i + 1.0) / 8.0));
-        y[i] = P(x[i]);
+        x[i] = 0.5 * zmax * (1.0 + std::cos(M_PI * (2.0 * i + 1.0) / (2.0 * n)));
+        dd[i] = P(x[i]);
     }
     // Newton divided differences -> monomial coefficients
-    double dd[4] = {y[0], y[1], y[2], y[3]};
-    for (int j = 1; j < 4; j++)
-        for (int i = 3; i >= j; i--) dd[i] = (dd[i] - dd[i - 1]) / (x[i] - x[i - j]);
-    double c[4] = {dd[3], 0, 0, 0}; // Horner expansion of the Newton form
-    int deg = 0;
-    for (int k = 2; k >= 0; k--)
+    for (int j = 1; j < n; j++)
+        for (int i = n - 1; i >= j; i--) dd[i] = (dd[i] - dd[i - 1]) / (x[i] - x[i - j]);
+    double c[4] = {dd[n - 1], 0, 0, 0}; // Horner expansion of the Newton form
+    int d = 0;
+    for (int k = n - 2; k >= 0; k--)
     {
-        // c(z) <- c(z) * (z - x[k]) + dd[k]
-        double nc[4] = {0, 0, 0, 0};
-        for (int i = 0; i <= deg; i++)
+        double nc[4] = {0, 0, 0, 0}; // c(z) <- c(z) * (z - x[k]) + dd[k]
+        for (int i = 0; i <= d; i++)
         {
             nc[i + 1] += c[i];
             nc[i] -= c[i] * x[k];
         }
         nc[0] += dd[k];
-        deg++;
-        for (int i = 0; i <= deg; i++) c[i] = nc[i];
+        d++;
+        for (int i = 0; i <= d; i++) c[i] = nc[i];
     }
-    for (int i = 0; i < 4; i++) pc[i] = static_cast<float>(c[i]);
+    for (int i = 0; i < 4; i++) pc[i] = i < n ? static_cast<float>(c[i]) : 0.f;
     double worst = 0.0;
     for (int i = 1; i <= 2000; i++)
     {
@@ -169,11 +168,17 @@ Thresholds make_thresholds(const double thr[2])
         const double tt = std::tan(tr1);
         T.tanT = static_cast<float>(tt);
         const double zmax = (tt * 1.01 + 1e-6) * (tt * 1.01 + 1e-6);
-        const double fit_err = fit_atan2_poly(zmax, T.pc);
-        if (fit_err > 5e-7) T.orient_all_exact = 1;
+        T.poly_deg = 2;
+        if (fit_atan2_poly(zmax, T.pc, 2) > 5e-7)
+        {
+            T.poly_deg = 3;
+            if (fit_atan2_poly(zmax, T.pc, 3) > 5e-7) T.orient_all_exact = 1;
+        }
     }
     // rounding of tanT to float + rcp (1 ulp) + two multiplies + polynomial-free compare
     T.t_band0 = static_cast<float>(26.0 * kU + 4.0 * kU * T.tanT);
+    T.t_lo0 = std::nextafter(T.tanT - T.t_band0, -1.0f);
+    T.t_hi0 = std::nextafter(T.tanT + T.t_band0, 2.0f);
     return T;
 }
 

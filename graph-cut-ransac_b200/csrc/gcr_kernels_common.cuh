@@ -12,8 +12,17 @@ constexpr int kChunk = 256;             // features per shared-memory stage
 constexpr int kChunkFloats = 3 * kChunk; // three SoA planes per chunk
 constexpr int kChunkBytes = kChunkFloats * 4;
 constexpr int kStages = 6;
-constexpr int kScoreThreads = 128;
-constexpr int kHB = 2; // hypotheses per thread in the fast kernel
+#ifndef GCR_THREADS
+#define GCR_THREADS 128
+#endif
+#ifndef GCR_HB
+#define GCR_HB 1
+#endif
+#ifndef GCR_MINB
+#define GCR_MINB 8
+#endif
+constexpr int kScoreThreads = GCR_THREADS;
+constexpr int kHB = GCR_HB; // hypotheses per thread in the fast kernel
 constexpr int kTileHyps = kScoreThreads * kHB;
 constexpr int kCandCap = 1024;
 constexpr int kIrrCap = 4096;
@@ -42,6 +51,8 @@ struct Thresholds
     float Tp;        // sqrt(tsq0) / (3 ln 2): scale threshold in log2 units of v
     float tanT;      // tan(sqrt(tsq1))
     float t_band0;   // constant part of the orientation band in tan units
+    float t_lo0, t_hi0; // tanT -/+ t_band0 (rounded outwards)
+    int poly_deg;    // 2 or 3: degree of the r^2 polynomial that meets the fit tolerance
     float pc[4];     // r^2 = z (pc0 + z (pc1 + z (pc2 + z pc3))), z = tan^2
     float scale_unit; // (3 ln 2)^2: converts sum of d^2 (log2 units) into sum of r^2
     int orient_all_exact; // orientation threshold outside the fast path's range -> every hypothesis exact

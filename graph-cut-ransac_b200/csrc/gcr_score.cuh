@@ -59,12 +59,12 @@ __device__ __forceinline__ Verdict orient_verdict(float n, float d, const HypReg
     const float mn = fminf(a1, a2), mx = fmaxf(fmaxf(a1, a2), 1e-30f);
     const float ri = rcp_approx(mx);
     const float t = mn * ri;
-    const float band = fmaf(H.dpr, ri, T.t_band0);
     Verdict e;
-    e.in = t <= T.tanT - band;
-    e.unc = (t <= T.tanT + band) && !e.in;
+    e.in = t <= fmaf(-H.dpr, ri, T.t_lo0);               // tanT - band0 - dpr / max
+    e.unc = (t <= fmaf(H.dpr, ri, T.t_hi0)) && !e.in;   // tanT + band0 + dpr / max
     z = t * t;
-    p = fmaf(z, fmaf(z, fmaf(z, T.pc[3], T.pc[2]), T.pc[1]), T.pc[0]);
+    if (T.poly_deg == 2) p = fmaf(z, fmaf(z, T.pc[2], T.pc[1]), T.pc[0]); // uniform branch (kernel parameter)
+    else p = fmaf(z, fmaf(z, fmaf(z, T.pc[3], T.pc[2]), T.pc[1]), T.pc[0]);
     return e;
 }
 
@@ -119,12 +119,14 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
             fb[0] = b.x; fb[1] = b.y; fb[2] = b.z; fb[3] = b.w;
             fc[0] = c.x; fc[1] = c.y; fc[2] = c.z; fc[3] = c.w;
         }
-        auto verdict = [&](int j, int e, float& x0, float& x1) -> Verdict {
+        // verdict of hypothesis j on one feature given its three plane values (FP32 or FP64 flavour)
+        auto verdict = [&](int j, float a32, float b32, float c32, double a64, double b64, double c64, float& x0,
+                           float& x1) -> Verdict {
             if constexpr (CLS == 0)
             {
                 float v;
-                if constexpr (PRECISE) v = static_cast<float>(fma(-H[j].h8d, db[e], fma(-H[j].h7d, da[e], dc[e])));
-                else v = fmaf(H[j].nh8, fb[e], fmaf(H[j].nh7, fa[e], fc[e]));
+                if constexpr (PRECISE) v = static_cast<float>(fma(-H[j].h8d, b64, fma(-H[j].h7d, a64, c64)));
+                else v = fmaf(H[j].nh8, b32, fmaf(H[j].nh7, a32, c32));
                 x1 = 0.f;
                 return scale_verdict(v, H[j], x0);
             }
@@ -133,13 +135,13 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
                 float n, d;
                 if constexpr (PRECISE)
                 {
-                    n = static_cast<float>(fma(da[e], -H[j].h7d, db[e])); // sin - k h7
-                    d = static_cast<float>(fma(da[e], H[j].h8d, dc[e]));  // cos + k h8
+                    n = static_cast<float>(fma(a64, -H[j].h7d, b64)); // sin - k h7
+                    d = static_cast<float>(fma(a64, H[j].h8d, c64));  // cos + k h8
                 }
                 else
                 {
-                    n = fmaf(fa[e], H[j].nh7, fb[e]);
-                    d = fmaf(-fa[e], H[j].nh8, fc[e]);
+                    n = fmaf(a32, H[j].nh7, b32);
+                    d = fmaf(-a32, H[j].nh8, c32);
                 }
                 return orient_verdict(n, d, H[j], T, x0, x1);
             }
@@ -152,7 +154,8 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
             for (int e = 0; e < G; e++)
             {
                 float x0, x1;
-                const Verdict r = verdict(j, e, x0, x1);
+                const Verdict r = PRECISE ? verdict(j, 0.f, 0.f, 0.f, da[e], db[e], dc[e], x0, x1)
+                                          : verdict(j, fa[e], fb[e], fc[e], 0.0, 0.0, 0.0, x0, x1);
                 if (r.in)
                 {
                     acc[j] = CLS == 0 ? fmaf(x0, x0, acc[j]) : fmaf(x0, x1, acc[j]);
@@ -164,17 +167,28 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
         }
         if (__any_sync(0xffffffffu, any_unc))
         {
-            // rare: re-derive which pairs of this group are inside the band (same instructions, same inputs)
+            // rare: re-derive which pairs of this group are inside the band (same instructions, same inputs,
+            // re-read from shared memory so that this path stays a small rolled loop out of the hot stream)
 #pragma unroll
             for (int j = 0; j < kHB; j++)
-#pragma unroll
+            {
+#pragma unroll 1
                 for (int e = 0; e < G; e++)
                 {
                     float x0, x1;
-                    const Verdict r = verdict(j, e, x0, x1);
+                    Verdict r;
+                    if constexpr (PRECISE)
+                    {
+                        const double* sd = reinterpret_cast<const double*>(stage);
+                        r = verdict(j, 0.f, 0.f, 0.f, sd[g * G + e], sd[NF + g * G + e], sd[2 * NF + g * G + e], x0, x1);
+                    }
+                    else
+                        r = verdict(j, stage[g * G + e], stage[NF + g * G + e], stage[2 * NF + g * G + e], 0.0, 0.0, 0.0,
+                                    x0, x1);
                     if (r.unc && H[j].active)
                         worklist_push(B, H[j].hyp, (CLS ? 0x80000000u : 0u) | static_cast<unsigned>(fbase + g * G + e));
                 }
+            }
         }
         if (MASKS && ((g + 1) * G) % 32 == 0)
         {
@@ -298,7 +312,7 @@ __device__ __forceinline__ void score_item(const Buffers& B, const Thresholds& T
 }
 
 template <bool MASKS>
-__global__ void __launch_bounds__(kScoreThreads, 6) k_score_fast(const __grid_constant__ Buffers B,
+__global__ void __launch_bounds__(kScoreThreads, GCR_MINB) k_score_fast(const __grid_constant__ Buffers B,
                                                               const __grid_constant__ Thresholds T)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];

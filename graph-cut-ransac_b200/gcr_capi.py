@@ -12,7 +12,7 @@ import os
 import numpy as np
 
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(PKG_DIR, "libgcr_b200.so")
+LIB_PATH = os.environ.get("GCR_B200_LIB", os.path.join(PKG_DIR, "libgcr_b200.so"))  # override: kernel-variant sweeps
 
 FLAG_SAMPLE_VALID, FLAG_SOLVED, FLAG_MODEL_VALID, FLAG_EXACT = 1, 2, 4, 8
 RUN_EMIT_MASKS, RUN_SAMPLES_ON_DEVICE, RUN_KEEP_PER_HYP, RUN_ALL_EXACT = 1, 2, 4, 8
