@@ -78,6 +78,8 @@ struct gcr_engine_s
     DevBuf<unsigned int> d_cand_hyp, d_cand_cnt, d_cand_masks, d_best_masks;
     DevBuf<Model4> d_cand_model;
     DevBuf<double> d_cand_score;
+    DevBuf<unsigned long long> d_cand_qsum;
+    DevBuf<unsigned int> d_cand_rawcnt;
     DevBuf<Counters> d_ctr;
     DevBuf<Record> d_record;
     DevBuf<double> d_dbg_in, d_dbg_out;
@@ -225,6 +227,8 @@ Buffers make_buffers(gcr_engine_s* h, unsigned long long seed, bool have_samples
     B.cand_model = h->d_cand_model.p;
     B.cand_score = h->d_cand_score.p;
     B.cand_cnt = h->d_cand_cnt.p;
+    B.cand_qsum = h->d_cand_qsum.p;
+    B.cand_rawcnt = h->d_cand_rawcnt.p;
     B.cand_masks = h->d_cand_masks.p;
     B.ctr = h->d_ctr.p;
     B.record = h->d_record.p;
@@ -242,6 +246,8 @@ int ensure_common(gcr_engine_s* h)
     GCR_CUDA(h->d_cand_model.ensure(kCandCap));
     GCR_CUDA(h->d_cand_score.ensure(kCandCap));
     GCR_CUDA(h->d_cand_cnt.ensure(2 * kCandCap));
+    GCR_CUDA(h->d_cand_qsum.ensure(2 * kCandCap));
+    GCR_CUDA(h->d_cand_rawcnt.ensure(2 * kCandCap));
     GCR_CUDA(h->d_cand_masks.ensure(W * kCandCap));
     GCR_CUDA(h->d_best_masks.ensure(W));
     return GCR_OK;
@@ -302,7 +308,7 @@ int gcr_destroy(gcr_handle h)
     h->d_cnts.release(); h->d_ninl.release(); h->d_masks.release(); h->d_fast_hyp.release();
     h->d_hard_hyp.release(); h->d_pf0.release(); h->d_pf1.release(); h->d_worklist.release();
     h->d_cand_hyp.release(); h->d_cand_cnt.release(); h->d_cand_masks.release(); h->d_best_masks.release();
-    h->d_cand_model.release(); h->d_cand_score.release(); h->d_ctr.release(); h->d_record.release();
+    h->d_cand_model.release(); h->d_cand_score.release(); h->d_cand_qsum.release(); h->d_cand_rawcnt.release(); h->d_ctr.release(); h->d_record.release();
     h->d_dbg_in.release(); h->d_dbg_out.release();
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
@@ -425,11 +431,11 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
         GCR_CUDA(cudaEventRecord(h->evk1, s));
     }
     k_fixup<<<h->n_sm * 2, 256, 0, s>>>(B, T);
-    k_exact_items<<<h->n_sm * 4, kExactThreads, 0, s>>>(B, T, 0);
+    k_exact_items<<<h->n_sm * 8, kExactThreads, 0, s>>>(B, T, 0);
     k_finalize<<<hb, 128, 0, s>>>(B, T);
     k_collect<<<hb, 128, 0, s>>>(B, 4e-5);
-    k_exact_items<<<64, kExactThreads, 0, s>>>(B, T, 1);
-    k_select<<<1, 128, 0, s>>>(B);
+    k_exact_items<<<h->n_sm * 2, kExactThreads, 0, s>>>(B, T, 1);
+    k_select<<<1, 128, 0, s>>>(B, T);
     GCR_CUDA(cudaEventRecord(h->ev1, s));
     GCR_CUDA(cudaGetLastError());
     h->have_run = true;
@@ -515,7 +521,8 @@ int gcr_score_model(gcr_handle h, const double model[4], const double thr[2], do
     const Model4 m = {model[0], model[1], model[2], model[3]};
     cudaStream_t s = h->stream;
     k_set_model<<<1, 1, 0, s>>>(B, m);
-    k_exact_items<<<1, kExactThreads, 0, s>>>(B, T, 2);
+    k_exact_items<<<h->n_sm * 2, kExactThreads, 0, s>>>(B, T, 2);
+    k_cand_value<<<1, 1, 0, s>>>(B, T);
     GCR_CUDA(cudaGetLastError());
     GCR_CUDA(cudaStreamSynchronize(s));
     const size_t ws = (h->ns + 31) / 32, wo = (h->no + 31) / 32;

@@ -335,78 +335,16 @@ __global__ void k_fixup(Buffers B, Thresholds T)
 
 // ------------------------------------------------------------------------------------------------
 // FP64 reference-order MSAC of whole hypotheses: MSACScoringFunction::getScore
-// (MSAC_scoring_function.hpp:53-130) with one CTA per hypothesis; a warp covers 32 consecutive features so
-// that __ballot_sync yields the packed mask word directly.
-//   mode 0: the hard list (results into the per-hypothesis arrays)
-//   mode 1: the candidate list (results into the candidate slots, value finalised)
-//   mode 2: one caller-supplied model in cand slot 0
+// (MSAC_scoring_function.hpp:53-130).  Work unit = (hypothesis, block of 256 consecutive features of one class);
+// a warp covers 32 consecutive features so that __ballot_sync yields the packed mask word directly.
+// Partial sums are accumulated ORDER-INDEPENDENTLY as 64-bit fixed point (units of tsq * 2^-44 per class), so the
+// result does not depend on how units are scheduled: equal models get bit-equal scores (S11 ties stay ties).
+//   mode 0: the hard list (accumulators: the hypothesis' own sums/cnts slots, reinterpreted as u64)
+//   mode 1: the candidate list; mode 2: one caller-supplied model in candidate slot 0
 constexpr int kExactThreads = 256;
+constexpr double kFix = 17592186044416.0; // 2^44
 
-__device__ inline void exact_score_block(const Buffers& B, const Thresholds& T, const Model4& m, double& sum0,
-                                         double& sum1, unsigned int& c0, unsigned int& c1, unsigned int* mask_out)
-{
-    __shared__ double red[2][kExactThreads / 32];
-    __shared__ unsigned int redc[2][kExactThreads / 32];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    double s[2] = {0.0, 0.0};
-    unsigned int c[2] = {0u, 0u};
-#pragma unroll
-    for (int cls = 0; cls < 2; cls++)
-    {
-        const int n = cls ? B.no : B.ns;
-        const double* F = cls ? B.orient : B.scale;
-        const int nw = (n + 31) >> 5;
-        for (int w = warp; w < nw; w += kExactThreads / 32)
-        {
-            const int f = w * 32 + lane;
-            bool in = false;
-            double r2 = 0.0;
-            if (f < n)
-            {
-                const double r = cls ? orientation_residual(F[3 * f], F[3 * f + 1], F[3 * f + 2], m)
-                                     : scale_residual(F[3 * f], F[3 * f + 1], F[3 * f + 2], m);
-                r2 = r * r;
-                in = r2 <= T.tsq[cls];
-            }
-            const unsigned int word = __ballot_sync(0xffffffffu, in);
-            if (in)
-            {
-                s[cls] += r2;
-                c[cls]++;
-            }
-            if (mask_out && lane == 0) mask_out[(cls ? B.ws : 0) + w] = word;
-        }
-    }
-#pragma unroll
-    for (int cls = 0; cls < 2; cls++)
-    {
-        double v = s[cls];
-        unsigned int k = c[cls];
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1)
-        {
-            v += __shfl_xor_sync(0xffffffffu, v, o);
-            k += __shfl_xor_sync(0xffffffffu, k, o);
-        }
-        if (lane == 0)
-        {
-            red[cls][warp] = v;
-            redc[cls][warp] = k;
-        }
-    }
-    __syncthreads();
-    double t0 = 0.0, t1 = 0.0;
-    unsigned int k0 = 0, k1 = 0;
-    for (int w = 0; w < kExactThreads / 32; w++)
-    {
-        t0 += red[0][w];
-        t1 += red[1][w];
-        k0 += redc[0][w];
-        k1 += redc[1][w];
-    }
-    __syncthreads();
-    sum0 = t0; sum1 = t1; c0 = k0; c1 = k1;
-}
+__device__ __forceinline__ double fix_to_double(unsigned long long q, double tsq) { return static_cast<double>(q) * (tsq / kFix); }
 
 // S2/S3: per-class value = -sum r^2 / tsq + n; any class below the minimal sample size (2) zeroes everything
 __device__ __forceinline__ double msac_value(const Thresholds& T, double s0, double s1, unsigned int c0, unsigned int c1,
@@ -424,38 +362,77 @@ __device__ __forceinline__ double msac_value(const Thresholds& T, double s0, dou
 
 __global__ void __launch_bounds__(kExactThreads) k_exact_items(Buffers B, Thresholds T, int mode)
 {
+    __shared__ unsigned long long red[kExactThreads / 32];
+    __shared__ unsigned int redc[kExactThreads / 32];
     const unsigned int n_items = mode == 0 ? B.ctr->n_hard : (mode == 1 ? min(B.ctr->n_candidates, static_cast<unsigned>(kCandCap)) : 1u);
-    for (unsigned int it = blockIdx.x; it < n_items; it += gridDim.x)
+    const unsigned int ups = (B.ns + kExactThreads - 1) / kExactThreads, upo = (B.no + kExactThreads - 1) / kExactThreads;
+    const unsigned int upi = ups + upo;
+    const unsigned long long n_units = static_cast<unsigned long long>(n_items) * upi;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (unsigned long long unit = blockIdx.x; unit < n_units; unit += gridDim.x)
     {
-        double s0, s1;
-        unsigned int c0, c1;
-        if (mode == 0)
+        const unsigned int it = static_cast<unsigned int>(unit / upi), u = static_cast<unsigned int>(unit % upi);
+        const int cls = u >= ups;
+        const int f = static_cast<int>((cls ? u - ups : u) * kExactThreads) + tid;
+        const int n = cls ? B.no : B.ns;
+        const double* F = cls ? B.orient : B.scale;
+        const unsigned int h = mode == 0 ? B.hard_hyp[it] : 0u;
+        const Model4 m = mode == 0 ? B.models[h] : B.cand_model[it];
+        unsigned int* mask_out = mode == 0 ? (B.masks ? B.masks + static_cast<size_t>(h) * B.wmask : nullptr)
+                                           : B.cand_masks + static_cast<size_t>(it) * B.wmask;
+        bool in = false;
+        unsigned long long q = 0ull;
+        if (f < n)
         {
-            const unsigned int h = B.hard_hyp[it];
-            const Model4 m = B.models[h];
-            exact_score_block(B, T, m, s0, s1, c0, c1, B.masks ? B.masks + static_cast<size_t>(h) * B.wmask : nullptr);
-            if (threadIdx.x == 0)
+            const double r = cls ? orientation_residual(F[3 * f], F[3 * f + 1], F[3 * f + 2], m)
+                                 : scale_residual(F[3 * f], F[3 * f + 1], F[3 * f + 2], m);
+            const double r2 = r * r;
+            in = r2 <= T.tsq[cls]; // S1
+            if (in) q = static_cast<unsigned long long>(r2 / T.tsq[cls] * kFix + 0.5);
+        }
+        const unsigned int word = __ballot_sync(0xffffffffu, in);
+        if (mask_out && lane == 0 && (f - lane) < n) mask_out[(cls ? B.ws : 0) + ((f - lane) >> 5)] = word;
+        unsigned int k = __popc(word);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+        if (lane == 0)
+        {
+            red[warp] = q;
+            redc[warp] = k;
+        }
+        __syncthreads();
+        if (tid == 0)
+        {
+            unsigned long long tq = 0ull;
+            unsigned int tk = 0u;
+            for (int w = 0; w < kExactThreads / 32; w++)
             {
-                B.sums[2 * h] = s0;
-                B.sums[2 * h + 1] = s1;
-                B.cnts[2 * h] = c0;
-                B.cnts[2 * h + 1] = c1;
+                tq += red[w];
+                tk += redc[w];
+            }
+            unsigned long long* qs = mode == 0 ? reinterpret_cast<unsigned long long*>(B.sums) + 2 * static_cast<size_t>(h)
+                                               : B.cand_qsum + 2 * static_cast<size_t>(it);
+            unsigned int* cs = mode == 0 ? B.cnts + 2 * static_cast<size_t>(h) : B.cand_rawcnt + 2 * static_cast<size_t>(it);
+            if (tk)
+            {
+                atomicAdd(qs + cls, tq);
+                atomicAdd(cs + cls, tk);
             }
         }
-        else
-        {
-            const Model4 m = B.cand_model[it];
-            exact_score_block(B, T, m, s0, s1, c0, c1, B.cand_masks + static_cast<size_t>(it) * B.wmask);
-            if (threadIdx.x == 0)
-            {
-                unsigned int n0, n1;
-                B.cand_score[it] = msac_value(T, s0, s1, c0, c1, n0, n1);
-                B.cand_cnt[2 * it] = n0;
-                B.cand_cnt[2 * it + 1] = n1;
-            }
-        }
+        __syncthreads();
     }
 }
+
+// candidate accumulators -> MSAC value + counts after the zero-reset rule
+__device__ __forceinline__ void cand_value(const Buffers& B, const Thresholds& T, unsigned int i)
+{
+    unsigned int n0, n1;
+    B.cand_score[i] = msac_value(T, fix_to_double(B.cand_qsum[2 * i], T.tsq[0]), fix_to_double(B.cand_qsum[2 * i + 1], T.tsq[1]),
+                                 B.cand_rawcnt[2 * i], B.cand_rawcnt[2 * i + 1], n0, n1);
+    B.cand_cnt[2 * i] = n0;
+    B.cand_cnt[2 * i + 1] = n1;
+}
+__global__ void k_cand_value(Buffers B, Thresholds T) { cand_value(B, T, 0); }
 
 // ------------------------------------------------------------------------------------------------
 // K4: per-hypothesis MSAC value + arg-max key over model-valid hypotheses.
@@ -468,7 +445,16 @@ __global__ void k_finalize(Buffers B, Thresholds T)
     {
         const unsigned char f = B.flags[h];
         unsigned int n0 = 0, n1 = 0;
-        if (f & 2) v = msac_value(T, B.sums[2 * h], B.sums[2 * h + 1], B.cnts[2 * h], B.cnts[2 * h + 1], n0, n1);
+        if (f & 2)
+        {
+            double s0 = B.sums[2 * h], s1 = B.sums[2 * h + 1];
+            if (f & 8) // FP64-kernel hypotheses hold fixed-point accumulators in the same slots
+            {
+                s0 = fix_to_double(reinterpret_cast<const unsigned long long*>(B.sums)[2 * h], T.tsq[0]);
+                s1 = fix_to_double(reinterpret_cast<const unsigned long long*>(B.sums)[2 * h + 1], T.tsq[1]);
+            }
+            v = msac_value(T, s0, s1, B.cnts[2 * h], B.cnts[2 * h + 1], n0, n1);
+        }
         B.score[h] = v;
         B.n_inl[2 * h] = n0;
         B.n_inl[2 * h + 1] = n1;
@@ -501,6 +487,8 @@ __global__ void k_collect(Buffers B, double rel_tol)
         {
             B.cand_hyp[slot] = h;
             B.cand_model[slot] = B.models[h];
+            B.cand_qsum[2 * slot] = B.cand_qsum[2 * slot + 1] = 0ull;
+            B.cand_rawcnt[2 * slot] = B.cand_rawcnt[2 * slot + 1] = 0u;
         }
         else
             atomicAdd(&B.ctr->n_cand_overflow, 1u);
@@ -518,11 +506,12 @@ struct Record // mirrors gcr_record
 
 // K6: final selection (GCRANSAC.h:440-462): highest exact score, earliest hypothesis on ties; writes the
 // winner record (also into the caller's buffer, e.g. an NCCL send buffer) and the winner's packed masks.
-__global__ void k_select(Buffers B)
+__global__ void k_select(Buffers B, Thresholds T)
 {
-    __shared__ double s_best;
     __shared__ unsigned int s_hyp, s_slot;
     const unsigned int n = min(B.ctr->n_candidates, static_cast<unsigned>(kCandCap));
+    for (unsigned int i = threadIdx.x; i < n; i += blockDim.x) cand_value(B, T, i);
+    __syncthreads();
     if (threadIdx.x == 0)
     {
         double best = 0.0;
@@ -538,7 +527,6 @@ __global__ void k_select(Buffers B)
                 bs = i;
             }
         }
-        s_best = best;
         s_hyp = bh;
         s_slot = bs;
         Record r;
@@ -570,6 +558,8 @@ __global__ void k_set_model(Buffers B, Model4 m)
 {
     B.cand_model[0] = m;
     B.cand_hyp[0] = 0;
+    B.cand_qsum[0] = B.cand_qsum[1] = 0ull;
+    B.cand_rawcnt[0] = B.cand_rawcnt[1] = 0u;
 }
 
 // helper-math probe (gcr_debug_eval)

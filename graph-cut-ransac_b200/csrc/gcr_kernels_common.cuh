@@ -97,7 +97,9 @@ struct Buffers
     unsigned int* cand_hyp;  // [kCandCap]
     Model4* cand_model;
     double* cand_score;
-    unsigned int* cand_cnt;  // [kCandCap,2]
+    unsigned int* cand_cnt;  // [kCandCap,2] after the zero-reset rule
+    unsigned long long* cand_qsum; // [kCandCap,2] fixed-point sums of r^2 (units of tsq 2^-44)
+    unsigned int* cand_rawcnt;     // [kCandCap,2]
     unsigned int* cand_masks; // [kCandCap, W]
     Counters* ctr;
     void* record;  // gcr_record (device), engine-owned
