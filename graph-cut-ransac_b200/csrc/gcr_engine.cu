@@ -83,6 +83,7 @@ struct gcr_engine_s
     DevBuf<Counters> d_ctr;
     DevBuf<Record> d_record;
     DevBuf<double> d_dbg_in, d_dbg_out;
+    DevBuf<Model4> d_user_models;
 
     int fail(int code, const std::string& msg)
     {
@@ -309,7 +310,7 @@ int gcr_destroy(gcr_handle h)
     h->d_hard_hyp.release(); h->d_pf0.release(); h->d_pf1.release(); h->d_worklist.release();
     h->d_cand_hyp.release(); h->d_cand_cnt.release(); h->d_cand_masks.release(); h->d_best_masks.release();
     h->d_cand_model.release(); h->d_cand_score.release(); h->d_cand_qsum.release(); h->d_cand_rawcnt.release(); h->d_ctr.release(); h->d_record.release();
-    h->d_dbg_in.release(); h->d_dbg_out.release();
+    h->d_dbg_in.release(); h->d_dbg_out.release(); h->d_user_models.release();
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
     if (h->evk0) cudaEventDestroy(h->evk0);
@@ -372,6 +373,17 @@ int gcr_set_features(gcr_handle h, const double* scale, int64_t ns, const double
                                                            h->d_irr_o.p);
     GCR_CUDA(cudaGetLastError());
     return ensure_common(h);
+}
+
+int gcr_get_features(gcr_handle h, double* scale, double* orient)
+{
+    if (!h) return GCR_ERR_INVALID;
+    if (h->ns < 2) return h->fail(GCR_ERR_STATE, "gcr_get_features before gcr_set_features");
+    GCR_CUDA(cudaSetDevice(h->device));
+    if (scale) GCR_CUDA(cudaMemcpyAsync(scale, h->scale_ptr, sizeof(double) * 3 * h->ns, cudaMemcpyDeviceToHost, h->stream));
+    if (orient) GCR_CUDA(cudaMemcpyAsync(orient, h->orient_ptr, sizeof(double) * 3 * h->no, cudaMemcpyDeviceToHost, h->stream));
+    GCR_CUDA(cudaStreamSynchronize(h->stream));
+    return GCR_OK;
 }
 
 int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, const int32_t* samples,
@@ -508,28 +520,56 @@ int gcr_fetch(gcr_handle h, uint8_t* flags, double* models, double* score, uint3
     return GCR_OK;
 }
 
+int gcr_score_models(gcr_handle h, const double* models, int64_t n, const double thr[2], uint32_t flags, double* score,
+                     uint32_t* n_inl, uint32_t* mask_words)
+{
+    if (!h || !models || !thr) return GCR_ERR_INVALID;
+    if (h->ns < 2) return h->fail(GCR_ERR_STATE, "gcr_score_models before gcr_set_features");
+    if (n < 1 || n > kCandCap) return h->fail(GCR_ERR_INVALID, "gcr_score_models: 1 <= n <= 1024 models per call");
+    if (!(thr[0] >= 0.0) || !(thr[1] >= 0.0) || !std::isfinite(thr[0]) || !std::isfinite(thr[1]))
+        return h->fail(GCR_ERR_INVALID, "thresholds must be finite and non-negative");
+    GCR_CUDA(cudaSetDevice(h->device));
+    int rc = ensure_common(h);
+    if (rc != GCR_OK) return rc;
+    GCR_CUDA(h->d_user_models.ensure(kCandCap));
+    Thresholds T = make_thresholds(thr);
+    if (flags & GCR_SCORE_TRUNCATED_SQ) // the relabelling threshold of the local optimisation, GCRANSAC.h:207-208,931-937
+    {
+        T.tsq[0] = (1.5 * thr[0]) * (1.5 * thr[0]);
+        T.tsq[1] = (1.5 * thr[1]) * (1.5 * thr[1]);
+    }
+    const Buffers B = make_buffers(h, 0, false, nullptr);
+    cudaStream_t s = h->stream;
+    const unsigned int un = static_cast<unsigned int>(n);
+    GCR_CUDA(cudaMemcpyAsync(h->d_user_models.p, models, sizeof(Model4) * n, cudaMemcpyHostToDevice, s));
+    k_set_models<<<(un + 127) / 128, 128, 0, s>>>(B, h->d_user_models.p, un);
+    const unsigned long long units =
+        static_cast<unsigned long long>(un) * ((h->ns + kExactThreads - 1) / kExactThreads + (h->no + kExactThreads - 1) / kExactThreads);
+    const int grid = static_cast<int>(std::min<unsigned long long>(units, static_cast<unsigned long long>(h->n_sm) * 8));
+    k_exact_items<<<grid, kExactThreads, 0, s>>>(B, T, 2, un);
+    k_cand_value<<<(un + 127) / 128, 128, 0, s>>>(B, T, un);
+    GCR_CUDA(cudaGetLastError());
+    const size_t W = static_cast<size_t>((h->ns + 31) / 32 + (h->no + 31) / 32);
+    if (score) GCR_CUDA(cudaMemcpyAsync(score, h->d_cand_score.p, sizeof(double) * n, cudaMemcpyDeviceToHost, s));
+    if (n_inl) GCR_CUDA(cudaMemcpyAsync(n_inl, h->d_cand_cnt.p, 2 * sizeof(unsigned int) * n, cudaMemcpyDeviceToHost, s));
+    if (mask_words) GCR_CUDA(cudaMemcpyAsync(mask_words, h->d_cand_masks.p, 4 * W * n, cudaMemcpyDeviceToHost, s));
+    GCR_CUDA(cudaStreamSynchronize(s));
+    return GCR_OK;
+}
+
 int gcr_score_model(gcr_handle h, const double model[4], const double thr[2], double* score, uint32_t n_inl[2],
                     uint32_t* scale_mask_words, uint32_t* orient_mask_words)
 {
     if (!h || !model || !thr) return GCR_ERR_INVALID;
     if (h->ns < 2) return h->fail(GCR_ERR_STATE, "gcr_score_model before gcr_set_features");
-    GCR_CUDA(cudaSetDevice(h->device));
-    int rc = ensure_common(h);
-    if (rc != GCR_OK) return rc;
-    const Thresholds T = make_thresholds(thr);
-    const Buffers B = make_buffers(h, 0, false, nullptr);
-    const Model4 m = {model[0], model[1], model[2], model[3]};
-    cudaStream_t s = h->stream;
-    k_set_model<<<1, 1, 0, s>>>(B, m);
-    k_exact_items<<<h->n_sm * 2, kExactThreads, 0, s>>>(B, T, 2);
-    k_cand_value<<<1, 1, 0, s>>>(B, T);
-    GCR_CUDA(cudaGetLastError());
-    GCR_CUDA(cudaStreamSynchronize(s));
     const size_t ws = (h->ns + 31) / 32, wo = (h->no + 31) / 32;
-    if (score) GCR_CUDA(cudaMemcpy(score, h->d_cand_score.p, sizeof(double), cudaMemcpyDeviceToHost));
-    if (n_inl) GCR_CUDA(cudaMemcpy(n_inl, h->d_cand_cnt.p, 2 * sizeof(unsigned int), cudaMemcpyDeviceToHost));
-    if (scale_mask_words) GCR_CUDA(cudaMemcpy(scale_mask_words, h->d_cand_masks.p, 4 * ws, cudaMemcpyDeviceToHost));
-    if (orient_mask_words) GCR_CUDA(cudaMemcpy(orient_mask_words, h->d_cand_masks.p + ws, 4 * wo, cudaMemcpyDeviceToHost));
+    std::vector<uint32_t> words;
+    const bool want_masks = scale_mask_words || orient_mask_words;
+    if (want_masks) words.resize(ws + wo);
+    const int rc = gcr_score_models(h, model, 1, thr, 0, score, n_inl, want_masks ? words.data() : nullptr);
+    if (rc != GCR_OK) return rc;
+    if (scale_mask_words) std::memcpy(scale_mask_words, words.data(), 4 * ws);
+    if (orient_mask_words) std::memcpy(orient_mask_words, words.data() + ws, 4 * wo);
     return GCR_OK;
 }
 

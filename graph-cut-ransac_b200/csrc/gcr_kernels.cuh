@@ -340,7 +340,7 @@ __global__ void k_fixup(Buffers B, Thresholds T)
 // Partial sums are accumulated ORDER-INDEPENDENTLY as 64-bit fixed point (units of tsq * 2^-44 per class), so the
 // result does not depend on how units are scheduled: equal models get bit-equal scores (S11 ties stay ties).
 //   mode 0: the hard list (accumulators: the hypothesis' own sums/cnts slots, reinterpreted as u64)
-//   mode 1: the candidate list; mode 2: one caller-supplied model in candidate slot 0
+//   mode 1: the candidate list; mode 2: `n_direct` caller-supplied models in candidate slots [0, n_direct)
 constexpr int kExactThreads = 256;
 constexpr double kFix = 17592186044416.0; // 2^44
 
@@ -360,11 +360,11 @@ __device__ __forceinline__ double msac_value(const Thresholds& T, double s0, dou
     return (-s0 / T.tsq[0] + static_cast<double>(c0)) + (-s1 / T.tsq[1] + static_cast<double>(c1));
 }
 
-__global__ void __launch_bounds__(kExactThreads) k_exact_items(Buffers B, Thresholds T, int mode)
+__global__ void __launch_bounds__(kExactThreads) k_exact_items(Buffers B, Thresholds T, int mode, unsigned int n_direct = 1u)
 {
     __shared__ unsigned long long red[kExactThreads / 32];
     __shared__ unsigned int redc[kExactThreads / 32];
-    const unsigned int n_items = mode == 0 ? B.ctr->n_hard : (mode == 1 ? min(B.ctr->n_candidates, static_cast<unsigned>(kCandCap)) : 1u);
+    const unsigned int n_items = mode == 0 ? B.ctr->n_hard : (mode == 1 ? min(B.ctr->n_candidates, static_cast<unsigned>(kCandCap)) : n_direct);
     const unsigned int ups = (B.ns + kExactThreads - 1) / kExactThreads, upo = (B.no + kExactThreads - 1) / kExactThreads;
     const unsigned int upi = ups + upo;
     const unsigned long long n_units = static_cast<unsigned long long>(n_items) * upi;
@@ -432,7 +432,11 @@ __device__ __forceinline__ void cand_value(const Buffers& B, const Thresholds& T
     B.cand_cnt[2 * i] = n0;
     B.cand_cnt[2 * i + 1] = n1;
 }
-__global__ void k_cand_value(Buffers B, Thresholds T) { cand_value(B, T, 0); }
+__global__ void k_cand_value(Buffers B, Thresholds T, unsigned int n)
+{
+    const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) cand_value(B, T, i);
+}
 
 // ------------------------------------------------------------------------------------------------
 // K4: per-hypothesis MSAC value + arg-max key over model-valid hypotheses.
@@ -553,13 +557,15 @@ __global__ void k_select(Buffers B, Thresholds T)
         B.best_masks[w] = have ? B.cand_masks[static_cast<size_t>(s_slot) * B.wmask + w] : 0u;
 }
 
-// caller-supplied model -> candidate slot 0 (gcr_score_model)
-__global__ void k_set_model(Buffers B, Model4 m)
+// caller-supplied models -> candidate slots [0, n) (gcr_score_model / gcr_score_models)
+__global__ void k_set_models(Buffers B, const Model4* __restrict__ m, unsigned int n)
 {
-    B.cand_model[0] = m;
-    B.cand_hyp[0] = 0;
-    B.cand_qsum[0] = B.cand_qsum[1] = 0ull;
-    B.cand_rawcnt[0] = B.cand_rawcnt[1] = 0u;
+    const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    B.cand_model[i] = m[i];
+    B.cand_hyp[i] = i;
+    B.cand_qsum[2 * i] = B.cand_qsum[2 * i + 1] = 0ull;
+    B.cand_rawcnt[2 * i] = B.cand_rawcnt[2 * i + 1] = 0u;
 }
 
 // helper-math probe (gcr_debug_eval)

@@ -1,0 +1,374 @@
+// Host-side estimator on top of the C ABI (see gcr_host.hpp).
+#include "gcr_host.hpp"
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <limits>
+#include <map>
+#include <mutex>
+#include <random>
+#include <stdexcept>
+
+#include "../../../include/gcr_b200.h"
+#include "gcr_refit.hpp"
+
+namespace gcr_host
+{
+namespace
+{
+
+// One engine handle per device, created on first use and kept for the life of the process (device buffers are
+// reused between calls).  The reference is re-entrant; so is this: a handle is checked out for one call.
+class EnginePool
+{
+public:
+    gcr_handle acquire(int device)
+    {
+        {
+            std::lock_guard<std::mutex> lock(mu_);
+            auto& idle = idle_[device];
+            if (!idle.empty())
+            {
+                gcr_handle h = idle.back();
+                idle.pop_back();
+                return h;
+            }
+        }
+        gcr_handle h = nullptr;
+        const int rc = gcr_create(device, &h);
+        if (rc != GCR_OK)
+        {
+            const std::string msg = h ? gcr_last_error(h) : "gcr_create failed";
+            if (h) gcr_destroy(h);
+            throw DeviceError("gcr_b200: cannot create an engine on device " + std::to_string(device) + ": " + msg);
+        }
+        return h;
+    }
+    void release(int device, gcr_handle h)
+    {
+        std::lock_guard<std::mutex> lock(mu_);
+        idle_[device].push_back(h);
+    }
+
+private:
+    std::mutex mu_;
+    std::map<int, std::vector<gcr_handle>> idle_;
+};
+
+EnginePool& pool()
+{
+    static EnginePool* p = new EnginePool(); // leaked on purpose: no CUDA calls during static destruction
+    return *p;
+}
+
+struct Lease
+{
+    int device;
+    gcr_handle h;
+    explicit Lease(int d) : device(d), h(pool().acquire(d)) {}
+    ~Lease() { pool().release(device, h); }
+    void check(int rc, const char* what) const
+    {
+        if (rc == GCR_OK) return;
+        const std::string msg = std::string("gcr_b200: ") + what + ": " + gcr_last_error(h);
+        if (rc == GCR_ERR_INVALID) throw std::invalid_argument(msg);
+        throw DeviceError(msg);
+    }
+};
+
+// splitmix64: the host-side stream for the local optimisation's inner sampler
+struct SplitMix
+{
+    uint64_t s;
+    uint64_t next()
+    {
+        uint64_t z = (s += 0x9E3779B97F4A7C15ull);
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+        return z ^ (z >> 31);
+    }
+    // uniform in [0, n)
+    uint32_t below(uint32_t n) { return static_cast<uint32_t>(((next() >> 32) * static_cast<uint64_t>(n)) >> 32); }
+};
+
+// k distinct entries of `from`, uniformly (partial Fisher-Yates); the role of get_random_subset (GCRANSAC.h:53-80)
+void drawSubset(const std::vector<uint32_t>& from, size_t k, SplitMix& rng, std::vector<uint32_t>& scratch,
+                std::vector<uint32_t>& out)
+{
+    scratch = from;
+    out.clear();
+    for (size_t i = 0; i < k; ++i)
+    {
+        const size_t j = i + rng.below(static_cast<uint32_t>(scratch.size() - i));
+        std::swap(scratch[i], scratch[j]);
+        out.push_back(scratch[i]);
+    }
+}
+
+void wordsToIndices(const uint32_t* words, size_t n, std::vector<uint32_t>& out)
+{
+    out.clear();
+    for (size_t w = 0; w < (n + 31) / 32; ++w)
+    {
+        uint32_t bits = words[w];
+        while (bits)
+        {
+            const int b = __builtin_ctz(bits);
+            bits &= bits - 1;
+            const size_t i = 32 * w + b;
+            if (i < n) out.push_back(static_cast<uint32_t>(i));
+        }
+    }
+}
+
+struct Best
+{
+    bool have = false;
+    double score = 0.0;
+    double model[4] = {0, 0, 0, 0};
+    uint32_t n_inl[2] = {0, 0};
+    std::vector<uint32_t> words; // packed masks, scale class then orientation class
+};
+
+} // namespace
+
+size_t iterationNumber(const uint32_t n_inl[2], size_t ns, size_t no, double confidence)
+{
+    const double r0 = static_cast<double>(n_inl[0]) / static_cast<double>(ns);
+    const double r1 = static_cast<double>(n_inl[1]) / static_cast<double>(no);
+    const double q = std::pow(r0, 2.0) * std::pow(r1, 2.0);
+    const double lg = std::log(1.0 - q);
+    if (std::fabs(lg) < std::numeric_limits<double>::epsilon()) return std::numeric_limits<size_t>::max();
+    const double it = std::ceil(std::log(1.0 - confidence) / lg);
+    if (!(it < 1.8e19)) return std::numeric_limits<size_t>::max();
+    return it <= 0.0 ? 0 : static_cast<size_t>(it);
+}
+
+int findRectifyingHomographySIFT(const double* scale, size_t ns, const double* orient, size_t no, double thr_s, double thr_o,
+                                 double /*spatial_coherence_weight: unused by the two-class path, GCRANSAC.h:922-944*/,
+                                 size_t min_iters, size_t max_iters, size_t max_lo, std::vector<bool>& scale_inliers,
+                                 std::vector<bool>& orientation_inliers, std::vector<double>& homography,
+                                 gcransac::SIFTRectifyingHomography& model, const Options& opt, Stats* stats_out)
+{
+    const auto t_begin = std::chrono::steady_clock::now();
+    Stats st;
+    if (!scale || !orient) throw std::invalid_argument("null feature pointer");
+    // GCRANSAC.h:222-228: fewer rows than the minimal sample of a class
+    if (ns < 2 || no < 2) throw std::runtime_error("Data set smaller than minimal sample size for corresponding data type");
+    if (!(thr_s >= 0.0) || !(thr_o >= 0.0) || !std::isfinite(thr_s) || !std::isfinite(thr_o))
+        throw std::invalid_argument("residual thresholds must be finite and non-negative");
+    const double thr[2] = {thr_s, thr_o};
+    const size_t ws = (ns + 31) / 32, wo = (no + 31) / 32, W = ws + wo;
+
+    st.seed = opt.seed;
+    if (!opt.has_seed)
+    {
+        std::random_device rd; // the reference seeds every draw from random_device (GCRANSAC.h:67-70)
+        st.seed = (static_cast<uint64_t>(rd()) << 32) | rd();
+    }
+
+    Lease eng(opt.device);
+    eng.check(gcr_set_features(eng.h, scale, static_cast<int64_t>(ns), orient, static_cast<int64_t>(no),
+                               opt.features_on_device ? 1 : 0),
+              "gcr_set_features");
+
+    // ---- hypothesise / verify: while (iter < min_iters || iter < min(max_iteration, max_iters)), GCRANSAC.h:286-287,
+    //      in device batches; every drawn sample is one iteration (S13)
+    Best best;
+    best.words.assign(W, 0u);
+    size_t done = 0;
+    const uint32_t one_each[2] = {1u, 1u}; // GCRANSAC.h:233-236: the initial max_iteration assumes one inlier per class
+    size_t target = opt.samples ? static_cast<size_t>(opt.n_samples)
+                                : std::max(min_iters, std::min(iterationNumber(one_each, ns, no, opt.confidence), max_iters));
+    while (done < target)
+    {
+        // The reference re-evaluates its stopping rule after every iteration; here it is evaluated between device
+        // batches: the first batch covers min_iters (at least `batch_quantum` slots), later ones double.
+        size_t n = std::min(target - done, opt.max_batch);
+        if (!opt.samples) n = std::min(n, std::max(done == 0 ? min_iters : done, opt.batch_quantum));
+        gcr_result res;
+        eng.check(gcr_run(eng.h, static_cast<int64_t>(n), st.seed, done, opt.samples ? opt.samples + 4 * done : nullptr, thr, 0,
+                          nullptr, &res),
+                  "gcr_run");
+        st.device_calls++;
+        st.n_sample_valid += res.n_sample_valid;
+        st.n_solved += res.n_solved;
+        st.n_rechecked += res.n_rechecked;
+        st.n_exact_hyp += res.n_exact_hyp;
+        st.hypothesis_stage_ms += res.device_ms;
+        st.score_kernel_ms += res.score_kernel_ms;
+        if (res.best_index >= 0 && res.best_score > best.score) // strict: the earliest batch wins ties (S11)
+        {
+            best.have = true;
+            best.score = res.best_score;
+            std::memcpy(best.model, res.best_model, sizeof(best.model));
+            best.n_inl[0] = res.best_n_inl[0];
+            best.n_inl[1] = res.best_n_inl[1];
+            st.best_index = res.best_index;
+            eng.check(gcr_best(eng.h, nullptr, nullptr, nullptr, best.words.data(), best.words.data() + ws, nullptr), "gcr_best");
+        }
+        done += n;
+        if (!opt.samples)
+        {
+            // max_iteration = getIterationNumber(best inlier counts), GCRANSAC.h:480-483
+            const size_t adaptive = iterationNumber(best.have ? best.n_inl : one_each, ns, no, opt.confidence);
+            target = std::max(min_iters, std::min(adaptive, max_iters));
+        }
+    }
+    st.iteration_number = static_cast<int64_t>(done);
+    st.best_raw_score = best.score;
+
+    scale_inliers.assign(ns, false);
+    orientation_inliers.assign(no, false);
+    model = gcransac::SIFTRectifyingHomography();
+    auto finish = [&](int n_total) {
+        const auto Hm = model.getHomography();
+        homography.assign(Hm.begin(), Hm.end());
+        st.total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count();
+        if (stats_out) *stats_out = st;
+        return n_total;
+    };
+    // GCRANSAC.h:535-541: a best model supported by no more than a minimal sample per class is "not found"
+    if (!best.have || (best.n_inl[0] <= 2 && best.n_inl[1] <= 2)) return finish(0);
+
+    // ---- local optimisation on the selected model (graphCutLocalOptimization for two classes, GCRANSAC.h:873-1062)
+    std::vector<double> h_scale, h_orient; // host rows for the fits
+    const double* fs = scale;
+    const double* fo = orient;
+    if (opt.features_on_device)
+    {
+        h_scale.resize(3 * ns);
+        h_orient.resize(3 * no);
+        eng.check(gcr_get_features(eng.h, h_scale.data(), h_orient.data()), "gcr_get_features");
+        fs = h_scale.data();
+        fo = h_orient.data();
+    }
+    SplitMix rng{st.seed ^ 0x6C6F63616C6F7074ull};
+    std::vector<uint32_t> lab_words(W), in_s, in_o, smp_s, smp_o, scratch;
+    std::vector<double> trial_models, trial_scores;
+    std::vector<uint32_t> trial_cnt, trial_words;
+    auto asArray = [](const gcransac::SIFTRectifyingHomography& m, double out[4]) {
+        out[0] = m.h7; out[1] = m.h8; out[2] = m.alpha; out[3] = m.phi;
+    };
+
+    if (opt.do_local_optimization && max_lo > 0)
+    {
+        Best lo = best; // max_score / best_model / best_inliers of the reference
+        while (static_cast<size_t>(++st.graph_cut_number) < opt.max_graph_cut_number)
+        {
+            bool updated = false;
+            // relabel every feature with the truncated threshold r^2 <= (1.5 t)^2   (GCRANSAC.h:931-937)
+            eng.check(gcr_score_models(eng.h, lo.model, 1, thr, GCR_SCORE_TRUNCATED_SQ, nullptr, nullptr, lab_words.data()),
+                      "gcr_score_models(label)");
+            wordsToIndices(lab_words.data(), ns, in_s);
+            wordsToIndices(lab_words.data() + ws, no, in_o);
+            // inner RANSAC on the labelled inliers: min(7 x sample size, n) per class  (GCRANSAC.h:955-996)
+            const size_t k_s = std::min<size_t>(14, in_s.size()), k_o = std::min<size_t>(14, in_o.size());
+            if (in_s.size() <= 2 || in_o.size() <= 2) break; // sampling fails: neither a draw nor "use all" applies
+            trial_models.clear();
+            for (size_t trial = 0; trial < max_lo; ++trial)
+            {
+                if (k_s < in_s.size()) drawSubset(in_s, k_s, rng, scratch, smp_s); else smp_s = in_s;
+                if (k_o < in_o.size()) drawSubset(in_o, k_o, rng, scratch, smp_o); else smp_o = in_o;
+                gcransac::SIFTRectifyingHomography m;
+                if (!fitNonMinimal(fs, smp_s, fo, smp_o, m)) continue;
+                double a[4];
+                asArray(m, a);
+                trial_models.insert(trial_models.end(), a, a + 4);
+                if (trial_models.size() / 4 == 1024) break; // one device pass holds 1024 models
+            }
+            const size_t nt = trial_models.size() / 4;
+            if (nt > 0)
+            {
+                trial_scores.resize(nt);
+                trial_cnt.resize(2 * nt);
+                trial_words.resize(nt * W);
+                eng.check(gcr_score_models(eng.h, trial_models.data(), static_cast<int64_t>(nt), thr, 0, trial_scores.data(),
+                                           trial_cnt.data(), trial_words.data()),
+                          "gcr_score_models(trials)");
+                st.lo_models_scored += static_cast<int>(nt);
+                for (size_t t = 0; t < nt; ++t)
+                    if (lo.score < trial_scores[t]) // strict, in trial order (GCRANSAC.h:1034)
+                    {
+                        updated = true;
+                        lo.score = trial_scores[t];
+                        std::memcpy(lo.model, &trial_models[4 * t], sizeof(lo.model));
+                        lo.n_inl[0] = trial_cnt[2 * t];
+                        lo.n_inl[1] = trial_cnt[2 * t + 1];
+                        lo.words.assign(trial_words.begin() + t * W, trial_words.begin() + (t + 1) * W);
+                    }
+            }
+            if (!updated) break;
+        }
+        if (best.score < lo.score) best = lo;
+    }
+    st.lo_score = best.score;
+
+    // ---- final model: one least-squares refit on all inliers, kept if it scores higher (GCRANSAC.h:628-667; the
+    //      iterated re-weighted fit before it never produces a model in the reference)
+    wordsToIndices(best.words.data(), ns, in_s);
+    wordsToIndices(best.words.data() + ws, no, in_o);
+    {
+        gcransac::SIFTRectifyingHomography m;
+        if (fitNonMinimal(fs, in_s, fo, in_o, m))
+        {
+            double a[4], sc = 0.0;
+            uint32_t cnt[2];
+            asArray(m, a);
+            eng.check(gcr_score_models(eng.h, a, 1, thr, 0, &sc, cnt, lab_words.data()), "gcr_score_models(refit)");
+            if (best.score < sc)
+            {
+                st.refit_accepted = true;
+                best.score = sc;
+                std::memcpy(best.model, a, sizeof(a));
+                best.n_inl[0] = cnt[0];
+                best.n_inl[1] = cnt[1];
+                best.words = lab_words;
+            }
+        }
+    }
+    st.final_score = best.score;
+
+    model.h7 = best.model[0];
+    model.h8 = best.model[1];
+    model.alpha = best.model[2];
+    model.phi = best.model[3];
+    wordsToIndices(best.words.data(), ns, in_s);
+    wordsToIndices(best.words.data() + ws, no, in_o);
+    for (uint32_t i : in_s) scale_inliers[i] = true;
+    for (uint32_t i : in_o) orientation_inliers[i] = true;
+    return finish(static_cast<int>(in_s.size() + in_o.size()));
+}
+
+} // namespace gcr_host
+
+int findRectifyingHomographySIFT_(const std::vector<double>& scale_features, const std::vector<double>& orientation_features,
+                                  double scale_residual_thresh, double orientation_residual_thresh,
+                                  double spatial_coherence_weight, size_t min_iteration_number, size_t max_iteration_number,
+                                  size_t max_local_optimization_number, std::vector<bool>& scale_inliers,
+                                  std::vector<bool>& orientation_inliers, std::vector<double>& homography,
+                                  gcransac::SIFTRectifyingHomography& model, unsigned int verbose_level)
+{
+    // gcransac_python.cpp:18-30,277-282: a flat vector whose length is not a multiple of 3 is reported and yields 0
+    for (const auto* v : {&scale_features, &orientation_features})
+        if (v->size() % 3 != 0)
+        {
+            std::fprintf(stderr, "Feature vector size (%zu) is not a multiple of the feature size (3).\n", v->size());
+            return 0;
+        }
+    gcr_host::Stats st;
+    const int n = gcr_host::findRectifyingHomographySIFT(
+        scale_features.data(), scale_features.size() / 3, orientation_features.data(), orientation_features.size() / 3,
+        scale_residual_thresh, orientation_residual_thresh, spatial_coherence_weight, min_iteration_number,
+        max_iteration_number, max_local_optimization_number, scale_inliers, orientation_inliers, homography, model,
+        gcr_host::Options(), &st);
+    if (verbose_level > 0)
+        std::printf("\nFinal model:\n\nh7: %g, h8: %g, alpha: %g\n\nx0: %g, y0: %g, s: %g\n\nRectified image vanishing point "
+                    "direction: %g\nNumber of inliers: %d\nIterations: %lld (device %.3f ms)\n",
+                    model.h7, model.h8, model.alpha, model.x0, model.y0, model.s, model.phi * 180.0 / 3.14159265358979323846, n,
+                    static_cast<long long>(st.iteration_number), st.hypothesis_stage_ms);
+    return n;
+}

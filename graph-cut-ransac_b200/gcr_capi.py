@@ -18,8 +18,9 @@ FLAG_SAMPLE_VALID, FLAG_SOLVED, FLAG_MODEL_VALID, FLAG_EXACT = 1, 2, 4, 8
 RUN_EMIT_MASKS, RUN_SAMPLES_ON_DEVICE, RUN_KEEP_PER_HYP, RUN_ALL_EXACT = 1, 2, 4, 8
 
 EXPORTS = [
-    "gcr_create", "gcr_destroy", "gcr_last_error", "gcr_set_stream", "gcr_set_features", "gcr_run", "gcr_best",
-    "gcr_fetch", "gcr_score_model", "gcr_debug_eval", "gcr_version",
+    "gcr_create", "gcr_destroy", "gcr_last_error", "gcr_set_stream", "gcr_set_features", "gcr_get_features", "gcr_run",
+    "gcr_best",
+    "gcr_fetch", "gcr_score_model", "gcr_score_models", "gcr_debug_eval", "gcr_version",
 ]
 
 
@@ -56,10 +57,12 @@ def load_library() -> C.CDLL:
     lib.gcr_last_error.restype = C.c_char_p
     lib.gcr_set_stream.argtypes = [vp, vp]
     lib.gcr_set_features.argtypes = [vp, vp, i64, vp, i64, C.c_int]
+    lib.gcr_get_features.argtypes = [vp, vp, vp]
     lib.gcr_run.argtypes = [vp, i64, u64, u64, vp, C.POINTER(C.c_double), u32, vp, C.POINTER(GcrResult)]
     lib.gcr_best.argtypes = [vp, vp, vp, vp, vp, vp, vp]
     lib.gcr_fetch.argtypes = [vp, vp, vp, vp, vp, vp, vp]
     lib.gcr_score_model.argtypes = [vp, vp, vp, vp, vp, vp, vp]
+    lib.gcr_score_models.argtypes = [vp, vp, i64, vp, u32, vp, vp, vp]
     lib.gcr_debug_eval.argtypes = [vp, C.c_int, vp, i64, vp, vp]
     lib.gcr_version.restype = C.c_char_p
     for name in EXPORTS:
@@ -175,6 +178,19 @@ class Engine:
         self._check(self.lib.gcr_score_model(self.h, model.ctypes.data, thr.ctypes.data, C.byref(score),
                                              n_inl.ctypes.data, sm.ctypes.data, om.ctypes.data))
         return score.value, n_inl, unpack_mask(sm, self.ns), unpack_mask(om, self.no)
+
+    def score_models(self, models, thr, truncated_sq=False, masks=False):
+        """Batched exact scoring of caller-supplied models f64[n,4] (n <= 1024)."""
+        models = np.ascontiguousarray(models, np.float64).reshape(-1, 4)
+        thr = np.ascontiguousarray(thr, np.float64)
+        n = len(models)
+        W = (self.ns + 31) // 32 + (self.no + 31) // 32
+        score = np.zeros(n)
+        n_inl = np.zeros((n, 2), np.uint32)
+        words = np.zeros((n, W), np.uint32) if masks else None
+        self._check(self.lib.gcr_score_models(self.h, models.ctypes.data, n, thr.ctypes.data, 1 if truncated_sq else 0,
+                                              score.ctypes.data, n_inl.ctypes.data, words.ctypes.data if masks else None))
+        return score, n_inl, words
 
     def debug_eval(self, which, abc, model=None):
         abc = np.ascontiguousarray(abc, np.float64).reshape(-1, 3)

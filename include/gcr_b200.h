@@ -94,6 +94,10 @@ int gcr_set_stream(gcr_handle h, void* cuda_stream);
  * gcransac_python.cpp:284-296.  Requires ns >= 2 and no >= 2 (bindings.cpp:199-224). */
 int gcr_set_features(gcr_handle h, const double* scale, int64_t ns, const double* orient, int64_t no, int on_device);
 
+/* Copy the resident feature arrays back to HOST buffers f64[Ns,3] / f64[No,3] (either may be NULL).  The host-side
+ * local optimisation and refit need the rows of the inliers when the caller handed over device tensors.  Synchronises. */
+int gcr_get_features(gcr_handle h, double* scale, double* orient);
+
 /* The hypothesis stage over `n_hyp` hypothesis slots with global indices
  * [first_hyp, first_hyp + n_hyp).
  *   samples == NULL : draw minimal samples on the device, Philox4x32-10 keyed by `seed`, counter =
@@ -123,6 +127,17 @@ int gcr_fetch(gcr_handle h, uint8_t* flags, double* models, double* score, uint3
  * optimisation.  Host output buffers, any may be NULL.  Synchronises. */
 int gcr_score_model(gcr_handle h, const double model[4], const double thr[2], double* score, uint32_t n_inl[2],
                     uint32_t* scale_mask_words, uint32_t* orient_mask_words);
+
+/* Batched form of gcr_score_model: `n` (<= 1024) caller-supplied models f64[n,4] scored against the resident
+ * features in ONE device pass -- the rescoring step of the local optimisation's inner RANSAC
+ * (GCRANSAC.h:963-1046: every trial model goes through getScore) and of the final refit (:628-667).
+ * flags: GCR_SCORE_TRUNCATED_SQ compares r^2 with (1.5 t)^2, the relabelling rule of
+ * graphCutLocalOptimization (GCRANSAC.h:207-208,931-937), instead of MSAC's (2.25 t) t.
+ * Host outputs, any may be NULL: score f64[n], n_inl u32[n,2] (after the zero-reset rule),
+ * mask_words u32[n, ceil(Ns/32)+ceil(No/32)].  Synchronises. */
+#define GCR_SCORE_TRUNCATED_SQ 1u
+int gcr_score_models(gcr_handle h, const double* models, int64_t n, const double thr[2], uint32_t flags, double* score,
+                     uint32_t* n_inl, uint32_t* mask_words);
 
 /* Device-side helper math, evaluated on the GPU by the same __device__ functions the kernels use.
  * which: 0 clipAngle(a) 1 minAngleDiff(a,b) 2 linesAnglesDiff(a,b)

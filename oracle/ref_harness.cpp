@@ -175,6 +175,25 @@ int gcr_ref_find_sift(const double* scale, long ns, const double* orient, long n
     return n;
 }
 
+// The reference's non-minimal fit from ALL rows given (estimateModelNonminimal,
+// rectifying_homography_estimator.h:164-227 -> two_sift.hpp:423-612); note that its linear solve runs through the
+// shim's column-pivoted QR (oracle/shim/Eigen), the row construction and the phi histogram are the reference's own.
+// Returns 1 and model7 = (x0,y0,s,h7,h8,alpha,phi) on success.
+int gcr_ref_fit_nonminimal(const double* scale, long ns, const double* orient, long no, double* model7)
+{
+    DataType data{make_mat(scale, ns), make_mat(orient, no)};
+    const Estimator estimator;
+    Inliers inl{};
+    for (long i = 0; i < ns; ++i) inl[0].push_back(static_cast<size_t>(i));
+    for (long i = 0; i < no; ++i) inl[1].push_back(static_cast<size_t>(i));
+    std::vector<gcransac::SIFTRectifyingHomography> models;
+    if (!estimator.estimateModelNonminimal(data, inl, models) || models.empty()) return 0;
+    const auto& m = models[0];
+    model7[0] = m.x0; model7[1] = m.y0; model7[2] = m.s;
+    model7[3] = m.h7; model7[4] = m.h8; model7[5] = m.alpha; model7[6] = m.phi;
+    return 1;
+}
+
 // ---- known-answer probes of the helper math (the functions tests/unit_tests.cpp pins) ----
 double gcr_ref_clip_angle(double a) { return gcransac::utils::clipAngle(a); }
 double gcr_ref_min_angle_diff(double a, double b) { return gcransac::utils::minAngleDiff(a, b); }

@@ -230,6 +230,24 @@ class Oracle:
                     H=Hm.reshape(3, 3), model=model, seconds=float(sec[0]))
 
 
+    def fit_nonminimal(self, scale, orient):
+        """estimateModelNonminimal on all rows given (reference only); None when the fit fails."""
+        assert self.kind == "reference"
+        scale = np.ascontiguousarray(scale, np.float64)
+        orient = np.ascontiguousarray(orient, np.float64)
+        model = np.zeros(7)
+        f = self.lib.gcr_ref_fit_nonminimal
+        f.restype = C.c_int
+        f.argtypes = [_dp, C.c_long, _dp, C.c_long, _dp]
+        return model if f(scale, len(scale), orient, len(orient), model) else None
+
+    def homography(self, model7):
+        assert self.kind == "reference"
+        out = np.zeros(9)
+        self._f("homography", None, [_dp, _dp])(np.ascontiguousarray(model7, np.float64), out)
+        return out.reshape(3, 3)
+
+
 def unpack_mask(words: np.ndarray, n: int) -> np.ndarray:
     """u32 words (bit j of word w <-> feature 32w+j) -> bool[n]."""
     bits = np.unpackbits(np.ascontiguousarray(words, np.uint32).view(np.uint8), bitorder="little")

@@ -254,3 +254,36 @@ def test_error_conventions(eng):
         eng.run(1, sc.thr, samples=bad, flags=gcr_capi.RUN_KEEP_PER_HYP)
     with pytest.raises(gcr_capi.GcrError):
         eng.run(10, [float("nan"), 0.1])
+
+
+def test_batched_model_scoring_vs_oracle(eng, port):
+    """gcr_score_models: the rescoring step of the local optimisation (GCRANSAC.h:1004-1046) for a batch of caller
+    models: scores, counts and masks of every model against the oracle; the truncated-threshold relabelling
+    (GCRANSAC.h:931-937) against the oracle's per-feature residuals."""
+    import gcr_scenes as gs
+    sc = gs.make_scene(1500, 333, 0.35, 909)
+    smp = gs.draw_samples(400, 1500, 333, 17)
+    ora = port.replay(sc.scale, sc.orient, smp, sc.thr)
+    models = np.vstack([sc.model, ora["models"][(ora["flags"] & 2) > 0][:97]])
+    eng.set_features(sc.scale, sc.orient)
+    score, n_inl, words = eng.score_models(models, sc.thr, masks=True)
+    ws = (1500 + 31) // 32
+    for k, m in enumerate(models):
+        val, cnt, smask, omask = port.score_model(sc.scale, sc.orient, m, sc.thr)
+        assert np.array_equal(n_inl[k], cnt), k
+        assert score[k] == pytest.approx(val, rel=1e-9, abs=1e-12), k
+        from gcr_capi import unpack_mask
+        assert np.array_equal(unpack_mask(words[k, :ws], 1500), smask) and np.array_equal(unpack_mask(words[k, ws:], 333), omask)
+    # single-model entry point is the n = 1 case
+    v1, c1, sm1, om1 = eng.score_model(models[3], sc.thr)
+    assert v1 == score[3] and np.array_equal(c1, n_inl[3])
+    # relabelling with (1.5 t)^2
+    _, _, lab = eng.score_models(models[:5], sc.thr, truncated_sq=True, masks=True)
+    tsq = (1.5 * sc.thr) ** 2
+    for k in range(5):
+        rs, ro = port.residuals(sc.scale, sc.orient, models[k])
+        from gcr_capi import unpack_mask
+        assert np.array_equal(unpack_mask(lab[k, :ws], 1500), rs * rs <= tsq[0])
+        assert np.array_equal(unpack_mask(lab[k, ws:], 333), ro * ro <= tsq[1])
+    with pytest.raises(Exception):
+        eng.score_models(np.zeros((1025, 4)), sc.thr)
