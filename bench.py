@@ -224,9 +224,7 @@ def run_ours(args):
         e2e_eng.lib.gcr_set_features(e2e_eng.h, h_scale.data_ptr(), ns, h_orient.data_ptr(), no, 0)
         e2e_eng.ns, e2e_eng.no = ns, no
         thr_c = (gcr_capi.C.c_double * 2)(*scene.thr)
-        out = gcr_capi.GcrResult()
-        rc = e2e_eng.lib.gcr_run(e2e_eng.h, n_hyp, 0, first_hyp, gcr_capi.C.c_void_p(h_samples.data_ptr()), thr_c, 0, None,
-                                 gcr_capi.C.byref(out))
+        rc = e2e_eng.lib.gcr_run(e2e_eng.h, n_hyp, 0, first_hyp, gcr_capi.C.c_void_p(h_samples.data_ptr()), thr_c, 0, None, None)
         assert rc == 0, e2e_eng.lib.gcr_last_error(e2e_eng.h)
         e2e_eng.n_hyp = n_hyp
         return e2e_eng.best()
@@ -244,7 +242,7 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_s = float(t.item())
     h2d = scene.scale.nbytes + scene.orient.nbytes + samples.nbytes
-    d2h = 64 + 4 * ((ns + 31) // 32 + (no + 31) // 32) + 64
+    d2h = 128 + 4 * ((ns + 31) // 32 + (no + 31) // 32)  # winner record + run counters + packed masks, one copy
     e2e = {"value": world * n_hyp * nfeat / e2e_s, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
            "ms_per_step": 1e3 * e2e_s, "api": "gcr_set_features + gcr_run + gcr_best (C ABI, pinned host buffers)"}
 
@@ -259,7 +257,7 @@ def run_ours(args):
                            "l2": "flushed between timed steps (256 MiB write)", "hypotheses_scored_per_step": int(res.n_solved),
                            "guard_band_pairs": int(res.n_rechecked), "exact_hypotheses": int(res.n_exact_hyp),
                            "best_index": int(best["index"]), "best_score": float(best["score"])},
-                "clocks": sampler.summary(), "e2e": e2e, "gpu_launches": 8 * args.steps, "roofline": roofline,
+                "clocks": sampler.summary(), "e2e": e2e, "gpu_launches": 3 * args.steps, "roofline": roofline,
                 "cpu_baseline": cpu_leg}
         print(json.dumps(line))
     if world > 1:

@@ -49,6 +49,7 @@ struct gcr_engine_s
     int device = 0;
     int n_sm = 148;
     int score_grid[2] = {148, 148};
+    int tail_grid = 148;
     cudaStream_t own_stream = nullptr, stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, evk0 = nullptr, evk1 = nullptr;
     std::string err;
@@ -69,19 +70,23 @@ struct gcr_engine_s
     unsigned long long first_hyp = 0;
     bool have_masks = false, have_run = false;
     DevBuf<int> d_samples;
+    const int* samples_view = nullptr; // where the samples of the last run live (own buffer or the caller's device array)
     DevBuf<Model4> d_models;
     DevBuf<unsigned char> d_flags;
     DevBuf<double> d_sums, d_score;
     DevBuf<unsigned int> d_cnts, d_ninl, d_masks, d_fast_hyp, d_hard_hyp;
     DevBuf<float4> d_pf0, d_pf1;
     DevBuf<uint2> d_worklist;
-    DevBuf<unsigned int> d_cand_hyp, d_cand_cnt, d_cand_masks, d_best_masks;
+    DevBuf<unsigned int> d_cand_hyp, d_cand_cnt, d_cand_masks;
     DevBuf<Model4> d_cand_model;
     DevBuf<double> d_cand_score;
     DevBuf<unsigned long long> d_cand_qsum;
     DevBuf<unsigned int> d_cand_rawcnt;
     DevBuf<Counters> d_ctr;
-    DevBuf<Record> d_record;
+    // result block of a run, one contiguous D2H copy: [gcr_record 64 B][Counters snapshot 64 B][winner masks W words]
+    DevBuf<unsigned int> d_best;
+    unsigned int* h_best = nullptr; // pinned staging of the same layout
+    size_t h_best_words = 0;
     DevBuf<double> d_dbg_in, d_dbg_out;
     DevBuf<Model4> d_user_models;
 
@@ -207,7 +212,7 @@ Buffers make_buffers(gcr_engine_s* h, unsigned long long seed, bool have_samples
     B.n_hyp = h->n_hyp;
     B.first_hyp = h->first_hyp;
     B.seed = seed;
-    B.samples = h->d_samples.p;
+    B.samples = const_cast<int*>(h->samples_view);
     B.have_samples = have_samples ? 1 : 0;
     B.models = h->d_models.p;
     B.flags = h->d_flags.p;
@@ -232,17 +237,22 @@ Buffers make_buffers(gcr_engine_s* h, unsigned long long seed, bool have_samples
     B.cand_rawcnt = h->d_cand_rawcnt.p;
     B.cand_masks = h->d_cand_masks.p;
     B.ctr = h->d_ctr.p;
-    B.record = h->d_record.p;
+    B.record = h->d_best.p;
+    B.ctr_snap = reinterpret_cast<Counters*>(h->d_best.p + 16);
     B.record_user = record_user;
-    B.best_masks = h->d_best_masks.p;
+    B.best_masks = h->d_best.p + 32;
     return B;
 }
 
 int ensure_common(gcr_engine_s* h)
 {
     const size_t W = static_cast<size_t>((h->ns + 31) / 32 + (h->no + 31) / 32);
-    GCR_CUDA(h->d_ctr.ensure(1));
-    GCR_CUDA(h->d_record.ensure(1));
+    if (h->d_ctr.cap < 1)
+    {
+        // live run counters: cleared by the last kernel of every run after it has snapshotted them into the result block
+        GCR_CUDA(h->d_ctr.ensure(1));
+        GCR_CUDA(cudaMemset(h->d_ctr.p, 0, sizeof(Counters)));
+    }
     GCR_CUDA(h->d_cand_hyp.ensure(kCandCap));
     GCR_CUDA(h->d_cand_model.ensure(kCandCap));
     GCR_CUDA(h->d_cand_score.ensure(kCandCap));
@@ -250,7 +260,15 @@ int ensure_common(gcr_engine_s* h)
     GCR_CUDA(h->d_cand_qsum.ensure(2 * kCandCap));
     GCR_CUDA(h->d_cand_rawcnt.ensure(2 * kCandCap));
     GCR_CUDA(h->d_cand_masks.ensure(W * kCandCap));
-    GCR_CUDA(h->d_best_masks.ensure(W));
+    GCR_CUDA(h->d_best.ensure(32 + W));
+    if (h->h_best_words < 32 + W)
+    {
+        if (h->h_best) cudaFreeHost(h->h_best);
+        h->h_best = nullptr;
+        h->h_best_words = 0;
+        GCR_CUDA(cudaMallocHost(&h->h_best, sizeof(unsigned int) * (32 + W + 64)));
+        h->h_best_words = 32 + W + 64;
+    }
     return GCR_OK;
 }
 
@@ -286,6 +304,19 @@ int gcr_create(int device, gcr_handle* out)
               : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_score_fast<false>, kScoreThreads, sizeof(ScoreSmem));
         h->score_grid[m] = h->n_sm * std::max(1, per_sm);
     }
+    if (e == cudaSuccess)
+    {
+        int per_sm = 1, coop = 0;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_tail, kExactThreads, 0);
+        if (e == cudaSuccess) e = cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device);
+        h->tail_grid = h->n_sm * std::max(1, std::min(per_sm, 2));
+        if (e == cudaSuccess && !coop)
+        {
+            h->err = "device does not support cooperative launches";
+            *out = h;
+            return GCR_ERR_CUDA;
+        }
+    }
     if (e != cudaSuccess)
     {
         // keep the handle so that gcr_last_error can be read; every later call fails with GCR_ERR_CUDA
@@ -308,8 +339,9 @@ int gcr_destroy(gcr_handle h)
     h->d_models.release(); h->d_flags.release(); h->d_sums.release(); h->d_score.release();
     h->d_cnts.release(); h->d_ninl.release(); h->d_masks.release(); h->d_fast_hyp.release();
     h->d_hard_hyp.release(); h->d_pf0.release(); h->d_pf1.release(); h->d_worklist.release();
-    h->d_cand_hyp.release(); h->d_cand_cnt.release(); h->d_cand_masks.release(); h->d_best_masks.release();
-    h->d_cand_model.release(); h->d_cand_score.release(); h->d_cand_qsum.release(); h->d_cand_rawcnt.release(); h->d_ctr.release(); h->d_record.release();
+    h->d_cand_hyp.release(); h->d_cand_cnt.release(); h->d_cand_masks.release(); h->d_best.release();
+    if (h->h_best) cudaFreeHost(h->h_best);
+    h->d_cand_model.release(); h->d_cand_score.release(); h->d_cand_qsum.release(); h->d_cand_rawcnt.release(); h->d_ctr.release();
     h->d_dbg_in.release(); h->d_dbg_out.release(); h->d_user_models.release();
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
@@ -417,10 +449,11 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
     if (rc != GCR_OK) return rc;
 
     cudaStream_t s = h->stream;
+    h->samples_view = h->d_samples.p;
     if (samples)
     {
         if (flags & GCR_RUN_SAMPLES_ON_DEVICE)
-            GCR_CUDA(cudaMemcpyAsync(h->d_samples.p, samples, sizeof(int) * 4 * H, cudaMemcpyDeviceToDevice, s));
+            h->samples_view = samples; // read in place: the caller keeps the array alive until the run has finished
         else
             GCR_CUDA(cudaMemcpyAsync(h->d_samples.p, samples, sizeof(int) * 4 * H, cudaMemcpyHostToDevice, s));
     }
@@ -428,8 +461,9 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
     const Buffers B = make_buffers(h, seed, samples != nullptr, d_record);
     const int all_exact = (flags & GCR_RUN_ALL_EXACT) ? 1 : 0;
 
+    // launch sequence: sample+solve -> FP32 scoring -> fused cooperative tail (3 kernels; the run counters were
+    // cleared by the previous run's tail)
     GCR_CUDA(cudaEventRecord(h->ev0, s));
-    GCR_CUDA(cudaMemsetAsync(h->d_ctr.p, 0, sizeof(Counters), s));
     if (h->have_masks) GCR_CUDA(cudaMemsetAsync(h->d_masks.p, 0, sizeof(unsigned int) * H * W, s));
     const int hb = static_cast<int>((H + 127) / 128);
     k_sample_solve<<<hb, 128, 0, s>>>(B, T, all_exact);
@@ -442,23 +476,23 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
             k_score_fast<false><<<grid, kScoreThreads, sizeof(ScoreSmem), s>>>(B, T);
         GCR_CUDA(cudaEventRecord(h->evk1, s));
     }
-    k_fixup<<<h->n_sm * 2, 256, 0, s>>>(B, T);
-    k_exact_items<<<h->n_sm * 8, kExactThreads, 0, s>>>(B, T, 0);
-    k_finalize<<<hb, 128, 0, s>>>(B, T);
-    k_collect<<<hb, 128, 0, s>>>(B, 4e-5);
-    k_exact_items<<<h->n_sm * 2, kExactThreads, 0, s>>>(B, T, 1);
-    k_select<<<1, 128, 0, s>>>(B, T);
+    {
+        double rel_tol = 4e-5;
+        void* args[] = {const_cast<Buffers*>(&B), const_cast<Thresholds*>(&T), &rel_tol};
+        GCR_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(k_tail), dim3(h->tail_grid), dim3(kExactThreads), args, 0, s));
+    }
     GCR_CUDA(cudaEventRecord(h->ev1, s));
     GCR_CUDA(cudaGetLastError());
     h->have_run = true;
 
     if (out)
     {
-        GCR_CUDA(cudaStreamSynchronize(s));
         Counters c;
         Record r;
-        GCR_CUDA(cudaMemcpy(&c, h->d_ctr.p, sizeof(c), cudaMemcpyDeviceToHost));
-        GCR_CUDA(cudaMemcpy(&r, h->d_record.p, sizeof(r), cudaMemcpyDeviceToHost));
+        GCR_CUDA(cudaMemcpyAsync(h->h_best, h->d_best.p, 128, cudaMemcpyDeviceToHost, s));
+        GCR_CUDA(cudaStreamSynchronize(s));
+        std::memcpy(&r, h->h_best, sizeof(r));
+        std::memcpy(&c, h->h_best + 16, sizeof(c));
         std::memset(out, 0, sizeof(*out));
         out->best_index = r.index;
         out->best_score = r.score;
@@ -485,16 +519,19 @@ int gcr_best(gcr_handle h, double model[4], double* score, uint32_t n_inl[2], ui
     if (!h) return GCR_ERR_INVALID;
     if (!h->have_run) return h->fail(GCR_ERR_STATE, "gcr_best before gcr_run");
     GCR_CUDA(cudaSetDevice(h->device));
+    const size_t ws = (h->ns + 31) / 32, wo = (h->no + 31) / 32;
+    const bool want_masks = scale_mask_words || orient_mask_words;
+    GCR_CUDA(cudaMemcpyAsync(h->h_best, h->d_best.p, sizeof(unsigned int) * (want_masks ? 32 + ws + wo : 16), cudaMemcpyDeviceToHost,
+                             h->stream));
     GCR_CUDA(cudaStreamSynchronize(h->stream));
     Record r;
-    GCR_CUDA(cudaMemcpy(&r, h->d_record.p, sizeof(r), cudaMemcpyDeviceToHost));
+    std::memcpy(&r, h->h_best, sizeof(r));
     if (model) for (int i = 0; i < 4; i++) model[i] = r.model[i];
     if (score) *score = r.score;
     if (n_inl) { n_inl[0] = r.n_inl[0]; n_inl[1] = r.n_inl[1]; }
     if (hyp_index) *hyp_index = r.index;
-    const size_t ws = (h->ns + 31) / 32, wo = (h->no + 31) / 32;
-    if (scale_mask_words) GCR_CUDA(cudaMemcpy(scale_mask_words, h->d_best_masks.p, 4 * ws, cudaMemcpyDeviceToHost));
-    if (orient_mask_words) GCR_CUDA(cudaMemcpy(orient_mask_words, h->d_best_masks.p + ws, 4 * wo, cudaMemcpyDeviceToHost));
+    if (scale_mask_words) std::memcpy(scale_mask_words, h->h_best + 32, 4 * ws);
+    if (orient_mask_words) std::memcpy(orient_mask_words, h->h_best + 32 + ws, 4 * wo);
     return GCR_OK;
 }
 
@@ -511,7 +548,7 @@ int gcr_fetch(gcr_handle h, uint8_t* flags, double* models, double* score, uint3
     if (models) GCR_CUDA(cudaMemcpy(models, h->d_models.p, H * sizeof(Model4), cudaMemcpyDeviceToHost));
     if (score) GCR_CUDA(cudaMemcpy(score, h->d_score.p, H * sizeof(double), cudaMemcpyDeviceToHost));
     if (n_inl) GCR_CUDA(cudaMemcpy(n_inl, h->d_ninl.p, 2 * H * sizeof(unsigned int), cudaMemcpyDeviceToHost));
-    if (samples) GCR_CUDA(cudaMemcpy(samples, h->d_samples.p, 4 * H * sizeof(int), cudaMemcpyDeviceToHost));
+    if (samples) GCR_CUDA(cudaMemcpy(samples, h->samples_view, 4 * H * sizeof(int), cudaMemcpyDeviceToHost));
     if (masks)
     {
         if (!h->have_masks) return h->fail(GCR_ERR_STATE, "masks were not kept: run with GCR_RUN_EMIT_MASKS");

@@ -17,6 +17,7 @@
 #pragma once
 #include "gcr_kernels_common.cuh"
 #include "gcr_score.cuh"
+#include <cooperative_groups.h>
 
 namespace gcr
 {
@@ -285,9 +286,9 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
 
 // ------------------------------------------------------------------------------------------------
 // K3x: FP64 re-evaluation of guard-band pairs and of irregular features, patched in with atomics.
-__global__ void k_fixup(Buffers B, Thresholds T)
+__device__ __forceinline__ void fixup_phase(const Buffers& B, const Thresholds& T)
 {
-    const unsigned int n_wl = min(B.ctr->n_worklist, B.worklist_cap);
+    const unsigned int n_wl = min(__ldcg(&B.ctr->n_worklist), B.worklist_cap);
     const unsigned int stride = gridDim.x * blockDim.x;
     const unsigned int t0 = blockIdx.x * blockDim.x + threadIdx.x;
     for (unsigned int i = t0; i < n_wl; i += stride)
@@ -360,11 +361,11 @@ __device__ __forceinline__ double msac_value(const Thresholds& T, double s0, dou
     return (-s0 / T.tsq[0] + static_cast<double>(c0)) + (-s1 / T.tsq[1] + static_cast<double>(c1));
 }
 
-__global__ void __launch_bounds__(kExactThreads) k_exact_items(Buffers B, Thresholds T, int mode, unsigned int n_direct = 1u)
+__device__ __forceinline__ void exact_items_phase(const Buffers& B, const Thresholds& T, int mode, unsigned int n_direct)
 {
     __shared__ unsigned long long red[kExactThreads / 32];
     __shared__ unsigned int redc[kExactThreads / 32];
-    const unsigned int n_items = mode == 0 ? B.ctr->n_hard : (mode == 1 ? min(B.ctr->n_candidates, static_cast<unsigned>(kCandCap)) : n_direct);
+    const unsigned int n_items = mode == 0 ? __ldcg(&B.ctr->n_hard) : (mode == 1 ? min(__ldcg(&B.ctr->n_candidates), static_cast<unsigned>(kCandCap)) : n_direct);
     const unsigned int ups = (B.ns + kExactThreads - 1) / kExactThreads, upo = (B.no + kExactThreads - 1) / kExactThreads;
     const unsigned int upi = ups + upo;
     const unsigned long long n_units = static_cast<unsigned long long>(n_items) * upi;
@@ -423,6 +424,11 @@ __global__ void __launch_bounds__(kExactThreads) k_exact_items(Buffers B, Thresh
     }
 }
 
+__global__ void __launch_bounds__(kExactThreads) k_exact_items(Buffers B, Thresholds T, int mode, unsigned int n_direct = 1u)
+{
+    exact_items_phase(B, T, mode, n_direct);
+}
+
 // candidate accumulators -> MSAC value + counts after the zero-reset rule
 __device__ __forceinline__ void cand_value(const Buffers& B, const Thresholds& T, unsigned int i)
 {
@@ -439,16 +445,20 @@ __global__ void k_cand_value(Buffers B, Thresholds T, unsigned int n)
 }
 
 // ------------------------------------------------------------------------------------------------
-// K4: per-hypothesis MSAC value + arg-max key over model-valid hypotheses.
-__global__ void k_finalize(Buffers B, Thresholds T)
+// K4-K6 as phases of ONE cooperative kernel (k_tail): at small sizes (C2) six dependent launches of 4-7 us each cost
+// as much as the scoring kernel; grid-wide barriers between the phases cost ~1-2 us.
+//
+// finalize: per-hypothesis MSAC value + arg-max key over model-valid hypotheses.
+__device__ __forceinline__ void finalize_phase(const Buffers& B, const Thresholds& T)
 {
-    const int h = blockIdx.x * blockDim.x + threadIdx.x;
-    double v = 0.0;
-    bool contender = false;
-    if (h < B.n_hyp)
+    unsigned long long key = 0ull;
+    for (int base = blockIdx.x * blockDim.x; base < B.n_hyp; base += gridDim.x * blockDim.x)
     {
+        const int h = base + threadIdx.x;
+        if (h >= B.n_hyp) continue;
         const unsigned char f = B.flags[h];
         unsigned int n0 = 0, n1 = 0;
+        double v = 0.0;
         if (f & 2)
         {
             double s0 = B.sums[2 * h], s1 = B.sums[2 * h + 1];
@@ -462,9 +472,12 @@ __global__ void k_finalize(Buffers B, Thresholds T)
         B.score[h] = v;
         B.n_inl[2 * h] = n0;
         B.n_inl[2 * h + 1] = n1;
-        contender = (f & 4) && v > 0.0; // S10 + S11 (initial best is 0, strict '<')
+        if ((f & 4) && v > 0.0) // S10 + S11 (initial best is 0, strict '<')
+        {
+            const unsigned long long k = ordered_bits(v);
+            key = k > key ? k : key;
+        }
     }
-    unsigned long long key = contender ? ordered_bits(v) : 0ull;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1)
     {
@@ -474,18 +487,19 @@ __global__ void k_finalize(Buffers B, Thresholds T)
     if ((threadIdx.x & 31) == 0 && key) atomicMax(&B.ctr->best_key, key);
 }
 
-// K5: hypotheses whose FP32-path score is within the path's error of the best one are re-scored in FP64
+// collect: hypotheses whose FP32-path score is within the path's error of the best one are re-scored in FP64
 // so that the selection rule sees reference-order scores.
-__global__ void k_collect(Buffers B, double rel_tol)
+__device__ __forceinline__ void collect_phase(const Buffers& B, double rel_tol)
 {
-    const int h = blockIdx.x * blockDim.x + threadIdx.x;
-    const unsigned long long bk = B.ctr->best_key;
-    if (h >= B.n_hyp || bk == 0ull) return;
+    const unsigned long long bk = __ldcg(&B.ctr->best_key);
+    if (bk == 0ull) return;
     const double best = from_ordered_bits(bk);
-    const unsigned char f = B.flags[h];
-    const double v = B.score[h];
-    if ((f & 4) && v > 0.0 && v >= best - rel_tol * best)
+    const double floor_v = best - rel_tol * best;
+    for (int h = blockIdx.x * blockDim.x + threadIdx.x; h < B.n_hyp; h += gridDim.x * blockDim.x)
     {
+        const double v = B.score[h];
+        if (!(v > 0.0) || v < floor_v) continue;
+        if (!(B.flags[h] & 4)) continue;
         const unsigned int slot = atomicAdd(&B.ctr->n_candidates, 1u);
         if (slot < kCandCap)
         {
@@ -508,12 +522,13 @@ struct Record // mirrors gcr_record
     unsigned long long reserved;
 };
 
-// K6: final selection (GCRANSAC.h:440-462): highest exact score, earliest hypothesis on ties; writes the
-// winner record (also into the caller's buffer, e.g. an NCCL send buffer) and the winner's packed masks.
-__global__ void k_select(Buffers B, Thresholds T)
+// select (one block): final selection (GCRANSAC.h:440-462): highest exact score, earliest hypothesis on ties; writes
+// the winner record (also into the caller's buffer, e.g. an NCCL send buffer) and the winner's packed masks; then
+// snapshots the run counters into the result block for the host and clears them for the next run.
+__device__ __forceinline__ void select_phase(const Buffers& B, const Thresholds& T)
 {
     __shared__ unsigned int s_hyp, s_slot;
-    const unsigned int n = min(B.ctr->n_candidates, static_cast<unsigned>(kCandCap));
+    const unsigned int n = min(__ldcg(&B.ctr->n_candidates), static_cast<unsigned>(kCandCap));
     for (unsigned int i = threadIdx.x; i < n; i += blockDim.x) cand_value(B, T, i);
     __syncthreads();
     if (threadIdx.x == 0)
@@ -550,11 +565,33 @@ __global__ void k_select(Buffers B, Thresholds T)
         }
         *reinterpret_cast<Record*>(B.record) = r;
         if (B.record_user) *reinterpret_cast<Record*>(B.record_user) = r;
+        *B.ctr_snap = B.ctr[0];
+        Counters z;
+        memset(&z, 0, sizeof(z));
+        B.ctr[0] = z;
     }
     __syncthreads();
     const bool have = s_hyp != 0xffffffffu;
     for (int w = threadIdx.x; w < B.wmask; w += blockDim.x)
         B.best_masks[w] = have ? B.cand_masks[static_cast<size_t>(s_slot) * B.wmask + w] : 0u;
+}
+
+// The fused tail: fixup + whole-hypothesis FP64 items | finalize | collect | FP64 re-scoring of the candidates | select.
+// Cooperative launch (all CTAs co-resident), kExactThreads threads per CTA.
+__global__ void __launch_bounds__(kExactThreads) k_tail(const __grid_constant__ Buffers B, const __grid_constant__ Thresholds T,
+                                                        double rel_tol)
+{
+    cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+    fixup_phase(B, T);
+    exact_items_phase(B, T, 0, 0u);
+    grid.sync();
+    finalize_phase(B, T);
+    grid.sync();
+    collect_phase(B, rel_tol);
+    grid.sync();
+    exact_items_phase(B, T, 1, 0u);
+    grid.sync();
+    if (blockIdx.x == 0) select_phase(B, T);
 }
 
 // caller-supplied models -> candidate slots [0, n) (gcr_score_model / gcr_score_models)

@@ -101,7 +101,8 @@ struct Buffers
     unsigned long long* cand_qsum; // [kCandCap,2] fixed-point sums of r^2 (units of tsq 2^-44)
     unsigned int* cand_rawcnt;     // [kCandCap,2]
     unsigned int* cand_masks; // [kCandCap, W]
-    Counters* ctr;
+    Counters* ctr;      // live counters of the run in flight
+    Counters* ctr_snap; // snapshot for the host, written by the last kernel
     void* record;  // gcr_record (device), engine-owned
     void* record_user; // optional caller-owned copy target
     unsigned int* best_masks; // [W]
