@@ -17,6 +17,8 @@ using namespace gcr;
 
 static_assert(sizeof(Record) == sizeof(gcr_record), "record layout");
 static_assert(sizeof(Model4) == 32, "model layout");
+static_assert(sizeof(Counters) == 64, "counters layout");
+constexpr size_t kResultHeaderWords = 48; // record (16) + counters (16) + phase stamps (16)
 
 template <typename T>
 struct DevBuf
@@ -83,7 +85,7 @@ struct gcr_engine_s
     DevBuf<unsigned long long> d_cand_qsum;
     DevBuf<unsigned int> d_cand_rawcnt;
     DevBuf<Counters> d_ctr;
-    // result block of a run, one contiguous D2H copy: [gcr_record 64 B][Counters snapshot 64 B][winner masks W words]
+    // result block of a run, one contiguous D2H copy: [gcr_record 64 B][Counters snapshot 64 B][8 phase stamps 64 B][winner masks W words]
     DevBuf<unsigned int> d_best;
     unsigned int* h_best = nullptr; // pinned staging of the same layout
     size_t h_best_words = 0;
@@ -239,8 +241,9 @@ Buffers make_buffers(gcr_engine_s* h, unsigned long long seed, bool have_samples
     B.ctr = h->d_ctr.p;
     B.record = h->d_best.p;
     B.ctr_snap = reinterpret_cast<Counters*>(h->d_best.p + 16);
+    B.phase_ns = reinterpret_cast<unsigned long long*>(h->d_best.p + 32);
     B.record_user = record_user;
-    B.best_masks = h->d_best.p + 32;
+    B.best_masks = h->d_best.p + kResultHeaderWords;
     return B;
 }
 
@@ -260,14 +263,14 @@ int ensure_common(gcr_engine_s* h)
     GCR_CUDA(h->d_cand_qsum.ensure(2 * kCandCap));
     GCR_CUDA(h->d_cand_rawcnt.ensure(2 * kCandCap));
     GCR_CUDA(h->d_cand_masks.ensure(W * kCandCap));
-    GCR_CUDA(h->d_best.ensure(32 + W));
-    if (h->h_best_words < 32 + W)
+    GCR_CUDA(h->d_best.ensure(kResultHeaderWords + W));
+    if (h->h_best_words < kResultHeaderWords + W)
     {
         if (h->h_best) cudaFreeHost(h->h_best);
         h->h_best = nullptr;
         h->h_best_words = 0;
-        GCR_CUDA(cudaMallocHost(&h->h_best, sizeof(unsigned int) * (32 + W + 64)));
-        h->h_best_words = 32 + W + 64;
+        GCR_CUDA(cudaMallocHost(&h->h_best, sizeof(unsigned int) * (kResultHeaderWords + W + 64)));
+        h->h_best_words = kResultHeaderWords + W + 64;
     }
     return GCR_OK;
 }
@@ -489,10 +492,12 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
     {
         Counters c;
         Record r;
-        GCR_CUDA(cudaMemcpyAsync(h->h_best, h->d_best.p, 128, cudaMemcpyDeviceToHost, s));
+        GCR_CUDA(cudaMemcpyAsync(h->h_best, h->d_best.p, 4 * kResultHeaderWords, cudaMemcpyDeviceToHost, s));
         GCR_CUDA(cudaStreamSynchronize(s));
         std::memcpy(&r, h->h_best, sizeof(r));
         std::memcpy(&c, h->h_best + 16, sizeof(c));
+        unsigned long long ph[8];
+        std::memcpy(ph, h->h_best + 32, sizeof(ph));
         std::memset(out, 0, sizeof(*out));
         out->best_index = r.index;
         out->best_score = r.score;
@@ -507,6 +512,8 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
         out->n_candidates = c.n_candidates;
         GCR_CUDA(cudaEventElapsedTime(&out->device_ms, h->ev0, h->ev1));
         GCR_CUDA(cudaEventElapsedTime(&out->score_kernel_ms, h->evk0, h->evk1));
+        for (int i = 0; i < 5; i++) out->tail_phase_us[i] = static_cast<float>(static_cast<double>(ph[i + 1] - ph[i]) * 1e-3);
+        out->tail_phase_us[5] = 0.f;
         if (c.n_bad_sample) return h->fail(GCR_ERR_INVALID, "replayed sample indices out of range");
         if (c.n_worklist_overflow) return h->fail(GCR_ERR_STATE, "guard-band worklist overflow");
     }
@@ -521,7 +528,7 @@ int gcr_best(gcr_handle h, double model[4], double* score, uint32_t n_inl[2], ui
     GCR_CUDA(cudaSetDevice(h->device));
     const size_t ws = (h->ns + 31) / 32, wo = (h->no + 31) / 32;
     const bool want_masks = scale_mask_words || orient_mask_words;
-    GCR_CUDA(cudaMemcpyAsync(h->h_best, h->d_best.p, sizeof(unsigned int) * (want_masks ? 32 + ws + wo : 16), cudaMemcpyDeviceToHost,
+    GCR_CUDA(cudaMemcpyAsync(h->h_best, h->d_best.p, sizeof(unsigned int) * (want_masks ? kResultHeaderWords + ws + wo : 16), cudaMemcpyDeviceToHost,
                              h->stream));
     GCR_CUDA(cudaStreamSynchronize(h->stream));
     Record r;
@@ -530,8 +537,8 @@ int gcr_best(gcr_handle h, double model[4], double* score, uint32_t n_inl[2], ui
     if (score) *score = r.score;
     if (n_inl) { n_inl[0] = r.n_inl[0]; n_inl[1] = r.n_inl[1]; }
     if (hyp_index) *hyp_index = r.index;
-    if (scale_mask_words) std::memcpy(scale_mask_words, h->h_best + 32, 4 * ws);
-    if (orient_mask_words) std::memcpy(orient_mask_words, h->h_best + 32 + ws, 4 * wo);
+    if (scale_mask_words) std::memcpy(scale_mask_words, h->h_best + kResultHeaderWords, 4 * ws);
+    if (orient_mask_words) std::memcpy(orient_mask_words, h->h_best + kResultHeaderWords + ws, 4 * wo);
     return GCR_OK;
 }
 

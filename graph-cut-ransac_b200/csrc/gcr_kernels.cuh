@@ -527,25 +527,38 @@ struct Record // mirrors gcr_record
 // snapshots the run counters into the result block for the host and clears them for the next run.
 __device__ __forceinline__ void select_phase(const Buffers& B, const Thresholds& T)
 {
+    __shared__ double s_val[kExactThreads / 32];
+    __shared__ unsigned int s_h[kExactThreads / 32], s_i[kExactThreads / 32];
     __shared__ unsigned int s_hyp, s_slot;
     const unsigned int n = min(__ldcg(&B.ctr->n_candidates), static_cast<unsigned>(kCandCap));
-    for (unsigned int i = threadIdx.x; i < n; i += blockDim.x) cand_value(B, T, i);
+    // every thread: value of its candidates and its own best (score, then lowest hypothesis index)
+    double best = 0.0;
+    unsigned int bh = 0xffffffffu, bs = 0;
+    for (unsigned int i = threadIdx.x; i < n; i += blockDim.x)
+    {
+        cand_value(B, T, i);
+        const double v = B.cand_score[i];
+        const unsigned int h = B.cand_hyp[i];
+        if (v > best || (v == best && v > 0.0 && h < bh)) { best = v; bh = h; bs = i; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        const double ov = __shfl_xor_sync(0xffffffffu, best, o);
+        const unsigned int oh = __shfl_xor_sync(0xffffffffu, bh, o), oi = __shfl_xor_sync(0xffffffffu, bs, o);
+        if (ov > best || (ov == best && ov > 0.0 && oh < bh)) { best = ov; bh = oh; bs = oi; }
+    }
+    if ((threadIdx.x & 31) == 0)
+    {
+        s_val[threadIdx.x >> 5] = best;
+        s_h[threadIdx.x >> 5] = bh;
+        s_i[threadIdx.x >> 5] = bs;
+    }
     __syncthreads();
     if (threadIdx.x == 0)
     {
-        double best = 0.0;
-        unsigned int bh = 0xffffffffu, bs = 0;
-        for (unsigned int i = 0; i < n; i++)
-        {
-            const double v = B.cand_score[i];
-            const unsigned int h = B.cand_hyp[i];
-            if (v > best || (v == best && v > 0.0 && h < bh))
-            {
-                best = v;
-                bh = h;
-                bs = i;
-            }
-        }
+        for (unsigned int w = 1; w < blockDim.x / 32; w++)
+            if (s_val[w] > best || (s_val[w] == best && best > 0.0 && s_h[w] < bh)) { best = s_val[w]; bh = s_h[w]; bs = s_i[w]; }
         s_hyp = bh;
         s_slot = bs;
         Record r;
@@ -576,22 +589,36 @@ __device__ __forceinline__ void select_phase(const Buffers& B, const Thresholds&
         B.best_masks[w] = have ? B.cand_masks[static_cast<size_t>(s_slot) * B.wmask + w] : 0u;
 }
 
+__device__ __forceinline__ unsigned long long global_ns()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
 // The fused tail: fixup + whole-hypothesis FP64 items | finalize | collect | FP64 re-scoring of the candidates | select.
 // Cooperative launch (all CTAs co-resident), kExactThreads threads per CTA.
 __global__ void __launch_bounds__(kExactThreads) k_tail(const __grid_constant__ Buffers B, const __grid_constant__ Thresholds T,
                                                         double rel_tol)
 {
     cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+    const bool stamp = blockIdx.x == 0 && threadIdx.x == 0; // phase boundaries as seen by CTA 0 (diagnostics, ns)
+    if (stamp) B.phase_ns[0] = global_ns();
     fixup_phase(B, T);
     exact_items_phase(B, T, 0, 0u);
     grid.sync();
+    if (stamp) B.phase_ns[1] = global_ns();
     finalize_phase(B, T);
     grid.sync();
+    if (stamp) B.phase_ns[2] = global_ns();
     collect_phase(B, rel_tol);
     grid.sync();
+    if (stamp) B.phase_ns[3] = global_ns();
     exact_items_phase(B, T, 1, 0u);
     grid.sync();
+    if (stamp) B.phase_ns[4] = global_ns();
     if (blockIdx.x == 0) select_phase(B, T);
+    if (stamp) B.phase_ns[5] = global_ns();
 }
 
 // caller-supplied models -> candidate slots [0, n) (gcr_score_model / gcr_score_models)

@@ -103,6 +103,7 @@ struct Buffers
     unsigned int* cand_masks; // [kCandCap, W]
     Counters* ctr;      // live counters of the run in flight
     Counters* ctr_snap; // snapshot for the host, written by the last kernel
+    unsigned long long* phase_ns; // [8] %globaltimer at the phase boundaries of k_tail
     void* record;  // gcr_record (device), engine-owned
     void* record_user; // optional caller-owned copy target
     unsigned int* best_masks; // [W]

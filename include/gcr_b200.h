@@ -69,6 +69,7 @@ typedef struct gcr_result
     int64_t n_candidates;   /* near-best hypotheses re-scored in FP64 before the final selection */
     float device_ms;        /* CUDA-event time of the whole hypothesis stage on the engine stream */
     float score_kernel_ms;  /* CUDA-event time of the dominant FP32 scoring kernel alone */
+    float tail_phase_us[6]; /* diagnostics: fix-up+FP64 items | finalize | collect | candidate re-scoring | select (device timer) */
 } gcr_result;
 
 /* Winner record written to device memory by the last kernel of gcr_run when `d_record` is given:
