@@ -49,32 +49,57 @@ def workload(name: str, rank: int = 0):
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    """SM clock / throttle reasons sampled DURING the timed regions (device-timed steps and the e2e loop): NVML
+    polled every ~2 ms (pynvml), falling back to nvidia-smi when NVML is unavailable."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    BITS = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
 
     def __init__(self, index: int):
         super().__init__(daemon=True)
-        self.index, self.rows, self.stop_flag = index, [], False
+        self.index, self.sm, self.mx, self.reasons, self.stop_flag, self.active = index, [], [], set(), False, False
+        self.nvml = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nvml = pynvml
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.mx.append(float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM)))
+        except Exception:
+            self.nvml = None
+
+    def _sample_nvml(self):
+        n = self.nvml
+        self.sm.append(float(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM)))
+        try:
+            get = getattr(n, "nvmlDeviceGetCurrentClocksEventReasons", None) or n.nvmlDeviceGetCurrentClocksThrottleReasons
+            mask = int(get(self.handle))
+            self.reasons |= {k for k, b in self.BITS.items() if mask & b}
+        except Exception:
+            pass
+
+    def _sample_smi(self):
+        out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits"],
+                             capture_output=True, text=True, timeout=5).stdout.strip()
+        r = [x.strip() for x in out.split(",")]
+        if len(r) >= 7 and r[0].replace(".", "").isdigit():
+            self.sm.append(float(r[0]))
+            self.mx.append(float(r[1]))
+            self.reasons |= {k for k, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], r[3:7])
+                             if v.lower().startswith("active")}
 
     def run(self):
         while not self.stop_flag:
-            try:
-                out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits"],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([x.strip() for x in out.split(",")])
-            except Exception:
-                pass
-            time.sleep(0.05)
+            if self.active:
+                try:
+                    self._sample_nvml() if self.nvml else self._sample_smi()
+                except Exception:
+                    pass
+            time.sleep(0.002 if self.nvml else 0.05)
 
     def summary(self):
-        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({n for r in self.rows if len(r) >= 7 for n, v in zip(names, r[3:7]) if v.lower().startswith("active")})
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": max(self.mx) if self.mx else None,
+                "reasons": sorted(self.reasons), "samples": len(self.sm), "source": "nvml" if self.nvml else "nvidia-smi"}
 
 
 def cpu_reference_leg(name: str, budget_hyp: int, nthreads: int = 0):
@@ -153,10 +178,18 @@ def run_ours(args):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
     eng.set_features_device(d_scale.data_ptr(), ns, d_orient.data_ptr(), no)
 
+    # N > 1: the path's one exchange (64-byte winner records) is fused into the engine's last kernel: peer-memory stores
+    # over NVLink + acquire loads, no collective launch; --exchange nccl times the all_gather form instead
+    fused = world > 1 and args.exchange == "p2p"
+    if fused:
+        import gcr_parallel
+        gcr_parallel.attach_peers(eng, rank, world)
+    run_flags = gcr_capi.RUN_EXCHANGE if fused else 0
+
     def step():
         eng.run(n_hyp, scene.thr, first_hyp=first_hyp, samples_ptr=d_samples.data_ptr(), record_ptr=d_record.data_ptr(),
-                sync=False)
-        if world > 1:  # the path's one exchange: 64-byte winner records, every rank then knows the global best
+                flags=run_flags, sync=False)
+        if world > 1 and not fused:
             dist.all_gather_into_tensor(d_gather, d_record)
 
     for _ in range(max(args.warmup, 3)):
@@ -168,6 +201,7 @@ def run_ours(args):
     sampler = ClockSampler(local)
     sampler.start()
     torch.cuda.synchronize()
+    sampler.active = True
     evs = []
     for _ in range(args.steps):
         flush.zero_()
@@ -180,7 +214,14 @@ def run_ours(args):
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
-    sampler.stop_flag = True
+    sampler.active = False
+    if world > 1:  # every rank must hold the same global winner (checked outside the timed region)
+        mine = d_record.clone()
+        allr = torch.empty(8 * world, dtype=torch.float64, device="cuda")
+        dist.all_gather_into_tensor(allr, mine)
+        recs = np.frombuffer(allr.cpu().numpy().tobytes(), dtype=gcr_capi.RECORD_DTYPE)
+        if fused:
+            assert all(r["index"] == recs[0]["index"] and r["score"] == recs[0]["score"] for r in recs), recs
     total_ms = sum(a.elapsed_time(b) for a, b in evs)
     t = torch.tensor([total_ms], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -233,10 +274,13 @@ def run_ours(args):
         best = e2e_step()
     if world > 1:
         dist.barrier()
+    sampler.active = True
     t0 = time.perf_counter()
     for _ in range(args.steps):
         best = e2e_step()
     e2e_s = (time.perf_counter() - t0) / args.steps
+    sampler.active = False
+    sampler.stop_flag = True
     t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -254,7 +298,9 @@ def run_ours(args):
                 "vs_baseline": None, "dtype": "f32 (+f64 solver, guard-band and winner re-scoring)", "data": "synthetic",
                 "config": {"workload": f"{name}: {c['n_scale']} scale + {c['n_orient']} orientation features, "
                                        f"{int(100 * c['inlier_ratio'])}% inliers, {n_hyp} replayed hypotheses per GPU per step",
-                           "l2": "flushed between timed steps (256 MiB write)", "hypotheses_scored_per_step": int(res.n_solved),
+                           "l2": "flushed between timed steps (256 MiB write)",
+                           "exchange": ("fused peer-memory stores in k_tail (NVLink P2P, 64 B per rank pair)" if fused else
+                                        ("nccl all_gather of 64 B records" if world > 1 else "none (1 GPU)")), "hypotheses_scored_per_step": int(res.n_solved),
                            "guard_band_pairs": int(res.n_rechecked), "exact_hypotheses": int(res.n_exact_hyp),
                            "best_index": int(best["index"]), "best_score": float(best["score"])},
                 "clocks": sampler.summary(), "e2e": e2e, "gpu_launches": 3 * args.steps, "roofline": roofline,
@@ -271,6 +317,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="C2", choices=sorted(gs.CONFIGS))
+    ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"], help="N>1: fused peer-memory exchange or NCCL all_gather")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

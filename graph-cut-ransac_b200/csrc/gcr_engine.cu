@@ -92,6 +92,15 @@ struct gcr_engine_s
     DevBuf<double> d_dbg_in, d_dbg_out;
     DevBuf<Model4> d_user_models;
 
+    // multi-GPU winner exchange (peer memory)
+    DevBuf<unsigned long long> d_xchg;
+    void* peer_ptr[kMaxPeers] = {};
+    bool peer_ipc[kMaxPeers] = {};
+    int xchg_world = 0, xchg_rank = 0;
+    unsigned long long xchg_seq = 0;
+    bool last_run_exchanged = false;
+    double last_thr[2] = {-1.0, -1.0};
+
     int fail(int code, const std::string& msg)
     {
         err = msg;
@@ -244,6 +253,10 @@ Buffers make_buffers(gcr_engine_s* h, unsigned long long seed, bool have_samples
     B.phase_ns = reinterpret_cast<unsigned long long*>(h->d_best.p + 32);
     B.record_user = record_user;
     B.best_masks = h->d_best.p + kResultHeaderWords;
+    for (int p = 0; p < kMaxPeers; p++) B.xchg_peer[p] = static_cast<unsigned long long*>(h->peer_ptr[p]);
+    B.xchg_world = 0; // set by gcr_run for exchanging runs
+    B.xchg_rank = h->xchg_rank;
+    B.xchg_seq = 0;
     return B;
 }
 
@@ -276,6 +289,31 @@ int ensure_common(gcr_engine_s* h)
 }
 
 } // namespace
+
+static int peer_release(gcr_engine_s* h)
+{
+    for (int p = 0; p < kMaxPeers; p++)
+    {
+        if (h->peer_ipc[p] && h->peer_ptr[p]) cudaIpcCloseMemHandle(h->peer_ptr[p]);
+        h->peer_ptr[p] = nullptr;
+        h->peer_ipc[p] = false;
+    }
+    h->xchg_world = 0;
+    h->xchg_rank = 0;
+    h->xchg_seq = 0;
+    return GCR_OK;
+}
+
+static int peer_buffer(gcr_engine_s* h)
+{
+    if (!h->d_xchg.p)
+    {
+        GCR_CUDA(cudaSetDevice(h->device));
+        GCR_CUDA(h->d_xchg.ensure(kXchgWords));
+        GCR_CUDA(cudaMemset(h->d_xchg.p, 0, sizeof(unsigned long long) * kXchgWords));
+    }
+    return GCR_OK;
+}
 
 extern "C"
 {
@@ -337,6 +375,8 @@ int gcr_destroy(gcr_handle h)
     if (!h) return GCR_ERR_INVALID;
     cudaSetDevice(h->device);
     if (h->own_stream) cudaStreamSynchronize(h->own_stream);
+    peer_release(h);
+    h->d_xchg.release();
     h->d_scale.release(); h->d_orient.release(); h->d_fs.release(); h->d_fo.release(); h->d_fsd.release(); h->d_fod.release();
     h->d_irr_s.release(); h->d_irr_o.release(); h->d_scene.release(); h->d_samples.release();
     h->d_models.release(); h->d_flags.release(); h->d_sums.release(); h->d_score.release();
@@ -410,6 +450,85 @@ int gcr_set_features(gcr_handle h, const double* scale, int64_t ns, const double
     return ensure_common(h);
 }
 
+int gcr_peer_export(gcr_handle h, void* ipc_handle_64)
+{
+    if (!h || !ipc_handle_64) return GCR_ERR_INVALID;
+    static_assert(sizeof(cudaIpcMemHandle_t) == GCR_IPC_HANDLE_BYTES, "ipc handle size");
+    int rc = peer_buffer(h);
+    if (rc != GCR_OK) return rc;
+    cudaIpcMemHandle_t mh;
+    GCR_CUDA(cudaIpcGetMemHandle(&mh, h->d_xchg.p));
+    std::memcpy(ipc_handle_64, &mh, sizeof(mh));
+    return GCR_OK;
+}
+
+int gcr_peer_buffer(gcr_handle h, void** device_ptr)
+{
+    if (!h || !device_ptr) return GCR_ERR_INVALID;
+    int rc = peer_buffer(h);
+    if (rc != GCR_OK) return rc;
+    *device_ptr = h->d_xchg.p;
+    return GCR_OK;
+}
+
+int gcr_peer_attach_ptrs(gcr_handle h, void* const* peer_buffers, int world, int rank)
+{
+    if (!h || !peer_buffers) return GCR_ERR_INVALID;
+    if (world < 2 || world > kMaxPeers || rank < 0 || rank >= world) return h->fail(GCR_ERR_INVALID, "2 <= world <= 16, 0 <= rank < world");
+    int rc = peer_buffer(h);
+    if (rc != GCR_OK) return rc;
+    peer_release(h);
+    GCR_CUDA(cudaSetDevice(h->device));
+    GCR_CUDA(cudaStreamSynchronize(h->stream));
+    GCR_CUDA(cudaMemset(h->d_xchg.p, 0, sizeof(unsigned long long) * kXchgWords));
+    for (int p = 0; p < world; p++) h->peer_ptr[p] = p == rank ? static_cast<void*>(h->d_xchg.p) : peer_buffers[p];
+    h->xchg_world = world;
+    h->xchg_rank = rank;
+    return GCR_OK;
+}
+
+int gcr_peer_attach(gcr_handle h, const void* ipc_handles, int world, int rank)
+{
+    if (!h || !ipc_handles) return GCR_ERR_INVALID;
+    if (world < 2 || world > kMaxPeers || rank < 0 || rank >= world) return h->fail(GCR_ERR_INVALID, "2 <= world <= 16, 0 <= rank < world");
+    int rc = peer_buffer(h);
+    if (rc != GCR_OK) return rc;
+    peer_release(h);
+    GCR_CUDA(cudaSetDevice(h->device));
+    GCR_CUDA(cudaStreamSynchronize(h->stream));
+    GCR_CUDA(cudaMemset(h->d_xchg.p, 0, sizeof(unsigned long long) * kXchgWords));
+    for (int p = 0; p < world; p++)
+    {
+        if (p == rank)
+        {
+            h->peer_ptr[p] = h->d_xchg.p;
+            continue;
+        }
+        cudaIpcMemHandle_t mh;
+        std::memcpy(&mh, static_cast<const char*>(ipc_handles) + static_cast<size_t>(p) * sizeof(mh), sizeof(mh));
+        void* ptr = nullptr;
+        cudaError_t e = cudaIpcOpenMemHandle(&ptr, mh, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess)
+        {
+            peer_release(h);
+            return h->cuda_fail(e, "cudaIpcOpenMemHandle (peer exchange buffer)");
+        }
+        h->peer_ptr[p] = ptr;
+        h->peer_ipc[p] = true;
+    }
+    h->xchg_world = world;
+    h->xchg_rank = rank;
+    return GCR_OK;
+}
+
+int gcr_peer_detach(gcr_handle h)
+{
+    if (!h) return GCR_ERR_INVALID;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    return peer_release(h);
+}
+
 int gcr_get_features(gcr_handle h, double* scale, double* orient)
 {
     if (!h) return GCR_ERR_INVALID;
@@ -461,8 +580,18 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
             GCR_CUDA(cudaMemcpyAsync(h->d_samples.p, samples, sizeof(int) * 4 * H, cudaMemcpyHostToDevice, s));
     }
     const Thresholds T = make_thresholds(thr);
-    const Buffers B = make_buffers(h, seed, samples != nullptr, d_record);
+    Buffers B = make_buffers(h, seed, samples != nullptr, d_record);
     const int all_exact = (flags & GCR_RUN_ALL_EXACT) ? 1 : 0;
+    h->last_thr[0] = thr[0];
+    h->last_thr[1] = thr[1];
+    h->last_run_exchanged = false;
+    if (flags & GCR_RUN_EXCHANGE)
+    {
+        if (h->xchg_world < 2) return h->fail(GCR_ERR_STATE, "GCR_RUN_EXCHANGE without attached peers (gcr_peer_attach)");
+        B.xchg_world = h->xchg_world;
+        B.xchg_seq = ++h->xchg_seq;
+        h->last_run_exchanged = true;
+    }
 
     // launch sequence: sample+solve -> FP32 scoring -> fused cooperative tail (3 kernels; the run counters were
     // cleared by the previous run's tail)
@@ -481,7 +610,7 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
     }
     {
         double rel_tol = 4e-5;
-        void* args[] = {const_cast<Buffers*>(&B), const_cast<Thresholds*>(&T), &rel_tol};
+        void* args[] = {&B, const_cast<Thresholds*>(&T), &rel_tol};
         GCR_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(k_tail), dim3(h->tail_grid), dim3(kExactThreads), args, 0, s));
     }
     GCR_CUDA(cudaEventRecord(h->ev1, s));
@@ -514,6 +643,8 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
         GCR_CUDA(cudaEventElapsedTime(&out->score_kernel_ms, h->evk0, h->evk1));
         for (int i = 0; i < 5; i++) out->tail_phase_us[i] = static_cast<float>(static_cast<double>(ph[i + 1] - ph[i]) * 1e-3);
         out->tail_phase_us[5] = 0.f;
+        out->winner_rank = static_cast<int32_t>(r.reserved);
+        if (c.xchg_timeout) return h->fail(GCR_ERR_STATE, "winner exchange timed out: a peer rank did not run the same collective call");
         if (c.n_bad_sample) return h->fail(GCR_ERR_INVALID, "replayed sample indices out of range");
         if (c.n_worklist_overflow) return h->fail(GCR_ERR_STATE, "guard-band worklist overflow");
     }
@@ -537,6 +668,17 @@ int gcr_best(gcr_handle h, double model[4], double* score, uint32_t n_inl[2], ui
     if (score) *score = r.score;
     if (n_inl) { n_inl[0] = r.n_inl[0]; n_inl[1] = r.n_inl[1]; }
     if (hyp_index) *hyp_index = r.index;
+    if (want_masks && h->last_run_exchanged && r.index >= 0 && static_cast<int>(r.reserved) != h->xchg_rank)
+    {
+        // the winning hypothesis lives on another rank: its masks are recomputed here from the replicated features
+        if (h->last_thr[0] < 0.0) return h->fail(GCR_ERR_STATE, "no thresholds recorded");
+        std::vector<uint32_t> words(ws + wo);
+        const int rc = gcr_score_models(h, r.model, 1, h->last_thr, 0, nullptr, nullptr, words.data());
+        if (rc != GCR_OK) return rc;
+        if (scale_mask_words) std::memcpy(scale_mask_words, words.data(), 4 * ws);
+        if (orient_mask_words) std::memcpy(orient_mask_words, words.data() + ws, 4 * wo);
+        return GCR_OK;
+    }
     if (scale_mask_words) std::memcpy(scale_mask_words, h->h_best + kResultHeaderWords, 4 * ws);
     if (orient_mask_words) std::memcpy(orient_mask_words, h->h_best + kResultHeaderWords + ws, 4 * wo);
     return GCR_OK;

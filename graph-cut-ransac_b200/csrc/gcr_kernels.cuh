@@ -522,6 +522,101 @@ struct Record // mirrors gcr_record
     unsigned long long reserved;
 };
 
+__device__ __forceinline__ unsigned long long global_ns()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
+// ---- winner exchange across GPUs, executed by warp 0 of the selecting CTA (the "collective" of the path, fused into
+// the kernel that produces the record): lane p stores this rank's record into peer p's buffer over NVLink
+// (st.release.sys after the payload), then lane q waits for rank q's record in the local buffer (ld.acquire.sys).
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v)
+{
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p)
+{
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long ld_relaxed_sys(const unsigned long long* p)
+{
+    unsigned long long v;
+    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__device__ __forceinline__ bool record_better(double sa, long long ia, double sb, long long ib) // a beats b (S11 across ranks)
+{
+    if (!(sa > 0.0) || ia < 0) return false;
+    if (!(sb > 0.0) || ib < 0) return true;
+    return sa > sb || (sa == sb && ia < ib);
+}
+
+// Called by all 32 lanes of warp 0 with the local record in `w` (8 u64 words, same in every lane).  Returns the global
+// winner's words and its rank; on a timeout (a peer never arrived: 4 s) keeps the local record and flags the run.
+__device__ __forceinline__ void exchange_records(const Buffers& B, unsigned long long (&w)[8], unsigned int& winner_rank)
+{
+    const int lane = threadIdx.x & 31;
+    const int world = B.xchg_world, me = B.xchg_rank;
+    const unsigned long long seq = B.xchg_seq;
+    const size_t par = static_cast<size_t>(seq & 1ull) * kMaxPeers * kXchgSlotWords;
+    if (lane < world)
+    {
+        unsigned long long* dst = B.xchg_peer[lane] + par + static_cast<size_t>(me) * kXchgSlotWords;
+#pragma unroll
+        for (int k = 0; k < 8; k++) dst[k] = w[k];
+        st_release_sys(dst + 8, seq);
+    }
+    bool timeout = false;
+    unsigned long long mine[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) mine[k] = w[k];
+    if (lane < world)
+    {
+        const unsigned long long* src = B.xchg_peer[me] + par + static_cast<size_t>(lane) * kXchgSlotWords;
+        const unsigned long long t0 = global_ns();
+        while (ld_acquire_sys(src + 8) < seq)
+        {
+            if (global_ns() - t0 > 4000000000ull) { timeout = true; break; }
+            __nanosleep(64);
+        }
+        if (!timeout)
+        {
+#pragma unroll
+            for (int k = 0; k < 8; k++) mine[k] = ld_relaxed_sys(src + k);
+        }
+    }
+    timeout = __any_sync(0xffffffffu, timeout);
+    // lane q holds rank q's record: butterfly arg-best over (score, index)
+    double sc = lane < world ? __longlong_as_double(static_cast<long long>(mine[0])) : 0.0;
+    long long ix = lane < world ? static_cast<long long>(mine[1]) : -1;
+    unsigned int rk = lane;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        const double os = __shfl_xor_sync(0xffffffffu, sc, o);
+        const long long oi = __shfl_xor_sync(0xffffffffu, ix, o);
+        const unsigned int orank = __shfl_xor_sync(0xffffffffu, rk, o);
+        if (record_better(os, oi, sc, ix)) { sc = os; ix = oi; rk = orank; }
+    }
+    // every lane now agrees on rk (ties cannot occur: global indices are unique); fetch that lane's words
+    if (!(sc > 0.0) || ix < 0) rk = static_cast<unsigned int>(me);
+#pragma unroll
+    for (int k = 0; k < 8; k++) w[k] = __shfl_sync(0xffffffffu, mine[k], static_cast<int>(rk));
+    winner_rank = rk;
+    if (timeout)
+    {
+        if (lane == 0) B.ctr->xchg_timeout = 1u;
+        winner_rank = static_cast<unsigned int>(me);
+#pragma unroll
+        for (int k = 0; k < 8; k++) w[k] = __shfl_sync(0xffffffffu, mine[k], me); // lane `me` read its own slot (or kept w)
+    }
+}
+
 // select (one block): final selection (GCRANSAC.h:440-462): highest exact score, earliest hypothesis on ties; writes
 // the winner record (also into the caller's buffer, e.g. an NCCL send buffer) and the winner's packed masks; then
 // snapshots the run counters into the result block for the host and clears them for the next run.
@@ -530,6 +625,7 @@ __device__ __forceinline__ void select_phase(const Buffers& B, const Thresholds&
     __shared__ double s_val[kExactThreads / 32];
     __shared__ unsigned int s_h[kExactThreads / 32], s_i[kExactThreads / 32];
     __shared__ unsigned int s_hyp, s_slot;
+    __shared__ unsigned long long s_rec[8];
     const unsigned int n = min(__ldcg(&B.ctr->n_candidates), static_cast<unsigned>(kCandCap));
     // every thread: value of its candidates and its own best (score, then lowest hypothesis index)
     double best = 0.0;
@@ -576,24 +672,37 @@ __device__ __forceinline__ void select_phase(const Buffers& B, const Thresholds&
             r.n_inl[0] = B.cand_cnt[2 * bs];
             r.n_inl[1] = B.cand_cnt[2 * bs + 1];
         }
-        *reinterpret_cast<Record*>(B.record) = r;
-        if (B.record_user) *reinterpret_cast<Record*>(B.record_user) = r;
-        *B.ctr_snap = B.ctr[0];
-        Counters z;
-        memset(&z, 0, sizeof(z));
-        B.ctr[0] = z;
+        *reinterpret_cast<Record*>(s_rec) = r;
+    }
+    __syncthreads();
+    if (threadIdx.x < 32)
+    {
+        unsigned long long w[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) w[k] = s_rec[k];
+        unsigned int winner_rank = B.xchg_world > 1 ? static_cast<unsigned int>(B.xchg_rank) : 0u;
+        if (B.xchg_world > 1) exchange_records(B, w, winner_rank); // the GLOBAL winner replaces the local record
+        if (threadIdx.x == 0)
+        {
+            w[7] = winner_rank; // gcr_record.reserved: rank that owns the winning hypothesis
+            unsigned long long* out = reinterpret_cast<unsigned long long*>(B.record);
+            unsigned long long* usr = reinterpret_cast<unsigned long long*>(B.record_user);
+#pragma unroll
+            for (int k = 0; k < 8; k++)
+            {
+                out[k] = w[k];
+                if (usr) usr[k] = w[k];
+            }
+            *B.ctr_snap = B.ctr[0];
+            Counters z;
+            memset(&z, 0, sizeof(z));
+            B.ctr[0] = z;
+        }
     }
     __syncthreads();
     const bool have = s_hyp != 0xffffffffu;
     for (int w = threadIdx.x; w < B.wmask; w += blockDim.x)
         B.best_masks[w] = have ? B.cand_masks[static_cast<size_t>(s_slot) * B.wmask + w] : 0u;
-}
-
-__device__ __forceinline__ unsigned long long global_ns()
-{
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-    return t;
 }
 
 // The fused tail: fixup + whole-hypothesis FP64 items | finalize | collect | FP64 re-scoring of the candidates | select.

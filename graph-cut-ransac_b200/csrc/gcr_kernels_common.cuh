@@ -26,6 +26,9 @@ constexpr int kHB = GCR_HB; // hypotheses per thread in the fast kernel
 constexpr int kTileHyps = kScoreThreads * kHB;
 constexpr int kCandCap = 1024;
 constexpr int kIrrCap = 4096;
+constexpr int kMaxPeers = 16;
+constexpr int kXchgSlotWords = 16;  // u64 words per slot: 8 record words, 1 sequence word, padding to 128 B
+constexpr int kXchgWords = 2 * kMaxPeers * kXchgSlotWords; // two parities
 constexpr double kLn2 = 0.693147180559945309417;
 constexpr double kU = 5.9604644775390625e-8; // 2^-24, FP32 unit round-off
 
@@ -33,7 +36,7 @@ struct Counters
 {
     unsigned int n_sample_valid, n_solved, n_fast, n_hard;
     unsigned int n_worklist, n_worklist_overflow, n_candidates, n_cand_overflow;
-    unsigned int n_bad_sample, next_item, blocks_done, n_sens;
+    unsigned int n_bad_sample, next_item, xchg_timeout, n_sens;
     unsigned long long best_key; // ordered bits of the best fast score among model-valid hypotheses
     unsigned long long pad1;
 };
@@ -107,6 +110,11 @@ struct Buffers
     void* record;  // gcr_record (device), engine-owned
     void* record_user; // optional caller-owned copy target
     unsigned int* best_masks; // [W]
+    // multi-GPU winner exchange over peer memory (NVLink P2P): every rank stores its 64-byte record + a sequence number
+    // into slot [parity][rank] of every peer's exchange buffer, then reads the slots of its own buffer
+    unsigned long long* xchg_peer[kMaxPeers]; // exchange buffers of all ranks (own one included), device-mapped
+    int xchg_world, xchg_rank;                // xchg_world <= 1: no exchange
+    unsigned long long xchg_seq;              // 1, 2, 3, ... identical on every rank for the same collective run
 };
 
 // ------------------------------------------------------------------------------------------------

@@ -15,12 +15,14 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("GCR_B200_LIB", os.path.join(PKG_DIR, "libgcr_b200.so"))  # override: kernel-variant sweeps
 
 FLAG_SAMPLE_VALID, FLAG_SOLVED, FLAG_MODEL_VALID, FLAG_EXACT = 1, 2, 4, 8
-RUN_EMIT_MASKS, RUN_SAMPLES_ON_DEVICE, RUN_KEEP_PER_HYP, RUN_ALL_EXACT = 1, 2, 4, 8
+RUN_EMIT_MASKS, RUN_SAMPLES_ON_DEVICE, RUN_KEEP_PER_HYP, RUN_ALL_EXACT, RUN_EXCHANGE = 1, 2, 4, 8, 16
+IPC_HANDLE_BYTES = 64
 
 EXPORTS = [
     "gcr_create", "gcr_destroy", "gcr_last_error", "gcr_set_stream", "gcr_set_features", "gcr_get_features", "gcr_run",
     "gcr_best",
-    "gcr_fetch", "gcr_score_model", "gcr_score_models", "gcr_debug_eval", "gcr_version",
+    "gcr_fetch", "gcr_score_model", "gcr_score_models", "gcr_debug_eval", "gcr_version", "gcr_peer_export",
+    "gcr_peer_attach", "gcr_peer_buffer", "gcr_peer_attach_ptrs", "gcr_peer_detach",
 ]
 
 
@@ -30,7 +32,8 @@ class GcrResult(C.Structure):
         ("best_n_inl", C.c_uint32 * 2), ("pad_", C.c_uint32 * 2), ("n_hyp", C.c_int64),
         ("n_sample_valid", C.c_int64), ("n_solved", C.c_int64), ("n_rechecked", C.c_int64),
         ("n_exact_hyp", C.c_int64), ("n_candidates", C.c_int64), ("device_ms", C.c_float),
-        ("score_kernel_ms", C.c_float), ("tail_phase_us", C.c_float * 6),
+        ("score_kernel_ms", C.c_float), ("winner_rank", C.c_int32), ("pad2_", C.c_int32),
+        ("tail_phase_us", C.c_float * 6),
     ]
 
 
@@ -63,6 +66,11 @@ def load_library() -> C.CDLL:
     lib.gcr_fetch.argtypes = [vp, vp, vp, vp, vp, vp, vp]
     lib.gcr_score_model.argtypes = [vp, vp, vp, vp, vp, vp, vp]
     lib.gcr_score_models.argtypes = [vp, vp, i64, vp, u32, vp, vp, vp]
+    lib.gcr_peer_export.argtypes = [vp, vp]
+    lib.gcr_peer_attach.argtypes = [vp, vp, C.c_int, C.c_int]
+    lib.gcr_peer_buffer.argtypes = [vp, C.POINTER(vp)]
+    lib.gcr_peer_attach_ptrs.argtypes = [vp, C.POINTER(vp), C.c_int, C.c_int]
+    lib.gcr_peer_detach.argtypes = [vp]
     lib.gcr_debug_eval.argtypes = [vp, C.c_int, vp, i64, vp, vp]
     lib.gcr_version.restype = C.c_char_p
     for name in EXPORTS:
@@ -142,6 +150,18 @@ class Engine:
                               C.c_void_p(record_ptr) if record_ptr else None, C.byref(res) if sync else None)
         self._check(rc)
         return res if sync else None
+
+    def peer_export(self) -> bytes:
+        buf = C.create_string_buffer(IPC_HANDLE_BYTES)
+        self._check(self.lib.gcr_peer_export(self.h, buf))
+        return buf.raw
+
+    def peer_attach(self, handles: bytes, world: int, rank: int):
+        assert len(handles) == world * IPC_HANDLE_BYTES
+        self._check(self.lib.gcr_peer_attach(self.h, handles, world, rank))
+
+    def peer_detach(self):
+        self._check(self.lib.gcr_peer_detach(self.h))
 
     def best(self):
         model = np.zeros(4)

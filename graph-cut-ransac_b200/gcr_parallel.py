@@ -45,6 +45,34 @@ def gather_records(record_tensor, world: int, group=None):
     return np.frombuffer(out.cpu().numpy().tobytes(), dtype=RECORD_DTYPE)
 
 
+def attach_peers(engine, rank: int, world: int, group=None) -> None:
+    """One-time setup of the fused winner exchange (include/gcr_b200.h, gcr_peer_*): every rank exports the CUDA IPC
+    handle of its exchange buffer, the handles are all-gathered (torch.distributed is only the courier), every rank
+    maps its peers' buffers.  After this, runs with RUN_EXCHANGE return the GLOBAL winner on every rank with no
+    collective launched: the records travel as peer-memory stores inside the engine's last kernel."""
+    import torch.distributed as dist
+    handles = [None] * world
+    dist.all_gather_object(handles, engine.peer_export(), group=group)
+    engine.peer_attach(b"".join(handles), world, rank)
+    dist.barrier(group=group)  # nobody runs before every buffer has been cleared and mapped
+
+
+def run_sharded_fused(engine, n_hyp_total: int, thr, seed: int, rank: int, world: int, samples=None):
+    """As run_sharded, with the exchange fused into the engine's last kernel (needs attach_peers).  Returns the same
+    dict on every rank, or None."""
+    import gcr_capi
+    first, count = shard_range(n_hyp_total, rank, world)
+    if count < 1:
+        raise ValueError("every rank needs at least one hypothesis slot for a fused exchange")
+    smp = None if samples is None else np.ascontiguousarray(samples[first:first + count])
+    res = engine.run(count, thr, seed=seed, first_hyp=first, samples=smp, flags=gcr_capi.RUN_EXCHANGE, sync=True)
+    if res.best_index < 0:
+        return None
+    b = engine.best()  # masks of a remote winner are recomputed locally from the replicated features
+    return dict(model=b["model"], score=b["score"], index=b["index"], n_inl=b["n_inl"], scale_mask=b["scale_mask"],
+                orient_mask=b["orient_mask"], rank=int(res.winner_rank))
+
+
 def run_sharded(engine, n_hyp_total: int, thr, seed: int, rank: int, world: int, record_tensor, samples=None, group=None):
     """Hypothesis stage over `n_hyp_total` global slots split across `world` ranks.  Every rank returns the same
     dict(model, score, index, n_inl, scale_mask, orient_mask, rank) or None.  The winner's masks are recomputed

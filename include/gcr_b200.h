@@ -53,6 +53,7 @@ enum gcr_status
 #define GCR_RUN_SAMPLES_ON_DEVICE 2u /* `samples` is a device pointer */
 #define GCR_RUN_KEEP_PER_HYP 4u      /* keep per-hypothesis models/scores/counts for gcr_fetch (implied by EMIT_MASKS) */
 #define GCR_RUN_ALL_EXACT 8u         /* score every hypothesis with the FP64 reference-order kernel (validation) */
+#define GCR_RUN_EXCHANGE 16u         /* multi-GPU: exchange winner records with the attached peers inside the last kernel */
 
 typedef struct gcr_result
 {
@@ -69,6 +70,8 @@ typedef struct gcr_result
     int64_t n_candidates;   /* near-best hypotheses re-scored in FP64 before the final selection */
     float device_ms;        /* CUDA-event time of the whole hypothesis stage on the engine stream */
     float score_kernel_ms;  /* CUDA-event time of the dominant FP32 scoring kernel alone */
+    int32_t winner_rank;    /* rank owning best_index (0 unless the run exchanged records with peers) */
+    int32_t pad2_;
     float tail_phase_us[6]; /* diagnostics: fix-up+FP64 items | finalize | collect | candidate re-scoring | select (device timer) */
 } gcr_result;
 
@@ -80,7 +83,7 @@ typedef struct gcr_record
     int64_t index;       /* global hypothesis index, -1 when no model */
     double model[4];
     uint32_t n_inl[2];
-    uint64_t reserved;
+    uint64_t reserved;   /* rank that owns the winning hypothesis (exchanging runs), else 0 */
 } gcr_record;
 
 int gcr_create(int device, gcr_handle* out);
@@ -94,6 +97,25 @@ int gcr_set_stream(gcr_handle h, void* cuda_stream);
  * FP32 structure-of-arrays working set.  Replaces the cv::Mat construction of
  * gcransac_python.cpp:284-296.  Requires ns >= 2 and no >= 2 (bindings.cpp:199-224). */
 int gcr_set_features(gcr_handle h, const double* scale, int64_t ns, const double* orient, int64_t no, int on_device);
+
+/* ---- multi-GPU winner exchange over peer memory (NVLink / NVSwitch), one engine per GPU -----------------------------
+ * The path's only exchange step is "which rank holds the best model" (the reference is single-process; this is its
+ * best-model rule GCRANSAC.h:440-462 applied across shards).  It is fused into the kernel that produces the record:
+ * the selecting CTA stores its 64-byte gcr_record into every peer's exchange buffer with system-scope release stores and
+ * waits (acquire loads) for the peers' records in its own buffer, so gcr_run's result IS the global winner and no separate
+ * collective is launched.  Setup (once):
+ *   every rank: gcr_peer_export(h, handle)                      -> 64-byte CUDA IPC handle of its exchange buffer
+ *   all-gather the handles by any means (torch.distributed, MPI, a file)
+ *   every rank: gcr_peer_attach(h, handles (world x 64 B), world, rank); then a barrier
+ * Single-process multi-GPU callers use gcr_peer_buffer + gcr_peer_attach_ptrs with raw device pointers instead
+ * (peer access enabled by the caller).  Every rank must then issue the same sequence of GCR_RUN_EXCHANGE runs; a peer
+ * that never arrives makes the run fail with GCR_ERR_STATE after 4 s instead of hanging. */
+#define GCR_IPC_HANDLE_BYTES 64
+int gcr_peer_export(gcr_handle h, void* ipc_handle_64);
+int gcr_peer_attach(gcr_handle h, const void* ipc_handles, int world, int rank);
+int gcr_peer_buffer(gcr_handle h, void** device_ptr);
+int gcr_peer_attach_ptrs(gcr_handle h, void* const* peer_buffers, int world, int rank);
+int gcr_peer_detach(gcr_handle h);
 
 /* Copy the resident feature arrays back to HOST buffers f64[Ns,3] / f64[No,3] (either may be NULL).  The host-side
  * local optimisation and refit need the rows of the inliers when the caller handed over device tensors.  Synchronises. */

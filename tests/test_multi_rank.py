@@ -101,3 +101,16 @@ def test_sharded_run_equals_single_run():
     assert recs[w]["index"] == res.best_index and recs[w]["score"] == res.best_score
     assert np.array_equal(recs[w]["model"], np.array(res.best_model[:]))
     whole.close()
+
+
+@pytest.mark.gpu
+def test_fused_peer_exchange_two_gpus():
+    """Two processes, two GPUs: fused NVLink exchange == NCCL all_gather form == unsharded run (tools/check_multi_gpu.py)."""
+    import subprocess
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run by `gpurun --gpus 2`)")
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+                          "127.0.0.1", "--master-port", "29533", os.path.join(ROOT, "tools", "check_multi_gpu.py")],
+                         capture_output=True, text=True, timeout=600)
+    assert "MULTI_GPU_CHECK PASS" in out.stdout, out.stdout[-3000:] + out.stderr[-3000:]
