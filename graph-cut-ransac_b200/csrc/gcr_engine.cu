@@ -176,6 +176,8 @@ Thresholds make_thresholds(const double thr[2])
     const double tr0 = std::sqrt(T.tsq[0]), tr1 = std::sqrt(T.tsq[1]);
     T.Tp = static_cast<float>(tr0 / (3.0 * kLn2));
     T.scale_unit = static_cast<float>((3.0 * kLn2) * (3.0 * kLn2));
+    T.exp2_neg_Tp = std::exp2(-static_cast<double>(T.Tp));
+    T.exp2_pos_Tp = std::exp2(static_cast<double>(T.Tp));
     T.orient_all_exact = 0;
     if (!(tr1 < 0.6)) // beyond ~34 degrees the tan-domain test loses its margin: exact path
     {

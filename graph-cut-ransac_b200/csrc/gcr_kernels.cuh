@@ -211,7 +211,7 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
             const double mag = ah7 * sc.xq_max + ah8 * sc.yq_max + sc.iq_max; // bound of the terms of v
             const double A = log2(m.alpha);
             const double Tp = T.Tp;
-            const double v_lo = m.alpha * exp2(-Tp), v_hi = m.alpha * exp2(Tp);
+            const double v_lo = m.alpha * T.exp2_neg_Tp, v_hi = m.alpha * T.exp2_pos_Tp; // hypothesis-independent factors from the host
             const double kh = sc.k_max * (ah7 + ah8);
             const double eps_lg = 2.384185791015625e-7 + 3.0 * kU * (fabs(A) + Tp + 1.0); // MUFU.LG2 + roundings of A, d
             // FP32 tiles: v, numer, denom from FP32 features and FP32 (h7, h8)
@@ -252,24 +252,48 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
         B.cnts[2 * h] = 0u;
         B.cnts[2 * h + 1] = 0u;
     }
-    // warp-aggregated compaction of solved hypotheses into the fast / exact lists
-    const unsigned m_valid = __ballot_sync(0xffffffffu, sample_valid);
+    // block-aggregated compaction of solved hypotheses into the fast / precise / exact lists: warp ballots, a prefix over
+    // the block's warps in shared memory, ONE returning atomic per list and block (per-warp atomics on the same three
+    // counters serialise in L2 and were half of this kernel's time)
+    __shared__ unsigned int s_cnt[4][4];  // [list][warp]: fast, sens, hard, sample_valid
+    __shared__ unsigned int s_base[3];
+    const unsigned warp = threadIdx.x >> 5;
     const bool sens = sens_s || sens_o;
+    const unsigned m_valid = __ballot_sync(0xffffffffu, sample_valid);
     const unsigned m_fast = __ballot_sync(0xffffffffu, solved && !hard && !sens);
     const unsigned m_sens = __ballot_sync(0xffffffffu, solved && !hard && sens);
     const unsigned m_hard = __ballot_sync(0xffffffffu, solved && hard);
-    unsigned base_fast = 0, base_hard = 0, base_sens = 0;
     if (lane == 0)
     {
-        if (m_valid) atomicAdd(&B.ctr->n_sample_valid, __popc(m_valid));
-        if (m_fast | m_hard | m_sens) atomicAdd(&B.ctr->n_solved, __popc(m_fast) + __popc(m_hard) + __popc(m_sens));
-        if (m_fast) base_fast = atomicAdd(&B.ctr->n_fast, __popc(m_fast));
-        if (m_sens) base_sens = atomicAdd(&B.ctr->n_sens, __popc(m_sens));
-        if (m_hard) base_hard = atomicAdd(&B.ctr->n_hard, __popc(m_hard));
+        s_cnt[0][warp] = __popc(m_fast);
+        s_cnt[1][warp] = __popc(m_sens);
+        s_cnt[2][warp] = __popc(m_hard);
+        s_cnt[3][warp] = __popc(m_valid);
     }
-    base_fast = __shfl_sync(0xffffffffu, base_fast, 0);
-    base_sens = __shfl_sync(0xffffffffu, base_sens, 0);
-    base_hard = __shfl_sync(0xffffffffu, base_hard, 0);
+    __syncthreads();
+    if (threadIdx.x < 3)
+    {
+        const unsigned int tot = s_cnt[threadIdx.x][0] + s_cnt[threadIdx.x][1] + s_cnt[threadIdx.x][2] + s_cnt[threadIdx.x][3];
+        unsigned int* ctr = threadIdx.x == 0 ? &B.ctr->n_fast : (threadIdx.x == 1 ? &B.ctr->n_sens : &B.ctr->n_hard);
+        s_base[threadIdx.x] = tot ? atomicAdd(ctr, tot) : 0u;
+    }
+    else if (threadIdx.x == 32)
+    {
+        const unsigned int nv = s_cnt[3][0] + s_cnt[3][1] + s_cnt[3][2] + s_cnt[3][3];
+        unsigned int ns = 0;
+#pragma unroll
+        for (int l = 0; l < 3; l++) ns += s_cnt[l][0] + s_cnt[l][1] + s_cnt[l][2] + s_cnt[l][3];
+        if (nv) atomicAdd(&B.ctr->n_sample_valid, nv);
+        if (ns) atomicAdd(&B.ctr->n_solved, ns);
+    }
+    __syncthreads();
+    unsigned base_fast = s_base[0], base_sens = s_base[1], base_hard = s_base[2];
+    for (unsigned w = 0; w < warp; w++)
+    {
+        base_fast += s_cnt[0][w];
+        base_sens += s_cnt[1][w];
+        base_hard += s_cnt[2][w];
+    }
     const unsigned below = (1u << lane) - 1u;
     if (solved && !hard)
     {

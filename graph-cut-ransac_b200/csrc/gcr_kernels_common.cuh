@@ -51,6 +51,7 @@ struct Scene // written by k_prep_features
 struct Thresholds
 {
     double tsq[2];   // (2.25 t) t, S1
+    double exp2_neg_Tp, exp2_pos_Tp; // 2^-Tp, 2^+Tp: bounds of v / alpha for a scale inlier
     float Tp;        // sqrt(tsq0) / (3 ln 2): scale threshold in log2 units of v
     float tanT;      // tan(sqrt(tsq1))
     float t_band0;   // constant part of the orientation band in tan units

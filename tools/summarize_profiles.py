@@ -10,15 +10,16 @@ KEYS = ["gpu__time_duration.sum", "sm__cycles_elapsed.avg", "sm__cycles_active.a
         "lts__t_bytes.sum", "launch__registers_per_thread", "launch__grid_size", "launch__block_size", "launch__occupancy_limit_registers",
         "launch__occupancy_limit_shared_mem", "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__warps_eligible.avg.per_cycle_active",
         "smsp__thread_inst_executed_pred_on_per_inst_executed.ratio"]
-for cfg in ("c2", "c3"):
-    rep = f"gpurun_out/prof_{cfg}_score_{R}.ncu-rep"
+OUT = sys.argv[2] if len(sys.argv) > 2 else R
+for cfg, kern in (("c2", "k_score_fast"), ("c3", "k_score_fast"), ("c2", "k_sample_solve"), ("c2", "k_tail")):
+    rep = f"gpurun_out/prof_{cfg}_{kern}_{R}.ncu-rep"
     if not os.path.exists(rep):
         continue
     raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(raw.splitlines()))
     hdr, units = rows[0], rows[1]
-    with open(f"profiles/{R}_ncu_full_k_score_fast_{cfg}.txt", "w") as f:
-        f.write(f"# ncu --set full --clock-control none, kernel k_score_fast, bench.py config {cfg.upper()} ({rep})\n")
+    with open(f"profiles/{OUT}_ncu_full_{kern}_{cfg}.txt", "w") as f:
+        f.write(f"# ncu --set full --clock-control none, kernel {kern}, bench.py config {cfg.upper()} ({rep})\n")
         for r in rows[2:]:
             d = dict(zip(hdr, r))
             f.write(f"kernel: {d.get('Kernel Name')}  grid {d.get('Grid Size')} block {d.get('Block Size')}\n")
@@ -31,11 +32,11 @@ for r in rows:
     k = (r[4].split("(")[0], r[8], r[7])
     agg.setdefault(k, []).append(float(r[-1]))
 tot = sum(sum(v) for k, v in agg.items() if "gcr::" in k[0])
-with open(f"profiles/{R}_launch_list_c2.txt", "w") as f:
+with open(f"profiles/{OUT}_launch_list_c2.txt", "w") as f:
     f.write("# ncu --metrics gpu__time_duration.sum --clock-control none python bench.py --steps 5 --warmup 3 (config C2)\n")
     f.write("# per-launch times are cold-cache and serialised: compare SHARES, not absolutes\n")
     f.write(f"{'kernel':60s} {'grid':>16s} {'block':>14s} {'launches':>9s} {'mean_us':>9s} {'share_of_gcr':>12s}\n")
     for (n, g, b), v in agg.items():
         share = sum(v) / tot if "gcr::" in n else float("nan")
         f.write(f"{n[:60]:60s} {g:>16s} {b:>14s} {len(v):9d} {sum(v)/len(v)/1e3:9.2f} {share:12.3f}\n")
-print(open(f"profiles/{R}_launch_list_c2.txt").read())
+print(open(f"profiles/{OUT}_launch_list_c2.txt").read())
