@@ -50,6 +50,7 @@ struct gcr_engine_s
 {
     int device = 0;
     int n_sm = 148;
+    int problem = 0; // GCR_PROBLEM_*
     int score_grid[2] = {148, 148};
     int tail_grid = 148;
     cudaStream_t own_stream = nullptr, stream = nullptr;
@@ -167,10 +168,15 @@ double fit_atan2_poly(double zmax, float pc[4], int deg)
     return worst;
 }
 
-Thresholds make_thresholds(const double thr[2])
+Thresholds make_thresholds(const double thr_in[2], int problem)
 {
     Thresholds T;
     std::memset(&T, 0, sizeof(T));
+    // scale-only problems have one class: the orientation entries are placeholders that are never compared against
+    const double thr[2] = {thr_in[0], problem == 0 ? thr_in[1] : 0.05};
+    T.problem = problem;
+    T.min_inl[0] = problem == 0 ? 2u : 3u; // sampleSize(): two_sift.hpp:28-32 {2,2}; three_sift.hpp:30 {3}
+    T.min_inl[1] = problem == 0 ? 2u : 0u;
     T.tsq[0] = (2.25 * thr[0]) * thr[0]; // S1: MSAC_scoring_function.hpp:64
     T.tsq[1] = (2.25 * thr[1]) * thr[1];
     const double tr0 = std::sqrt(T.tsq[0]), tr1 = std::sqrt(T.tsq[1]);
@@ -410,9 +416,20 @@ int gcr_set_features(gcr_handle h, const double* scale, int64_t ns, const double
 {
     if (!h) return GCR_ERR_INVALID;
     if (!h->stream) return h->fail(GCR_ERR_STATE, "engine was not created successfully");
-    if (!scale || !orient) return h->fail(GCR_ERR_INVALID, "null feature pointer");
-    // bindings.cpp:206-224: at least 2 rows per class (the minimal sample size)
-    if (ns < 2 || no < 2) return h->fail(GCR_ERR_INVALID, "each feature class needs at least 2 rows of 3 columns");
+    if (h->problem == 0)
+    {
+        if (!scale || !orient) return h->fail(GCR_ERR_INVALID, "null feature pointer");
+        // bindings.cpp:206-224: at least 2 rows per class (the minimal sample size)
+        if (ns < 2 || no < 2) return h->fail(GCR_ERR_INVALID, "each feature class needs at least 2 rows of 3 columns");
+    }
+    else
+    {
+        // scale-only problems (bindings.cpp:19-179): one class, minimal sample of 3 rows; the orientation class is empty
+        if (!scale) return h->fail(GCR_ERR_INVALID, "null feature pointer");
+        if (ns < 3) return h->fail(GCR_ERR_INVALID, "scale features need at least 3 rows of 3 columns");
+        if (no != 0) return h->fail(GCR_ERR_INVALID, "scale-only problems take no orientation features (no = 0)");
+        orient = nullptr;
+    }
     if (ns > (1ll << 30) || no > (1ll << 30)) return h->fail(GCR_ERR_INVALID, "feature count too large");
     GCR_CUDA(cudaSetDevice(h->device));
     h->ns = static_cast<int>(ns);
@@ -430,7 +447,7 @@ int gcr_set_features(gcr_handle h, const double* scale, int64_t ns, const double
         GCR_CUDA(h->d_scale.ensure(3 * static_cast<size_t>(ns)));
         GCR_CUDA(h->d_orient.ensure(3 * static_cast<size_t>(no)));
         GCR_CUDA(cudaMemcpyAsync(h->d_scale.p, scale, sizeof(double) * 3 * ns, cudaMemcpyHostToDevice, h->stream));
-        GCR_CUDA(cudaMemcpyAsync(h->d_orient.p, orient, sizeof(double) * 3 * no, cudaMemcpyHostToDevice, h->stream));
+        if (no > 0) GCR_CUDA(cudaMemcpyAsync(h->d_orient.p, orient, sizeof(double) * 3 * no, cudaMemcpyHostToDevice, h->stream));
         h->scale_ptr = h->d_scale.p;
         h->orient_ptr = h->d_orient.p;
     }
@@ -450,6 +467,19 @@ int gcr_set_features(gcr_handle h, const double* scale, int64_t ns, const double
                                                            h->d_irr_o.p);
     GCR_CUDA(cudaGetLastError());
     return ensure_common(h);
+}
+
+int gcr_set_problem(gcr_handle h, int problem)
+{
+    if (!h) return GCR_ERR_INVALID;
+    if (problem < GCR_PROBLEM_HYBRID || problem > GCR_PROBLEM_SCALE_ONLY_ORIGINAL) return h->fail(GCR_ERR_INVALID, "unknown problem id");
+    if (problem != h->problem)
+    {
+        h->problem = problem;
+        h->ns = h->no = 0; // features must be uploaded again for the new problem
+        h->have_run = false;
+    }
+    return GCR_OK;
 }
 
 int gcr_peer_export(gcr_handle h, void* ipc_handle_64)
@@ -537,7 +567,7 @@ int gcr_get_features(gcr_handle h, double* scale, double* orient)
     if (h->ns < 2) return h->fail(GCR_ERR_STATE, "gcr_get_features before gcr_set_features");
     GCR_CUDA(cudaSetDevice(h->device));
     if (scale) GCR_CUDA(cudaMemcpyAsync(scale, h->scale_ptr, sizeof(double) * 3 * h->ns, cudaMemcpyDeviceToHost, h->stream));
-    if (orient) GCR_CUDA(cudaMemcpyAsync(orient, h->orient_ptr, sizeof(double) * 3 * h->no, cudaMemcpyDeviceToHost, h->stream));
+    if (orient && h->no > 0) GCR_CUDA(cudaMemcpyAsync(orient, h->orient_ptr, sizeof(double) * 3 * h->no, cudaMemcpyDeviceToHost, h->stream));
     GCR_CUDA(cudaStreamSynchronize(h->stream));
     return GCR_OK;
 }
@@ -547,8 +577,9 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
 {
     if (!h) return GCR_ERR_INVALID;
     if (h->ns < 2) return h->fail(GCR_ERR_STATE, "gcr_run before gcr_set_features");
+    if ((h->problem == 0) != (h->no >= 2)) return h->fail(GCR_ERR_STATE, "gcr_set_problem changed after gcr_set_features: upload the features again");
     if (n_hyp < 1 || n_hyp > (1ll << 30)) return h->fail(GCR_ERR_INVALID, "n_hyp out of range");
-    if (!thr || !(thr[0] >= 0.0) || !(thr[1] >= 0.0) || !std::isfinite(thr[0]) || !std::isfinite(thr[1]))
+    if (!thr || !(thr[0] >= 0.0) || !std::isfinite(thr[0]) || (h->problem == 0 && (!(thr[1] >= 0.0) || !std::isfinite(thr[1]))))
         return h->fail(GCR_ERR_INVALID, "thresholds must be finite and non-negative");
     GCR_CUDA(cudaSetDevice(h->device));
     const size_t H = static_cast<size_t>(n_hyp);
@@ -581,11 +612,11 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
         else
             GCR_CUDA(cudaMemcpyAsync(h->d_samples.p, samples, sizeof(int) * 4 * H, cudaMemcpyHostToDevice, s));
     }
-    const Thresholds T = make_thresholds(thr);
+    const Thresholds T = make_thresholds(thr, h->problem);
     Buffers B = make_buffers(h, seed, samples != nullptr, d_record);
     const int all_exact = (flags & GCR_RUN_ALL_EXACT) ? 1 : 0;
     h->last_thr[0] = thr[0];
-    h->last_thr[1] = thr[1];
+    h->last_thr[1] = h->problem == 0 ? thr[1] : 0.0;
     h->last_run_exchanged = false;
     if (flags & GCR_RUN_EXCHANGE)
     {
@@ -616,6 +647,14 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
         GCR_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(k_tail), dim3(h->tail_grid), dim3(kExactThreads), args, 0, s));
     }
     GCR_CUDA(cudaEventRecord(h->ev1, s));
+    if (flags & (GCR_RUN_KEEP_PER_HYP | GCR_RUN_EMIT_MASKS))
+    {
+        // reporting modes: FP64 re-scoring of the low-margin hypotheses (see k_refine_collect); off the timed stage
+        k_refine_collect<<<hb, 128, 0, s>>>(B);
+        k_exact_items<<<h->n_sm * 8, kExactThreads, 0, s>>>(B, T, 0);
+        k_refine_finalize<<<h->n_sm, 256, 0, s>>>(B, T);
+        k_refine_done<<<1, 1, 0, s>>>(B);
+    }
     GCR_CUDA(cudaGetLastError());
     h->have_run = true;
 
@@ -714,18 +753,19 @@ int gcr_score_models(gcr_handle h, const double* models, int64_t n, const double
     if (!h || !models || !thr) return GCR_ERR_INVALID;
     if (h->ns < 2) return h->fail(GCR_ERR_STATE, "gcr_score_models before gcr_set_features");
     if (n < 1 || n > kCandCap) return h->fail(GCR_ERR_INVALID, "gcr_score_models: 1 <= n <= 1024 models per call");
-    if (!(thr[0] >= 0.0) || !(thr[1] >= 0.0) || !std::isfinite(thr[0]) || !std::isfinite(thr[1]))
+    if (!(thr[0] >= 0.0) || !std::isfinite(thr[0]) || (h->problem == 0 && (!(thr[1] >= 0.0) || !std::isfinite(thr[1]))))
         return h->fail(GCR_ERR_INVALID, "thresholds must be finite and non-negative");
     GCR_CUDA(cudaSetDevice(h->device));
     int rc = ensure_common(h);
     if (rc != GCR_OK) return rc;
     GCR_CUDA(h->d_user_models.ensure(kCandCap));
-    Thresholds T = make_thresholds(thr);
+    Thresholds T = make_thresholds(thr, h->problem);
     if (flags & GCR_SCORE_TRUNCATED_SQ) // the relabelling threshold of the local optimisation, GCRANSAC.h:207-208,931-937
     {
         T.tsq[0] = (1.5 * thr[0]) * (1.5 * thr[0]);
         T.tsq[1] = (1.5 * thr[1]) * (1.5 * thr[1]);
     }
+    T.strict = (flags & GCR_SCORE_STRICT) ? 1 : 0;
     const Buffers B = make_buffers(h, 0, false, nullptr);
     cudaStream_t s = h->stream;
     const unsigned int un = static_cast<unsigned int>(n);

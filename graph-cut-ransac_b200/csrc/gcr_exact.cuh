@@ -48,12 +48,14 @@ struct Model4
 };
 
 // two_sift.hpp:621-645 with the identity normaliser (model.h:42-55, S6); model.h:194-204
-__device__ __forceinline__ double scale_residual(double x, double y, double s, const Model4& m)
+// `original`: the residual of three_sift_original.hpp:293-317, |log(rectified / alpha^3)| (its alpha is the reciprocal
+// class scale); otherwise three_sift.hpp:293-317 == two_sift.hpp:621-645, |log(alpha^3 * rectified)|.
+__device__ __forceinline__ double scale_residual(double x, double y, double s, const Model4& m, bool original = false)
 {
     const double rectified = s * pow(-m.h7 * x - m.h8 * y + 1.0, -3.0);
     if (rectified < 1e-9) return DBL_MAX;
     const double alpha_cube = m.alpha * m.alpha * m.alpha;
-    return fabs(log(alpha_cube * rectified));
+    return original ? fabs(log(rectified / alpha_cube)) : fabs(log(alpha_cube * rectified));
 }
 
 // two_sift.hpp:647-665; model.h:156-165
@@ -243,6 +245,32 @@ __device__ inline bool estimate_minimal(const double s0[3], const double s1[3], 
     out.h8 = sol[1];
     out.alpha = sol[2];
     out.phi = clip_angle(atan2(vp_in[1], vp_in[0]));
+    return true;
+}
+
+// Scale-only problems (three_sift.hpp:111-193, three_sift_original.hpp): the sample is valid unless its three positions
+// are "collinear" in the reference's signed sense (S7); rows [x, y, s^(1/3), 1] (original: [x, y, -s^(-1/3), -1]).
+__device__ inline bool estimate_minimal_scale3(const double s0[3], const double s1[3], const double s2[3], bool original,
+                                               Model4& out)
+{
+    double m[3][4];
+    const double* f[3] = {s0, s1, s2};
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+    {
+        m[i][0] = f[i][0];
+        m[i][1] = f[i][1];
+        m[i][2] = original ? -pow(f[i][2], -1.0 / 3.0) : pow(f[i][2], 1.0 / 3.0);
+        m[i][3] = original ? -1.0 : 1.0;
+    }
+    double sol[3];
+    gauss3(m, sol);
+    if (sol[0] != sol[0] || sol[1] != sol[1] || sol[2] != sol[2]) return false;
+    if (sol[2] < 1e-9) return false;
+    out.h7 = sol[0];
+    out.h8 = sol[1];
+    out.alpha = sol[2];
+    out.phi = 0.0;
     return true;
 }
 

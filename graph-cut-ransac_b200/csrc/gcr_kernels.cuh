@@ -162,7 +162,8 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
     float4 p0 = make_float4(0.f, 0.f, 0.f, 0.f), p1 = make_float4(0.f, 1.f, 0.f, 0.f);
     if (h < B.n_hyp)
     {
-        int s0, s1, o0, o1;
+        int s0, s1, o0, o1; // scale-only problems: (s0, s1, o0) index the scale class, o1 is unused (-1)
+        const bool scale_only = T.problem != 0;
         if (B.have_samples)
         {
             const int4 s = reinterpret_cast<const int4*>(B.samples)[h];
@@ -174,16 +175,40 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
             uint32_t c[4] = {static_cast<uint32_t>(g), static_cast<uint32_t>(g >> 32), 0x47435231u, 0u};
             philox4x32_10(c, static_cast<uint32_t>(B.seed), static_cast<uint32_t>(B.seed >> 32));
             draw_pair(c[0], c[1], static_cast<uint32_t>(B.ns), s0, s1);
-            draw_pair(c[2], c[3], static_cast<uint32_t>(B.no), o0, o1);
+            if (scale_only)
+            {
+                // third distinct index: uniform over the n - 2 remaining values, mapped around the two taken ones
+                int t = static_cast<int>(__umulhi(c[2], static_cast<uint32_t>(B.ns) - 2u));
+                const int lo = min(s0, s1), hi = max(s0, s1);
+                if (t >= lo) t++;
+                if (t >= hi) t++;
+                o0 = t;
+                o1 = -1;
+            }
+            else
+                draw_pair(c[2], c[3], static_cast<uint32_t>(B.no), o0, o1);
             if (B.samples) reinterpret_cast<int4*>(B.samples)[h] = make_int4(s0, s1, o0, o1);
         }
+        const unsigned n_third = static_cast<unsigned>(scale_only ? B.ns : B.no);
         const bool in_range = static_cast<unsigned>(s0) < static_cast<unsigned>(B.ns) &&
                               static_cast<unsigned>(s1) < static_cast<unsigned>(B.ns) &&
-                              static_cast<unsigned>(o0) < static_cast<unsigned>(B.no) &&
-                              static_cast<unsigned>(o1) < static_cast<unsigned>(B.no);
+                              static_cast<unsigned>(o0) < n_third && (scale_only || static_cast<unsigned>(o1) < n_third);
         if (!in_range)
         {
             atomicAdd(&B.ctr->n_bad_sample, 1u);
+        }
+        else if (scale_only)
+        {
+            double f0[3], f1[3], f2[3];
+#pragma unroll
+            for (int j = 0; j < 3; j++)
+            {
+                f0[j] = B.scale[3 * s0 + j];
+                f1[j] = B.scale[3 * s1 + j];
+                f2[j] = B.scale[3 * o0 + j];
+            }
+            sample_valid = !are_collinear(f0[0], f0[1], f1[0], f1[1], f2[0], f2[1], 1.0); // three_sift.hpp:111-143
+            if (sample_valid) solved = estimate_minimal_scale3(f0, f1, f2, T.problem == 2, m);
         }
         else
         {
@@ -204,14 +229,17 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
         if (solved)
         {
             f |= 2;
-            if (is_valid_model(m)) f |= 4; // consulted at selection time, GCRANSAC.h:440-446
+            // consulted at selection time, GCRANSAC.h:440-446; the scale-only solvers keep SolverEngine's default (always valid)
+            if (T.problem != 0 || is_valid_model(m)) f |= 4;
             // ---- scoring-path parameters and their proven error bands (DESIGN.md "error budget")
             const Scene sc = *B.scene;
             const double ah7 = fabs(m.h7), ah8 = fabs(m.h8);
             const double mag = ah7 * sc.xq_max + ah8 * sc.yq_max + sc.iq_max; // bound of the terms of v
-            const double A = log2(m.alpha);
+            // scale-only "original": residual |log(rectified / alpha^3)| = 3 ln2 |-lg2 alpha - lg2 v|: alpha enters reciprocally
+            const double alpha_eff = T.problem == 2 ? 1.0 / m.alpha : m.alpha;
+            const double A = log2(alpha_eff);
             const double Tp = T.Tp;
-            const double v_lo = m.alpha * T.exp2_neg_Tp, v_hi = m.alpha * T.exp2_pos_Tp; // hypothesis-independent factors from the host
+            const double v_lo = alpha_eff * T.exp2_neg_Tp, v_hi = alpha_eff * T.exp2_pos_Tp; // hypothesis-independent factors from the host
             const double kh = sc.k_max * (ah7 + ah8);
             const double eps_lg = 2.384185791015625e-7 + 3.0 * kU * (fabs(A) + Tp + 1.0); // MUFU.LG2 + roundings of A, d
             // FP32 tiles: v, numer, denom from FP32 features and FP32 (h7, h8)
@@ -321,7 +349,7 @@ __device__ __forceinline__ void fixup_phase(const Buffers& B, const Thresholds& 
         const unsigned int h = w.x, cls = w.y >> 31, f = w.y & 0x7fffffffu;
         const Model4 m = B.models[h];
         double r;
-        if (cls == 0) r = scale_residual(B.scale[3 * f], B.scale[3 * f + 1], B.scale[3 * f + 2], m);
+        if (cls == 0) r = scale_residual(B.scale[3 * f], B.scale[3 * f + 1], B.scale[3 * f + 2], m, T.problem == 2);
         else r = orientation_residual(B.orient[3 * f], B.orient[3 * f + 1], B.orient[3 * f + 2], m);
         const double r2 = r * r;
         if (r2 <= T.tsq[cls]) // S1
@@ -346,7 +374,7 @@ __device__ __forceinline__ void fixup_phase(const Buffers& B, const Thresholds& 
         const unsigned int f = cls ? B.irr_o[k - n_is] : B.irr_s[k];
         const Model4 m = B.models[h];
         double r;
-        if (cls == 0) r = scale_residual(B.scale[3 * f], B.scale[3 * f + 1], B.scale[3 * f + 2], m);
+        if (cls == 0) r = scale_residual(B.scale[3 * f], B.scale[3 * f + 1], B.scale[3 * f + 2], m, T.problem == 2);
         else r = orientation_residual(B.orient[3 * f], B.orient[3 * f + 1], B.orient[3 * f + 2], m);
         const double r2 = r * r;
         if (r2 <= T.tsq[cls])
@@ -371,18 +399,20 @@ constexpr double kFix = 17592186044416.0; // 2^44
 
 __device__ __forceinline__ double fix_to_double(unsigned long long q, double tsq) { return static_cast<double>(q) * (tsq / kFix); }
 
-// S2/S3: per-class value = -sum r^2 / tsq + n; any class below the minimal sample size (2) zeroes everything
+// S2/S3: per-class value = -sum r^2 / tsq + n; any class below its minimal sample size zeroes everything
 __device__ __forceinline__ double msac_value(const Thresholds& T, double s0, double s1, unsigned int c0, unsigned int c1,
                                              unsigned int& n0, unsigned int& n1)
 {
-    if (c0 < 2u || c1 < 2u)
+    if (c0 < T.min_inl[0] || c1 < T.min_inl[1])
     {
         n0 = n1 = 0u;
         return 0.0;
     }
     n0 = c0;
     n1 = c1;
-    return (-s0 / T.tsq[0] + static_cast<double>(c0)) + (-s1 / T.tsq[1] + static_cast<double>(c1));
+    const double v0 = -s0 / T.tsq[0] + static_cast<double>(c0);
+    if (T.problem != 0) return v0; // one class
+    return v0 + (-s1 / T.tsq[1] + static_cast<double>(c1));
 }
 
 __device__ __forceinline__ void exact_items_phase(const Buffers& B, const Thresholds& T, int mode, unsigned int n_direct)
@@ -410,9 +440,9 @@ __device__ __forceinline__ void exact_items_phase(const Buffers& B, const Thresh
         if (f < n)
         {
             const double r = cls ? orientation_residual(F[3 * f], F[3 * f + 1], F[3 * f + 2], m)
-                                 : scale_residual(F[3 * f], F[3 * f + 1], F[3 * f + 2], m);
+                                 : scale_residual(F[3 * f], F[3 * f + 1], F[3 * f + 2], m, T.problem == 2);
             const double r2 = r * r;
-            in = r2 <= T.tsq[cls]; // S1
+            in = T.strict ? r2 < T.tsq[cls] : r2 <= T.tsq[cls]; // S1 (strict: one-class graph-cut relabelling)
             if (in) q = static_cast<unsigned long long>(r2 / T.tsq[cls] * kFix + 0.5);
         }
         const unsigned int word = __ballot_sync(0xffffffffu, in);
@@ -753,6 +783,43 @@ __global__ void __launch_bounds__(kExactThreads) k_tail(const __grid_constant__ 
     if (blockIdx.x == 0) select_phase(B, T);
     if (stamp) B.phase_ns[5] = global_ns();
 }
+
+// ------------------------------------------------------------------------------------------------
+// Per-hypothesis reporting modes only (GCR_RUN_KEEP_PER_HYP / GCR_RUN_EMIT_MASKS): the MSAC value n - sum(r^2)/tsq
+// cancels when the inliers sit near the threshold, which amplifies the FP32 path's ~4e-6 n absolute error beyond the
+// 1e-5 relative bar for low-score hypotheses (never contenders).  Those with value < 0.6 n are re-scored by the FP64
+// reference-order kernel after the tail: collect -> k_exact_items(mode 0) -> refinalize.
+__global__ void k_refine_collect(Buffers B)
+{
+    const int h = blockIdx.x * blockDim.x + threadIdx.x;
+    if (h >= B.n_hyp) return;
+    const unsigned char f = B.flags[h];
+    if (!(f & 2) || (f & 8)) return;
+    const unsigned int n = B.n_inl[2 * h] + B.n_inl[2 * h + 1];
+    if (n == 0u || !(B.score[h] < 0.6 * static_cast<double>(n))) return;
+    B.hard_hyp[atomicAdd(&B.ctr->n_hard, 1u)] = h;
+    reinterpret_cast<unsigned long long*>(B.sums)[2 * h] = 0ull; // fixed-point accumulators of k_exact_items
+    reinterpret_cast<unsigned long long*>(B.sums)[2 * h + 1] = 0ull;
+    B.cnts[2 * h] = B.cnts[2 * h + 1] = 0u;
+    B.flags[h] = f | 8;
+}
+
+__global__ void k_refine_finalize(Buffers B, Thresholds T)
+{
+    const unsigned int n = B.ctr->n_hard;
+    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    {
+        const unsigned int h = B.hard_hyp[i];
+        unsigned int n0, n1;
+        B.score[h] = msac_value(T, fix_to_double(reinterpret_cast<const unsigned long long*>(B.sums)[2 * h], T.tsq[0]),
+                                fix_to_double(reinterpret_cast<const unsigned long long*>(B.sums)[2 * h + 1], T.tsq[1]),
+                                B.cnts[2 * h], B.cnts[2 * h + 1], n0, n1);
+        B.n_inl[2 * h] = n0;
+        B.n_inl[2 * h + 1] = n1;
+    }
+}
+
+__global__ void k_refine_done(Buffers B) { B.ctr->n_hard = 0u; }
 
 // caller-supplied models -> candidate slots [0, n) (gcr_score_model / gcr_score_models)
 __global__ void k_set_models(Buffers B, const Model4* __restrict__ m, unsigned int n)

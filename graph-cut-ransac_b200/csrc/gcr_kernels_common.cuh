@@ -60,6 +60,9 @@ struct Thresholds
     float pc[4];     // r^2 = z (pc0 + z (pc1 + z (pc2 + z pc3))), z = tan^2
     float scale_unit; // (3 ln 2)^2: converts sum of d^2 (log2 units) into sum of r^2
     int orient_all_exact; // orientation threshold outside the fast path's range -> every hypothesis exact
+    int problem;          // 0 hybrid (two_sift), 1 scale-only (three_sift), 2 scale-only "original" (three_sift_original)
+    int strict;           // gcr_score_models only: inlier iff r^2 < tsq
+    unsigned int min_inl[2]; // minimal sample size per class: fewer inliers than this resets the score to zero (S3)
 };
 
 struct Buffers

@@ -135,11 +135,18 @@ struct Best
 
 } // namespace
 
-size_t iterationNumber(const uint32_t n_inl[2], size_t ns, size_t no, double confidence)
+size_t iterationNumber(const uint32_t n_inl[2], size_t ns, size_t no, double confidence, int problem)
 {
     const double r0 = static_cast<double>(n_inl[0]) / static_cast<double>(ns);
-    const double r1 = static_cast<double>(n_inl[1]) / static_cast<double>(no);
-    const double q = std::pow(r0, 2.0) * std::pow(r1, 2.0);
+    double q = 1.0;
+    if (problem == GCR_PROBLEM_HYBRID)
+    {
+        const double r1 = static_cast<double>(n_inl[1]) / static_cast<double>(no);
+        q *= std::pow(r0, 2.0);
+        q *= std::pow(r1, 2.0);
+    }
+    else
+        q *= std::pow(r0, 3.0); // one class, sample size 3
     const double lg = std::log(1.0 - q);
     if (std::fabs(lg) < std::numeric_limits<double>::epsilon()) return std::numeric_limits<size_t>::max();
     const double it = std::ceil(std::log(1.0 - confidence) / lg);
@@ -147,17 +154,22 @@ size_t iterationNumber(const uint32_t n_inl[2], size_t ns, size_t no, double con
     return it <= 0.0 ? 0 : static_cast<size_t>(it);
 }
 
-int findRectifyingHomographySIFT(const double* scale, size_t ns, const double* orient, size_t no, double thr_s, double thr_o,
-                                 double /*spatial_coherence_weight: unused by the two-class path, GCRANSAC.h:922-944*/,
-                                 size_t min_iters, size_t max_iters, size_t max_lo, std::vector<bool>& scale_inliers,
-                                 std::vector<bool>& orientation_inliers, std::vector<double>& homography,
-                                 gcransac::SIFTRectifyingHomography& model, const Options& opt, Stats* stats_out)
+// The estimator for any of the three problems.  problem = GCR_PROBLEM_HYBRID: two classes with minimal samples {2, 2};
+// scale-only problems: one class (no == 0, orient == nullptr), minimal sample 3.
+static int estimateImpl(int problem, const double* scale, size_t ns, const double* orient, size_t no, double thr_s, double thr_o,
+                        size_t min_iters, size_t max_iters, size_t max_lo, std::vector<bool>& scale_inliers,
+                        std::vector<bool>& orientation_inliers, std::vector<double>& homography,
+                        gcransac::SIFTRectifyingHomography& model, const Options& opt, Stats* stats_out)
 {
+    const bool hybrid = problem == GCR_PROBLEM_HYBRID;
+    const size_t min_s = hybrid ? 2 : 3, min_o = hybrid ? 2 : 0; // sampleSize()
+    const size_t lim_s = 7 * min_s, lim_o = 7 * min_o;            // inlierLimit(), rectifying_homography_estimator.h:45-55
     const auto t_begin = std::chrono::steady_clock::now();
     Stats st;
-    if (!scale || !orient) throw std::invalid_argument("null feature pointer");
+    if (!scale || (hybrid && !orient)) throw std::invalid_argument("null feature pointer");
     // GCRANSAC.h:222-228: fewer rows than the minimal sample of a class
-    if (ns < 2 || no < 2) throw std::runtime_error("Data set smaller than minimal sample size for corresponding data type");
+    if (ns < min_s || no < min_o) throw std::runtime_error("Data set smaller than minimal sample size for corresponding data type");
+    if (!hybrid) thr_o = 0.0;
     if (!(thr_s >= 0.0) || !(thr_o >= 0.0) || !std::isfinite(thr_s) || !std::isfinite(thr_o))
         throw std::invalid_argument("residual thresholds must be finite and non-negative");
     const double thr[2] = {thr_s, thr_o};
@@ -171,6 +183,7 @@ int findRectifyingHomographySIFT(const double* scale, size_t ns, const double* o
     }
 
     Lease eng(opt.device);
+    eng.check(gcr_set_problem(eng.h, problem), "gcr_set_problem");
     eng.check(gcr_set_features(eng.h, scale, static_cast<int64_t>(ns), orient, static_cast<int64_t>(no),
                                opt.features_on_device ? 1 : 0),
               "gcr_set_features");
@@ -182,7 +195,7 @@ int findRectifyingHomographySIFT(const double* scale, size_t ns, const double* o
     size_t done = 0;
     const uint32_t one_each[2] = {1u, 1u}; // GCRANSAC.h:233-236: the initial max_iteration assumes one inlier per class
     size_t target = opt.samples ? static_cast<size_t>(opt.n_samples)
-                                : std::max(min_iters, std::min(iterationNumber(one_each, ns, no, opt.confidence), max_iters));
+                                : std::max(min_iters, std::min(iterationNumber(one_each, ns, no, opt.confidence, problem), max_iters));
     while (done < target)
     {
         // The reference re-evaluates its stopping rule after every iteration; here it is evaluated between device
@@ -214,7 +227,7 @@ int findRectifyingHomographySIFT(const double* scale, size_t ns, const double* o
         if (!opt.samples)
         {
             // max_iteration = getIterationNumber(best inlier counts), GCRANSAC.h:480-483
-            const size_t adaptive = iterationNumber(best.have ? best.n_inl : one_each, ns, no, opt.confidence);
+            const size_t adaptive = iterationNumber(best.have ? best.n_inl : one_each, ns, no, opt.confidence, problem);
             target = std::max(min_iters, std::min(adaptive, max_iters));
         }
     }
@@ -232,7 +245,7 @@ int findRectifyingHomographySIFT(const double* scale, size_t ns, const double* o
         return n_total;
     };
     // GCRANSAC.h:535-541: a best model supported by no more than a minimal sample per class is "not found"
-    if (!best.have || (best.n_inl[0] <= 2 && best.n_inl[1] <= 2)) return finish(0);
+    if (!best.have || (best.n_inl[0] <= min_s && best.n_inl[1] <= min_o)) return finish(0);
 
     // ---- local optimisation on the selected model (graphCutLocalOptimization for two classes, GCRANSAC.h:873-1062)
     std::vector<double> h_scale, h_orient; // host rows for the fits
@@ -242,7 +255,7 @@ int findRectifyingHomographySIFT(const double* scale, size_t ns, const double* o
     {
         h_scale.resize(3 * ns);
         h_orient.resize(3 * no);
-        eng.check(gcr_get_features(eng.h, h_scale.data(), h_orient.data()), "gcr_get_features");
+        eng.check(gcr_get_features(eng.h, h_scale.data(), hybrid ? h_orient.data() : nullptr), "gcr_get_features");
         fs = h_scale.data();
         fo = h_orient.data();
     }
@@ -253,6 +266,13 @@ int findRectifyingHomographySIFT(const double* scale, size_t ns, const double* o
     auto asArray = [](const gcransac::SIFTRectifyingHomography& m, double out[4]) {
         out[0] = m.h7; out[1] = m.h8; out[2] = m.alpha; out[3] = m.phi;
     };
+    auto fit = [&](const std::vector<uint32_t>& is, const std::vector<uint32_t>& io, gcransac::SIFTRectifyingHomography& m) {
+        return hybrid ? fitNonMinimal(fs, is, fo, io, m)
+                      : fitNonMinimalScale(fs, is, problem == GCR_PROBLEM_SCALE_ONLY_ORIGINAL, m);
+    };
+    // two classes: r^2 <= (1.5 t)^2 (GCRANSAC.h:931-937); one class: graph cut over the (empty) neighbourhood graph, which
+    // labels a feature an inlier iff r^2 < (1.5 t)^2 for any 0 <= lambda < 1 (GCRANSAC.h:759-870)
+    const uint32_t label_flags = hybrid ? GCR_SCORE_TRUNCATED_SQ : (GCR_SCORE_TRUNCATED_SQ | GCR_SCORE_STRICT);
 
     if (opt.do_local_optimization && max_lo > 0)
     {
@@ -261,20 +281,20 @@ int findRectifyingHomographySIFT(const double* scale, size_t ns, const double* o
         {
             bool updated = false;
             // relabel every feature with the truncated threshold r^2 <= (1.5 t)^2   (GCRANSAC.h:931-937)
-            eng.check(gcr_score_models(eng.h, lo.model, 1, thr, GCR_SCORE_TRUNCATED_SQ, nullptr, nullptr, lab_words.data()),
+            eng.check(gcr_score_models(eng.h, lo.model, 1, thr, label_flags, nullptr, nullptr, lab_words.data()),
                       "gcr_score_models(label)");
             wordsToIndices(lab_words.data(), ns, in_s);
             wordsToIndices(lab_words.data() + ws, no, in_o);
             // inner RANSAC on the labelled inliers: min(7 x sample size, n) per class  (GCRANSAC.h:955-996)
-            const size_t k_s = std::min<size_t>(14, in_s.size()), k_o = std::min<size_t>(14, in_o.size());
-            if (in_s.size() <= 2 || in_o.size() <= 2) break; // sampling fails: neither a draw nor "use all" applies
+            const size_t k_s = std::min(lim_s, in_s.size()), k_o = std::min(lim_o, in_o.size());
+            if (in_s.size() <= min_s || (hybrid && in_o.size() <= min_o)) break; // sampling fails: neither a draw nor "use all" applies
             trial_models.clear();
             for (size_t trial = 0; trial < max_lo; ++trial)
             {
                 if (k_s < in_s.size()) drawSubset(in_s, k_s, rng, scratch, smp_s); else smp_s = in_s;
                 if (k_o < in_o.size()) drawSubset(in_o, k_o, rng, scratch, smp_o); else smp_o = in_o;
                 gcransac::SIFTRectifyingHomography m;
-                if (!fitNonMinimal(fs, smp_s, fo, smp_o, m)) continue;
+                if (!fit(smp_s, smp_o, m)) continue;
                 double a[4];
                 asArray(m, a);
                 trial_models.insert(trial_models.end(), a, a + 4);
@@ -313,7 +333,7 @@ int findRectifyingHomographySIFT(const double* scale, size_t ns, const double* o
     wordsToIndices(best.words.data() + ws, no, in_o);
     {
         gcransac::SIFTRectifyingHomography m;
-        if (fitNonMinimal(fs, in_s, fo, in_o, m))
+        if (fit(in_s, in_o, m))
         {
             double a[4], sc = 0.0;
             uint32_t cnt[2];
@@ -343,7 +363,78 @@ int findRectifyingHomographySIFT(const double* scale, size_t ns, const double* o
     return finish(static_cast<int>(in_s.size() + in_o.size()));
 }
 
+int findRectifyingHomographySIFT(const double* scale, size_t ns, const double* orient, size_t no, double thr_s, double thr_o,
+                                 double /*spatial_coherence_weight: unused by the two-class path, GCRANSAC.h:922-944*/,
+                                 size_t min_iters, size_t max_iters, size_t max_lo, std::vector<bool>& scale_inliers,
+                                 std::vector<bool>& orientation_inliers, std::vector<double>& homography,
+                                 gcransac::SIFTRectifyingHomography& model, const Options& opt, Stats* stats_out)
+{
+    return estimateImpl(GCR_PROBLEM_HYBRID, scale, ns, orient, no, thr_s, thr_o, min_iters, max_iters, max_lo, scale_inliers,
+                        orientation_inliers, homography, model, opt, stats_out);
+}
+
+int findRectifyingHomographyScaleOnly(const double* features, size_t n, double thr, double spatial_coherence_weight, size_t min_iters,
+                                      size_t max_iters, size_t max_lo, bool original, std::vector<bool>& inliers,
+                                      std::vector<double>& homography, gcransac::ScaleBasedRectifyingHomography& model,
+                                      const Options& opt, Stats* stats_out)
+{
+    // the neighbourhood graph of the reference's driver is empty (gcransac_python.cpp:62-70), so the spatial coherence
+    // weight only rescales the unary terms of the graph cut; outside [0, 1) the reference's labelling degenerates
+    if (!(spatial_coherence_weight >= 0.0 && spatial_coherence_weight < 1.0))
+        throw std::invalid_argument("spatial_coherence_weight must be in [0, 1)");
+    std::vector<bool> unused;
+    gcransac::SIFTRectifyingHomography full;
+    const int total = estimateImpl(original ? GCR_PROBLEM_SCALE_ONLY_ORIGINAL : GCR_PROBLEM_SCALE_ONLY, features, n, nullptr, 0, thr,
+                                   0.0, min_iters, max_iters, max_lo, inliers, unused, homography, full, opt, stats_out);
+    model = gcransac::ScaleBasedRectifyingHomography();
+    model.h7 = full.h7;
+    model.h8 = full.h8;
+    if (total != 0) model.alpha = full.alpha;
+    return total;
+}
+
 } // namespace gcr_host
+
+namespace
+{
+int scaleOnlyEntry(const std::vector<double>& features, double thr, double scw, size_t min_iters, size_t max_iters, size_t max_lo,
+                   bool original, std::vector<bool>& inliers, std::vector<double>& homography,
+                   gcransac::ScaleBasedRectifyingHomography& model, unsigned int verbose_level)
+{
+    if (features.size() % 3 != 0)
+    {
+        std::fprintf(stderr, "Feature vector size (%zu) is not a multiple of the feature size (3).\n", features.size());
+        return 0;
+    }
+    const int n = gcr_host::findRectifyingHomographyScaleOnly(features.data(), features.size() / 3, thr, scw, min_iters, max_iters,
+                                                              max_lo, original, inliers, homography, model, gcr_host::Options(),
+                                                              nullptr);
+    if (verbose_level > 0)
+        std::printf("\nFinal model:\n\nh7: %g, h8: %g, alpha: %g\n\nNumber of scale-inliers: %d\n", model.h7, model.h8, model.alpha, n);
+    return n;
+}
+} // namespace
+
+// gcransac_python.h:7-31, gcransac_python.cpp:32-254
+int findRectifyingHomographyScaleOnly_(const std::vector<double>& features, double scale_residual_thresh,
+                                       double spatial_coherence_weight, size_t min_iteration_number, size_t max_iteration_number,
+                                       size_t max_local_optimization_number, std::vector<bool>& inliers,
+                                       std::vector<double>& homography, gcransac::ScaleBasedRectifyingHomography& model,
+                                       unsigned int verbose_level)
+{
+    return scaleOnlyEntry(features, scale_residual_thresh, spatial_coherence_weight, min_iteration_number, max_iteration_number,
+                          max_local_optimization_number, false, inliers, homography, model, verbose_level);
+}
+
+int findRectifyingHomographyScaleOnlyOriginal_(const std::vector<double>& features, double scale_residual_thresh,
+                                               double spatial_coherence_weight, size_t min_iteration_number,
+                                               size_t max_iteration_number, size_t max_local_optimization_number,
+                                               std::vector<bool>& inliers, std::vector<double>& homography,
+                                               gcransac::ScaleBasedRectifyingHomography& model, unsigned int verbose_level)
+{
+    return scaleOnlyEntry(features, scale_residual_thresh, spatial_coherence_weight, min_iteration_number, max_iteration_number,
+                          max_local_optimization_number, true, inliers, homography, model, verbose_level);
+}
 
 int findRectifyingHomographySIFT_(const std::vector<double>& scale_features, const std::vector<double>& orientation_features,
                                   double scale_residual_thresh, double orientation_residual_thresh,

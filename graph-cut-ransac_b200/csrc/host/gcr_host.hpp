@@ -65,12 +65,31 @@ int findRectifyingHomographySIFT(const double* scale, size_t ns, const double* o
                                  std::vector<bool>& orientation_inliers, std::vector<double>& homography,
                                  gcransac::SIFTRectifyingHomography& model, const Options& options, Stats* stats);
 
-// GCRANSAC::getIterationNumber for two classes with sample sizes {2, 2} (GCRANSAC.h:738-757)
-size_t iterationNumber(const uint32_t n_inl[2], size_t ns, size_t no, double confidence);
+// Scale-only estimators (gcransac_python.cpp:32-254): features f64[n,3] rows (x, y, s); `original` selects
+// findRectifyingHomographyScaleOnlyOriginal.  In replay mode Options::samples rows are (s0, s1, s2, ignored).
+int findRectifyingHomographyScaleOnly(const double* features, size_t n, double scale_residual_thresh, double spatial_coherence_weight,
+                                      size_t min_iteration_number, size_t max_iteration_number,
+                                      size_t max_local_optimization_number, bool original, std::vector<bool>& inliers,
+                                      std::vector<double>& homography, gcransac::ScaleBasedRectifyingHomography& model,
+                                      const Options& options, Stats* stats);
+
+// GCRANSAC::getIterationNumber (GCRANSAC.h:738-757): sample sizes {2, 2} for the hybrid problem (problem 0), {3} for the
+// scale-only problems
+size_t iterationNumber(const uint32_t n_inl[2], size_t ns, size_t no, double confidence, int problem = 0);
 
 } // namespace gcr_host
 
-// The reference's own entry point, same signature and meaning (gcransac_python.h:33-47).
+// The reference's own entry points, same signatures and meaning (gcransac_python.h:7-47).
+int findRectifyingHomographyScaleOnly_(const std::vector<double>& features, double scale_residual_thresh,
+                                       double spatial_coherence_weight, size_t min_iteration_number, size_t max_iteration_number,
+                                       size_t max_local_optimization_number, std::vector<bool>& inliers,
+                                       std::vector<double>& homography, gcransac::ScaleBasedRectifyingHomography& model,
+                                       unsigned int verbose_level = 0);
+int findRectifyingHomographyScaleOnlyOriginal_(const std::vector<double>& features, double scale_residual_thresh,
+                                               double spatial_coherence_weight, size_t min_iteration_number,
+                                               size_t max_iteration_number, size_t max_local_optimization_number,
+                                               std::vector<bool>& inliers, std::vector<double>& homography,
+                                               gcransac::ScaleBasedRectifyingHomography& model, unsigned int verbose_level = 0);
 int findRectifyingHomographySIFT_(const std::vector<double>& scale_features, const std::vector<double>& orientation_features,
                                   double scale_residual_thresh, double orientation_residual_thresh,
                                   double spatial_coherence_weight, size_t min_iteration_number, size_t max_iteration_number,

@@ -215,4 +215,28 @@ inline bool fitNonMinimal(const double* scale, const std::vector<uint32_t>& scal
     return true;
 }
 
+// Non-minimal fit of the scale-only estimators: rows [x, y, s^(1/3)] = 1 (three_sift.hpp:195-254) or, for the
+// "original" variant, [x, y, -s^(-1/3)] = -1 (three_sift_original.hpp:229-234).  Exactly a minimal sample (3 rows) goes
+// to the minimal solver in the reference; the local optimisation and the refit never present one (they need > 3 inliers).
+inline bool fitNonMinimalScale(const double* scale, const std::vector<uint32_t>& idx, bool original,
+                               gcransac::SIFTRectifyingHomography& model)
+{
+    if (idx.size() <= 3) return false;
+    StreamingLsq3 lsq;
+    for (uint32_t i : idx)
+    {
+        const double* f = scale + 3 * static_cast<size_t>(i);
+        if (original) lsq.addRow(f[0], f[1], -std::pow(f[2], -1.0 / 3.0), -1.0);
+        else lsq.addRow(f[0], f[1], std::pow(f[2], 1.0 / 3.0), 1.0);
+    }
+    double x[3];
+    if (!lsq.solve(x)) return false;
+    if (x[2] < 1e-9) return false;
+    model = gcransac::SIFTRectifyingHomography();
+    model.h7 = x[0];
+    model.h8 = x[1];
+    model.alpha = x[2];
+    return true;
+}
+
 } // namespace gcr_host

@@ -34,9 +34,9 @@ struct FeatureArg
 };
 
 // ndim == 2, rows >= 2, cols == 3 (bindings.cpp:199-224), float64, C-contiguous
-FeatureArg parseFeatures(const py::object& obj, const char* what)
+FeatureArg parseFeatures(const py::object& obj, const char* what, size_t kNumMinFeatures = 2)
 {
-    constexpr size_t kFeatureSize = 3, kNumMinFeatures = 2;
+    constexpr size_t kFeatureSize = 3;
     FeatureArg out;
     py::object src = obj;
     const bool is_cuda = py::hasattr(obj, "is_cuda") && py::hasattr(obj, "data_ptr") && obj.attr("is_cuda").cast<bool>();
@@ -56,7 +56,7 @@ FeatureArg parseFeatures(const py::object& obj, const char* what)
     if (shape[0] < kNumMinFeatures || shape[1] != kFeatureSize)
     {
         std::stringstream msg;
-        msg << what << " features should be an array with " << kFeatureSize << " columns and at least " << kNumMinFeatures
+        msg << what << (what[0] ? " features" : "Features") << " should be an array with " << kFeatureSize << " columns and at least " << kNumMinFeatures
             << " rows. It has " << shape[1] << " columns and " << shape[0] << " rows.";
         throw std::invalid_argument(msg.str());
     }
@@ -170,6 +170,69 @@ py::tuple findRectifyingHomographySIFT(py::object scale_features, py::object ori
     return py::make_tuple(H, smask, omask, M);
 }
 
+// findRectifyingHomographyScaleOnly / ...Original (bindings.cpp:19-179): (H, inliers, model) or (None, inliers)
+py::tuple scaleOnlyImpl(bool original, py::object features, double scale_residual_thresh, double spatial_coherence_weight,
+                        size_t min_iteration_number, size_t max_iteration_number, size_t max_local_optimization_number,
+                        py::object seed, int device, py::object samples, bool return_stats)
+{
+    FeatureArg f = parseFeatures(features, "", 3);
+    gcr_host::Options opt;
+    opt.device = device;
+    if (f.on_device)
+    {
+        opt.device = f.device;
+        opt.features_on_device = true;
+    }
+    if (!seed.is_none())
+    {
+        opt.has_seed = true;
+        opt.seed = seed.cast<uint64_t>();
+    }
+    py::array_t<int32_t, py::array::c_style | py::array::forcecast> smp;
+    if (!samples.is_none())
+    {
+        smp = py::array_t<int32_t, py::array::c_style | py::array::forcecast>::ensure(samples);
+        if (!smp || smp.ndim() != 2 || smp.shape(1) != 4 || smp.shape(0) < 1)
+            throw std::invalid_argument("samples must be an int32 array of shape [H,4] = (s0, s1, s2, ignored).");
+        opt.samples = smp.data();
+        opt.n_samples = smp.shape(0);
+    }
+    std::vector<double> homography(9);
+    std::vector<bool> inliers;
+    ScaleBasedRectifyingHomography model;
+    gcr_host::Stats st;
+    int num_inliers = 0;
+    {
+        py::gil_scoped_release nogil;
+        num_inliers = gcr_host::findRectifyingHomographyScaleOnly(f.ptr, f.rows, scale_residual_thresh, spatial_coherence_weight,
+                                                                  min_iteration_number, max_iteration_number,
+                                                                  max_local_optimization_number, original, inliers, homography,
+                                                                  model, opt, &st);
+    }
+    py::array_t<bool> mask = toMask(inliers);
+    if (num_inliers == 0)
+    {
+        if (return_stats) return py::make_tuple(py::none(), mask, toDict(st));
+        return py::make_tuple(py::none(), mask);
+    }
+    py::array_t<double> Harr({3, 3});
+    std::copy(homography.begin(), homography.end(), static_cast<double*>(Harr.request().ptr));
+    if (return_stats) return py::make_tuple(Harr, mask, py::cast(model), toDict(st));
+    return py::make_tuple(Harr, mask, py::cast(model));
+}
+
+py::tuple findRectifyingHomographyScaleOnly(py::object features, double thr, double scw, size_t min_it, size_t max_it, size_t max_lo,
+                                            py::object seed, int device, py::object samples, bool return_stats)
+{
+    return scaleOnlyImpl(false, features, thr, scw, min_it, max_it, max_lo, seed, device, samples, return_stats);
+}
+
+py::tuple findRectifyingHomographyScaleOnlyOriginal(py::object features, double thr, double scw, size_t min_it, size_t max_it,
+                                                    size_t max_lo, py::object seed, int device, py::object samples, bool return_stats)
+{
+    return scaleOnlyImpl(true, features, thr, scw, min_it, max_it, max_lo, seed, device, samples, return_stats);
+}
+
 // host-side non-minimal fit, exposed for the parity tests of the refit step (two_sift.hpp:423-579)
 py::object fitNonMinimalPy(py::array_t<double, py::array::c_style | py::array::forcecast> scale,
                            py::array_t<double, py::array::c_style | py::array::forcecast> orient)
@@ -238,6 +301,20 @@ PYBIND11_MODULE(pygcransac, m)
         m, "SIFTRectifyingHomography")
         .def(py::init<>());
 
+    m.def("findRectifyingHomographyScaleOnly", &findRectifyingHomographyScaleOnly,
+          "Scale-only rectifying-homography RANSAC (3 scale features per sample); hypothesis stage on the GPU.",
+          py::arg("features"), py::arg("scale_residual_thresh"), py::arg("spatial_coherence_weight") = 0.0,
+          py::arg("min_iteration_number") = 10000, py::arg("max_iteration_number") = 10000,
+          py::arg("max_local_optimization_number") = 50, py::kw_only(), py::arg("seed") = py::none(), py::arg("device") = 0,
+          py::arg("samples") = py::none(), py::arg("return_stats") = false);
+
+    m.def("findRectifyingHomographyScaleOnlyOriginal", &findRectifyingHomographyScaleOnlyOriginal,
+          "The 'original' scale-only formulation (rows [x, y, -s^(-1/3)] = -1); hypothesis stage on the GPU.",
+          py::arg("features"), py::arg("scale_residual_thresh"), py::arg("spatial_coherence_weight") = 0.0,
+          py::arg("min_iteration_number") = 10000, py::arg("max_iteration_number") = 10000,
+          py::arg("max_local_optimization_number") = 50, py::kw_only(), py::arg("seed") = py::none(), py::arg("device") = 0,
+          py::arg("samples") = py::none(), py::arg("return_stats") = false);
+
     m.def("findRectifyingHomographySIFT", &findRectifyingHomographySIFT,
           "Hybrid (scale + orientation) rectifying-homography RANSAC; hypothesis stage on the GPU.",
           py::arg("scale_features"), py::arg("orientation_features"), py::arg("scale_residual_thresh"),
@@ -246,13 +323,26 @@ PYBIND11_MODULE(pygcransac, m)
           py::arg("max_local_optimization_number") = 50, py::kw_only(), py::arg("seed") = py::none(),
           py::arg("device") = 0, py::arg("samples") = py::none(), py::arg("return_stats") = false);
 
+    m.def(
+        "_fit_non_minimal_scale",
+        [](py::array_t<double, py::array::c_style | py::array::forcecast> scale, bool original) -> py::object {
+            if (scale.ndim() != 2 || scale.shape(1) != 3) throw std::invalid_argument("features must be an [N,3] array");
+            std::vector<uint32_t> idx(scale.shape(0));
+            for (size_t i = 0; i < idx.size(); ++i) idx[i] = static_cast<uint32_t>(i);
+            SIFTRectifyingHomography m;
+            if (!gcr_host::fitNonMinimalScale(scale.data(), idx, original, m)) return py::none();
+            return py::cast(static_cast<ScaleBasedRectifyingHomography&>(m));
+        },
+        "Host non-minimal fit of the scale-only estimators from all rows given (test hook).", py::arg("features"),
+        py::arg("original") = false);
     m.def("_fit_non_minimal", &fitNonMinimalPy, "Host non-minimal fit from all rows given (test hook).", py::arg("scale_features"),
           py::arg("orientation_features"));
     m.def(
         "_iteration_number",
-        [](uint32_t n_scale_inliers, uint32_t n_orient_inliers, size_t ns, size_t no, double confidence) {
+        [](uint32_t n_scale_inliers, uint32_t n_orient_inliers, size_t ns, size_t no, double confidence, int problem) {
             const uint32_t n[2] = {n_scale_inliers, n_orient_inliers};
-            return gcr_host::iterationNumber(n, ns, no, confidence);
+            return gcr_host::iterationNumber(n, ns, no, confidence, problem);
         },
-        "GCRANSAC::getIterationNumber for sample sizes {2,2} (test hook).");
+        "GCRANSAC::getIterationNumber for sample sizes {2,2} (problem 0) or {3} (test hook).", py::arg("n_scale_inliers"),
+        py::arg("n_orient_inliers"), py::arg("ns"), py::arg("no"), py::arg("confidence"), py::arg("problem") = 0);
 }

@@ -17,9 +17,11 @@ LIB_PATH = os.environ.get("GCR_B200_LIB", os.path.join(PKG_DIR, "libgcr_b200.so"
 FLAG_SAMPLE_VALID, FLAG_SOLVED, FLAG_MODEL_VALID, FLAG_EXACT = 1, 2, 4, 8
 RUN_EMIT_MASKS, RUN_SAMPLES_ON_DEVICE, RUN_KEEP_PER_HYP, RUN_ALL_EXACT, RUN_EXCHANGE = 1, 2, 4, 8, 16
 IPC_HANDLE_BYTES = 64
+PROBLEM_HYBRID, PROBLEM_SCALE_ONLY, PROBLEM_SCALE_ONLY_ORIGINAL = 0, 1, 2
+SCORE_TRUNCATED_SQ, SCORE_STRICT = 1, 2
 
 EXPORTS = [
-    "gcr_create", "gcr_destroy", "gcr_last_error", "gcr_set_stream", "gcr_set_features", "gcr_get_features", "gcr_run",
+    "gcr_create", "gcr_destroy", "gcr_last_error", "gcr_set_stream", "gcr_set_problem", "gcr_set_features", "gcr_get_features", "gcr_run",
     "gcr_best",
     "gcr_fetch", "gcr_score_model", "gcr_score_models", "gcr_debug_eval", "gcr_version", "gcr_peer_export",
     "gcr_peer_attach", "gcr_peer_buffer", "gcr_peer_attach_ptrs", "gcr_peer_detach",
@@ -59,6 +61,7 @@ def load_library() -> C.CDLL:
     lib.gcr_last_error.argtypes = [vp]
     lib.gcr_last_error.restype = C.c_char_p
     lib.gcr_set_stream.argtypes = [vp, vp]
+    lib.gcr_set_problem.argtypes = [vp, C.c_int]
     lib.gcr_set_features.argtypes = [vp, vp, i64, vp, i64, C.c_int]
     lib.gcr_get_features.argtypes = [vp, vp, vp]
     lib.gcr_run.argtypes = [vp, i64, u64, u64, vp, C.POINTER(C.c_double), u32, vp, C.POINTER(GcrResult)]
@@ -116,15 +119,23 @@ class Engine:
     def set_stream(self, cuda_stream: int):
         self._check(self.lib.gcr_set_stream(self.h, C.c_void_p(cuda_stream)))
 
-    def set_features(self, scale: np.ndarray, orient: np.ndarray):
-        """Host float64 [N,3] arrays (copied to the device inside the call)."""
+    def set_problem(self, problem: int):
+        """PROBLEM_HYBRID (default), PROBLEM_SCALE_ONLY or PROBLEM_SCALE_ONLY_ORIGINAL; call before set_features."""
+        self._check(self.lib.gcr_set_problem(self.h, problem))
+        self.ns = self.no = 0
+
+    def set_features(self, scale: np.ndarray, orient: np.ndarray = None):
+        """Host float64 [N,3] arrays (copied to the device inside the call); orient=None for scale-only problems."""
         scale = np.ascontiguousarray(scale, np.float64)
+        if orient is None:
+            orient = np.zeros((0, 3))
         orient = np.ascontiguousarray(orient, np.float64)
         if scale.ndim != 2 or orient.ndim != 2 or scale.shape[1] != 3 or orient.shape[1] != 3:
             raise ValueError("features must be [N,3] arrays")
         self._keep = (scale, orient)
         self.ns, self.no = len(scale), len(orient)
-        self._check(self.lib.gcr_set_features(self.h, scale.ctypes.data, self.ns, orient.ctypes.data, self.no, 0))
+        self._check(self.lib.gcr_set_features(self.h, scale.ctypes.data, self.ns, orient.ctypes.data if self.no else None,
+                                              self.no, 0))
 
     def set_features_device(self, scale_ptr: int, ns: int, orient_ptr: int, no: int):
         """Device pointers to float64 [N,3] row-major arrays (zero-copy; caller keeps them alive)."""
@@ -199,7 +210,7 @@ class Engine:
                                              n_inl.ctypes.data, sm.ctypes.data, om.ctypes.data))
         return score.value, n_inl, unpack_mask(sm, self.ns), unpack_mask(om, self.no)
 
-    def score_models(self, models, thr, truncated_sq=False, masks=False):
+    def score_models(self, models, thr, truncated_sq=False, masks=False, strict=False):
         """Batched exact scoring of caller-supplied models f64[n,4] (n <= 1024)."""
         models = np.ascontiguousarray(models, np.float64).reshape(-1, 4)
         thr = np.ascontiguousarray(thr, np.float64)
@@ -208,7 +219,7 @@ class Engine:
         score = np.zeros(n)
         n_inl = np.zeros((n, 2), np.uint32)
         words = np.zeros((n, W), np.uint32) if masks else None
-        self._check(self.lib.gcr_score_models(self.h, models.ctypes.data, n, thr.ctypes.data, 1 if truncated_sq else 0,
+        self._check(self.lib.gcr_score_models(self.h, models.ctypes.data, n, thr.ctypes.data, (1 if truncated_sq else 0) | (2 if strict else 0),
                                               score.ctypes.data, n_inl.ctypes.data, words.ctypes.data if masks else None))
         return score, n_inl, words
 

@@ -120,6 +120,19 @@ def draw_samples(n_hyp: int, n_scale: int, n_orient: int, seed: int) -> np.ndarr
     return out
 
 
+def draw_samples_scale3(n_hyp: int, n_scale: int, seed: int) -> np.ndarray:
+    """Seeded ordered triples without replacement for the scale-only estimators: int32 [H,4] = (s0, s1, s2, -1)."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    a = rng.integers(0, n_scale, n_hyp)
+    b = rng.integers(0, n_scale - 1, n_hyp)
+    b += b >= a
+    c = rng.integers(0, n_scale - 2, n_hyp)
+    lo, hi = np.minimum(a, b), np.maximum(a, b)
+    c += c >= lo
+    c += c >= hi
+    return np.column_stack([a, b, c, np.full(n_hyp, -1)]).astype(np.int32)
+
+
 # The named BASELINE.json configurations (SURVEY.md 8): sizes, inlier ratio, scene seed.
 CONFIGS = {
     "C1": dict(n_scale=2000, n_orient=500, inlier_ratio=0.30, seed=1234, n_hyp=5000),

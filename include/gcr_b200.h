@@ -90,6 +90,20 @@ int gcr_create(int device, gcr_handle* out);
 int gcr_destroy(gcr_handle h);
 const char* gcr_last_error(gcr_handle h);
 
+/* Which of the reference's three estimators the engine runs (default: hybrid).  Call before gcr_set_features.
+ *   GCR_PROBLEM_HYBRID               findRectifyingHomographySIFT: 2 scale + 2 orientation samples (two_sift.hpp)
+ *   GCR_PROBLEM_SCALE_ONLY           findRectifyingHomographyScaleOnly: 3 scale samples, rows [x, y, s^(1/3)] = 1,
+ *                                    residual |log(alpha^3 s w^-3)| (three_sift.hpp:145-193,293-317)
+ *   GCR_PROBLEM_SCALE_ONLY_ORIGINAL  findRectifyingHomographyScaleOnlyOriginal: rows [x, y, -s^(-1/3)] = -1, residual
+ *                                    |log(s w^-3 / alpha^3)| (three_sift_original.hpp)
+ * Scale-only problems: gcr_set_features(h, scale, Ns >= 3, NULL, 0, .), samples are int32[H,4] = (s0, s1, s2, -1), thr[1]
+ * is ignored, models are (h7, h8, alpha, 0), every solved model is valid, a score needs >= 3 inliers, masks have
+ * ceil(Ns/32) words. */
+#define GCR_PROBLEM_HYBRID 0
+#define GCR_PROBLEM_SCALE_ONLY 1
+#define GCR_PROBLEM_SCALE_ONLY_ORIGINAL 2
+int gcr_set_problem(gcr_handle h, int problem);
+
 /* Use `cuda_stream` (a cudaStream_t) for all subsequent work; NULL restores the engine's own stream. */
 int gcr_set_stream(gcr_handle h, void* cuda_stream);
 
@@ -159,6 +173,7 @@ int gcr_score_model(gcr_handle h, const double model[4], const double thr[2], do
  * Host outputs, any may be NULL: score f64[n], n_inl u32[n,2] (after the zero-reset rule),
  * mask_words u32[n, ceil(Ns/32)+ceil(No/32)].  Synchronises. */
 #define GCR_SCORE_TRUNCATED_SQ 1u
+#define GCR_SCORE_STRICT 2u /* r^2 < t^2 instead of <=: the one-class relabelling by graph cut over an empty graph (GCRANSAC.h:759-870) */
 int gcr_score_models(gcr_handle h, const double* models, int64_t n, const double thr[2], uint32_t flags, double* score,
                      uint32_t* n_inl, uint32_t* mask_words);
 

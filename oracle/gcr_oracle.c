@@ -527,3 +527,147 @@ void gcr_o_sample_philox(uint64_t seed, uint64_t first_hyp, long H, long ns, lon
         draw_pair(c[2], c[3], (uint32_t)no, &samples[4 * h + 2], &samples[4 * h + 3]);
     }
 }
+
+/* ================================================================ scale-only estimators
+ * findRectifyingHomographyScaleOnly / ...Original: one feature class, minimal sample of 3 scale features.
+ * `original` != 0 selects estimators/solver_rectifying_homography_three_sift_original.hpp, whose rows and
+ * residual differ from three_sift.hpp as cited below.  Model = (h7, h8, alpha, 0). */
+
+/* three_sift.hpp:111-143 areAllPointsCollinear for a 3-sample + :40-43 isValidSample (= !collinear).  The
+ * collinearity test is the SIGNED one of math_utils.hpp:138-155 (S7). */
+int gcr_o_is_valid_sample_scale3(const double* s0, const double* s1, const double* s2)
+{
+    return gcr_o_are_collinear(s0[0], s0[1], s1[0], s1[1], s2[0], s2[1], 1.0) ? 0 : 1;
+}
+
+/* three_sift.hpp:145-193 estimateMinimalModel: rows [x, y, s^(1/3), 1] through gaussElimination<3>;
+ * three_sift_original.hpp:170-173: rows [x, y, -s^(-1/3), -1].  hasNaN reject, alpha < 1e-9 reject. */
+int gcr_o_estimate_minimal_scale3(const double* s0, const double* s1, const double* s2, int original, double model[4])
+{
+    const double* f[3] = {s0, s1, s2};
+    double m[3][4], x[3];
+    for (int i = 0; i < 3; i++)
+    {
+        m[i][0] = f[i][0];
+        m[i][1] = f[i][1];
+        m[i][2] = original ? -pow(f[i][2], -1.0 / 3.0) : pow(f[i][2], 1.0 / 3.0);
+        m[i][3] = original ? -1.0 : 1.0;
+    }
+    gcr_o_gauss3(m, x);
+    if (isnan(x[0]) || isnan(x[1]) || isnan(x[2])) return 0;
+    if (x[2] < 1e-9) return 0;
+    model[0] = x[0];
+    model[1] = x[1];
+    model[2] = x[2];
+    model[3] = 0.0;
+    return 1;
+}
+
+/* three_sift.hpp:293-317 (== the hybrid scale residual) / three_sift_original.hpp:293-317 */
+double gcr_o_scale_residual_variant(double x, double y, double s, const double model[4], int original)
+{
+    if (!original) return gcr_o_scale_residual(x, y, s, model);
+    const double rectified = s * pow(-model[0] * x - model[1] * y + 1.0, -3.0);
+    if (rectified < 1e-9) return DBL_MAX;
+    const double alpha_cube = model[2] * model[2] * model[2];
+    return fabs(log(rectified / alpha_cube));
+}
+
+/* MSAC for one class (MSAC_scoring_function.hpp:53-130 with sampleSize() = {3}).  n_inl after the zero-reset. */
+double gcr_o_score_scale(const double* scale, long ns, const double model[4], double thr, int original,
+                         uint32_t* n_inl, uint32_t* smask)
+{
+    const double tsq = (2.25 * thr) * thr;
+    uint64_t cnt = 0;
+    double val = 0.0;
+    if (smask) memset(smask, 0, sizeof(uint32_t) * (size_t)((ns + 31) / 32));
+    for (long i = 0; i < ns; i++)
+    {
+        const double r = gcr_o_scale_residual_variant(scale[3 * i], scale[3 * i + 1], scale[3 * i + 2], model, original);
+        const double r2 = r * r;
+        if (r2 <= tsq)
+        {
+            cnt++;
+            val += -r2;
+            if (smask) smask[i >> 5] |= 1u << (i & 31);
+        }
+    }
+    if (cnt < 3)
+    {
+        *n_inl = 0;
+        return 0.0;
+    }
+    *n_inl = (uint32_t)cnt;
+    /* score.hpp:52-58 reset_value: sum <- sum - old + new with sum == old == val */
+    const double msac = val / tsq + (double)cnt;
+    double sum = val;
+    sum -= val;
+    sum += msac;
+    return sum;
+}
+
+/* Hypothesis stage for replayed 3-samples: samples int32[H,4] = (s0, s1, s2, ignored).  Outputs as gcr_o_replay with
+ * n_inl[h] = (count, 0) and masks of ceil(ns/32) words; every solved model is valid (solver_engine.h:80-90). */
+int gcr_o_replay_scale(const double* scale, long ns, const int32_t* samples, long H, double thr, int original,
+                       uint8_t* flags, double* models, double* score, uint32_t* n_inl, uint32_t* masks, int nthreads)
+{
+    const long ws = (ns + 31) / 32;
+    int used = 1;
+#ifdef _OPENMP
+    if (nthreads > 0) omp_set_num_threads(nthreads);
+    used = nthreads > 0 ? nthreads : omp_get_max_threads();
+#pragma omp parallel for schedule(dynamic, 16)
+#endif
+    for (long h = 0; h < H; h++)
+    {
+        const double* s0 = scale + 3 * (long)samples[4 * h + 0];
+        const double* s1 = scale + 3 * (long)samples[4 * h + 1];
+        const double* s2 = scale + 3 * (long)samples[4 * h + 2];
+        uint8_t f = 0;
+        double m[4] = {0, 0, 0, 0}, val = 0.0;
+        uint32_t cnt = 0;
+        uint32_t* sm = masks ? masks + h * ws : NULL;
+        if (masks) memset(masks + h * ws, 0, sizeof(uint32_t) * (size_t)ws);
+        if (gcr_o_is_valid_sample_scale3(s0, s1, s2))
+        {
+            f |= GCR_O_SAMPLE_VALID;
+            if (gcr_o_estimate_minimal_scale3(s0, s1, s2, original, m))
+            {
+                f |= GCR_O_SOLVED | GCR_O_MODEL_VALID;
+                val = gcr_o_score_scale(scale, ns, m, thr, original, &cnt, sm);
+            }
+            else
+            {
+                m[0] = m[1] = m[2] = m[3] = 0.0;
+            }
+        }
+        flags[h] = f;
+        for (int k = 0; k < 4; k++) models[4 * h + k] = m[k];
+        score[h] = val;
+        n_inl[2 * h] = cnt;
+        n_inl[2 * h + 1] = 0;
+    }
+    return used;
+}
+
+/* CPU twin of the device sampler for scale-only problems: ordered triple without replacement from Philox words
+ * 0..2 (pair as draw_pair, third index uniform over the n-2 remaining values, mapped around the two taken). */
+void gcr_o_sample_philox_scale3(uint64_t seed, uint64_t first_hyp, long H, long ns, int32_t* samples)
+{
+    for (long h = 0; h < H; h++)
+    {
+        const uint64_t g = first_hyp + (uint64_t)h;
+        uint32_t c[4] = {(uint32_t)g, (uint32_t)(g >> 32), 0x47435231u, 0u};
+        philox4x32_10(c, (uint32_t)seed, (uint32_t)(seed >> 32));
+        int32_t a, b;
+        draw_pair(c[0], c[1], (uint32_t)ns, &a, &b);
+        int32_t t = (int32_t)(((uint64_t)c[2] * (uint32_t)(ns - 2)) >> 32);
+        const int32_t lo = a < b ? a : b, hi = a < b ? b : a;
+        if (t >= lo) t++;
+        if (t >= hi) t++;
+        samples[4 * h + 0] = a;
+        samples[4 * h + 1] = b;
+        samples[4 * h + 2] = t;
+        samples[4 * h + 3] = -1;
+    }
+}

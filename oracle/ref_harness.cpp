@@ -33,6 +33,72 @@ std::unique_ptr<const cv::Mat> make_mat(const double* src, long n)
 }
 } // namespace
 
+namespace
+{
+constexpr uint8_t kRefSampleValid = 1, kRefSolved = 2, kRefModelValid = 4;
+
+// hypothesis stage of a one-class estimator (three_sift / three_sift_original), see gcr_ref_replay_scale
+template <class Est>
+int replay_scale(const double* scale, long ns, const int32_t* samples, long H, double thr, uint8_t* flags, double* models,
+                 double* score, uint32_t* n_inl, uint32_t* masks, int nthreads)
+{
+    using Sc = gcransac::MSACScoringFunction<Est>;
+    typename Est::DataType data{make_mat(scale, ns)};
+    const Est estimator;
+    const Sc scoring;
+    gcransac::utils::Settings settings(1);
+    settings.threshold(0) = thr;
+    const typename Est::ResidualType truncated = 1.5 * settings.threshold;
+    const long ws = (ns + 31) / 32;
+    int used = 1;
+#ifdef _OPENMP
+    if (nthreads > 0) omp_set_num_threads(nthreads);
+    used = nthreads > 0 ? nthreads : omp_get_max_threads();
+#pragma omp parallel
+#endif
+    {
+        typename Est::InlierContainerType sample{}, inl{};
+        std::vector<typename Est::Model> found;
+#ifdef _OPENMP
+#pragma omp for schedule(dynamic, 16)
+#endif
+        for (long h = 0; h < H; ++h)
+        {
+            uint8_t f = 0;
+            double m[4] = {0, 0, 0, 0}, val = 0.0;
+            uint32_t cnt = 0;
+            if (masks) std::memset(masks + h * ws, 0, sizeof(uint32_t) * ws);
+            sample[0] = {static_cast<size_t>(samples[4 * h]), static_cast<size_t>(samples[4 * h + 1]),
+                         static_cast<size_t>(samples[4 * h + 2])};
+            found.clear();
+            if (estimator.isValidSample(data, sample))
+            {
+                f |= kRefSampleValid;
+                if (estimator.estimateModel(data, sample, found) && !found.empty())
+                {
+                    f |= kRefSolved;
+                    auto& model = found[0];
+                    m[0] = model.h7; m[1] = model.h8; m[2] = model.alpha;
+                    const auto s = scoring.getScore(data, model, estimator, settings.threshold, inl);
+                    val = s.value();
+                    cnt = static_cast<uint32_t>(s.num_inliers_by_type(0));
+                    bool updated = false;
+                    if (estimator.isValidModel(model, data, inl, sample, truncated, updated)) f |= kRefModelValid;
+                    if (masks) for (size_t i : inl[0]) masks[h * ws + i / 32] |= 1u << (i % 32);
+                }
+            }
+            flags[h] = f;
+            for (int k = 0; k < 4; ++k) models[4 * h + k] = m[k];
+            score[h] = val;
+            n_inl[2 * h] = cnt;
+            n_inl[2 * h + 1] = 0;
+        }
+    }
+    return used;
+}
+} // namespace
+
+
 extern "C"
 {
 
@@ -192,6 +258,64 @@ int gcr_ref_fit_nonminimal(const double* scale, long ns, const double* orient, l
     model7[0] = m.x0; model7[1] = m.y0; model7[2] = m.s;
     model7[3] = m.h7; model7[4] = m.h8; model7[5] = m.alpha; model7[6] = m.phi;
     return 1;
+}
+
+// ---- scale-only estimators (gcransac_python.cpp:32-254; three_sift.hpp / three_sift_original.hpp) ----
+// Hypothesis stage of the scale-only estimators per replayed 3-sample (s0, s1, s2, ignored); outputs as gcr_ref_replay.
+int gcr_ref_replay_scale(const double* scale, long ns, const int32_t* samples, long H, double thr, int original,
+                         uint8_t* flags, double* models, double* score, uint32_t* n_inl, uint32_t* masks, int nthreads)
+{
+    if (original)
+        return replay_scale<gcransac::utils::OriginalScaleBasedRectifyingHomographyEstimator>(scale, ns, samples, H, thr, flags,
+                                                                                               models, score, n_inl, masks, nthreads);
+    return replay_scale<gcransac::utils::ScaleBasedRectifyingHomographyEstimator>(scale, ns, samples, H, thr, flags, models, score,
+                                                                                  n_inl, masks, nthreads);
+}
+
+// Non-minimal fit of the scale-only estimators from all rows given (estimateModelNonminimal -> three_sift*.hpp:195-254).
+int gcr_ref_fit_nonminimal_scale(const double* scale, long ns, int original, double* model6)
+{
+    gcransac::ScaleBasedRectifyingHomography m;
+    std::vector<gcransac::ScaleBasedRectifyingHomography> models;
+    bool ok;
+    if (original)
+    {
+        using Est = gcransac::utils::OriginalScaleBasedRectifyingHomographyEstimator;
+        Est::DataType data{make_mat(scale, ns)};
+        Est::InlierContainerType inl{};
+        for (long i = 0; i < ns; ++i) inl[0].push_back(static_cast<size_t>(i));
+        ok = Est().estimateModelNonminimal(data, inl, models);
+    }
+    else
+    {
+        using Est = gcransac::utils::ScaleBasedRectifyingHomographyEstimator;
+        Est::DataType data{make_mat(scale, ns)};
+        Est::InlierContainerType inl{};
+        for (long i = 0; i < ns; ++i) inl[0].push_back(static_cast<size_t>(i));
+        ok = Est().estimateModelNonminimal(data, inl, models);
+    }
+    if (!ok || models.empty()) return 0;
+    m = models[0];
+    model6[0] = m.x0; model6[1] = m.y0; model6[2] = m.s; model6[3] = m.h7; model6[4] = m.h8; model6[5] = m.alpha;
+    return 1;
+}
+
+// The reference's full scale-only drivers, unmodified.  model6 = (x0,y0,s,h7,h8,alpha).
+int gcr_ref_find_scale_only(const double* scale, long ns, double thr, double spatial_coherence_weight, unsigned long min_iters,
+                            unsigned long max_iters, unsigned long max_lo, int original, uint8_t* mask, double* H9, double* model6)
+{
+    std::vector<double> sv(scale, scale + 3 * ns), Hh;
+    std::vector<bool> sm;
+    gcransac::ScaleBasedRectifyingHomography model;
+    const int n = original ? findRectifyingHomographyScaleOnlyOriginal_(sv, thr, spatial_coherence_weight, min_iters, max_iters,
+                                                                        max_lo, sm, Hh, model, 0)
+                           : findRectifyingHomographyScaleOnly_(sv, thr, spatial_coherence_weight, min_iters, max_iters, max_lo,
+                                                                sm, Hh, model, 0);
+    for (long i = 0; i < ns && i < static_cast<long>(sm.size()); ++i) mask[i] = sm[i] ? 1 : 0;
+    for (size_t i = 0; i < 9 && i < Hh.size(); ++i) H9[i] = Hh[i];
+    model6[0] = model.x0; model6[1] = model.y0; model6[2] = model.s;
+    model6[3] = model.h7; model6[4] = model.h8; model6[5] = model.alpha;
+    return n;
 }
 
 // ---- known-answer probes of the helper math (the functions tests/unit_tests.cpp pins) ----

@@ -230,6 +230,67 @@ class Oracle:
                     H=Hm.reshape(3, 3), model=model, seconds=float(sec[0]))
 
 
+    # ------------------------------------------------------------------ scale-only estimators
+    def replay_scale(self, scale, samples, thr, original=False, want_masks=True, nthreads=1):
+        """Hypothesis stage of findRectifyingHomographyScaleOnly[Original] per replayed 3-sample (s0, s1, s2, ignored)."""
+        scale = np.ascontiguousarray(scale, np.float64)
+        samples = np.ascontiguousarray(samples, np.int32)
+        ns, H = len(scale), len(samples)
+        ws = (ns + 31) // 32
+        flags, models, score = np.zeros(H, np.uint8), np.zeros((H, 4)), np.zeros(H)
+        n_inl = np.zeros((H, 2), np.uint32)
+        masks = np.zeros((H, ws), np.uint32) if want_masks else None
+        f = getattr(self.lib, self.p + "replay_scale")
+        f.restype = C.c_int
+        f.argtypes = [_dp, C.c_long, _ip, C.c_long, C.c_double, C.c_int, _u8, _dp, _dp, _u32, C.c_void_p, C.c_int]
+        used = f(scale, ns, samples, H, float(thr), int(original), flags, models, score, n_inl,
+                 masks.ctypes.data if want_masks else None, nthreads)
+        return dict(flags=flags, models=models, score=score, n_inl=n_inl, masks=masks, threads=used)
+
+    def sample_philox_scale3(self, seed, first_hyp, H, ns):
+        assert self.kind == "port"
+        out = np.zeros((H, 4), np.int32)
+        f = self.lib.gcr_o_sample_philox_scale3
+        f.restype = None
+        f.argtypes = [C.c_uint64, C.c_uint64, C.c_long, C.c_long, _ip]
+        f(seed, first_hyp, H, ns, out)
+        return out
+
+    def score_scale(self, scale, model, thr, original=False):
+        """One-class MSAC of one model (port only): value, count, bool mask."""
+        assert self.kind == "port"
+        scale = np.ascontiguousarray(scale, np.float64)
+        model = np.ascontiguousarray(model, np.float64)
+        ns = len(scale)
+        n = np.zeros(1, np.uint32)
+        sm = np.zeros((ns + 31) // 32, np.uint32)
+        f = self.lib.gcr_o_score_scale
+        f.restype = C.c_double
+        f.argtypes = [_dp, C.c_long, _dp, C.c_double, C.c_int, _u32, _u32]
+        val = f(scale, ns, model, float(thr), int(original), n, sm)
+        return float(val), int(n[0]), unpack_mask(sm, ns)
+
+    def find_scale_only(self, scale, thr, min_iters, max_iters, max_lo=50, scw=0.0, original=False):
+        """The reference's full scale-only driver (reference only)."""
+        assert self.kind == "reference"
+        scale = np.ascontiguousarray(scale, np.float64)
+        ns = len(scale)
+        sm, Hm, model = np.zeros(ns, np.uint8), np.zeros(9), np.zeros(6)
+        f = self.lib.gcr_ref_find_scale_only
+        f.restype = C.c_int
+        f.argtypes = [_dp, C.c_long, C.c_double, C.c_double, C.c_ulong, C.c_ulong, C.c_ulong, C.c_int, _u8, _dp, _dp]
+        n = f(scale, ns, thr, scw, min_iters, max_iters, max_lo, int(original), sm, Hm, model)
+        return dict(n_inliers=n, mask=sm.astype(bool), H=Hm.reshape(3, 3), model=model)
+
+    def fit_nonminimal_scale(self, scale, original=False):
+        assert self.kind == "reference"
+        scale = np.ascontiguousarray(scale, np.float64)
+        model = np.zeros(6)
+        f = self.lib.gcr_ref_fit_nonminimal_scale
+        f.restype = C.c_int
+        f.argtypes = [_dp, C.c_long, C.c_int, _dp]
+        return model if f(scale, len(scale), int(original), model) else None
+
     def fit_nonminimal(self, scale, orient):
         """estimateModelNonminimal on all rows given (reference only); None when the fit fails."""
         assert self.kind == "reference"
