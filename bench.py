@@ -310,6 +310,95 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def run_batched(args):
+    """C4: a batch of independent images per GPU (BASELINE.json configs[3]): 256 images x (4000 + 1000) features, 100k
+    device-sampled hypotheses each, images/world per rank, no communication.  A step = the rank's whole image slice;
+    images are spread over `--engines` engine handles, each on its own stream, so that the low-occupancy kernels of one
+    image (sample+solve, tail) overlap the scoring kernel of another."""
+    import torch
+    import torch.distributed as dist
+    import gcr_capi
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    c = gs.CONFIGS[args.config]
+    n_img = c["n_images"] // 8 if args.images is None else args.images  # per GPU: the 256-image batch is cut for 8 GPUs
+    n_hyp, nfeat = c["n_hyp"], c["n_scale"] + c["n_orient"]
+    scenes = [gs.config_scene(args.config, image=rank * n_img + i) for i in range(n_img)]
+    d_scale = [torch.from_numpy(sc.scale).cuda() for sc in scenes]
+    d_orient = [torch.from_numpy(sc.orient).cuda() for sc in scenes]
+    K = max(1, min(args.engines, n_img))
+    main = torch.cuda.Stream()
+    streams = [torch.cuda.Stream() for _ in range(K)]
+    engines = [gcr_capi.Engine(local) for _ in range(K)]
+    for e, st in zip(engines, streams):
+        e.set_stream(st.cuda_stream)
+    records = torch.zeros(n_img, 8, dtype=torch.float64, device="cuda")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+    def step():
+        start = torch.cuda.Event()
+        start.record(main)
+        for st in streams:
+            st.wait_event(start)
+        for i in range(n_img):
+            e = engines[i % K]
+            e.set_features_device(d_scale[i].data_ptr(), c["n_scale"], d_orient[i].data_ptr(), c["n_orient"])
+            e.run(n_hyp, scenes[i].thr, seed=1000 + rank * n_img + i, record_ptr=records[i].data_ptr(), sync=False)
+        for st in streams:
+            done = torch.cuda.Event()
+            done.record(st)
+            main.wait_event(done)
+
+    with torch.cuda.stream(main):
+        for _ in range(max(args.warmup, 3)):
+            flush.zero_()
+            step()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        sampler = ClockSampler(local)
+        sampler.start()
+        sampler.active = True
+        evs = []
+        for _ in range(args.steps):
+            flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(main)
+            step()
+            e1.record(main)
+            evs.append((e0, e1))
+        torch.cuda.synchronize()
+        sampler.active = False
+        sampler.stop_flag = True
+    total_ms = sum(a.elapsed_time(b) for a, b in evs)
+    t = torch.tensor([total_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.barrier()
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_per_step = float(t.item()) / args.steps
+    value = world * n_img * n_hyp * nfeat / (ms_per_step * 1e-3)
+    recs = np.frombuffer(records.cpu().numpy().tobytes(), dtype=gcr_capi.RECORD_DTYPE)
+    err = [float(np.hypot(*(r["model"][:2] - sc.model[:2])) / np.hypot(*sc.model[:2])) for r, sc in zip(recs, scenes)]
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+                "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32 (+f64 solver, guard-band and winner re-scoring)", "data": "synthetic",
+                "config": {"workload": f"{args.config}: {n_img} images per GPU x ({c['n_scale']} scale + {c['n_orient']} orientation features), "
+                                       f"{n_hyp} device-sampled (Philox) hypotheses per image, {K} engines/streams in flight",
+                           "l2": "flushed between timed steps (256 MiB write)", "images_with_model": int((recs["index"] >= 0).sum()),
+                           "median_vanishing_line_error": float(np.median(err))},
+                "clocks": sampler.summary(), "e2e": None, "gpu_launches": 4 * n_img * args.steps, "roofline": None, "cpu_baseline": None,
+                "images_per_s": world * n_img / (ms_per_step * 1e-3)}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -318,8 +407,12 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="C2", choices=sorted(gs.CONFIGS))
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"], help="N>1: fused peer-memory exchange or NCCL all_gather")
+    ap.add_argument("--engines", type=int, default=4, help="C4: engine handles / streams in flight per GPU")
+    ap.add_argument("--images", type=int, default=None, help="C4: images per GPU (default 256 / 8)")
     args = ap.parse_args()
-    if args.impl == "reference":
+    if args.impl == "ours" and "n_images" in gs.CONFIGS[args.config]:
+        run_batched(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_ours(args)
