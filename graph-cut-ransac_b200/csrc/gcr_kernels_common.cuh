@@ -21,6 +21,15 @@ constexpr int kStages = 6;
 #ifndef GCR_MINB
 #define GCR_MINB 8
 #endif
+// Packed f32x2 arithmetic (FFMA2 / FMUL2: two IEEE operations per issue slot) in the FP32 tiles of the scoring kernel:
+// 0 none, 1 scale class, 2 + the six leading FMAs of an orientation evaluation, 3 + the rest of the orientation evaluation.
+// Interleaved A/B on one B200 (tools/compare_variants.py, C3 kernel): 9.94 / 9.60 / 9.80 / 9.75 ms for levels 0 / 1 / 2 / 3:
+// the pair forms save issue slots but hold the FMA pipe for two cycles, so only the scale class (FMA-light) gains.
+#ifndef GCR_F2
+#define GCR_F2 1
+#endif
+template <int CLS>
+constexpr bool kPacked = CLS == 0 ? (GCR_F2 >= 1) : (GCR_F2 >= 2);
 constexpr int kScoreThreads = GCR_THREADS;
 constexpr int kHB = GCR_HB; // hypotheses per thread in the fast kernel
 constexpr int kTileHyps = kScoreThreads * kHB;

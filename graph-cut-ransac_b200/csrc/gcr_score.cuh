@@ -36,23 +36,32 @@ struct Verdict
 
 // rectified scale = v^-3, residual r = 3 ln2 |A - lg2 v|  (S4, two_sift.hpp:621-645).  v <= 0 (beyond the
 // horizon: DBL_MAX residual in the reference) gives NaN / inf and fails both tests.
-__device__ __forceinline__ Verdict scale_verdict(float v, const HypRegs& H, float& d)
+__device__ __forceinline__ Verdict scale_verdict_d(float d, const HypRegs& H)
 {
-    d = H.A - lg2_approx(v);
     Verdict e;
     e.in = fabsf(d) <= H.Tin;
     e.unc = (fabsf(d) <= H.Tout) && !e.in;
     return e;
 }
+__device__ __forceinline__ Verdict scale_verdict(float v, const HypRegs& H, float& d)
+{
+    d = H.A - lg2_approx(v);
+    return scale_verdict_d(d, H);
+}
 
 // (denom, numer) of rectifiedAngle (model.h:156-165) rotated by -phi; the residual (S5, two_sift.hpp:647-665)
 // is the angle of that vector to the nearest multiple of pi/2 = atan(min/max) of its absolute components;
 // r^2 = z p(z), z = tan^2, by an even polynomial.
+__device__ __forceinline__ Verdict orient_verdict_cs(float c1, float s1, const HypRegs& H, const Thresholds& T, float& z, float& p);
 __device__ __forceinline__ Verdict orient_verdict(float n, float d, const HypRegs& H, const Thresholds& T, float& z,
                                                   float& p)
 {
     const float c1 = fmaf(n, H.sphi, d * H.cphi);
     const float s1 = fmaf(n, H.cphi, -(d * H.sphi));
+    return orient_verdict_cs(c1, s1, H, T, z, p);
+}
+__device__ __forceinline__ Verdict orient_verdict_cs(float c1, float s1, const HypRegs& H, const Thresholds& T, float& z, float& p)
+{
     const float a1 = fabsf(c1), a2 = fabsf(s1);
     // the 1e-30 floor keeps an exact 0/0 (numer = denom = 0, where the reference evaluates atan2 of round-off)
     // finite: t = 0 with an enormous band -> worklist
@@ -150,12 +159,81 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
 #pragma unroll
         for (int j = 0; j < kHB; j++)
         {
+            // FP32 tiles, packed form (GCR_F2): the FMAs that do not depend on a predicate are issued as f32x2 pairs
+            // (FFMA2 / FMUL2: two IEEE operations per issue slot, bit-identical to the scalar form)
+            float pk0[G], pk1[G];
+            Verdict pv[G];
+            if constexpr (!PRECISE && kPacked<CLS>)
+            {
+#pragma unroll
+                for (int e = 0; e < G; e += 2)
+                {
+                    const float2 a2 = make_float2(fa[e], fa[e + 1]), b2 = make_float2(fb[e], fb[e + 1]), c2 = make_float2(fc[e], fc[e + 1]);
+                    if constexpr (CLS == 0)
+                    {
+                        const float2 v = __ffma2_rn(make_float2(H[j].nh8, H[j].nh8), b2,
+                                                    __ffma2_rn(make_float2(H[j].nh7, H[j].nh7), a2, c2));
+                        const float2 L = make_float2(lg2_approx(v.x), lg2_approx(v.y));
+                        const float2 d = __ffma2_rn(L, make_float2(-1.f, -1.f), make_float2(H[j].A, H[j].A)); // A - L, one rounding
+                        pk0[e] = d.x; pk0[e + 1] = d.y;
+                        pk1[e] = pk1[e + 1] = 0.f;
+                        pv[e] = scale_verdict_d(d.x, H[j]);
+                        pv[e + 1] = scale_verdict_d(d.y, H[j]);
+                    }
+                    else
+                    {
+                        // same operations, in the same order, as orient_verdict / orient_verdict_cs, two features per instruction
+                        const float2 n = __ffma2_rn(a2, make_float2(H[j].nh7, H[j].nh7), b2);
+                        const float2 d = __ffma2_rn(a2, make_float2(-H[j].nh8, -H[j].nh8), c2);
+                        const float2 c1 = __ffma2_rn(n, make_float2(H[j].sphi, H[j].sphi), __fmul2_rn(d, make_float2(H[j].cphi, H[j].cphi)));
+                        const float2 s1 = __ffma2_rn(n, make_float2(H[j].cphi, H[j].cphi), __fmul2_rn(d, make_float2(-H[j].sphi, -H[j].sphi)));
+                        if constexpr (GCR_F2 >= 3)
+                        {
+                            const float a1x = fabsf(c1.x), a2x = fabsf(s1.x), a1y = fabsf(c1.y), a2y = fabsf(s1.y);
+                            const float2 mn = make_float2(fminf(a1x, a2x), fminf(a1y, a2y));
+                            const float2 ri = make_float2(rcp_approx(fmaxf(fmaxf(a1x, a2x), 1e-30f)), rcp_approx(fmaxf(fmaxf(a1y, a2y), 1e-30f)));
+                            const float2 t = __fmul2_rn(mn, ri);
+                            const float2 lo = __ffma2_rn(make_float2(-H[j].dpr, -H[j].dpr), ri, make_float2(T.t_lo0, T.t_lo0));
+                            const float2 hi = __ffma2_rn(make_float2(H[j].dpr, H[j].dpr), ri, make_float2(T.t_hi0, T.t_hi0));
+                            const float2 z = __fmul2_rn(t, t);
+                            float2 pl;
+                            if (T.poly_deg == 2)
+                                pl = __ffma2_rn(z, __ffma2_rn(z, make_float2(T.pc[2], T.pc[2]), make_float2(T.pc[1], T.pc[1])),
+                                                make_float2(T.pc[0], T.pc[0]));
+                            else
+                                pl = __ffma2_rn(z, __ffma2_rn(z, __ffma2_rn(z, make_float2(T.pc[3], T.pc[3]), make_float2(T.pc[2], T.pc[2])),
+                                                              make_float2(T.pc[1], T.pc[1])),
+                                                make_float2(T.pc[0], T.pc[0]));
+                            pk0[e] = z.x; pk0[e + 1] = z.y;
+                            pk1[e] = pl.x; pk1[e + 1] = pl.y;
+                            pv[e].in = t.x <= lo.x;
+                            pv[e].unc = (t.x <= hi.x) && !pv[e].in;
+                            pv[e + 1].in = t.y <= lo.y;
+                            pv[e + 1].unc = (t.y <= hi.y) && !pv[e + 1].in;
+                        }
+                        else
+                        {
+                            // the rest of the evaluation stays scalar (see GCR_F2 in gcr_kernels_common.cuh)
+                            pv[e] = orient_verdict_cs(c1.x, s1.x, H[j], T, pk0[e], pk1[e]);
+                            pv[e + 1] = orient_verdict_cs(c1.y, s1.y, H[j], T, pk0[e + 1], pk1[e + 1]);
+                        }
+                    }
+                }
+            }
 #pragma unroll
             for (int e = 0; e < G; e++)
             {
                 float x0, x1;
-                const Verdict r = PRECISE ? verdict(j, 0.f, 0.f, 0.f, da[e], db[e], dc[e], x0, x1)
-                                          : verdict(j, fa[e], fb[e], fc[e], 0.0, 0.0, 0.0, x0, x1);
+                Verdict r;
+                if constexpr (!PRECISE && kPacked<CLS>)
+                {
+                    x0 = pk0[e];
+                    x1 = pk1[e];
+                    r = pv[e];
+                }
+                else
+                    r = PRECISE ? verdict(j, 0.f, 0.f, 0.f, da[e], db[e], dc[e], x0, x1)
+                                : verdict(j, fa[e], fb[e], fc[e], 0.0, 0.0, 0.0, x0, x1);
                 if (r.in)
                 {
                     acc[j] = CLS == 0 ? fmaf(x0, x0, acc[j]) : fmaf(x0, x1, acc[j]);
