@@ -28,6 +28,14 @@ constexpr int kStages = 6;
 #ifndef GCR_F2
 #define GCR_F2 1
 #endif
+#ifndef GCR_VOTE
+#define GCR_VOTE 4
+#endif
+#ifndef GCR_UNROLL
+#define GCR_UNROLL (GCR_VOTE < 4 ? GCR_VOTE : 4)
+#endif
+constexpr int kScoreUnroll = GCR_UNROLL;
+constexpr int kVoteGroups = GCR_VOTE; // groups of 4 (FP32) / 2 (precise) features between two warp votes of the band check
 template <int CLS>
 constexpr bool kPacked = CLS == 0 ? (GCR_F2 >= 1) : (GCR_F2 >= 2);
 constexpr int kScoreThreads = GCR_THREADS;

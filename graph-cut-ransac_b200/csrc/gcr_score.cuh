@@ -107,7 +107,10 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
         acc[j] = cntf[j] = 0.f;
         mword[j] = 0u;
     }
-#pragma unroll 2
+    bool unc_j[kHB]; // hypothesis j had an evaluation of the last kVoteGroups groups inside the band (per thread)
+#pragma unroll
+    for (int j = 0; j < kHB; j++) unc_j[j] = false;
+#pragma unroll kScoreUnroll
     for (int g = 0; g < NF / G; g++)
     {
         float fa[G], fb[G], fc[G];   // FP32 planes
@@ -155,7 +158,6 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
                 return orient_verdict(n, d, H[j], T, x0, x1);
             }
         };
-        bool any_unc = false;
 #pragma unroll
         for (int j = 0; j < kHB; j++)
         {
@@ -240,33 +242,43 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
                     cntf[j] += 1.0f;
                     if (MASKS) mword[j] |= 1u << ((g * G + e) & 31);
                 }
-                any_unc |= r.unc;
+                unc_j[j] |= r.unc;
             }
         }
-        if (__any_sync(0xffffffffu, any_unc))
+        // the band check is voted once per kVoteGroups groups (the vote + branch cost ~5 issue slots)
+        if (g % kVoteGroups == kVoteGroups - 1)
         {
-            // rare: re-derive which pairs of this group are inside the band (same instructions, same inputs,
-            // re-read from shared memory so that this path stays a small rolled loop out of the hot stream)
+            bool any_unc = false;
 #pragma unroll
-            for (int j = 0; j < kHB; j++)
+            for (int j = 0; j < kHB; j++) any_unc |= unc_j[j];
+            if (__any_sync(0xffffffffu, any_unc))
             {
-#pragma unroll 1
-                for (int e = 0; e < G; e++)
+                // rare: re-derive which pairs of these groups are inside the band (same instructions, same inputs,
+                // re-read from shared memory so that this path stays a small rolled loop out of the hot stream)
+                const int f0 = (g - (kVoteGroups - 1)) * G;
+#pragma unroll
+                for (int j = 0; j < kHB; j++)
                 {
-                    float x0, x1;
-                    Verdict r;
-                    if constexpr (PRECISE)
+                    if (!unc_j[j]) continue; // usually one hypothesis of one lane
+#pragma unroll 1
+                    for (int f = f0; f < f0 + kVoteGroups * G; f++)
                     {
-                        const double* sd = reinterpret_cast<const double*>(stage);
-                        r = verdict(j, 0.f, 0.f, 0.f, sd[g * G + e], sd[NF + g * G + e], sd[2 * NF + g * G + e], x0, x1);
+                        float x0, x1;
+                        Verdict r;
+                        if constexpr (PRECISE)
+                        {
+                            const double* sd = reinterpret_cast<const double*>(stage);
+                            r = verdict(j, 0.f, 0.f, 0.f, sd[f], sd[NF + f], sd[2 * NF + f], x0, x1);
+                        }
+                        else
+                            r = verdict(j, stage[f], stage[NF + f], stage[2 * NF + f], 0.0, 0.0, 0.0, x0, x1);
+                        if (r.unc && H[j].active)
+                            worklist_push(B, H[j].hyp, (CLS ? 0x80000000u : 0u) | static_cast<unsigned>(fbase + f));
                     }
-                    else
-                        r = verdict(j, stage[g * G + e], stage[NF + g * G + e], stage[2 * NF + g * G + e], 0.0, 0.0, 0.0,
-                                    x0, x1);
-                    if (r.unc && H[j].active)
-                        worklist_push(B, H[j].hyp, (CLS ? 0x80000000u : 0u) | static_cast<unsigned>(fbase + g * G + e));
                 }
             }
+#pragma unroll
+            for (int j = 0; j < kHB; j++) unc_j[j] = false;
         }
         if (MASKS && ((g + 1) * G) % 32 == 0)
         {
