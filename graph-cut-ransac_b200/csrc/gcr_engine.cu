@@ -1,6 +1,7 @@
 // Host side of libgcr_b200.so: buffer management, launch sequence and the extern "C" ABI declared in
 // include/gcr_b200.h.  Compiled for sm_100a only, with -fmad=false (see gcr_exact.cuh).
 #include "gcr_kernels.cuh"
+#include "gcr_fit.cuh"
 #include "../../include/gcr_b200.h"
 
 #include <cmath>
@@ -10,6 +11,7 @@
 #include <vector>
 #include <algorithm>
 #include <new>
+#include <unordered_map>
 
 namespace
 {
@@ -39,6 +41,30 @@ struct DevBuf
     void release()
     {
         if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+// pinned host staging that only grows
+struct PinnedBuf
+{
+    unsigned char* p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t n)
+    {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        cap = 0;
+        const size_t want = n + n / 4 + 256;
+        cudaError_t e = cudaMallocHost(reinterpret_cast<void**>(&p), want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release()
+    {
+        if (p) cudaFreeHost(p);
         p = nullptr;
         cap = 0;
     }
@@ -92,6 +118,11 @@ struct gcr_engine_s
     size_t h_best_words = 0;
     DevBuf<double> d_dbg_in, d_dbg_out;
     DevBuf<Model4> d_user_models;
+
+    // non-minimal fits (gcr_fit_models)
+    DevBuf<unsigned char> d_fit_in, d_fit_out;
+    DevBuf<double> d_fit_lines, d_fit_partial;
+    PinnedBuf h_fit_in, h_fit_out;
 
     // multi-GPU winner exchange (peer memory)
     DevBuf<unsigned long long> d_xchg;
@@ -394,6 +425,8 @@ int gcr_destroy(gcr_handle h)
     if (h->h_best) cudaFreeHost(h->h_best);
     h->d_cand_model.release(); h->d_cand_score.release(); h->d_cand_qsum.release(); h->d_cand_rawcnt.release(); h->d_ctr.release();
     h->d_dbg_in.release(); h->d_dbg_out.release(); h->d_user_models.release();
+    h->d_fit_in.release(); h->d_fit_out.release(); h->d_fit_lines.release(); h->d_fit_partial.release();
+    h->h_fit_in.release(); h->h_fit_out.release();
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
     if (h->evk0) cudaEventDestroy(h->evk0);
@@ -782,6 +815,117 @@ int gcr_score_models(gcr_handle h, const double* models, int64_t n, const double
     if (n_inl) GCR_CUDA(cudaMemcpyAsync(n_inl, h->d_cand_cnt.p, 2 * sizeof(unsigned int) * n, cudaMemcpyDeviceToHost, s));
     if (mask_words) GCR_CUDA(cudaMemcpyAsync(mask_words, h->d_cand_masks.p, 4 * W * n, cudaMemcpyDeviceToHost, s));
     GCR_CUDA(cudaStreamSynchronize(s));
+    return GCR_OK;
+}
+
+int gcr_fit_models(gcr_handle h, int64_t n_fits, const uint32_t* scale_idx, const int64_t* scale_off,
+                   const uint32_t* orient_idx, const int64_t* orient_off, double* models, int32_t* ok)
+{
+    if (!h || !scale_idx || !scale_off || !models || !ok) return GCR_ERR_INVALID;
+    if (h->ns < 2) return h->fail(GCR_ERR_STATE, "gcr_fit_models before gcr_set_features");
+    const bool hybrid = h->problem == 0;
+    if (hybrid && (!orient_idx || !orient_off)) return h->fail(GCR_ERR_INVALID, "gcr_fit_models: the hybrid problem needs orientation index lists");
+    if (n_fits < 1 || n_fits > kCandCap) return h->fail(GCR_ERR_INVALID, "gcr_fit_models: 1 <= n_fits <= 1024 per call");
+    const size_t K = static_cast<size_t>(n_fits);
+    if (scale_off[0] != 0 || (hybrid && orient_off[0] != 0)) return h->fail(GCR_ERR_INVALID, "gcr_fit_models: offsets must start at 0");
+    for (size_t k = 0; k < K; ++k)
+        if (scale_off[k + 1] < scale_off[k] || (hybrid && orient_off[k + 1] < orient_off[k]) ||
+            scale_off[k + 1] - scale_off[k] > h->ns || (hybrid && orient_off[k + 1] - orient_off[k] > h->no))
+            return h->fail(GCR_ERR_INVALID, "gcr_fit_models: offsets must be non-decreasing, a list no longer than its class");
+    const size_t S = static_cast<size_t>(scale_off[K]), O = hybrid ? static_cast<size_t>(orient_off[K]) : 0;
+    for (size_t i = 0; i < S; ++i)
+        if (scale_idx[i] >= static_cast<uint32_t>(h->ns)) return h->fail(GCR_ERR_INVALID, "gcr_fit_models: scale index out of range");
+    for (size_t i = 0; i < O; ++i)
+        if (orient_idx[i] >= static_cast<uint32_t>(h->no)) return h->fail(GCR_ERR_INVALID, "gcr_fit_models: orientation index out of range");
+    GCR_CUDA(cudaSetDevice(h->device));
+
+    auto align16 = [](size_t x) { return (x + 15) & ~static_cast<size_t>(15); };
+    const size_t in_desc = 0, in_s = align16(K * sizeof(FitDesc)), in_o = align16(in_s + 4 * S), in_bytes = align16(in_o + 4 * O);
+    GCR_CUDA(h->h_fit_in.ensure(in_bytes));
+    GCR_CUDA(h->d_fit_in.ensure(in_bytes));
+    FitDesc* desc = reinterpret_cast<FitDesc*>(h->h_fit_in.p + in_desc);
+    unsigned long long units = 0, entries = 0;
+    for (size_t k = 0; k < K; ++k)
+    {
+        FitDesc& D = desc[k];
+        D.s_off = scale_off[k];
+        D.ns = static_cast<int>(scale_off[k + 1] - scale_off[k]);
+        D.o_off = hybrid ? orient_off[k] : 0;
+        D.no = hybrid ? static_cast<int>(orient_off[k + 1] - orient_off[k]) : 0;
+        // two_sift.hpp:431-447,603-609 / three_sift.hpp:203-211: fewer constraints than a minimal sample -> no model; exactly a
+        // minimal sample belongs to the minimal solver, which neither the local optimisation nor the refit presents
+        D.valid = hybrid ? ((D.ns >= 2 && D.no >= 2 && !(D.ns == 2 && D.no == 2)) ? 1 : 0) : (D.ns > 3 ? 1 : 0);
+        D.pad_ = 0;
+        const unsigned long long rows =
+            static_cast<unsigned long long>(D.ns) + (hybrid ? static_cast<unsigned long long>(D.no) * (D.no > 0 ? D.no - 1 : 0) / 2 : 0);
+        D.unit_first = static_cast<unsigned int>(units);
+        D.ent_off = static_cast<unsigned int>(entries);
+        units += std::max<unsigned long long>(1, (rows + kFitUnitRows - 1) / kFitUnitRows);
+        entries += static_cast<unsigned long long>(std::min(D.no, kPhiBins));
+        if (units > 0x7fffffffull) return h->fail(GCR_ERR_INVALID, "gcr_fit_models: too many rows");
+    }
+    std::memcpy(h->h_fit_in.p + in_s, scale_idx, 4 * S);
+    if (O) std::memcpy(h->h_fit_in.p + in_o, orient_idx, 4 * O);
+    const size_t out_models = 0, out_ok = align16(K * 32), out_nent = align16(out_ok + 4 * K), out_ent = align16(out_nent + 4 * K),
+                 out_bytes = align16(out_ent + entries * sizeof(FitEntry));
+    GCR_CUDA(h->h_fit_out.ensure(out_bytes));
+    GCR_CUDA(h->d_fit_out.ensure(out_bytes));
+    GCR_CUDA(h->d_fit_lines.ensure(3 * std::max<size_t>(O, 1)));
+    GCR_CUDA(h->d_fit_partial.ensure(static_cast<size_t>(units) * 2 * kFitGram));
+
+    cudaStream_t s = h->stream;
+    GCR_CUDA(cudaMemcpyAsync(h->d_fit_in.p, h->h_fit_in.p, in_bytes, cudaMemcpyHostToDevice, s));
+    FitBuffers F;
+    F.scale = h->scale_ptr;
+    F.orient = h->orient_ptr;
+    F.desc = reinterpret_cast<const FitDesc*>(h->d_fit_in.p + in_desc);
+    F.idx_s = reinterpret_cast<const unsigned int*>(h->d_fit_in.p + in_s);
+    F.idx_o = reinterpret_cast<const unsigned int*>(h->d_fit_in.p + in_o);
+    F.lines = h->d_fit_lines.p;
+    F.partial = h->d_fit_partial.p;
+    F.models = reinterpret_cast<double*>(h->d_fit_out.p + out_models);
+    F.ok = reinterpret_cast<int*>(h->d_fit_out.p + out_ok);
+    F.n_ent = reinterpret_cast<unsigned int*>(h->d_fit_out.p + out_nent);
+    F.ent = reinterpret_cast<FitEntry*>(h->d_fit_out.p + out_ent);
+    F.n_fits = static_cast<int>(K);
+    F.n_units = static_cast<unsigned int>(units);
+    F.n_lines = static_cast<long long>(O);
+    F.problem = h->problem;
+    if (O) k_fit_lines<<<static_cast<unsigned int>((O + kFitThreads - 1) / kFitThreads), kFitThreads, 0, s>>>(F);
+    k_fit_rows<<<F.n_units, kFitThreads, 0, s>>>(F);
+    k_fit_solve<<<static_cast<unsigned int>(K), 32, 0, s>>>(F);
+    if (hybrid) k_fit_phi<<<static_cast<unsigned int>(K), kFitThreads, 0, s>>>(F);
+    GCR_CUDA(cudaGetLastError());
+    GCR_CUDA(cudaMemcpyAsync(h->h_fit_out.p, h->d_fit_out.p, out_bytes, cudaMemcpyDeviceToHost, s));
+    GCR_CUDA(cudaStreamSynchronize(s));
+
+    const double* m = reinterpret_cast<const double*>(h->h_fit_out.p + out_models);
+    const int* okd = reinterpret_cast<const int*>(h->h_fit_out.p + out_ok);
+    const unsigned int* nent = reinterpret_cast<const unsigned int*>(h->h_fit_out.p + out_nent);
+    const FitEntry* ent = reinterpret_cast<const FitEntry*>(h->h_fit_out.p + out_ent);
+    for (size_t k = 0; k < K; ++k)
+    {
+        std::memcpy(models + 4 * k, m + 4 * k, 32);
+        ok[k] = okd[k];
+        if (!hybrid || !okd[k]) continue;
+        // findWeightedMode (two_sift.hpp:354-394): heaviest bin, the first strictly heavier one in the iteration order
+        // of an unordered_map<int, double> filled in input order; with unit weights the weight order is the count order
+        std::unordered_map<int, double> bin_weight;
+        const FitEntry* e = ent + desc[k].ent_off;
+        for (unsigned int i = 0; i < nent[k]; ++i) bin_weight[e[i].bin] += static_cast<double>(e[i].count);
+        int mode_bin = 0;
+        double heaviest = -1.0;
+        for (const auto& kv : bin_weight)
+            if (kv.second > heaviest)
+            {
+                heaviest = kv.second;
+                mode_bin = kv.first;
+            }
+        double phi = 0.0;
+        for (unsigned int i = 0; i < nent[k]; ++i)
+            if (e[i].bin == mode_bin) phi = static_cast<double>(e[i].moment) / kPhiFixedPoint / static_cast<double>(e[i].count);
+        models[4 * k + 3] = phi;
+    }
     return GCR_OK;
 }
 

@@ -165,6 +165,12 @@ static int estimateImpl(int problem, const double* scale, size_t ns, const doubl
     const size_t min_s = hybrid ? 2 : 3, min_o = hybrid ? 2 : 0; // sampleSize()
     const size_t lim_s = 7 * min_s, lim_o = 7 * min_o;            // inlierLimit(), rectifying_homography_estimator.h:45-55
     const auto t_begin = std::chrono::steady_clock::now();
+    auto lap = [t = t_begin]() mutable {
+        const auto now = std::chrono::steady_clock::now();
+        const double ms = std::chrono::duration<double, std::milli>(now - t).count();
+        t = now;
+        return ms;
+    };
     Stats st;
     if (!scale || (hybrid && !orient)) throw std::invalid_argument("null feature pointer");
     // GCRANSAC.h:222-228: fewer rows than the minimal sample of a class
@@ -190,6 +196,7 @@ static int estimateImpl(int problem, const double* scale, size_t ns, const doubl
 
     // ---- hypothesise / verify: while (iter < min_iters || iter < min(max_iteration, max_iters)), GCRANSAC.h:286-287,
     //      in device batches; every drawn sample is one iteration (S13)
+    st.setup_ms = lap();
     Best best;
     best.words.assign(W, 0u);
     size_t done = 0;
@@ -233,6 +240,7 @@ static int estimateImpl(int problem, const double* scale, size_t ns, const doubl
     }
     st.iteration_number = static_cast<int64_t>(done);
     st.best_raw_score = best.score;
+    st.loop_ms = lap();
 
     scale_inliers.assign(ns, false);
     orientation_inliers.assign(no, false);
@@ -248,27 +256,40 @@ static int estimateImpl(int problem, const double* scale, size_t ns, const doubl
     if (!best.have || (best.n_inl[0] <= min_s && best.n_inl[1] <= min_o)) return finish(0);
 
     // ---- local optimisation on the selected model (graphCutLocalOptimization for two classes, GCRANSAC.h:873-1062)
-    std::vector<double> h_scale, h_orient; // host rows for the fits
-    const double* fs = scale;
-    const double* fo = orient;
-    if (opt.features_on_device)
-    {
-        h_scale.resize(3 * ns);
-        h_orient.resize(3 * no);
-        eng.check(gcr_get_features(eng.h, h_scale.data(), hybrid ? h_orient.data() : nullptr), "gcr_get_features");
-        fs = h_scale.data();
-        fo = h_orient.data();
-    }
     SplitMix rng{st.seed ^ 0x6C6F63616C6F7074ull};
     std::vector<uint32_t> lab_words(W), in_s, in_o, smp_s, smp_o, scratch;
     std::vector<double> trial_models, trial_scores;
     std::vector<uint32_t> trial_cnt, trial_words;
-    auto asArray = [](const gcransac::SIFTRectifyingHomography& m, double out[4]) {
-        out[0] = m.h7; out[1] = m.h8; out[2] = m.alpha; out[3] = m.phi;
+    // Non-minimal fits run on the device (gcr_fit_models), all trials of one inner RANSAC in one pass
+    std::vector<uint32_t> fit_idx_s, fit_idx_o;
+    std::vector<int64_t> fit_off_s, fit_off_o;
+    std::vector<double> fit_models;
+    std::vector<int32_t> fit_ok;
+    auto fitBegin = [&] {
+        fit_idx_s.clear();
+        fit_idx_o.clear();
+        fit_off_s.assign(1, 0);
+        fit_off_o.assign(1, 0);
     };
-    auto fit = [&](const std::vector<uint32_t>& is, const std::vector<uint32_t>& io, gcransac::SIFTRectifyingHomography& m) {
-        return hybrid ? fitNonMinimal(fs, is, fo, io, m)
-                      : fitNonMinimalScale(fs, is, problem == GCR_PROBLEM_SCALE_ONLY_ORIGINAL, m);
+    auto fitAdd = [&](const std::vector<uint32_t>& is, const std::vector<uint32_t>& io) {
+        fit_idx_s.insert(fit_idx_s.end(), is.begin(), is.end());
+        fit_off_s.push_back(static_cast<int64_t>(fit_idx_s.size()));
+        if (hybrid)
+        {
+            fit_idx_o.insert(fit_idx_o.end(), io.begin(), io.end());
+            fit_off_o.push_back(static_cast<int64_t>(fit_idx_o.size()));
+        }
+    };
+    auto fitRun = [&] {
+        const size_t k = fit_off_s.size() - 1;
+        fit_models.resize(4 * k);
+        fit_ok.resize(k);
+        if (fit_idx_s.empty()) fit_idx_s.push_back(0u); // keep the pointers non-null for empty lists
+        if (hybrid && fit_idx_o.empty()) fit_idx_o.push_back(0u);
+        eng.check(gcr_fit_models(eng.h, static_cast<int64_t>(k), fit_idx_s.data(), fit_off_s.data(), hybrid ? fit_idx_o.data() : nullptr,
+                                 hybrid ? fit_off_o.data() : nullptr, fit_models.data(), fit_ok.data()),
+                  "gcr_fit_models");
+        return k;
     };
     // two classes: r^2 <= (1.5 t)^2 (GCRANSAC.h:931-937); one class: graph cut over the (empty) neighbourhood graph, which
     // labels a feature an inlier iff r^2 < (1.5 t)^2 for any 0 <= lambda < 1 (GCRANSAC.h:759-870)
@@ -289,17 +310,16 @@ static int estimateImpl(int problem, const double* scale, size_t ns, const doubl
             const size_t k_s = std::min(lim_s, in_s.size()), k_o = std::min(lim_o, in_o.size());
             if (in_s.size() <= min_s || (hybrid && in_o.size() <= min_o)) break; // sampling fails: neither a draw nor "use all" applies
             trial_models.clear();
-            for (size_t trial = 0; trial < max_lo; ++trial)
+            fitBegin();
+            for (size_t trial = 0; trial < std::min<size_t>(max_lo, 1024); ++trial) // one device pass holds 1024 fits / models
             {
                 if (k_s < in_s.size()) drawSubset(in_s, k_s, rng, scratch, smp_s); else smp_s = in_s;
                 if (k_o < in_o.size()) drawSubset(in_o, k_o, rng, scratch, smp_o); else smp_o = in_o;
-                gcransac::SIFTRectifyingHomography m;
-                if (!fit(smp_s, smp_o, m)) continue;
-                double a[4];
-                asArray(m, a);
-                trial_models.insert(trial_models.end(), a, a + 4);
-                if (trial_models.size() / 4 == 1024) break; // one device pass holds 1024 models
+                fitAdd(smp_s, smp_o);
             }
+            const size_t n_fit = fitRun();
+            for (size_t t = 0; t < n_fit; ++t)
+                if (fit_ok[t]) trial_models.insert(trial_models.end(), &fit_models[4 * t], &fit_models[4 * t] + 4);
             const size_t nt = trial_models.size() / 4;
             if (nt > 0)
             {
@@ -326,18 +346,21 @@ static int estimateImpl(int problem, const double* scale, size_t ns, const doubl
         if (best.score < lo.score) best = lo;
     }
     st.lo_score = best.score;
+    st.lo_ms = lap();
 
     // ---- final model: one least-squares refit on all inliers, kept if it scores higher (GCRANSAC.h:628-667; the
     //      iterated re-weighted fit before it never produces a model in the reference)
     wordsToIndices(best.words.data(), ns, in_s);
     wordsToIndices(best.words.data() + ws, no, in_o);
     {
-        gcransac::SIFTRectifyingHomography m;
-        if (fit(in_s, in_o, m))
+        fitBegin();
+        fitAdd(in_s, in_o);
+        fitRun();
+        if (fit_ok[0])
         {
             double a[4], sc = 0.0;
             uint32_t cnt[2];
-            asArray(m, a);
+            std::memcpy(a, fit_models.data(), sizeof(a));
             eng.check(gcr_score_models(eng.h, a, 1, thr, 0, &sc, cnt, lab_words.data()), "gcr_score_models(refit)");
             if (best.score < sc)
             {
@@ -351,6 +374,7 @@ static int estimateImpl(int problem, const double* scale, size_t ns, const doubl
         }
     }
     st.final_score = best.score;
+    st.refit_ms = lap();
 
     model.h7 = best.model[0];
     model.h8 = best.model[1];

@@ -45,6 +45,7 @@ struct Stats
     double hypothesis_stage_ms = 0.0; // CUDA-event time of the device hypothesis stage, summed over batches
     double score_kernel_ms = 0.0;
     double total_ms = 0.0;            // wall time of the whole call
+    double setup_ms = 0.0, loop_ms = 0.0, lo_ms = 0.0, refit_ms = 0.0; // wall time of: engine lease + feature upload | hypothesis loop | local optimisation | final refit
     int device_calls = 0;
 };
 

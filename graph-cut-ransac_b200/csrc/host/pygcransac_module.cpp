@@ -108,6 +108,10 @@ py::dict toDict(const gcr_host::Stats& st)
     d["hypothesis_stage_ms"] = st.hypothesis_stage_ms;
     d["score_kernel_ms"] = st.score_kernel_ms;
     d["total_ms"] = st.total_ms;
+    d["setup_ms"] = st.setup_ms;
+    d["loop_ms"] = st.loop_ms;
+    d["lo_ms"] = st.lo_ms;
+    d["refit_ms"] = st.refit_ms;
     d["device_calls"] = st.device_calls;
     return d;
 }

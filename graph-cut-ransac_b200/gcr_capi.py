@@ -23,7 +23,7 @@ SCORE_TRUNCATED_SQ, SCORE_STRICT = 1, 2
 EXPORTS = [
     "gcr_create", "gcr_destroy", "gcr_last_error", "gcr_set_stream", "gcr_set_problem", "gcr_set_features", "gcr_get_features", "gcr_run",
     "gcr_best",
-    "gcr_fetch", "gcr_score_model", "gcr_score_models", "gcr_debug_eval", "gcr_version", "gcr_peer_export",
+    "gcr_fetch", "gcr_score_model", "gcr_score_models", "gcr_fit_models", "gcr_debug_eval", "gcr_version", "gcr_peer_export",
     "gcr_peer_attach", "gcr_peer_buffer", "gcr_peer_attach_ptrs", "gcr_peer_detach",
 ]
 
@@ -69,6 +69,7 @@ def load_library() -> C.CDLL:
     lib.gcr_fetch.argtypes = [vp, vp, vp, vp, vp, vp, vp]
     lib.gcr_score_model.argtypes = [vp, vp, vp, vp, vp, vp, vp]
     lib.gcr_score_models.argtypes = [vp, vp, i64, vp, u32, vp, vp, vp]
+    lib.gcr_fit_models.argtypes = [vp, i64, vp, vp, vp, vp, vp, vp]
     lib.gcr_peer_export.argtypes = [vp, vp]
     lib.gcr_peer_attach.argtypes = [vp, vp, C.c_int, C.c_int]
     lib.gcr_peer_buffer.argtypes = [vp, C.POINTER(vp)]
@@ -222,6 +223,25 @@ class Engine:
         self._check(self.lib.gcr_score_models(self.h, models.ctypes.data, n, thr.ctypes.data, (1 if truncated_sq else 0) | (2 if strict else 0),
                                               score.ctypes.data, n_inl.ctypes.data, words.ctypes.data if masks else None))
         return score, n_inl, words
+
+    def fit_models(self, scale_lists, orient_lists=None):
+        """Device non-minimal fits from index lists (one list per fit and class); -> (models f64[K,4], ok bool[K])."""
+        K = len(scale_lists)
+        def pack(lists):
+            off = np.zeros(K + 1, np.int64)
+            off[1:] = np.cumsum([len(l) for l in lists])
+            idx = np.ascontiguousarray(np.concatenate([np.asarray(l, np.uint32).ravel() for l in lists]) if off[-1] else np.zeros(1, np.uint32), np.uint32)
+            return idx, off
+        si, so = pack(scale_lists)
+        if orient_lists is not None:
+            assert len(orient_lists) == K
+            oi, oo = pack(orient_lists)
+        models = np.zeros((K, 4))
+        ok = np.zeros(K, np.int32)
+        self._check(self.lib.gcr_fit_models(self.h, K, si.ctypes.data, so.ctypes.data,
+                                            oi.ctypes.data if orient_lists is not None else None,
+                                            oo.ctypes.data if orient_lists is not None else None, models.ctypes.data, ok.ctypes.data))
+        return models, ok.astype(bool)
 
     def debug_eval(self, which, abc, model=None):
         abc = np.ascontiguousarray(abc, np.float64).reshape(-1, 3)

@@ -177,6 +177,19 @@ int gcr_score_model(gcr_handle h, const double model[4], const double thr[2], do
 int gcr_score_models(gcr_handle h, const double* models, int64_t n, const double thr[2], uint32_t flags, double* score,
                      uint32_t* n_inl, uint32_t* mask_words);
 
+/* Non-minimal least-squares fits on the device, `n_fits` (<= 1024) per call: the model-fitting step of the local
+ * optimisation's inner RANSAC (GCRANSAC.h:955-1002 -> estimator.estimateModelNonminimal) and of the final refit on all
+ * inliers (GCRANSAC.h:628-645).  Replaces RectifyingHomographyEstimator::estimateModelNonminimal
+ * (rectifying_homography_estimator.h:164-227) with unit weights, i.e. estimateNonMinimalModel of two_sift.hpp:423-579
+ * (rows per scale feature and per PAIR of orientation features, least squares, phi by the 0.5-degree histogram mode),
+ * three_sift.hpp:195-254 and three_sift_original.hpp:229-234 for the scale-only problems (gcr_set_problem).
+ * Fit k uses the resident scale features scale_idx[scale_off[k] .. scale_off[k+1]) and orientation features
+ * orient_idx[orient_off[k] .. orient_off[k+1]) (HOST arrays; offsets start at 0; orient_* NULL for scale-only).
+ * Host outputs: models f64[n_fits,4] = (h7, h8, alpha, phi), ok i32[n_fits] (0 where the reference's solver returns no
+ * model: too few constraints, non-finite solution, alpha < 1e-9).  Parity: model <= 1e-6 relative.  Synchronises. */
+int gcr_fit_models(gcr_handle h, int64_t n_fits, const uint32_t* scale_idx, const int64_t* scale_off,
+                   const uint32_t* orient_idx, const int64_t* orient_off, double* models, int32_t* ok);
+
 /* Device-side helper math, evaluated on the GPU by the same __device__ functions the kernels use.
  * which: 0 clipAngle(a) 1 minAngleDiff(a,b) 2 linesAnglesDiff(a,b)
  *        3 scaleResidual(x=a,y=b,s=c; model) 4 orientationResidual(x=a,y=b,theta=c; model)
