@@ -2,6 +2,7 @@
 // include/gcr_b200.h.  Compiled for sm_100a only, with -fmad=false (see gcr_exact.cuh).
 #include "gcr_kernels.cuh"
 #include "gcr_fit.cuh"
+#include "gcr_front.cuh"
 #include "../../include/gcr_b200.h"
 
 #include <cmath>
@@ -123,6 +124,15 @@ struct gcr_engine_s
     DevBuf<unsigned char> d_fit_in, d_fit_out;
     DevBuf<double> d_fit_lines, d_fit_partial;
     PinnedBuf h_fit_in, h_fit_out;
+
+    // keypoint front end (gcr_set_keypoints)
+    DevBuf<unsigned char> d_kp;
+    DevBuf<unsigned int> d_front_table, d_front_counts;
+    DevBuf<double> d_front_sizes;
+    // rows gcr_get_features returns: the resident features, or everything the last gcr_set_keypoints built
+    const double* fetch_scale = nullptr;
+    const double* fetch_orient = nullptr;
+    int64_t fetch_ns = 0, fetch_no = 0;
 
     // multi-GPU winner exchange (peer memory)
     DevBuf<unsigned long long> d_xchg;
@@ -354,6 +364,30 @@ static int peer_buffer(gcr_engine_s* h)
     return GCR_OK;
 }
 
+// Derived feature planes of the rows at h->scale_ptr / h->orient_ptr (device memory), sizes in h->ns / h->no
+static int finish_features(gcr_handle h)
+{
+    h->ncs = (h->ns + kChunk - 1) / kChunk;
+    h->nco = (h->no + kChunk - 1) / kChunk;
+    h->have_run = false;
+    GCR_CUDA(h->d_fs.ensure(static_cast<size_t>(h->ncs) * kChunkFloats));
+    GCR_CUDA(h->d_fo.ensure(static_cast<size_t>(h->nco) * kChunkFloats));
+    h->ncsd = (h->ns + kChunk / 2 - 1) / (kChunk / 2);
+    h->ncod = (h->no + kChunk / 2 - 1) / (kChunk / 2);
+    GCR_CUDA(h->d_fsd.ensure(static_cast<size_t>(h->ncsd) * (kChunkFloats / 2)));
+    GCR_CUDA(h->d_fod.ensure(static_cast<size_t>(h->ncod) * (kChunkFloats / 2)));
+    GCR_CUDA(h->d_irr_s.ensure(kIrrCap));
+    GCR_CUDA(h->d_irr_o.ensure(kIrrCap));
+    GCR_CUDA(h->d_scene.ensure(1));
+    GCR_CUDA(cudaMemsetAsync(h->d_scene.p, 0, sizeof(Scene), h->stream));
+    const int n = std::max(h->ncs, h->nco) * kChunk;
+    k_prep_features<<<(n + 255) / 256, 256, 0, h->stream>>>(h->scale_ptr, h->ns, h->orient_ptr, h->no, h->d_fs.p,
+                                                           h->d_fo.p, h->ncs, h->nco, h->d_fsd.p, h->d_fod.p, h->ncsd, h->ncod, h->d_scene.p, h->d_irr_s.p,
+                                                           h->d_irr_o.p);
+    GCR_CUDA(cudaGetLastError());
+    return ensure_common(h);
+}
+
 extern "C"
 {
 
@@ -427,6 +461,7 @@ int gcr_destroy(gcr_handle h)
     h->d_dbg_in.release(); h->d_dbg_out.release(); h->d_user_models.release();
     h->d_fit_in.release(); h->d_fit_out.release(); h->d_fit_lines.release(); h->d_fit_partial.release();
     h->h_fit_in.release(); h->h_fit_out.release();
+    h->d_kp.release(); h->d_front_table.release(); h->d_front_counts.release(); h->d_front_sizes.release();
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
     if (h->evk0) cudaEventDestroy(h->evk0);
@@ -467,9 +502,6 @@ int gcr_set_features(gcr_handle h, const double* scale, int64_t ns, const double
     GCR_CUDA(cudaSetDevice(h->device));
     h->ns = static_cast<int>(ns);
     h->no = static_cast<int>(no);
-    h->ncs = (h->ns + kChunk - 1) / kChunk;
-    h->nco = (h->no + kChunk - 1) / kChunk;
-    h->have_run = false;
     if (on_device)
     {
         h->scale_ptr = scale;
@@ -484,22 +516,79 @@ int gcr_set_features(gcr_handle h, const double* scale, int64_t ns, const double
         h->scale_ptr = h->d_scale.p;
         h->orient_ptr = h->d_orient.p;
     }
-    GCR_CUDA(h->d_fs.ensure(static_cast<size_t>(h->ncs) * kChunkFloats));
-    GCR_CUDA(h->d_fo.ensure(static_cast<size_t>(h->nco) * kChunkFloats));
-    h->ncsd = (h->ns + kChunk / 2 - 1) / (kChunk / 2);
-    h->ncod = (h->no + kChunk / 2 - 1) / (kChunk / 2);
-    GCR_CUDA(h->d_fsd.ensure(static_cast<size_t>(h->ncsd) * (kChunkFloats / 2)));
-    GCR_CUDA(h->d_fod.ensure(static_cast<size_t>(h->ncod) * (kChunkFloats / 2)));
-    GCR_CUDA(h->d_irr_s.ensure(kIrrCap));
-    GCR_CUDA(h->d_irr_o.ensure(kIrrCap));
-    GCR_CUDA(h->d_scene.ensure(1));
-    GCR_CUDA(cudaMemsetAsync(h->d_scene.p, 0, sizeof(Scene), h->stream));
-    const int n = std::max(h->ncs, h->nco) * kChunk;
-    k_prep_features<<<(n + 255) / 256, 256, 0, h->stream>>>(h->scale_ptr, h->ns, h->orient_ptr, h->no, h->d_fs.p,
-                                                           h->d_fo.p, h->ncs, h->nco, h->d_fsd.p, h->d_fod.p, h->ncsd, h->ncod, h->d_scene.p, h->d_irr_s.p,
-                                                           h->d_irr_o.p);
+    h->fetch_scale = h->scale_ptr;
+    h->fetch_orient = h->orient_ptr;
+    h->fetch_ns = h->ns;
+    h->fetch_no = h->no;
+    return finish_features(h);
+}
+
+int gcr_set_keypoints(gcr_handle h, const void* keypoints, int64_t n, int is_f32, int on_device, int64_t* n_scale,
+                      int64_t* n_orient, double* orient_sizes)
+{
+    if (!h) return GCR_ERR_INVALID;
+    if (!h->stream) return h->fail(GCR_ERR_STATE, "engine was not created successfully");
+    if (!keypoints || n < 1 || n > (1ll << 30)) return h->fail(GCR_ERR_INVALID, "gcr_set_keypoints: 1 <= n <= 2^30 rows of (x, y, size, angle)");
+    GCR_CUDA(cudaSetDevice(h->device));
+    const size_t row_bytes = is_f32 ? 16 : 32;
+    const void* d_kp = keypoints;
+    cudaStream_t s = h->stream;
+    if (on_device)
+    {
+        if (reinterpret_cast<uintptr_t>(keypoints) % 16 != 0) return h->fail(GCR_ERR_INVALID, "gcr_set_keypoints: device rows must be 16-byte aligned");
+    }
+    else
+    {
+        GCR_CUDA(h->d_kp.ensure(row_bytes * static_cast<size_t>(n)));
+        GCR_CUDA(cudaMemcpyAsync(h->d_kp.p, keypoints, row_bytes * static_cast<size_t>(n), cudaMemcpyHostToDevice, s));
+        d_kp = h->d_kp.p;
+    }
+    size_t cap = 1024;
+    while (cap < 2 * static_cast<size_t>(n)) cap <<= 1;
+    const unsigned int nb = static_cast<unsigned int>((n + kFrontThreads - 1) / kFrontThreads);
+    GCR_CUDA(h->d_front_table.ensure(cap));
+    GCR_CUDA(h->d_front_counts.ensure(2 * static_cast<size_t>(nb) + 2));
+    GCR_CUDA(h->d_scale.ensure(3 * static_cast<size_t>(n)));
+    GCR_CUDA(h->d_orient.ensure(3 * static_cast<size_t>(n)));
+    GCR_CUDA(h->d_front_sizes.ensure(static_cast<size_t>(n)));
+    GCR_CUDA(cudaMemsetAsync(h->d_front_table.p, 0xff, sizeof(unsigned int) * cap, s));
+    FrontBuffers F;
+    F.kp = d_kp;
+    F.is_f32 = is_f32 ? 1 : 0;
+    F.n = static_cast<unsigned int>(n);
+    F.table = h->d_front_table.p;
+    F.cap_mask = static_cast<unsigned int>(cap - 1);
+    F.block_counts = h->d_front_counts.p;
+    F.n_blocks = nb;
+    F.scale = h->d_scale.p;
+    F.orient = h->d_orient.p;
+    F.sizes = h->d_front_sizes.p;
+    k_front_insert<<<nb, kFrontThreads, 0, s>>>(F);
+    k_front_compact<false><<<nb, kFrontThreads, 0, s>>>(F);
+    k_front_scan<<<1, kFrontThreads, 0, s>>>(F);
+    k_front_compact<true><<<nb, kFrontThreads, 0, s>>>(F);
     GCR_CUDA(cudaGetLastError());
-    return ensure_common(h);
+    unsigned int totals[2] = {0, 0};
+    GCR_CUDA(cudaMemcpyAsync(totals, h->d_front_counts.p + 2 * static_cast<size_t>(nb), sizeof(totals), cudaMemcpyDeviceToHost, s));
+    GCR_CUDA(cudaStreamSynchronize(s));
+    if (n_scale) *n_scale = totals[0];
+    if (n_orient) *n_orient = totals[1];
+    if (orient_sizes && totals[1])
+        GCR_CUDA(cudaMemcpy(orient_sizes, h->d_front_sizes.p, sizeof(double) * totals[1], cudaMemcpyDeviceToHost));
+    h->ns = h->no = 0;
+    h->have_run = false;
+    h->fetch_scale = h->d_scale.p;
+    h->fetch_orient = h->d_orient.p;
+    h->fetch_ns = totals[0];
+    h->fetch_no = totals[1];
+    const bool hybrid = h->problem == 0;
+    // fewer rows than a minimal sample: the rows can be fetched, but the engine holds no features to run on
+    if (totals[0] < (hybrid ? 2u : 3u) || (hybrid && totals[1] < 2u)) return GCR_OK;
+    h->ns = static_cast<int>(totals[0]);
+    h->no = hybrid ? static_cast<int>(totals[1]) : 0;
+    h->scale_ptr = h->d_scale.p;
+    h->orient_ptr = hybrid ? h->d_orient.p : nullptr;
+    return finish_features(h);
 }
 
 int gcr_set_problem(gcr_handle h, int problem)
@@ -597,10 +686,12 @@ int gcr_peer_detach(gcr_handle h)
 int gcr_get_features(gcr_handle h, double* scale, double* orient)
 {
     if (!h) return GCR_ERR_INVALID;
-    if (h->ns < 2) return h->fail(GCR_ERR_STATE, "gcr_get_features before gcr_set_features");
+    if (!h->fetch_scale) return h->fail(GCR_ERR_STATE, "gcr_get_features before gcr_set_features / gcr_set_keypoints");
     GCR_CUDA(cudaSetDevice(h->device));
-    if (scale) GCR_CUDA(cudaMemcpyAsync(scale, h->scale_ptr, sizeof(double) * 3 * h->ns, cudaMemcpyDeviceToHost, h->stream));
-    if (orient && h->no > 0) GCR_CUDA(cudaMemcpyAsync(orient, h->orient_ptr, sizeof(double) * 3 * h->no, cudaMemcpyDeviceToHost, h->stream));
+    if (scale && h->fetch_ns > 0)
+        GCR_CUDA(cudaMemcpyAsync(scale, h->fetch_scale, sizeof(double) * 3 * h->fetch_ns, cudaMemcpyDeviceToHost, h->stream));
+    if (orient && h->fetch_no > 0 && h->fetch_orient)
+        GCR_CUDA(cudaMemcpyAsync(orient, h->fetch_orient, sizeof(double) * 3 * h->fetch_no, cudaMemcpyDeviceToHost, h->stream));
     GCR_CUDA(cudaStreamSynchronize(h->stream));
     return GCR_OK;
 }

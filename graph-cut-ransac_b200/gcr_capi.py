@@ -18,12 +18,13 @@ FLAG_SAMPLE_VALID, FLAG_SOLVED, FLAG_MODEL_VALID, FLAG_EXACT = 1, 2, 4, 8
 RUN_EMIT_MASKS, RUN_SAMPLES_ON_DEVICE, RUN_KEEP_PER_HYP, RUN_ALL_EXACT, RUN_EXCHANGE = 1, 2, 4, 8, 16
 IPC_HANDLE_BYTES = 64
 PROBLEM_HYBRID, PROBLEM_SCALE_ONLY, PROBLEM_SCALE_ONLY_ORIGINAL = 0, 1, 2
+ERR_INVALID, ERR_CUDA, ERR_STATE, ERR_NOMEM = -1, -2, -3, -4
 SCORE_TRUNCATED_SQ, SCORE_STRICT = 1, 2
 
 EXPORTS = [
     "gcr_create", "gcr_destroy", "gcr_last_error", "gcr_set_stream", "gcr_set_problem", "gcr_set_features", "gcr_get_features", "gcr_run",
     "gcr_best",
-    "gcr_fetch", "gcr_score_model", "gcr_score_models", "gcr_fit_models", "gcr_debug_eval", "gcr_version", "gcr_peer_export",
+    "gcr_fetch", "gcr_score_model", "gcr_score_models", "gcr_fit_models", "gcr_set_keypoints", "gcr_debug_eval", "gcr_version", "gcr_peer_export",
     "gcr_peer_attach", "gcr_peer_buffer", "gcr_peer_attach_ptrs", "gcr_peer_detach",
 ]
 
@@ -70,6 +71,7 @@ def load_library() -> C.CDLL:
     lib.gcr_score_model.argtypes = [vp, vp, vp, vp, vp, vp, vp]
     lib.gcr_score_models.argtypes = [vp, vp, i64, vp, u32, vp, vp, vp]
     lib.gcr_fit_models.argtypes = [vp, i64, vp, vp, vp, vp, vp, vp]
+    lib.gcr_set_keypoints.argtypes = [vp, vp, i64, C.c_int, C.c_int, vp, vp, vp]
     lib.gcr_peer_export.argtypes = [vp, vp]
     lib.gcr_peer_attach.argtypes = [vp, vp, C.c_int, C.c_int]
     lib.gcr_peer_buffer.argtypes = [vp, C.POINTER(vp)]
@@ -101,6 +103,7 @@ class Engine:
             raise GcrError(rc, msg)
         self.ns = self.no = 0
         self.n_hyp = 0
+        self.problem = PROBLEM_HYBRID
 
     def close(self):
         if getattr(self, "h", None):
@@ -123,6 +126,7 @@ class Engine:
     def set_problem(self, problem: int):
         """PROBLEM_HYBRID (default), PROBLEM_SCALE_ONLY or PROBLEM_SCALE_ONLY_ORIGINAL; call before set_features."""
         self._check(self.lib.gcr_set_problem(self.h, problem))
+        self.problem = problem
         self.ns = self.no = 0
 
     def set_features(self, scale: np.ndarray, orient: np.ndarray = None):
@@ -135,12 +139,45 @@ class Engine:
             raise ValueError("features must be [N,3] arrays")
         self._keep = (scale, orient)
         self.ns, self.no = len(scale), len(orient)
+        self.fetch_ns, self.fetch_no = self.ns, self.no
         self._check(self.lib.gcr_set_features(self.h, scale.ctypes.data, self.ns, orient.ctypes.data if self.no else None,
                                               self.no, 0))
+
+    def set_keypoints(self, keypoints=None, device_ptr: int = None, n: int = None, is_f32: bool = None, want_sizes=True):
+        """Keypoint rows (x, y, size, angle_deg) -> resident scale / orientation features (examples/utils.py:5-49 on the
+        device).  Either a host array [n,4] (float32 or float64) or a device pointer with n and is_f32.
+        Returns (n_scale, n_orient, sizes f64[n_orient] or None)."""
+        if device_ptr is None:
+            keypoints = np.asarray(keypoints)
+            if keypoints.dtype != np.float32:
+                keypoints = keypoints.astype(np.float64, copy=False)
+            keypoints = np.ascontiguousarray(keypoints)
+            if keypoints.ndim != 2 or keypoints.shape[1] != 4:
+                raise ValueError("keypoints must be an [N,4] array of (x, y, size, angle in degrees)")
+            n, is_f32, ptr, on_dev = len(keypoints), keypoints.dtype == np.float32, keypoints.ctypes.data, 0
+        else:
+            ptr, on_dev = device_ptr, 1
+        ns, no = C.c_int64(0), C.c_int64(0)
+        sizes = np.zeros(max(n, 1)) if want_sizes else None
+        rc = self.lib.gcr_set_keypoints(self.h, C.c_void_p(ptr), n, 1 if is_f32 else 0, on_dev, C.byref(ns), C.byref(no),
+                                        sizes.ctypes.data if want_sizes else None)
+        self._check(rc)
+        self.fetch_ns, self.fetch_no = int(ns.value), int(no.value)
+        enough = self.fetch_ns >= (2 if self.problem == 0 else 3) and (self.problem != 0 or self.fetch_no >= 2)
+        self.ns, self.no = (self.fetch_ns, self.fetch_no if self.problem == 0 else 0) if enough else (0, 0)
+        return int(ns.value), int(no.value), (sizes[:no.value] if want_sizes else None)
+
+    def get_features(self):
+        """The resident feature rows as host arrays (scale f64[ns,3], orient f64[no,3])."""
+        ns, no = getattr(self, "fetch_ns", self.ns), getattr(self, "fetch_no", self.no)
+        scale, orient = np.zeros((ns, 3)), np.zeros((no, 3))
+        self._check(self.lib.gcr_get_features(self.h, scale.ctypes.data, orient.ctypes.data if no else None))
+        return scale, orient
 
     def set_features_device(self, scale_ptr: int, ns: int, orient_ptr: int, no: int):
         """Device pointers to float64 [N,3] row-major arrays (zero-copy; caller keeps them alive)."""
         self.ns, self.no = ns, no
+        self.fetch_ns, self.fetch_no = ns, no
         self._check(self.lib.gcr_set_features(self.h, C.c_void_p(scale_ptr), ns, C.c_void_p(orient_ptr), no, 1))
 
     def run(self, n_hyp, thr, seed=0, first_hyp=0, samples=None, flags=0, record_ptr=None, sync=True,

@@ -90,6 +90,22 @@ int gcr_create(int device, gcr_handle* out);
 int gcr_destroy(gcr_handle h);
 const char* gcr_last_error(gcr_handle h);
 
+
+/* Feature front end on the device: the reference's examples/utils.py:5-49 between cv2.SIFT and pygcransac, for keypoint
+ * rows (x, y, size, angle in degrees; angle == -1: no orientation), float32 (is_f32 = 1, what cv2.KeyPoint holds) or
+ * float64, in host memory or, on_device = 1, device memory of the engine's device (16-byte aligned).
+ *   scale features       one (x, y, size) row per unique (int(x), int(y)): the first keypoint of each coordinate, in
+ *                        order of first appearance                          (scale_features_from_sift, utils.py:5-26)
+ *   orientation features (x, y, deg2rad(angle)) of every keypoint with angle != -1, in input order; 0.5 * size per
+ *                        row goes to orient_sizes                    (orientation_features_from_sift, utils.py:29-49)
+ * The two arrays become the engine's resident features exactly as after gcr_set_features (scale-only problems keep
+ * the scale rows only); gcr_get_features returns them.  n_scale / n_orient (nullable) receive the row counts;
+ * orient_sizes (nullable) is a HOST buffer of capacity n.  Results are bit-identical to the Python functions.
+ * When a class ends up with fewer rows than a minimal sample the call still succeeds and the rows can be fetched,
+ * but the engine holds no features to run on (gcr_run: GCR_ERR_STATE).  Synchronises. */
+int gcr_set_keypoints(gcr_handle h, const void* keypoints, int64_t n, int is_f32, int on_device, int64_t* n_scale,
+                      int64_t* n_orient, double* orient_sizes);
+
 /* Which of the reference's three estimators the engine runs (default: hybrid).  Call before gcr_set_features.
  *   GCR_PROBLEM_HYBRID               findRectifyingHomographySIFT: 2 scale + 2 orientation samples (two_sift.hpp)
  *   GCR_PROBLEM_SCALE_ONLY           findRectifyingHomographyScaleOnly: 3 scale samples, rows [x, y, s^(1/3)] = 1,
