@@ -91,6 +91,7 @@ struct gcr_engine_s
     const double* orient_ptr = nullptr;
     DevBuf<float> d_fs, d_fo;
     DevBuf<double> d_fsd, d_fod; // FP64 SoA for the precise tiles
+    DevBuf<double> d_aux_s, d_aux_o; // per-feature inputs of the minimal solvers (k_prep_features)
     int ncsd = 0, ncod = 0;
     DevBuf<unsigned int> d_irr_s, d_irr_o;
     DevBuf<Scene> d_scene;
@@ -256,6 +257,8 @@ Buffers make_buffers(gcr_engine_s* h, unsigned long long seed, bool have_samples
     std::memset(&B, 0, sizeof(B));
     B.scale = h->scale_ptr;
     B.orient = h->orient_ptr;
+    B.aux_s = h->d_aux_s.p;
+    B.aux_o = h->d_aux_o.p;
     B.ns = h->ns;
     B.no = h->no;
     B.fs = h->d_fs.p;
@@ -376,6 +379,8 @@ static int finish_features(gcr_handle h)
     h->ncod = (h->no + kChunk / 2 - 1) / (kChunk / 2);
     GCR_CUDA(h->d_fsd.ensure(static_cast<size_t>(h->ncsd) * (kChunkFloats / 2)));
     GCR_CUDA(h->d_fod.ensure(static_cast<size_t>(h->ncod) * (kChunkFloats / 2)));
+    GCR_CUDA(h->d_aux_s.ensure(static_cast<size_t>(std::max(h->ns, 1))));
+    GCR_CUDA(h->d_aux_o.ensure(2 * static_cast<size_t>(std::max(h->no, 1))));
     GCR_CUDA(h->d_irr_s.ensure(kIrrCap));
     GCR_CUDA(h->d_irr_o.ensure(kIrrCap));
     GCR_CUDA(h->d_scene.ensure(1));
@@ -383,7 +388,7 @@ static int finish_features(gcr_handle h)
     const int n = std::max(h->ncs, h->nco) * kChunk;
     k_prep_features<<<(n + 255) / 256, 256, 0, h->stream>>>(h->scale_ptr, h->ns, h->orient_ptr, h->no, h->d_fs.p,
                                                            h->d_fo.p, h->ncs, h->nco, h->d_fsd.p, h->d_fod.p, h->ncsd, h->ncod, h->d_scene.p, h->d_irr_s.p,
-                                                           h->d_irr_o.p);
+                                                           h->d_irr_o.p, h->d_aux_s.p, h->d_aux_o.p, h->problem);
     GCR_CUDA(cudaGetLastError());
     return ensure_common(h);
 }
@@ -451,6 +456,7 @@ int gcr_destroy(gcr_handle h)
     peer_release(h);
     h->d_xchg.release();
     h->d_scale.release(); h->d_orient.release(); h->d_fs.release(); h->d_fo.release(); h->d_fsd.release(); h->d_fod.release();
+    h->d_aux_s.release(); h->d_aux_o.release();
     h->d_irr_s.release(); h->d_irr_o.release(); h->d_scene.release(); h->d_samples.release();
     h->d_models.release(); h->d_flags.release(); h->d_sums.release(); h->d_score.release();
     h->d_cnts.release(); h->d_ninl.release(); h->d_masks.release(); h->d_fast_hyp.release();
@@ -807,7 +813,9 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
         GCR_CUDA(cudaEventElapsedTime(&out->device_ms, h->ev0, h->ev1));
         GCR_CUDA(cudaEventElapsedTime(&out->score_kernel_ms, h->evk0, h->evk1));
         for (int i = 0; i < 5; i++) out->tail_phase_us[i] = static_cast<float>(static_cast<double>(ph[i + 1] - ph[i]) * 1e-3);
-        out->tail_phase_us[5] = 0.f;
+        out->tail_phase_us[5] = static_cast<float>(static_cast<double>(ph[0] - ph[7]) * 1e-3); // k_score_fast start -> k_tail start
+        out->stage_phase_us[0] = static_cast<float>(static_cast<double>(ph[7] - ph[6]) * 1e-3); // k_sample_solve start -> k_score_fast start
+        out->stage_phase_us[1] = static_cast<float>(static_cast<double>(ph[5] - ph[6]) * 1e-3); // k_sample_solve start -> end of k_tail
         out->winner_rank = static_cast<int32_t>(r.reserved);
         if (c.xchg_timeout) return h->fail(GCR_ERR_STATE, "winner exchange timed out: a peer rank did not run the same collective call");
         if (c.n_bad_sample) return h->fail(GCR_ERR_INVALID, "replayed sample indices out of range");

@@ -97,6 +97,14 @@ __device__ __forceinline__ void line_from_point_angle(double x, double y, double
     l[2] = y * c - x * s;
 }
 
+// the same line from a precomputed (sin, cos) pair
+__device__ __forceinline__ void line_from_sincos(double x, double y, double s, double c, double l[3])
+{
+    l[0] = s;
+    l[1] = -c;
+    l[2] = y * c - x * s;
+}
+
 __device__ __forceinline__ void cross3(const double a[3], const double b[3], double r[3])
 {
     r[0] = a[1] * b[2] - a[2] * b[1];
@@ -121,12 +129,13 @@ __device__ __forceinline__ bool are_collinear(double x1, double y1, double x2, d
 
 // two_sift.hpp:141-215 (S8).  Convex hull of the 4 sample points: math_utils.hpp:239-284, point test :291-321.
 // vp_out = l1 x l2 (unnormalised), reused by the solver (two_sift.hpp:309-311 recomputes the same value).
+// sc0 / sc1: (sin, cos) of the two orientations as sincos returns them (hoisted to feature preparation)
 __device__ inline bool is_valid_sample(const double s0[3], const double s1[3], const double o0[3],
-                                       const double o1[3], double vp_out[3])
+                                       const double o1[3], const double sc0[2], const double sc1[2], double vp_out[3])
 {
     double l1[3], l2[3], vp[3];
-    line_from_point_angle(o0[0], o0[1], o0[2], l1);
-    line_from_point_angle(o1[0], o1[1], o1[2], l2);
+    line_from_sincos(o0[0], o0[1], sc0[0], sc0[1], l1);
+    line_from_sincos(o1[0], o1[1], sc1[0], sc1[1], l2);
     cross3(l1, l2, vp);
     vp_out[0] = vp[0];
     vp_out[1] = vp[1];
@@ -228,12 +237,13 @@ __device__ inline void gauss3(double m[3][4], double x[3])
     }
 }
 
-// two_sift.hpp:261-344 (S9) given vp = l1 x l2
-__device__ inline bool estimate_minimal(const double s0[3], const double s1[3], const double vp_in[3], Model4& out)
+// two_sift.hpp:261-344 (S9) given vp = l1 x l2 and pw0 / pw1 = pow(s, 1/3) of the two scale features
+__device__ inline bool estimate_minimal(const double s0[3], const double s1[3], double pw0, double pw1, const double vp_in[3],
+                                        Model4& out)
 {
     double m[3][4];
-    m[0][0] = s0[0]; m[0][1] = s0[1]; m[0][2] = pow(s0[2], 1.0 / 3.0); m[0][3] = 1.0;
-    m[1][0] = s1[0]; m[1][1] = s1[1]; m[1][2] = pow(s1[2], 1.0 / 3.0); m[1][3] = 1.0;
+    m[0][0] = s0[0]; m[0][1] = s0[1]; m[0][2] = pw0; m[0][3] = 1.0;
+    m[1][0] = s1[0]; m[1][1] = s1[1]; m[1][2] = pw1; m[1][3] = 1.0;
     m[2][0] = vp_in[0]; m[2][1] = vp_in[1]; m[2][2] = 0.0; m[2][3] = vp_in[2];
     double sol[3];
     gauss3(m, sol);
@@ -250,8 +260,9 @@ __device__ inline bool estimate_minimal(const double s0[3], const double s1[3], 
 
 // Scale-only problems (three_sift.hpp:111-193, three_sift_original.hpp): the sample is valid unless its three positions
 // are "collinear" in the reference's signed sense (S7); rows [x, y, s^(1/3), 1] (original: [x, y, -s^(-1/3), -1]).
-__device__ inline bool estimate_minimal_scale3(const double s0[3], const double s1[3], const double s2[3], bool original,
-                                               Model4& out)
+// pw: pow(s, 1/3) of the three features (original: pow(s, -1/3))
+__device__ inline bool estimate_minimal_scale3(const double s0[3], const double s1[3], const double s2[3], const double pw[3],
+                                               bool original, Model4& out)
 {
     double m[3][4];
     const double* f[3] = {s0, s1, s2};
@@ -260,7 +271,7 @@ __device__ inline bool estimate_minimal_scale3(const double s0[3], const double 
     {
         m[i][0] = f[i][0];
         m[i][1] = f[i][1];
-        m[i][2] = original ? -pow(f[i][2], -1.0 / 3.0) : pow(f[i][2], 1.0 / 3.0);
+        m[i][2] = original ? -pw[i] : pw[i];
         m[i][3] = original ? -1.0 : 1.0;
     }
     double sol[3];

@@ -33,7 +33,8 @@ namespace gcr
 __global__ void k_prep_features(const double* __restrict__ scale, int ns, const double* __restrict__ orient, int no,
                                 float* __restrict__ fs, float* __restrict__ fo, int ncs, int nco,
                                 double* __restrict__ fsd, double* __restrict__ fod, int ncsd, int ncod, Scene* scene,
-                                unsigned int* irr_s, unsigned int* irr_o)
+                                unsigned int* irr_s, unsigned int* irr_o, double* __restrict__ aux_s, double* __restrict__ aux_o,
+                                int problem)
 {
     constexpr int kCD = kChunk / 2; // features per FP64 chunk (same byte size as an FP32 chunk)
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -46,6 +47,9 @@ __global__ void k_prep_features(const double* __restrict__ scale, int ns, const 
         if (i < ns)
         {
             const double x = scale[3 * i], y = scale[3 * i + 1], s = scale[3 * i + 2];
+            // the minimal solvers' third column (two_sift.hpp:288-299, three_sift.hpp:153-160, three_sift_original.hpp):
+            // a per-FEATURE value, evaluated here once with the very function the solver would call per hypothesis
+            aux_s[i] = problem == 2 ? pow(s, -1.0 / 3.0) : pow(s, 1.0 / 3.0);
             const double q = cbrt(s);
             const double xa = x / q, ya = y / q, ia = 1.0 / q;
             const bool ok = isfinite(xa) && isfinite(ya) && isfinite(ia) && fabs(xa) < 1e12 && fabs(ya) < 1e12 &&
@@ -88,6 +92,8 @@ __global__ void k_prep_features(const double* __restrict__ scale, int ns, const 
             const double x = orient[3 * i], y = orient[3 * i + 1], t = orient[3 * i + 2];
             double st, ct;
             sincos(t, &st, &ct);
+            aux_o[2 * i] = st; // lineFromPointAndAngle's sine / cosine (math_utils.hpp:104-109), per feature
+            aux_o[2 * i + 1] = ct;
             const double k = x * st - y * ct;
             const bool ok = isfinite(k) && isfinite(st) && isfinite(ct) && fabs(k) < 1e12;
             if (ok)
@@ -157,6 +163,7 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
 {
     const int h = blockIdx.x * blockDim.x + threadIdx.x;
     const unsigned lane = threadIdx.x & 31;
+    if (h == 0) B.phase_ns[6] = global_ns(); // diagnostics: start of the stage as seen by the first CTA
     bool solved = false, hard = false, sample_valid = false, sens_s = false, sens_o = false;
     Model4 m = {0.0, 0.0, 0.0, 0.0};
     float4 p0 = make_float4(0.f, 0.f, 0.f, 0.f), p1 = make_float4(0.f, 1.f, 0.f, 0.f);
@@ -207,8 +214,9 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
                 f1[j] = B.scale[3 * s1 + j];
                 f2[j] = B.scale[3 * o0 + j];
             }
+            const double pw[3] = {B.aux_s[s0], B.aux_s[s1], B.aux_s[o0]};
             sample_valid = !are_collinear(f0[0], f0[1], f1[0], f1[1], f2[0], f2[1], 1.0); // three_sift.hpp:111-143
-            if (sample_valid) solved = estimate_minimal_scale3(f0, f1, f2, T.problem == 2, m);
+            if (sample_valid) solved = estimate_minimal_scale3(f0, f1, f2, pw, T.problem == 2, m);
         }
         else
         {
@@ -221,8 +229,10 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
                 fo0[j] = B.orient[3 * o0 + j];
                 fo1[j] = B.orient[3 * o1 + j];
             }
-            sample_valid = is_valid_sample(fs0, fs1, fo0, fo1, vp); // GCRANSAC.h:315
-            if (sample_valid) solved = estimate_minimal(fs0, fs1, vp, m); // GCRANSAC.h:326
+            const double sc0[2] = {B.aux_o[2 * o0], B.aux_o[2 * o0 + 1]}, sc1[2] = {B.aux_o[2 * o1], B.aux_o[2 * o1 + 1]};
+            const double pw0 = B.aux_s[s0], pw1 = B.aux_s[s1];
+            sample_valid = is_valid_sample(fs0, fs1, fo0, fo1, sc0, sc1, vp); // GCRANSAC.h:315
+            if (sample_valid) solved = estimate_minimal(fs0, fs1, pw0, pw1, vp, m); // GCRANSAC.h:326
         }
         unsigned char f = 0;
         if (sample_valid) f |= 1;
@@ -575,13 +585,6 @@ struct Record // mirrors gcr_record
     unsigned int n_inl[2];
     unsigned long long reserved;
 };
-
-__device__ __forceinline__ unsigned long long global_ns()
-{
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
-    return t;
-}
 
 // ---- winner exchange across GPUs, executed by warp 0 of the selecting CTA (the "collective" of the path, fused into
 // the kernel that produces the record): lane p stores this rank's record into peer p's buffer over NVLink

@@ -28,6 +28,10 @@ constexpr int kStages = 6;
 #ifndef GCR_F2
 #define GCR_F2 1
 #endif
+#ifndef GCR_ITEMS
+#define GCR_ITEMS 16
+#endif
+constexpr int kItemsPerCta = GCR_ITEMS; // work items per resident CTA the chunk lists are cut for (k_score_fast)
 #ifndef GCR_VOTE
 #define GCR_VOTE 4
 #endif
@@ -87,6 +91,8 @@ struct Buffers
     // features
     const double* scale;
     const double* orient;
+    const double* aux_s; // [ns] pow(s, 1/3) (scale-only original: pow(s, -1/3)): the solvers' per-feature column
+    const double* aux_o; // [no,2] (sin, cos) of the orientation
     int ns, no;
     const float* fs; // chunked SoA, scale class: (x/q, y/q, 1/q)
     const float* fo; // chunked SoA, orientation class: (k, sin, cos)
@@ -207,5 +213,12 @@ __device__ __forceinline__ double from_ordered_bits(unsigned long long b)
     return __longlong_as_double(static_cast<long long>(b));
 }
 
+
+__device__ __forceinline__ unsigned long long global_ns()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
 
 } // namespace gcr

@@ -409,6 +409,7 @@ __global__ void __launch_bounds__(kScoreThreads, GCR_MINB) k_score_fast(const __
     ScoreSmem& S = *reinterpret_cast<ScoreSmem*>(smem_raw);
     if (threadIdx.x == 0)
     {
+        if (blockIdx.x == 0) B.phase_ns[7] = global_ns(); // diagnostics
         for (int s = 0; s < kStages; s++)
         {
             mbar_init(&S.full[s], 1);
@@ -424,7 +425,7 @@ __global__ void __launch_bounds__(kScoreThreads, GCR_MINB) k_score_fast(const __
     // Work decomposition, identical in every CTA: the chunk lists are cut so that there are ~8 items per resident
     // CTA; items are handed out dynamically (atomic counter), costliest first: precise tiles, then FP32 tiles from
     // the orientation end of the chunk list (an orientation evaluation costs about twice a scale evaluation).
-    const int target = 8 * static_cast<int>(gridDim.x);
+    const int target = kItemsPerCta * static_cast<int>(gridDim.x);
     const int tiles = tiles_a + 2 * tiles_b; // a precise tile has twice the chunks
     int splits_a = 1;
     if (tiles > 0 && tiles < target) splits_a = min(chunks_a, (target + tiles - 1) / tiles);

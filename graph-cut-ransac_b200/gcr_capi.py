@@ -37,6 +37,7 @@ class GcrResult(C.Structure):
         ("n_exact_hyp", C.c_int64), ("n_candidates", C.c_int64), ("device_ms", C.c_float),
         ("score_kernel_ms", C.c_float), ("winner_rank", C.c_int32), ("pad2_", C.c_int32),
         ("tail_phase_us", C.c_float * 6),
+        ("stage_phase_us", C.c_float * 2),
     ]
 
 

@@ -72,7 +72,8 @@ typedef struct gcr_result
     float score_kernel_ms;  /* CUDA-event time of the dominant FP32 scoring kernel alone */
     int32_t winner_rank;    /* rank owning best_index (0 unless the run exchanged records with peers) */
     int32_t pad2_;
-    float tail_phase_us[6]; /* diagnostics: fix-up+FP64 items | finalize | collect | candidate re-scoring | select (device timer) */
+    float tail_phase_us[6]; /* diagnostics (device timer): fix-up+FP64 items | finalize | collect | candidate re-scoring | select | start of the scoring kernel -> start of the tail */
+    float stage_phase_us[2]; /* diagnostics (device timer): start of the sampler/solver kernel -> start of the scoring kernel | -> end of the tail */
 } gcr_result;
 
 /* Winner record written to device memory by the last kernel of gcr_run when `d_record` is given:
