@@ -99,7 +99,7 @@ struct gcr_engine_s
     // hypotheses
     int n_hyp = 0;
     unsigned long long first_hyp = 0;
-    bool have_masks = false, have_run = false;
+    bool have_masks = false, have_run = false, have_per_hyp = false;
     DevBuf<int> d_samples;
     const int* samples_view = nullptr; // where the samples of the last run live (own buffer or the caller's device array)
     DevBuf<Model4> d_models;
@@ -744,6 +744,8 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
     }
     const Thresholds T = make_thresholds(thr, h->problem);
     Buffers B = make_buffers(h, seed, samples != nullptr, d_record);
+    h->have_per_hyp = (flags & (GCR_RUN_KEEP_PER_HYP | GCR_RUN_EMIT_MASKS)) != 0;
+    B.per_hyp = h->have_per_hyp ? 1 : 0;
     const int all_exact = (flags & GCR_RUN_ALL_EXACT) ? 1 : 0;
     h->last_thr[0] = thr[0];
     h->last_thr[1] = h->problem == 0 ? thr[1] : 0.0;
@@ -866,6 +868,8 @@ int gcr_fetch(gcr_handle h, uint8_t* flags, double* models, double* score, uint3
     GCR_CUDA(cudaStreamSynchronize(h->stream));
     const size_t H = static_cast<size_t>(h->n_hyp);
     const size_t W = static_cast<size_t>((h->ns + 31) / 32 + (h->no + 31) / 32);
+    if ((score || n_inl) && !h->have_per_hyp)
+        return h->fail(GCR_ERR_STATE, "per-hypothesis scores were not kept: run with GCR_RUN_KEEP_PER_HYP or GCR_RUN_EMIT_MASKS");
     if (flags) GCR_CUDA(cudaMemcpy(flags, h->d_flags.p, H, cudaMemcpyDeviceToHost));
     if (models) GCR_CUDA(cudaMemcpy(models, h->d_models.p, H * sizeof(Model4), cudaMemcpyDeviceToHost));
     if (score) GCR_CUDA(cudaMemcpy(score, h->d_score.p, H * sizeof(double), cudaMemcpyDeviceToHost));

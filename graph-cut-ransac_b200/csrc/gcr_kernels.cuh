@@ -513,33 +513,77 @@ __global__ void k_cand_value(Buffers B, Thresholds T, unsigned int n)
 // as much as the scoring kernel; grid-wide barriers between the phases cost ~1-2 us.
 //
 // finalize: per-hypothesis MSAC value + arg-max key over model-valid hypotheses.
+// MSAC value of a scored hypothesis from its accumulators (flag 8: fixed-point accumulators of the FP64 kernel)
+__device__ __forceinline__ double hyp_value(const Buffers& B, const Thresholds& T, unsigned int h, unsigned char f,
+                                            unsigned int& n0, unsigned int& n1)
+{
+    double s0 = B.sums[2 * h], s1 = B.sums[2 * h + 1];
+    if (f & 8)
+    {
+        s0 = fix_to_double(reinterpret_cast<const unsigned long long*>(B.sums)[2 * h], T.tsq[0]);
+        s1 = fix_to_double(reinterpret_cast<const unsigned long long*>(B.sums)[2 * h + 1], T.tsq[1]);
+    }
+    return msac_value(T, s0, s1, B.cnts[2 * h], B.cnts[2 * h + 1], n0, n1);
+}
+
+// i-th scored hypothesis: FP32 tiles (front of fast_hyp), precise tiles (back), FP64 list
+__device__ __forceinline__ unsigned int scored_hyp(const Buffers& B, unsigned int i, unsigned int n_fast, unsigned int n_sens)
+{
+    if (i < n_fast) return B.fast_hyp[i];
+    if (i < n_fast + n_sens) return B.fast_hyp[static_cast<unsigned int>(B.n_hyp) - 1u - (i - n_fast)];
+    return B.hard_hyp[i - n_fast - n_sens];
+}
+
+// Small batches walk the slots directly (one dependent load less than through the compact lists, and the phase is
+// latency-bound there); big ones walk the compact lists (29 % of the slots at C2's validity rate).
+__device__ __forceinline__ bool tail_direct(const Buffers& B)
+{
+    return B.per_hyp || static_cast<unsigned int>(B.n_hyp) <= 2u * gridDim.x * blockDim.x;
+}
+
 __device__ __forceinline__ void finalize_phase(const Buffers& B, const Thresholds& T)
 {
     unsigned long long key = 0ull;
-    for (int base = blockIdx.x * blockDim.x; base < B.n_hyp; base += gridDim.x * blockDim.x)
+    if (tail_direct(B))
     {
-        const int h = base + threadIdx.x;
-        if (h >= B.n_hyp) continue;
-        const unsigned char f = B.flags[h];
-        unsigned int n0 = 0, n1 = 0;
-        double v = 0.0;
-        if (f & 2)
+        for (int base = blockIdx.x * blockDim.x; base < B.n_hyp; base += gridDim.x * blockDim.x)
         {
-            double s0 = B.sums[2 * h], s1 = B.sums[2 * h + 1];
-            if (f & 8) // FP64-kernel hypotheses hold fixed-point accumulators in the same slots
+            const int h = base + threadIdx.x;
+            if (h >= B.n_hyp) continue;
+            const unsigned char f = B.flags[h];
+            unsigned int n0 = 0, n1 = 0;
+            double v = 0.0;
+            if ((f & 2) && (B.per_hyp || (f & 4))) v = hyp_value(B, T, h, f, n0, n1);
+            if (B.per_hyp) // reporting modes: value and inlier counts of EVERY slot are outputs
             {
-                s0 = fix_to_double(reinterpret_cast<const unsigned long long*>(B.sums)[2 * h], T.tsq[0]);
-                s1 = fix_to_double(reinterpret_cast<const unsigned long long*>(B.sums)[2 * h + 1], T.tsq[1]);
+                B.score[h] = v;
+                B.n_inl[2 * h] = n0;
+                B.n_inl[2 * h + 1] = n1;
             }
-            v = msac_value(T, s0, s1, B.cnts[2 * h], B.cnts[2 * h + 1], n0, n1);
+            if ((f & 4) && v > 0.0) // S10 + S11 (initial best is 0, strict '<')
+            {
+                const unsigned long long k = ordered_bits(v);
+                key = k > key ? k : key;
+            }
         }
-        B.score[h] = v;
-        B.n_inl[2 * h] = n0;
-        B.n_inl[2 * h + 1] = n1;
-        if ((f & 4) && v > 0.0) // S10 + S11 (initial best is 0, strict '<')
+    }
+    else
+    {
+        // winner only: the scored hypotheses through the compact lists, nothing written
+        const unsigned int n_fast = __ldcg(&B.ctr->n_fast), n_sens = __ldcg(&B.ctr->n_sens), n_hard = __ldcg(&B.ctr->n_hard);
+        const unsigned int total = n_fast + n_sens + n_hard;
+        for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x)
         {
-            const unsigned long long k = ordered_bits(v);
-            key = k > key ? k : key;
+            const unsigned int h = scored_hyp(B, i, n_fast, n_sens);
+            const unsigned char f = B.flags[h];
+            if (!(f & 4)) continue; // S10: an invalid model is never selected
+            unsigned int n0, n1;
+            const double v = hyp_value(B, T, h, f, n0, n1);
+            if (v > 0.0)
+            {
+                const unsigned long long k = ordered_bits(v);
+                key = k > key ? k : key;
+            }
         }
     }
 #pragma unroll
@@ -553,27 +597,50 @@ __device__ __forceinline__ void finalize_phase(const Buffers& B, const Threshold
 
 // collect: hypotheses whose FP32-path score is within the path's error of the best one are re-scored in FP64
 // so that the selection rule sees reference-order scores.
-__device__ __forceinline__ void collect_phase(const Buffers& B, double rel_tol)
+__device__ __forceinline__ void collect_candidate(const Buffers& B, unsigned int h)
+{
+    const unsigned int slot = atomicAdd(&B.ctr->n_candidates, 1u);
+    if (slot < kCandCap)
+    {
+        B.cand_hyp[slot] = h;
+        B.cand_model[slot] = B.models[h];
+        B.cand_qsum[2 * slot] = B.cand_qsum[2 * slot + 1] = 0ull;
+        B.cand_rawcnt[2 * slot] = B.cand_rawcnt[2 * slot + 1] = 0u;
+    }
+    else
+        atomicAdd(&B.ctr->n_cand_overflow, 1u);
+}
+
+__device__ __forceinline__ void collect_phase(const Buffers& B, const Thresholds& T, double rel_tol)
 {
     const unsigned long long bk = __ldcg(&B.ctr->best_key);
     if (bk == 0ull) return;
     const double best = from_ordered_bits(bk);
     const double floor_v = best - rel_tol * best;
-    for (int h = blockIdx.x * blockDim.x + threadIdx.x; h < B.n_hyp; h += gridDim.x * blockDim.x)
+    if (tail_direct(B))
     {
-        const double v = B.score[h];
-        if (!(v > 0.0) || v < floor_v) continue;
-        if (!(B.flags[h] & 4)) continue;
-        const unsigned int slot = atomicAdd(&B.ctr->n_candidates, 1u);
-        if (slot < kCandCap)
+        for (int h = blockIdx.x * blockDim.x + threadIdx.x; h < B.n_hyp; h += gridDim.x * blockDim.x)
         {
-            B.cand_hyp[slot] = h;
-            B.cand_model[slot] = B.models[h];
-            B.cand_qsum[2 * slot] = B.cand_qsum[2 * slot + 1] = 0ull;
-            B.cand_rawcnt[2 * slot] = B.cand_rawcnt[2 * slot + 1] = 0u;
+            const unsigned char f = B.flags[h];
+            if ((f & 6) != 6) continue; // solved and model-valid
+            unsigned int n0, n1;
+            const double v = B.per_hyp ? B.score[h] : hyp_value(B, T, h, f, n0, n1);
+            if (!(v > 0.0) || v < floor_v) continue;
+            collect_candidate(B, h);
         }
-        else
-            atomicAdd(&B.ctr->n_cand_overflow, 1u);
+        return;
+    }
+    const unsigned int n_fast = __ldcg(&B.ctr->n_fast), n_sens = __ldcg(&B.ctr->n_sens), n_hard = __ldcg(&B.ctr->n_hard);
+    const unsigned int total = n_fast + n_sens + n_hard;
+    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x)
+    {
+        const unsigned int h = scored_hyp(B, i, n_fast, n_sens);
+        const unsigned char f = B.flags[h];
+        if (!(f & 4)) continue;
+        unsigned int n0, n1;
+        const double v = hyp_value(B, T, h, f, n0, n1); // the same arithmetic on the same inputs as in finalize
+        if (!(v > 0.0) || v < floor_v) continue;
+        collect_candidate(B, h);
     }
 }
 
@@ -777,7 +844,7 @@ __global__ void __launch_bounds__(kExactThreads) k_tail(const __grid_constant__ 
     finalize_phase(B, T);
     grid.sync();
     if (stamp) B.phase_ns[2] = global_ns();
-    collect_phase(B, rel_tol);
+    collect_phase(B, T, rel_tol);
     grid.sync();
     if (stamp) B.phase_ns[3] = global_ns();
     exact_items_phase(B, T, 1, 0u);

@@ -91,6 +91,7 @@ struct Buffers
     // features
     const double* scale;
     const double* orient;
+    int per_hyp;         // reporting mode: per-hypothesis scores / inlier counts are outputs (GCR_RUN_KEEP_PER_HYP / EMIT_MASKS)
     const double* aux_s; // [ns] pow(s, 1/3) (scale-only original: pow(s, -1/3)): the solvers' per-feature column
     const double* aux_o; // [no,2] (sin, cos) of the orientation
     int ns, no;

@@ -45,7 +45,17 @@ def _run_replay(eng, scale, orient, samples, thr, masks=True, extra_flags=0):
     eng.set_features(scale, orient)
     flags = (gcr_capi.RUN_EMIT_MASKS if masks else gcr_capi.RUN_KEEP_PER_HYP) | extra_flags
     res = eng.run(len(samples), thr, samples=samples, flags=flags)
-    return res, eng.fetch(masks=masks)
+    dev = eng.fetch(masks=masks)
+    best = eng.best()
+    # the winner-only mode (no per-hypothesis outputs: what bench.py and the estimator run) selects the same record
+    res0 = eng.run(len(samples), thr, samples=samples, flags=extra_flags)
+    assert (res0.best_index, res0.best_score, tuple(res0.best_n_inl)) == (res.best_index, res.best_score, tuple(res.best_n_inl))
+    b0 = eng.best()
+    assert np.array_equal(b0["scale_words"], best["scale_words"]) and np.array_equal(b0["orient_words"], best["orient_words"])
+    assert (res0.n_solved, res0.n_sample_valid) == (res.n_solved, res.n_sample_valid)
+    with pytest.raises(Exception):
+        eng.fetch()  # per-hypothesis scores were not kept by that run
+    return res, dev
 
 
 def test_device_helper_math(eng, port):
