@@ -249,6 +249,12 @@ def run_ours(args):
                 "kernel": "k_score_fast", "kernel_ms": k_ms, "kernel_evals": int(n_fast) * nfeat,
                 "kernel_evals_per_s": n_fast * nfeat / (k_ms * 1e-3),
                 "hbm": {"algorithmic_bytes": int(alg_bytes), "achieved_gbs": alg_bytes / (k_ms * 1e-3) / 1e9}}
+    try:  # DRAM bytes of this kernel from the committed `ncu --set full` capture (tools/summarize_profiles.py)
+        tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))[args.config]["k_score_fast"]
+        roofline["traffic"] = tr["dram_bytes_per_launch"]
+        roofline["traffic_source"] = tr["source"]
+    except Exception:
+        pass
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         roofline["hbm"]["peak_gbs_measured"] = peaks.get("hbm_gbs")

@@ -11,6 +11,8 @@ KEYS = ["gpu__time_duration.sum", "sm__cycles_elapsed.avg", "sm__cycles_active.a
         "launch__occupancy_limit_shared_mem", "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__warps_eligible.avg.per_cycle_active",
         "smsp__thread_inst_executed_pred_on_per_inst_executed.ratio"]
 OUT = sys.argv[2] if len(sys.argv) > 2 else R
+import json
+TRAFFIC = {}
 for cfg, kern in (("c2", "k_score_fast"), ("c3", "k_score_fast"), ("c2", "k_sample_solve"), ("c2", "k_tail")):
     rep = f"gpurun_out/prof_{cfg}_{kern}_{R}.ncu-rep"
     if not os.path.exists(rep):
@@ -26,6 +28,14 @@ for cfg, kern in (("c2", "k_score_fast"), ("c3", "k_score_fast"), ("c2", "k_samp
             for h, u, v in zip(hdr, units, r):
                 if h in KEYS or "issue_stalled" in h and "per_issue_active" in h:
                     f.write(f"{h:90s} {u:16s} {v}\n")
+            scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+            tr = 0.0
+            for h, u, v in zip(hdr, units, r):
+                if h in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                    tr += float(v.replace(",", "")) * scale.get(u, 1.0)
+            TRAFFIC.setdefault(cfg.upper(), {})[kern] = {"dram_bytes_per_launch": tr, "source": f"profiles/{OUT}_ncu_full_{kern}_{cfg}.txt"}
+if TRAFFIC:
+    json.dump(TRAFFIC, open("profiles/traffic.json", "w"), indent=1)
 rows = [r for r in csv.reader(open(f"gpurun_out/launches_c2_{R}.csv")) if len(r) > 10 and r[0].isdigit()]
 agg = collections.OrderedDict()
 for r in rows:
