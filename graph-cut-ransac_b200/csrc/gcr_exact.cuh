@@ -50,7 +50,8 @@ struct Model4
 // two_sift.hpp:621-645 with the identity normaliser (model.h:42-55, S6); model.h:194-204
 // `original`: the residual of three_sift_original.hpp:293-317, |log(rectified / alpha^3)| (its alpha is the reciprocal
 // class scale); otherwise three_sift.hpp:293-317 == two_sift.hpp:621-645, |log(alpha^3 * rectified)|.
-__device__ __forceinline__ double scale_residual(double x, double y, double s, const Model4& m, bool original = false)
+// (not inlined: one copy per kernel keeps the cold-start instruction footprint of the tail small)
+__device__ __noinline__ double scale_residual(double x, double y, double s, const Model4& m, bool original = false)
 {
     const double rectified = s * pow(-m.h7 * x - m.h8 * y + 1.0, -3.0);
     if (rectified < 1e-9) return DBL_MAX;
@@ -59,7 +60,7 @@ __device__ __forceinline__ double scale_residual(double x, double y, double s, c
 }
 
 // two_sift.hpp:647-665; model.h:156-165
-__device__ __forceinline__ double orientation_residual(double x, double y, double t, const Model4& m)
+__device__ __noinline__ double orientation_residual(double x, double y, double t, const Model4& m)
 {
     double st, ct;
     sincos(t, &st, &ct);

@@ -13,8 +13,10 @@ for lib in libs:
     gcr_capi.LIB_PATH = os.path.join(ROOT, lib)
     e = gcr_capi.Engine(0); e.set_features(sc.scale, sc.orient); engines.append(e)
 res = {lib: ([], []) for lib in libs}
+flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda") if os.environ.get("FLUSH") else None  # > L2: cold caches per run, as bench.py
 for rnd in range(12):
     for lib, e in zip(libs, engines):
+        if flush is not None: flush.zero_(); torch.cuda.synchronize()
         r = e.run(c["n_hyp"], sc.thr, samples_ptr=smp.data_ptr())
         if rnd >= 2:
             res[lib][0].append(r.score_kernel_ms); res[lib][1].append(r.device_ms)
