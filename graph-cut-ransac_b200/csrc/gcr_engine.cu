@@ -774,7 +774,13 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
         GCR_CUDA(cudaEventRecord(h->evk1, s));
     }
     {
-        double rel_tol = 4e-5;
+        // Candidate window: hypotheses whose FP32-path value is within rel_tol of the best one are re-scored in FP64.
+        // The FP32 value error per inlier is ~ 2 (delta d) / T' (scale: MUFU.LG2 + roundings, delta d ~ 4e-7) and
+        // ~ 2 (delta t) / sqrt(tsq) (orientation), i.e. it grows as the thresholds tighten; 4e-5 was validated at the
+        // default thresholds (T' = 0.096, sqrt(tsq_o) = 0.0785) and is scaled from there, with a factor 2 on top.
+        double rel_tol = 2.0 * std::max(2e-5, 4e-5 * 0.096 / static_cast<double>(T.Tp));
+        if (h->problem == 0) rel_tol = std::max(rel_tol, 2.0 * 4e-5 * 0.0785 / std::sqrt(T.tsq[1]));
+        rel_tol = std::min(rel_tol, 0.05);
         void* args[] = {&B, const_cast<Thresholds*>(&T), &rel_tol};
         GCR_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(k_tail), dim3(h->tail_grid), dim3(kExactThreads), args, 0, s));
     }
@@ -782,7 +788,10 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
     if (flags & (GCR_RUN_KEEP_PER_HYP | GCR_RUN_EMIT_MASKS))
     {
         // reporting modes: FP64 re-scoring of the low-margin hypotheses (see k_refine_collect); off the timed stage
-        k_refine_collect<<<hb, 128, 0, s>>>(B);
+        // tighter-than-default thresholds amplify the FP32 path's relative score error past the 1e-5 reporting bar for
+        // every hypothesis, not only the low-margin ones: re-score them all
+        const int refine_all = (T.Tp < 0.7f * 0.096f || (h->problem == 0 && std::sqrt(T.tsq[1]) < 0.7 * 0.0785)) ? 1 : 0;
+        k_refine_collect<<<hb, 128, 0, s>>>(B, refine_all);
         k_exact_items<<<h->n_sm * 8, kExactThreads, 0, s>>>(B, T, 0);
         k_refine_finalize<<<h->n_sm, 256, 0, s>>>(B, T);
         k_refine_done<<<1, 1, 0, s>>>(B);

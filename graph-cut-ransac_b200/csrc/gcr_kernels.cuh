@@ -429,7 +429,7 @@ __device__ __forceinline__ void exact_items_phase(const Buffers& B, const Thresh
 {
     __shared__ unsigned long long red[kExactThreads / 32];
     __shared__ unsigned int redc[kExactThreads / 32];
-    const unsigned int n_items = mode == 0 ? __ldcg(&B.ctr->n_hard) : (mode == 1 ? min(__ldcg(&B.ctr->n_candidates), static_cast<unsigned>(kCandCap)) : n_direct);
+    const unsigned int n_items = mode == 0 ? __ldcg(&B.ctr->n_hard) : (mode == 1 ? min(__ldcg(&B.ctr->n_candidates) - n_direct, static_cast<unsigned>(kCandCap)) : n_direct);
     const unsigned int ups = (B.ns + kExactThreads - 1) / kExactThreads, upo = (B.no + kExactThreads - 1) / kExactThreads;
     const unsigned int upi = ups + upo;
     const unsigned long long n_units = static_cast<unsigned long long>(n_items) * upi;
@@ -597,36 +597,48 @@ __device__ __forceinline__ void finalize_phase(const Buffers& B, const Threshold
 
 // collect: hypotheses whose FP32-path score is within the path's error of the best one are re-scored in FP64
 // so that the selection rule sees reference-order scores.
-__device__ __forceinline__ void collect_candidate(const Buffers& B, unsigned int h)
+// Candidate slots are handed out from cumulative counters (slot = ticket - cand_base of this round).  A hypothesis that
+// finds the 1024 slots of the round taken is marked "deferred" (flag bit 16) and collected by a later round.
+__device__ __forceinline__ void collect_candidate(const Buffers& B, unsigned int h, unsigned int base, unsigned char f)
 {
-    const unsigned int slot = atomicAdd(&B.ctr->n_candidates, 1u);
+    const unsigned int slot = atomicAdd(&B.ctr->n_candidates, 1u) - base;
     if (slot < kCandCap)
     {
         B.cand_hyp[slot] = h;
         B.cand_model[slot] = B.models[h];
         B.cand_qsum[2 * slot] = B.cand_qsum[2 * slot + 1] = 0ull;
         B.cand_rawcnt[2 * slot] = B.cand_rawcnt[2 * slot + 1] = 0u;
+        if (f & 16) B.flags[h] = f & ~16;
     }
     else
+    {
         atomicAdd(&B.ctr->n_cand_overflow, 1u);
+        if (!(f & 16)) B.flags[h] = f | 16;
+    }
 }
 
-__device__ __forceinline__ void collect_phase(const Buffers& B, const Thresholds& T, double rel_tol)
+// round 0: every model-valid hypothesis inside the window; later rounds: the deferred ones
+__device__ __forceinline__ void collect_phase(const Buffers& B, const Thresholds& T, double rel_tol, int round, unsigned int base)
 {
     const unsigned long long bk = __ldcg(&B.ctr->best_key);
     if (bk == 0ull) return;
     const double best = from_ordered_bits(bk);
     const double floor_v = best - rel_tol * best;
-    if (tail_direct(B))
+    if (tail_direct(B) || round > 0)
     {
         for (int h = blockIdx.x * blockDim.x + threadIdx.x; h < B.n_hyp; h += gridDim.x * blockDim.x)
         {
             const unsigned char f = B.flags[h];
             if ((f & 6) != 6) continue; // solved and model-valid
+            if (round > 0)
+            {
+                if (f & 16) collect_candidate(B, h, base, f);
+                continue;
+            }
             unsigned int n0, n1;
             const double v = B.per_hyp ? B.score[h] : hyp_value(B, T, h, f, n0, n1);
             if (!(v > 0.0) || v < floor_v) continue;
-            collect_candidate(B, h);
+            collect_candidate(B, h, base, f);
         }
         return;
     }
@@ -640,7 +652,7 @@ __device__ __forceinline__ void collect_phase(const Buffers& B, const Thresholds
         unsigned int n0, n1;
         const double v = hyp_value(B, T, h, f, n0, n1); // the same arithmetic on the same inputs as in finalize
         if (!(v > 0.0) || v < floor_v) continue;
-        collect_candidate(B, h);
+        collect_candidate(B, h, base, f);
     }
 }
 
@@ -744,13 +756,15 @@ __device__ __forceinline__ void exchange_records(const Buffers& B, unsigned long
 // select (one block): final selection (GCRANSAC.h:440-462): highest exact score, earliest hypothesis on ties; writes
 // the winner record (also into the caller's buffer, e.g. an NCCL send buffer) and the winner's packed masks; then
 // snapshots the run counters into the result block for the host and clears them for the next run.
-__device__ __forceinline__ void select_phase(const Buffers& B, const Thresholds& T)
+// One round of the selection: best of this round's candidates (score, then lowest hypothesis index: S11), merged with
+// the running best of earlier rounds (kept in the result block).  `final`: no deferred candidates remain.
+__device__ __forceinline__ void select_phase(const Buffers& B, const Thresholds& T, int round, bool final, unsigned int cand_base)
 {
     __shared__ double s_val[kExactThreads / 32];
     __shared__ unsigned int s_h[kExactThreads / 32], s_i[kExactThreads / 32];
     __shared__ unsigned int s_hyp, s_slot;
     __shared__ unsigned long long s_rec[8];
-    const unsigned int n = min(__ldcg(&B.ctr->n_candidates), static_cast<unsigned>(kCandCap));
+    const unsigned int n = min(__ldcg(&B.ctr->n_candidates) - cand_base, static_cast<unsigned>(kCandCap));
     // every thread: value of its candidates and its own best (score, then lowest hypothesis index)
     double best = 0.0;
     unsigned int bh = 0xffffffffu, bs = 0;
@@ -779,15 +793,25 @@ __device__ __forceinline__ void select_phase(const Buffers& B, const Thresholds&
     {
         for (unsigned int w = 1; w < blockDim.x / 32; w++)
             if (s_val[w] > best || (s_val[w] == best && best > 0.0 && s_h[w] < bh)) { best = s_val[w]; bh = s_h[w]; bs = s_i[w]; }
-        s_hyp = bh;
-        s_slot = bs;
         Record r;
         r.score = 0.0;
         r.index = -1;
         r.model[0] = r.model[1] = r.model[2] = r.model[3] = 0.0;
         r.n_inl[0] = r.n_inl[1] = 0;
         r.reserved = 0;
-        if (bh != 0xffffffffu)
+        bool keep_running = false;
+        if (round > 0)
+        {
+            // running best of the earlier rounds (its masks are already in the result block)
+            const Record run = *reinterpret_cast<const Record*>(B.record);
+            const long long cand_index = bh != 0xffffffffu ? static_cast<long long>(B.first_hyp + bh) : -1;
+            if (run.index >= 0 && !(bh != 0xffffffffu && (best > run.score || (best == run.score && cand_index < run.index))))
+            {
+                r = run;
+                keep_running = true;
+            }
+        }
+        if (!keep_running && bh != 0xffffffffu)
         {
             const Model4 m = B.cand_model[bs];
             r.score = best;
@@ -796,6 +820,8 @@ __device__ __forceinline__ void select_phase(const Buffers& B, const Thresholds&
             r.n_inl[0] = B.cand_cnt[2 * bs];
             r.n_inl[1] = B.cand_cnt[2 * bs + 1];
         }
+        s_hyp = keep_running ? 0xfffffffeu : bh; // 0xfffffffe: keep the masks of the running best
+        s_slot = bs;
         *reinterpret_cast<Record*>(s_rec) = r;
     }
     __syncthreads();
@@ -805,25 +831,29 @@ __device__ __forceinline__ void select_phase(const Buffers& B, const Thresholds&
 #pragma unroll
         for (int k = 0; k < 8; k++) w[k] = s_rec[k];
         unsigned int winner_rank = B.xchg_world > 1 ? static_cast<unsigned int>(B.xchg_rank) : 0u;
-        if (B.xchg_world > 1) exchange_records(B, w, winner_rank); // the GLOBAL winner replaces the local record
+        if (final && B.xchg_world > 1) exchange_records(B, w, winner_rank); // the GLOBAL winner replaces the local record
         if (threadIdx.x == 0)
         {
-            w[7] = winner_rank; // gcr_record.reserved: rank that owns the winning hypothesis
+            if (final) w[7] = winner_rank; // gcr_record.reserved: rank that owns the winning hypothesis
             unsigned long long* out = reinterpret_cast<unsigned long long*>(B.record);
             unsigned long long* usr = reinterpret_cast<unsigned long long*>(B.record_user);
 #pragma unroll
             for (int k = 0; k < 8; k++)
             {
                 out[k] = w[k];
-                if (usr) usr[k] = w[k];
+                if (final && usr) usr[k] = w[k];
             }
-            *B.ctr_snap = B.ctr[0];
-            Counters z;
-            memset(&z, 0, sizeof(z));
-            B.ctr[0] = z;
+            if (final)
+            {
+                *B.ctr_snap = B.ctr[0];
+                Counters z;
+                memset(&z, 0, sizeof(z));
+                B.ctr[0] = z;
+            }
         }
     }
     __syncthreads();
+    if (s_hyp == 0xfffffffeu) return;
     const bool have = s_hyp != 0xffffffffu;
     for (int w = threadIdx.x; w < B.wmask; w += blockDim.x)
         B.best_masks[w] = have ? B.cand_masks[static_cast<size_t>(s_slot) * B.wmask + w] : 0u;
@@ -844,13 +874,27 @@ __global__ void __launch_bounds__(kExactThreads) k_tail(const __grid_constant__ 
     finalize_phase(B, T);
     grid.sync();
     if (stamp) B.phase_ns[2] = global_ns();
-    collect_phase(B, T, rel_tol);
-    grid.sync();
-    if (stamp) B.phase_ns[3] = global_ns();
-    exact_items_phase(B, T, 1, 0u);
-    grid.sync();
-    if (stamp) B.phase_ns[4] = global_ns();
-    if (blockIdx.x == 0) select_phase(B, T);
+    // Candidate rounds: one, unless more than kCandCap hypotheses sit inside the window (massive ties).  The candidate
+    // counters are cumulative; every CTA tracks the bases of the current round in registers (the counters are stable
+    // between the barrier after a collect phase and the next collect phase, so all CTAs read the same values).
+    unsigned int cand_base = 0u, ovf_base = 0u;
+    for (int round = 0;; round++)
+    {
+        collect_phase(B, T, rel_tol, round, cand_base);
+        grid.sync();
+        if (stamp && round == 0) B.phase_ns[3] = global_ns();
+        exact_items_phase(B, T, 1, cand_base);
+        grid.sync();
+        if (stamp && round == 0) B.phase_ns[4] = global_ns();
+        // '>' (not '!='): in the last round the selecting CTA zeroes the counters while slower CTAs may still be reading
+        const unsigned int cand_now = __ldcg(&B.ctr->n_candidates), ovf_now = __ldcg(&B.ctr->n_cand_overflow);
+        const bool more = ovf_now > ovf_base;
+        if (blockIdx.x == 0) select_phase(B, T, round, !more, cand_base);
+        if (!more) break;
+        cand_base = cand_now;
+        ovf_base = ovf_now;
+        grid.sync(); // the running best is in the result block before the next round's selection reads it
+    }
     if (stamp) B.phase_ns[5] = global_ns();
 }
 
@@ -859,14 +903,14 @@ __global__ void __launch_bounds__(kExactThreads) k_tail(const __grid_constant__ 
 // cancels when the inliers sit near the threshold, which amplifies the FP32 path's ~4e-6 n absolute error beyond the
 // 1e-5 relative bar for low-score hypotheses (never contenders).  Those with value < 0.6 n are re-scored by the FP64
 // reference-order kernel after the tail: collect -> k_exact_items(mode 0) -> refinalize.
-__global__ void k_refine_collect(Buffers B)
+__global__ void k_refine_collect(Buffers B, int refine_all)
 {
     const int h = blockIdx.x * blockDim.x + threadIdx.x;
     if (h >= B.n_hyp) return;
     const unsigned char f = B.flags[h];
     if (!(f & 2) || (f & 8)) return;
     const unsigned int n = B.n_inl[2 * h] + B.n_inl[2 * h + 1];
-    if (n == 0u || !(B.score[h] < 0.6 * static_cast<double>(n))) return;
+    if (n == 0u || !(refine_all || B.score[h] < 0.6 * static_cast<double>(n))) return;
     B.hard_hyp[atomicAdd(&B.ctr->n_hard, 1u)] = h;
     reinterpret_cast<unsigned long long*>(B.sums)[2 * h] = 0ull; // fixed-point accumulators of k_exact_items
     reinterpret_cast<unsigned long long*>(B.sums)[2 * h + 1] = 0ull;

@@ -297,3 +297,75 @@ def test_batched_model_scoring_vs_oracle(eng, port):
         assert np.array_equal(unpack_mask(lab[k, ws:], 333), ro * ro <= tsq[1])
     with pytest.raises(Exception):
         eng.score_models(np.zeros((1025, 4)), sc.thr)
+
+
+def test_randomised_scenes_vs_oracle(eng, port):
+    """40 seeded scenes of ragged sizes, thresholds from tight to loose, different inlier ratios, with awkward rows
+    injected (duplicates, zero / negative / tiny / huge scales, repeated and out-of-range angles, far-away points):
+    every per-hypothesis output against the CPU oracle on the same replayed samples."""
+    import gcr_scenes as gs
+    rng = np.random.Generator(np.random.PCG64(20261104))
+    n_solved = 0
+    for case in range(40):
+        ns, no = int(rng.integers(2, 700)), int(rng.integers(2, 400))
+        ratio = float(rng.choice([0.05, 0.2, 0.5, 0.9]))
+        lvl = float(rng.choice([0.25, 1.0, 3.0, 8.0, 25.0]))
+        sc = gs.make_scene(ns, no, ratio, 5000 + case, thr_scale=0.05 * lvl, thr_orient=math.radians(lvl))
+        scale, orient = sc.scale.copy(), sc.orient.copy()
+        if case % 3 == 0 and ns > 12 and no > 12:
+            scale[3] = scale[2]
+            scale[5, 2] = 0.0
+            scale[6, 2] = -1.5
+            scale[7, :2] = [3e5, -2e5]
+            scale[8, 2] = 1e-11
+            scale[9, 2] = 1e11
+            orient[4] = orient[1]
+            orient[6, 2] = orient[5, 2]
+            # (two orientation features at the SAME position put the vanishing point on a hull vertex, where the sign of an
+            #  exactly-zero cross product is decided by the last ulp of sin/cos: see the edge fixture, which skips those slots)
+            orient[8, 2] = orient[5, 2] + math.pi
+            orient[9, 2] = 9.5 * math.pi
+            orient[10, 2] = -2.75 * math.pi
+        H = int(rng.integers(1, 1500))
+        smp = gs.draw_samples(H, ns, no, 900 + case)
+        if case % 3 == 0 and ns > 12 and no > 12 and H > 64:
+            smp[:64, :2] = rng.integers(0, 11, (64, 2))
+            smp[:64, 2:] = rng.integers(0, 11, (64, 2))
+            same = smp[:64, 0] == smp[:64, 1]
+            smp[:64, 1][same] = (smp[:64, 1][same] + 1) % 11
+            same = smp[:64, 2] == smp[:64, 3]
+            smp[:64, 3][same] = (smp[:64, 3][same] + 1) % 11
+        ora = port.replay(scale, orient, smp, sc.thr, nthreads=0)
+        res, dev = _run_replay(eng, scale, orient, smp, sc.thr)
+        _compare(dev, ora, ns, no, label=f"random case {case} ({ns}+{no} features, level {lvl}, {H} hypotheses)")
+        want = port.select_best(ora["score"], ora["flags"])
+        tie = np.isclose(ora["score"], ora["score"][want], rtol=1e-12) & ((ora["flags"] & 4) > 0) if want >= 0 else None
+        if want < 0 or tie.sum() == 1:
+            assert res.best_index == want, case
+        n_solved += int(((ora["flags"] & 2) > 0).sum())
+    assert n_solved > 2000
+
+
+def test_thousands_of_tied_hypotheses_select_the_earliest(eng, port):
+    """More near-best hypotheses than the re-scoring pass holds at once (1024): a scene whose minimal samples all come from
+    a handful of exactly consistent features, so that thousands of hypotheses tie; the reference keeps the first (S11)."""
+    import gcr_scenes as gs
+    sc = gs.make_scene(40, 30, 1.0, 77, thr_scale=0.2, thr_orient=math.radians(3.0))
+    # noise-free inliers: regenerate the scale / orientation values exactly from the ground-truth model
+    scale, orient = sc.scale.copy(), sc.orient.copy()
+    h7, h8, alpha, phi = sc.model
+    w = 1.0 - h7 * scale[:, 0] - h8 * scale[:, 1]
+    scale[:, 2] = (w / alpha) ** 3
+    H = 6000
+    smp = gs.draw_samples(H, 40, 30, 3)
+    smp[:, :2] = smp[0, :2]  # every hypothesis uses the same two scale features ...
+    smp[:, 2:] = smp[np.arange(H) % 2, 2:]  # ... and one of 2 orientation pairs: 2 distinct models, 3000 copies each
+    ora = port.replay(scale, orient, smp, sc.thr, nthreads=0)
+    want = port.select_best(ora["score"], ora["flags"])
+    assert want >= 0
+    n_tied = int(np.sum(ora["score"] == ora["score"][want]))
+    assert n_tied > 2000  # more than the 1024 candidate slots of one re-scoring pass
+    res, dev = _run_replay(eng, scale, orient, smp, sc.thr)
+    _compare(dev, ora, 40, 30, label="ties")
+    assert res.best_index == want, (res.best_index, want, n_tied, res.n_candidates)
+    assert res.best_score == pytest.approx(ora["score"][want], rel=1e-12)
