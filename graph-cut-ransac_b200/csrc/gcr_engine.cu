@@ -8,6 +8,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <string>
 #include <vector>
 #include <algorithm>
@@ -21,7 +22,6 @@ using namespace gcr;
 static_assert(sizeof(Record) == sizeof(gcr_record), "record layout");
 static_assert(sizeof(Model4) == 32, "model layout");
 static_assert(sizeof(Counters) == 64, "counters layout");
-constexpr size_t kResultHeaderWords = 48; // record (16) + counters (16) + phase stamps (16)
 
 template <typename T>
 struct DevBuf
@@ -87,6 +87,8 @@ struct gcr_engine_s
     // features
     int ns = 0, no = 0, ncs = 0, nco = 0;
     DevBuf<double> d_scale, d_orient;
+    const double* prep_src_scale = nullptr; // set_features from mapped host memory: what k_prep_features reads (else null)
+    const double* prep_src_orient = nullptr;
     const double* scale_ptr = nullptr; // adopted or owned
     const double* orient_ptr = nullptr;
     DevBuf<float> d_fs, d_fo;
@@ -141,7 +143,7 @@ struct gcr_engine_s
     bool peer_ipc[kMaxPeers] = {};
     int xchg_world = 0, xchg_rank = 0;
     unsigned long long xchg_seq = 0;
-    bool last_run_exchanged = false;
+    bool last_run_exchanged = false, last_run_mirrored = false;
     double last_thr[2] = {-1.0, -1.0};
 
     int fail(int code, const std::string& msg)
@@ -305,6 +307,7 @@ Buffers make_buffers(gcr_engine_s* h, unsigned long long seed, bool have_samples
     B.phase_ns = reinterpret_cast<unsigned long long*>(h->d_best.p + 32);
     B.record_user = record_user;
     B.best_masks = h->d_best.p + kResultHeaderWords;
+    B.host_block = nullptr;
     for (int p = 0; p < kMaxPeers; p++) B.xchg_peer[p] = static_cast<unsigned long long*>(h->peer_ptr[p]);
     B.xchg_world = 0; // set by gcr_run for exchanging runs
     B.xchg_rank = h->xchg_rank;
@@ -367,6 +370,18 @@ static int peer_buffer(gcr_engine_s* h)
     return GCR_OK;
 }
 
+// device-side address of a page-locked, device-mapped host array (nullptr for pageable memory or when disabled)
+static const double* mapped_host_pointer(const void* p)
+{
+    static const bool disabled = std::getenv("GCR_NO_ZEROCOPY") != nullptr;
+    cudaPointerAttributes attr;
+    if (!disabled && p && cudaPointerGetAttributes(&attr, p) == cudaSuccess && attr.type == cudaMemoryTypeHost && attr.devicePointer &&
+        reinterpret_cast<uintptr_t>(attr.devicePointer) % 8 == 0)
+        return static_cast<const double*>(attr.devicePointer);
+    cudaGetLastError();
+    return nullptr;
+}
+
 // Derived feature planes of the rows at h->scale_ptr / h->orient_ptr (device memory), sizes in h->ns / h->no
 static int finish_features(gcr_handle h)
 {
@@ -386,9 +401,13 @@ static int finish_features(gcr_handle h)
     GCR_CUDA(h->d_scene.ensure(1));
     GCR_CUDA(cudaMemsetAsync(h->d_scene.p, 0, sizeof(Scene), h->stream));
     const int n = std::max(h->ncs, h->nco) * kChunk;
-    k_prep_features<<<(n + 255) / 256, 256, 0, h->stream>>>(h->scale_ptr, h->ns, h->orient_ptr, h->no, h->d_fs.p,
+    const bool in_place = h->prep_src_scale != nullptr;
+    k_prep_features<<<(n + 255) / 256, 256, 0, h->stream>>>(in_place ? h->prep_src_scale : h->scale_ptr, h->ns,
+                                                           in_place && h->prep_src_orient ? h->prep_src_orient : h->orient_ptr, h->no, h->d_fs.p,
                                                            h->d_fo.p, h->ncs, h->nco, h->d_fsd.p, h->d_fod.p, h->ncsd, h->ncod, h->d_scene.p, h->d_irr_s.p,
-                                                           h->d_irr_o.p, h->d_aux_s.p, h->d_aux_o.p, h->problem);
+                                                           h->d_irr_o.p, h->d_aux_s.p, h->d_aux_o.p, h->problem, in_place ? h->d_scale.p : nullptr,
+                                                           in_place && h->prep_src_orient ? h->d_orient.p : nullptr);
+    h->prep_src_scale = h->prep_src_orient = nullptr;
     GCR_CUDA(cudaGetLastError());
     return ensure_common(h);
 }
@@ -517,8 +536,16 @@ int gcr_set_features(gcr_handle h, const double* scale, int64_t ns, const double
     {
         GCR_CUDA(h->d_scale.ensure(3 * static_cast<size_t>(ns)));
         GCR_CUDA(h->d_orient.ensure(3 * static_cast<size_t>(no)));
-        GCR_CUDA(cudaMemcpyAsync(h->d_scale.p, scale, sizeof(double) * 3 * ns, cudaMemcpyHostToDevice, h->stream));
-        if (no > 0) GCR_CUDA(cudaMemcpyAsync(h->d_orient.p, orient, sizeof(double) * 3 * no, cudaMemcpyHostToDevice, h->stream));
+        // page-locked, device-mapped host arrays are read in place by the preparation kernel, which then also writes the
+        // device copy (no separate host-to-device copies in front of it)
+        h->prep_src_scale = mapped_host_pointer(scale);
+        h->prep_src_orient = no > 0 ? mapped_host_pointer(orient) : nullptr;
+        if (!h->prep_src_scale || (no > 0 && !h->prep_src_orient))
+        {
+            h->prep_src_scale = h->prep_src_orient = nullptr;
+            GCR_CUDA(cudaMemcpyAsync(h->d_scale.p, scale, sizeof(double) * 3 * ns, cudaMemcpyHostToDevice, h->stream));
+            if (no > 0) GCR_CUDA(cudaMemcpyAsync(h->d_orient.p, orient, sizeof(double) * 3 * no, cudaMemcpyHostToDevice, h->stream));
+        }
         h->scale_ptr = h->d_scale.p;
         h->orient_ptr = h->d_orient.p;
     }
@@ -740,10 +767,36 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
         if (flags & GCR_RUN_SAMPLES_ON_DEVICE)
             h->samples_view = samples; // read in place: the caller keeps the array alive until the run has finished
         else
-            GCR_CUDA(cudaMemcpyAsync(h->d_samples.p, samples, sizeof(int) * 4 * H, cudaMemcpyHostToDevice, s));
+        {
+            // Page-locked, device-mapped host memory is read IN PLACE by the sampler/solver kernel (one coalesced 16-byte read
+            // per hypothesis): the PCIe transfer then overlaps that kernel instead of preceding it.  As with any asynchronous
+            // copy from pinned memory, the caller must leave the array alone until the run has finished.
+            const int* mapped = nullptr;
+            cudaPointerAttributes attr;
+            static const bool no_zero_copy = std::getenv("GCR_NO_ZEROCOPY") != nullptr;
+            if (!no_zero_copy && cudaPointerGetAttributes(&attr, samples) == cudaSuccess && attr.type == cudaMemoryTypeHost &&
+                attr.devicePointer != nullptr && reinterpret_cast<uintptr_t>(attr.devicePointer) % 16 == 0)
+                mapped = static_cast<const int*>(attr.devicePointer);
+            else
+                cudaGetLastError(); // pageable memory: cudaPointerGetAttributes may leave an error state on old drivers
+            if (mapped)
+                h->samples_view = mapped;
+            else
+                GCR_CUDA(cudaMemcpyAsync(h->d_samples.p, samples, sizeof(int) * 4 * H, cudaMemcpyHostToDevice, s));
+        }
     }
     const Thresholds T = make_thresholds(thr, h->problem);
     Buffers B = make_buffers(h, seed, samples != nullptr, d_record);
+    {
+        // the tail writes the result block straight into the pinned staging buffer (device-mapped): no copy after the run
+        static const bool no_mirror = std::getenv("GCR_NO_ZEROCOPY") != nullptr;
+        void* dp = nullptr;
+        // (only for synchronous runs, out != NULL: an asynchronous caller that reads nothing back should not pay the ~2 us the
+        //  host writes add to the tail)
+        h->last_run_mirrored = out != nullptr && !no_mirror && cudaHostGetDevicePointer(&dp, h->h_best, 0) == cudaSuccess && dp != nullptr;
+        if (h->last_run_mirrored) B.host_block = static_cast<unsigned int*>(dp);
+        else cudaGetLastError();
+    }
     h->have_per_hyp = (flags & (GCR_RUN_KEEP_PER_HYP | GCR_RUN_EMIT_MASKS)) != 0;
     B.per_hyp = h->have_per_hyp ? 1 : 0;
     const int all_exact = (flags & GCR_RUN_ALL_EXACT) ? 1 : 0;
@@ -803,7 +856,7 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
     {
         Counters c;
         Record r;
-        GCR_CUDA(cudaMemcpyAsync(h->h_best, h->d_best.p, 4 * kResultHeaderWords, cudaMemcpyDeviceToHost, s));
+        if (!h->last_run_mirrored) GCR_CUDA(cudaMemcpyAsync(h->h_best, h->d_best.p, 4 * kResultHeaderWords, cudaMemcpyDeviceToHost, s));
         GCR_CUDA(cudaStreamSynchronize(s));
         std::memcpy(&r, h->h_best, sizeof(r));
         std::memcpy(&c, h->h_best + 16, sizeof(c));
@@ -843,8 +896,9 @@ int gcr_best(gcr_handle h, double model[4], double* score, uint32_t n_inl[2], ui
     GCR_CUDA(cudaSetDevice(h->device));
     const size_t ws = (h->ns + 31) / 32, wo = (h->no + 31) / 32;
     const bool want_masks = scale_mask_words || orient_mask_words;
-    GCR_CUDA(cudaMemcpyAsync(h->h_best, h->d_best.p, sizeof(unsigned int) * (want_masks ? kResultHeaderWords + ws + wo : 16), cudaMemcpyDeviceToHost,
-                             h->stream));
+    if (!h->last_run_mirrored)
+        GCR_CUDA(cudaMemcpyAsync(h->h_best, h->d_best.p, sizeof(unsigned int) * (want_masks ? kResultHeaderWords + ws + wo : 16),
+                                 cudaMemcpyDeviceToHost, h->stream));
     GCR_CUDA(cudaStreamSynchronize(h->stream));
     Record r;
     std::memcpy(&r, h->h_best, sizeof(r));

@@ -34,7 +34,7 @@ __global__ void k_prep_features(const double* __restrict__ scale, int ns, const 
                                 float* __restrict__ fs, float* __restrict__ fo, int ncs, int nco,
                                 double* __restrict__ fsd, double* __restrict__ fod, int ncsd, int ncod, Scene* scene,
                                 unsigned int* irr_s, unsigned int* irr_o, double* __restrict__ aux_s, double* __restrict__ aux_o,
-                                int problem)
+                                int problem, double* __restrict__ scale_copy, double* __restrict__ orient_copy)
 {
     constexpr int kCD = kChunk / 2; // features per FP64 chunk (same byte size as an FP32 chunk)
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -47,6 +47,12 @@ __global__ void k_prep_features(const double* __restrict__ scale, int ns, const 
         if (i < ns)
         {
             const double x = scale[3 * i], y = scale[3 * i + 1], s = scale[3 * i + 2];
+            if (scale_copy) // the rows were read in place from pinned host memory: keep the device copy the other kernels use
+            {
+                scale_copy[3 * i] = x;
+                scale_copy[3 * i + 1] = y;
+                scale_copy[3 * i + 2] = s;
+            }
             // the minimal solvers' third column (two_sift.hpp:288-299, three_sift.hpp:153-160, three_sift_original.hpp):
             // a per-FEATURE value, evaluated here once with the very function the solver would call per hypothesis
             aux_s[i] = problem == 2 ? pow(s, -1.0 / 3.0) : pow(s, 1.0 / 3.0);
@@ -90,6 +96,12 @@ __global__ void k_prep_features(const double* __restrict__ scale, int ns, const 
         if (i < no)
         {
             const double x = orient[3 * i], y = orient[3 * i + 1], t = orient[3 * i + 2];
+            if (orient_copy)
+            {
+                orient_copy[3 * i] = x;
+                orient_copy[3 * i + 1] = y;
+                orient_copy[3 * i + 2] = t;
+            }
             double st, ct;
             sincos(t, &st, &ct);
             aux_o[2 * i] = st; // lineFromPointAndAngle's sine / cosine (math_utils.hpp:104-109), per feature
@@ -853,10 +865,21 @@ __device__ __forceinline__ void select_phase(const Buffers& B, const Thresholds&
         }
     }
     __syncthreads();
-    if (s_hyp == 0xfffffffeu) return;
-    const bool have = s_hyp != 0xffffffffu;
-    for (int w = threadIdx.x; w < B.wmask; w += blockDim.x)
-        B.best_masks[w] = have ? B.cand_masks[static_cast<size_t>(s_slot) * B.wmask + w] : 0u;
+    if (s_hyp != 0xfffffffeu)
+    {
+        const bool have = s_hyp != 0xffffffffu;
+        for (int w = threadIdx.x; w < B.wmask; w += blockDim.x)
+            B.best_masks[w] = have ? B.cand_masks[static_cast<size_t>(s_slot) * B.wmask + w] : 0u;
+    }
+    if (final && B.host_block)
+    {
+        // mirror of the result block in page-locked host memory: the caller needs no device-to-host copy after the run,
+        // only the stream synchronisation ([record 16 words][counters 16][phase stamps 16][winner masks])
+        __syncthreads();
+        const unsigned int* src = reinterpret_cast<const unsigned int*>(B.record);
+        for (int w = threadIdx.x; w < 32; w += blockDim.x) B.host_block[w] = __ldcg(src + w);
+        for (int w = threadIdx.x; w < B.wmask; w += blockDim.x) B.host_block[kResultHeaderWords + w] = __ldcg(B.best_masks + w);
+    }
 }
 
 // The fused tail: fixup + whole-hypothesis FP64 items | finalize | collect | FP64 re-scoring of the candidates | select.
@@ -895,7 +918,12 @@ __global__ void __launch_bounds__(kExactThreads) k_tail(const __grid_constant__ 
         ovf_base = ovf_now;
         grid.sync(); // the running best is in the result block before the next round's selection reads it
     }
-    if (stamp) B.phase_ns[5] = global_ns();
+    if (stamp)
+    {
+        B.phase_ns[5] = global_ns();
+        if (B.host_block)
+            for (int k = 0; k < 8; k++) reinterpret_cast<unsigned long long*>(B.host_block + 32)[k] = B.phase_ns[k];
+    }
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -28,6 +28,7 @@ constexpr int kStages = 6;
 #ifndef GCR_F2
 #define GCR_F2 1
 #endif
+constexpr int kResultHeaderWords = 48; // result block: record (16 words) + counters (16) + phase stamps (16), then the winner's masks
 #ifndef GCR_ITEMS
 #define GCR_ITEMS 16
 #endif
@@ -138,6 +139,7 @@ struct Buffers
     void* record;  // gcr_record (device), engine-owned
     void* record_user; // optional caller-owned copy target
     unsigned int* best_masks; // [W]
+    unsigned int* host_block; // optional: device-mapped pinned host mirror of the whole result block, written by the tail
     // multi-GPU winner exchange over peer memory (NVLink P2P): every rank stores its 64-byte record + a sequence number
     // into slot [parity][rank] of every peer's exchange buffer, then reads the slots of its own buffer
     unsigned long long* xchg_peer[kMaxPeers]; // exchange buffers of all ranks (own one included), device-mapped
