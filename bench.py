@@ -58,6 +58,7 @@ class ClockSampler(threading.Thread):
     def __init__(self, index: int):
         super().__init__(daemon=True)
         self.index, self.sm, self.mx, self.reasons, self.stop_flag, self.active = index, [], [], set(), False, False
+        self.interval = float(os.environ.get("GCR_BENCH_SAMPLE_MS", "2")) * 1e-3
         self.nvml = None
         try:
             import pynvml
@@ -95,7 +96,7 @@ class ClockSampler(threading.Thread):
                     self._sample_nvml() if self.nvml else self._sample_smi()
                 except Exception:
                     pass
-            time.sleep(0.002 if self.nvml else 0.05)
+            time.sleep(self.interval if self.nvml else 0.05)
 
     def summary(self):
         return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": max(self.mx) if self.mx else None,
@@ -201,7 +202,14 @@ def run_ours(args):
     sampler = ClockSampler(local)
     sampler.start()
     torch.cuda.synchronize()
-    sampler.active = True
+    sampler.active = rank == 0 or os.environ.get("GCR_BENCH_SAMPLE_ALL") is not None  # one poller per job: NVML calls can stall that GPU's launches
+    if world > 1:
+        # The ranks leave the host barrier up to milliseconds apart, and every step ends in an exchange that waits for the
+        # slowest rank: a few untimed steps right here absorb that start-up skew, so that the K timed steps measure the
+        # lock-step rate of the job (they are enqueued back to back behind these, with no host synchronisation between).
+        for _ in range(4):
+            flush.zero_()
+            step()
     evs = []
     for _ in range(args.steps):
         flush.zero_()
@@ -290,7 +298,7 @@ def run_ours(args):
         best = e2e_step()
     if world > 1:
         dist.barrier()
-    sampler.active = True
+    sampler.active = rank == 0 or os.environ.get("GCR_BENCH_SAMPLE_ALL") is not None
     t0 = time.perf_counter()
     for _ in range(args.steps):
         best = e2e_step()
