@@ -369,3 +369,38 @@ def test_thousands_of_tied_hypotheses_select_the_earliest(eng, port):
     _compare(dev, ora, 40, 30, label="ties")
     assert res.best_index == want, (res.best_index, want, n_tied, res.n_candidates)
     assert res.best_score == pytest.approx(ora["score"][want], rel=1e-12)
+
+
+def test_pinned_host_inputs_are_read_in_place_with_identical_results(eng, port):
+    """Page-locked host inputs take the zero-copy route (k_prep_features / k_sample_solve read them over PCIe, the tail
+    writes the result block into pinned staging): every output equals the pageable-memory route's."""
+    import ctypes as C
+    import torch
+    import gcr_capi
+    import gcr_scenes as gs
+    sc = gs.make_scene(777, 333, 0.3, 12)
+    smp = gs.draw_samples(5000, 777, 333, 13)
+    eng.set_features(sc.scale, sc.orient)  # pageable numpy arrays: staged copies
+    ref_res = eng.run(len(smp), sc.thr, samples=smp, flags=gcr_capi.RUN_EMIT_MASKS)
+    ref = eng.fetch(masks=True, samples=True)
+    ref_best = eng.best()
+    e = gcr_capi.Engine(0)
+    p_scale, p_orient = torch.from_numpy(sc.scale).pin_memory(), torch.from_numpy(sc.orient).pin_memory()
+    p_smp = torch.from_numpy(smp).pin_memory()
+    assert e.lib.gcr_set_features(e.h, C.c_void_p(p_scale.data_ptr()), 777, C.c_void_p(p_orient.data_ptr()), 333, 0) == 0
+    e.ns, e.no, e.fetch_ns, e.fetch_no = 777, 333, 777, 333
+    thr_c = (C.c_double * 2)(*sc.thr)
+    out = gcr_capi.GcrResult()
+    assert e.lib.gcr_run(e.h, len(smp), 0, 0, C.c_void_p(p_smp.data_ptr()), thr_c, gcr_capi.RUN_EMIT_MASKS, None, C.byref(out)) == 0
+    e.n_hyp = len(smp)
+    got = e.fetch(masks=True, samples=True)
+    for k in ("flags", "models", "n_inl", "masks", "samples"):
+        assert np.array_equal(got[k], ref[k]), k
+    # FP32-path sums of a hypothesis split over several work items are combined with FP64 atomics: last-ulp run-to-run freedom
+    assert np.allclose(got["score"], ref["score"], rtol=1e-12, atol=0.0)
+    assert (out.best_index, out.best_score, tuple(out.best_n_inl)) == (ref_res.best_index, ref_res.best_score, tuple(ref_res.best_n_inl))
+    b = e.best()
+    assert np.array_equal(b["scale_words"], ref_best["scale_words"]) and np.array_equal(b["orient_words"], ref_best["orient_words"])
+    s, o = e.get_features()
+    assert np.array_equal(s, sc.scale) and np.array_equal(o, sc.orient)  # the device copy written by the preparation kernel
+    e.close()
