@@ -819,12 +819,13 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
     k_sample_solve<<<hb, 128, 0, s>>>(B, T, all_exact);
     {
         const int grid = h->score_grid[h->have_masks ? 1 : 0]; // persistent: one CTA per resident slot
-        GCR_CUDA(cudaEventRecord(h->evk0, s));
+        const bool time_kernels = (flags & GCR_RUN_TIME_KERNELS) != 0;
+        if (time_kernels) GCR_CUDA(cudaEventRecord(h->evk0, s));
         if (h->have_masks)
             k_score_fast<true><<<grid, kScoreThreads, sizeof(ScoreSmem), s>>>(B, T);
         else
             k_score_fast<false><<<grid, kScoreThreads, sizeof(ScoreSmem), s>>>(B, T);
-        GCR_CUDA(cudaEventRecord(h->evk1, s));
+        if (time_kernels) GCR_CUDA(cudaEventRecord(h->evk1, s));
     }
     {
         // Candidate window: hypotheses whose FP32-path value is within rel_tol of the best one are re-scored in FP64.
@@ -875,7 +876,7 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
         out->n_exact_hyp = c.n_hard;
         out->n_candidates = c.n_candidates;
         GCR_CUDA(cudaEventElapsedTime(&out->device_ms, h->ev0, h->ev1));
-        GCR_CUDA(cudaEventElapsedTime(&out->score_kernel_ms, h->evk0, h->evk1));
+        if (flags & GCR_RUN_TIME_KERNELS) GCR_CUDA(cudaEventElapsedTime(&out->score_kernel_ms, h->evk0, h->evk1));
         for (int i = 0; i < 5; i++) out->tail_phase_us[i] = static_cast<float>(static_cast<double>(ph[i + 1] - ph[i]) * 1e-3);
         out->tail_phase_us[5] = static_cast<float>(static_cast<double>(ph[0] - ph[7]) * 1e-3); // k_score_fast start -> k_tail start
         out->stage_phase_us[0] = static_cast<float>(static_cast<double>(ph[7] - ph[6]) * 1e-3); // k_sample_solve start -> k_score_fast start
@@ -893,13 +894,16 @@ int gcr_best(gcr_handle h, double model[4], double* score, uint32_t n_inl[2], ui
 {
     if (!h) return GCR_ERR_INVALID;
     if (!h->have_run) return h->fail(GCR_ERR_STATE, "gcr_best before gcr_run");
-    GCR_CUDA(cudaSetDevice(h->device));
     const size_t ws = (h->ns + 31) / 32, wo = (h->no + 31) / 32;
     const bool want_masks = scale_mask_words || orient_mask_words;
     if (!h->last_run_mirrored)
+    {
+        GCR_CUDA(cudaSetDevice(h->device));
         GCR_CUDA(cudaMemcpyAsync(h->h_best, h->d_best.p, sizeof(unsigned int) * (want_masks ? kResultHeaderWords + ws + wo : 16),
                                  cudaMemcpyDeviceToHost, h->stream));
-    GCR_CUDA(cudaStreamSynchronize(h->stream));
+        GCR_CUDA(cudaStreamSynchronize(h->stream));
+    }
+    // (a mirrored run was synchronous: the staging block is complete and the stream idle)
     Record r;
     std::memcpy(&r, h->h_best, sizeof(r));
     if (model) for (int i = 0; i < 4; i++) model[i] = r.model[i];

@@ -15,7 +15,7 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("GCR_B200_LIB", os.path.join(PKG_DIR, "libgcr_b200.so"))  # override: kernel-variant sweeps
 
 FLAG_SAMPLE_VALID, FLAG_SOLVED, FLAG_MODEL_VALID, FLAG_EXACT = 1, 2, 4, 8
-RUN_EMIT_MASKS, RUN_SAMPLES_ON_DEVICE, RUN_KEEP_PER_HYP, RUN_ALL_EXACT, RUN_EXCHANGE = 1, 2, 4, 8, 16
+RUN_EMIT_MASKS, RUN_SAMPLES_ON_DEVICE, RUN_KEEP_PER_HYP, RUN_ALL_EXACT, RUN_EXCHANGE, RUN_TIME_KERNELS = 1, 2, 4, 8, 16, 32
 IPC_HANDLE_BYTES = 64
 PROBLEM_HYBRID, PROBLEM_SCALE_ONLY, PROBLEM_SCALE_ONLY_ORIGINAL = 0, 1, 2
 ERR_INVALID, ERR_CUDA, ERR_STATE, ERR_NOMEM = -1, -2, -3, -4

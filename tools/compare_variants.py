@@ -17,7 +17,7 @@ flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda") if os.environ.g
 for rnd in range(12):
     for lib, e in zip(libs, engines):
         if flush is not None: flush.zero_(); torch.cuda.synchronize()
-        r = e.run(c["n_hyp"], sc.thr, samples_ptr=smp.data_ptr())
+        r = e.run(c["n_hyp"], sc.thr, samples_ptr=smp.data_ptr(), flags=gcr_capi.RUN_TIME_KERNELS)
         if rnd >= 2:
             res[lib][0].append(r.score_kernel_ms); res[lib][1].append(r.device_ms)
 for lib in libs:

@@ -11,7 +11,7 @@ smp = gs.draw_samples(H, 2000, 500, gs.SAMPLE_SEED)
 t = time.time(); ora = Oracle("port").replay(sc.scale, sc.orient, smp, sc.thr, nthreads=0); print("oracle s", time.time() - t, "threads", ora["threads"])
 eng = gcr_capi.Engine(0); eng.set_features(sc.scale, sc.orient)
 for rep in range(3):
-    res = eng.run(H, sc.thr, samples=smp, flags=gcr_capi.RUN_KEEP_PER_HYP)
+    res = eng.run(H, sc.thr, samples=smp, flags=gcr_capi.RUN_KEEP_PER_HYP | gcr_capi.RUN_TIME_KERNELS)
     print(f"run {rep}: stage {res.device_ms:.3f} ms, score kernel {res.score_kernel_ms:.3f} ms, solved {res.n_solved}, rechecked {res.n_rechecked}, exact hyps {res.n_exact_hyp}, cands {res.n_candidates}")
 dev = eng.fetch()
 rel = np.abs(dev["score"] - ora["score"]) / np.maximum(ora["score"], 1e-9)

@@ -24,7 +24,7 @@ def run(eng, port, sc, n_hyp, seed):
     eng.set_features(sc.scale, sc.orient)
     for _ in range(2):
         res = eng.run(n_hyp, sc.thr, seed=seed)
-    rs = [eng.run(n_hyp, sc.thr, seed=seed) for _ in range(3)]
+    rs = [eng.run(n_hyp, sc.thr, seed=seed, flags=gcr_capi.RUN_TIME_KERNELS) for _ in range(3)]
     res = rs[0]
     stage = float(np.median([r.device_ms for r in rs]))
     kern = float(np.median([r.score_kernel_ms for r in rs]))
