@@ -813,7 +813,7 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
 
     // launch sequence: sample+solve -> FP32 scoring -> fused cooperative tail (3 kernels; the run counters were
     // cleared by the previous run's tail)
-    GCR_CUDA(cudaEventRecord(h->ev0, s));
+    if (out) GCR_CUDA(cudaEventRecord(h->ev0, s)); // stage timing only for synchronous callers (gcr_result.device_ms)
     if (h->have_masks) GCR_CUDA(cudaMemsetAsync(h->d_masks.p, 0, sizeof(unsigned int) * H * W, s));
     const int hb = static_cast<int>((H + 127) / 128);
     k_sample_solve<<<hb, 128, 0, s>>>(B, T, all_exact);
@@ -838,7 +838,7 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
         void* args[] = {&B, const_cast<Thresholds*>(&T), &rel_tol};
         GCR_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(k_tail), dim3(h->tail_grid), dim3(kExactThreads), args, 0, s));
     }
-    GCR_CUDA(cudaEventRecord(h->ev1, s));
+    if (out) GCR_CUDA(cudaEventRecord(h->ev1, s));
     if (flags & (GCR_RUN_KEEP_PER_HYP | GCR_RUN_EMIT_MASKS))
     {
         // reporting modes: FP64 re-scoring of the low-margin hypotheses (see k_refine_collect); off the timed stage
