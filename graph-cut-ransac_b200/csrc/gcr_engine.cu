@@ -813,13 +813,13 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
 
     // launch sequence: sample+solve -> FP32 scoring -> fused cooperative tail (3 kernels; the run counters were
     // cleared by the previous run's tail)
-    if (out) GCR_CUDA(cudaEventRecord(h->ev0, s)); // stage timing only for synchronous callers (gcr_result.device_ms)
+    const bool time_kernels = out != nullptr && (flags & GCR_RUN_TIME_KERNELS) != 0; // opt-in: every event record is an in-stream operation
+    if (time_kernels) GCR_CUDA(cudaEventRecord(h->ev0, s));
     if (h->have_masks) GCR_CUDA(cudaMemsetAsync(h->d_masks.p, 0, sizeof(unsigned int) * H * W, s));
     const int hb = static_cast<int>((H + 127) / 128);
     k_sample_solve<<<hb, 128, 0, s>>>(B, T, all_exact);
     {
         const int grid = h->score_grid[h->have_masks ? 1 : 0]; // persistent: one CTA per resident slot
-        const bool time_kernels = (flags & GCR_RUN_TIME_KERNELS) != 0;
         if (time_kernels) GCR_CUDA(cudaEventRecord(h->evk0, s));
         if (h->have_masks)
             k_score_fast<true><<<grid, kScoreThreads, sizeof(ScoreSmem), s>>>(B, T);
@@ -838,7 +838,7 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
         void* args[] = {&B, const_cast<Thresholds*>(&T), &rel_tol};
         GCR_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(k_tail), dim3(h->tail_grid), dim3(kExactThreads), args, 0, s));
     }
-    if (out) GCR_CUDA(cudaEventRecord(h->ev1, s));
+    if (time_kernels) GCR_CUDA(cudaEventRecord(h->ev1, s));
     if (flags & (GCR_RUN_KEEP_PER_HYP | GCR_RUN_EMIT_MASKS))
     {
         // reporting modes: FP64 re-scoring of the low-margin hypotheses (see k_refine_collect); off the timed stage
@@ -875,8 +875,11 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
         out->n_rechecked = c.n_worklist;
         out->n_exact_hyp = c.n_hard;
         out->n_candidates = c.n_candidates;
-        GCR_CUDA(cudaEventElapsedTime(&out->device_ms, h->ev0, h->ev1));
-        if (flags & GCR_RUN_TIME_KERNELS) GCR_CUDA(cudaEventElapsedTime(&out->score_kernel_ms, h->evk0, h->evk1));
+        if (time_kernels)
+        {
+            GCR_CUDA(cudaEventElapsedTime(&out->device_ms, h->ev0, h->ev1));
+            GCR_CUDA(cudaEventElapsedTime(&out->score_kernel_ms, h->evk0, h->evk1));
+        }
         for (int i = 0; i < 5; i++) out->tail_phase_us[i] = static_cast<float>(static_cast<double>(ph[i + 1] - ph[i]) * 1e-3);
         out->tail_phase_us[5] = static_cast<float>(static_cast<double>(ph[0] - ph[7]) * 1e-3); // k_score_fast start -> k_tail start
         out->stage_phase_us[0] = static_cast<float>(static_cast<double>(ph[7] - ph[6]) * 1e-3); // k_sample_solve start -> k_score_fast start

@@ -210,8 +210,8 @@ static int estimateImpl(int problem, const double* scale, size_t ns, const doubl
         size_t n = std::min(target - done, opt.max_batch);
         if (!opt.samples) n = std::min(n, std::max(done == 0 ? min_iters : done, opt.batch_quantum));
         gcr_result res;
-        eng.check(gcr_run(eng.h, static_cast<int64_t>(n), st.seed, done, opt.samples ? opt.samples + 4 * done : nullptr, thr, 0,
-                          nullptr, &res),
+        eng.check(gcr_run(eng.h, static_cast<int64_t>(n), st.seed, done, opt.samples ? opt.samples + 4 * done : nullptr, thr,
+                          stats_out ? GCR_RUN_TIME_KERNELS : 0u, nullptr, &res), // device timings only when the caller asked for statistics
                   "gcr_run");
         st.device_calls++;
         st.n_sample_valid += res.n_sample_valid;

@@ -54,7 +54,8 @@ enum gcr_status
 #define GCR_RUN_KEEP_PER_HYP 4u      /* keep per-hypothesis models/scores/counts for gcr_fetch (implied by EMIT_MASKS) */
 #define GCR_RUN_ALL_EXACT 8u         /* score every hypothesis with the FP64 reference-order kernel (validation) */
 #define GCR_RUN_EXCHANGE 16u         /* multi-GPU: exchange winner records with the attached peers inside the last kernel */
-#define GCR_RUN_TIME_KERNELS 32u     /* diagnostics: bracket the scoring kernel with CUDA events (gcr_result.score_kernel_ms); two more stream operations */
+#define GCR_RUN_TIME_KERNELS 32u     /* diagnostics: CUDA events around the whole stage and around the scoring kernel (gcr_result.device_ms,
+                                      * score_kernel_ms; both 0 without it): four more in-stream operations, ~2.5 us each */
 
 typedef struct gcr_result
 {
@@ -69,7 +70,7 @@ typedef struct gcr_result
     int64_t n_rechecked;    /* (hypothesis, feature) pairs inside the FP32 guard band, re-evaluated in FP64 */
     int64_t n_exact_hyp;    /* hypotheses scored entirely in FP64 */
     int64_t n_candidates;   /* near-best hypotheses re-scored in FP64 before the final selection */
-    float device_ms;        /* CUDA-event time of the whole hypothesis stage on the engine stream */
+    float device_ms;        /* CUDA-event time of the whole hypothesis stage on the engine stream (GCR_RUN_TIME_KERNELS; else 0) */
     float score_kernel_ms;  /* CUDA-event time of the dominant FP32 scoring kernel alone (GCR_RUN_TIME_KERNELS; else 0) */
     int32_t winner_rank;    /* rank owning best_index (0 unless the run exchanged records with peers) */
     int32_t pad2_;
