@@ -212,7 +212,24 @@ double fit_atan2_poly(double zmax, float pc[4], int deg)
     return worst;
 }
 
+Thresholds make_thresholds_uncached(const double thr_in[2], int problem);
+
+// The orientation polynomial is fitted and verified on a 2000-point grid (~30 us of host time): callers repeat the same
+// thresholds run after run, so the last result is kept.
 Thresholds make_thresholds(const double thr_in[2], int problem)
+{
+    struct Entry { double t0, t1; int problem; bool valid; Thresholds T; };
+    static thread_local Entry cache = {0.0, 0.0, 0, false, {}};
+    if (cache.valid && cache.t0 == thr_in[0] && cache.t1 == thr_in[1] && cache.problem == problem) return cache.T;
+    cache.T = make_thresholds_uncached(thr_in, problem);
+    cache.t0 = thr_in[0];
+    cache.t1 = thr_in[1];
+    cache.problem = problem;
+    cache.valid = true;
+    return cache.T;
+}
+
+Thresholds make_thresholds_uncached(const double thr_in[2], int problem)
 {
     Thresholds T;
     std::memset(&T, 0, sizeof(T));
