@@ -126,7 +126,7 @@ struct gcr_engine_s
     // non-minimal fits (gcr_fit_models)
     DevBuf<unsigned char> d_fit_in, d_fit_out;
     DevBuf<double> d_fit_lines, d_fit_partial;
-    PinnedBuf h_fit_in, h_fit_out;
+    PinnedBuf h_fit_in, h_fit_out, h_score_io;
 
     // keypoint front end (gcr_set_keypoints)
     DevBuf<unsigned char> d_kp;
@@ -502,7 +502,7 @@ int gcr_destroy(gcr_handle h)
     h->d_cand_model.release(); h->d_cand_score.release(); h->d_cand_qsum.release(); h->d_cand_rawcnt.release(); h->d_ctr.release();
     h->d_dbg_in.release(); h->d_dbg_out.release(); h->d_user_models.release();
     h->d_fit_in.release(); h->d_fit_out.release(); h->d_fit_lines.release(); h->d_fit_partial.release();
-    h->h_fit_in.release(); h->h_fit_out.release();
+    h->h_fit_in.release(); h->h_fit_out.release(); h->h_score_io.release();
     h->d_kp.release(); h->d_front_table.release(); h->d_front_counts.release(); h->d_front_sizes.release();
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
@@ -992,15 +992,39 @@ int gcr_score_models(gcr_handle h, const double* models, int64_t n, const double
     const Buffers B = make_buffers(h, 0, false, nullptr);
     cudaStream_t s = h->stream;
     const unsigned int un = static_cast<unsigned int>(n);
-    GCR_CUDA(cudaMemcpyAsync(h->d_user_models.p, models, sizeof(Model4) * n, cudaMemcpyHostToDevice, s));
-    k_set_models<<<(un + 127) / 128, 128, 0, s>>>(B, h->d_user_models.p, un);
+    const size_t W = static_cast<size_t>((h->ns + 31) / 32 + (h->no + 31) / 32);
     const unsigned long long units =
         static_cast<unsigned long long>(un) * ((h->ns + kExactThreads - 1) / kExactThreads + (h->no + kExactThreads - 1) / kExactThreads);
     const int grid = static_cast<int>(std::min<unsigned long long>(units, static_cast<unsigned long long>(h->n_sm) * 8));
+    // models in and results out through ONE page-locked staging block that the kernels read / write in place
+    auto align16 = [](size_t x) { return (x + 15) & ~static_cast<size_t>(15); };
+    const size_t off_score = align16(sizeof(Model4) * n), off_cnt = align16(off_score + 8 * n), off_masks = align16(off_cnt + 8 * n),
+                 total = off_masks + (mask_words ? 4 * W * n : 0);
+    GCR_CUDA(h->h_score_io.ensure(total));
+    void* dp = nullptr;
+    static const bool no_zero_copy = std::getenv("GCR_NO_ZEROCOPY") != nullptr;
+    if (!no_zero_copy && cudaHostGetDevicePointer(&dp, h->h_score_io.p, 0) == cudaSuccess && dp)
+    {
+        unsigned char* d = static_cast<unsigned char*>(dp);
+        std::memcpy(h->h_score_io.p, models, sizeof(Model4) * n);
+        k_set_models<<<(un + 127) / 128, 128, 0, s>>>(B, reinterpret_cast<const Model4*>(d), un);
+        k_exact_items<<<grid, kExactThreads, 0, s>>>(B, T, 2, un);
+        k_score_out<<<std::max(1, std::min<int>(h->n_sm, static_cast<int>((W * n + 255) / 256))), 256, 0, s>>>(
+            B, T, un, reinterpret_cast<double*>(d + off_score), reinterpret_cast<unsigned int*>(d + off_cnt),
+            mask_words ? reinterpret_cast<unsigned int*>(d + off_masks) : nullptr);
+        GCR_CUDA(cudaGetLastError());
+        GCR_CUDA(cudaStreamSynchronize(s));
+        if (score) std::memcpy(score, h->h_score_io.p + off_score, sizeof(double) * n);
+        if (n_inl) std::memcpy(n_inl, h->h_score_io.p + off_cnt, 2 * sizeof(unsigned int) * n);
+        if (mask_words) std::memcpy(mask_words, h->h_score_io.p + off_masks, 4 * W * n);
+        return GCR_OK;
+    }
+    cudaGetLastError();
+    GCR_CUDA(cudaMemcpyAsync(h->d_user_models.p, models, sizeof(Model4) * n, cudaMemcpyHostToDevice, s));
+    k_set_models<<<(un + 127) / 128, 128, 0, s>>>(B, h->d_user_models.p, un);
     k_exact_items<<<grid, kExactThreads, 0, s>>>(B, T, 2, un);
     k_cand_value<<<(un + 127) / 128, 128, 0, s>>>(B, T, un);
     GCR_CUDA(cudaGetLastError());
-    const size_t W = static_cast<size_t>((h->ns + 31) / 32 + (h->no + 31) / 32);
     if (score) GCR_CUDA(cudaMemcpyAsync(score, h->d_cand_score.p, sizeof(double) * n, cudaMemcpyDeviceToHost, s));
     if (n_inl) GCR_CUDA(cudaMemcpyAsync(n_inl, h->d_cand_cnt.p, 2 * sizeof(unsigned int) * n, cudaMemcpyDeviceToHost, s));
     if (mask_words) GCR_CUDA(cudaMemcpyAsync(mask_words, h->d_cand_masks.p, 4 * W * n, cudaMemcpyDeviceToHost, s));

@@ -520,6 +520,26 @@ __global__ void k_cand_value(Buffers B, Thresholds T, unsigned int n)
     if (i < n) cand_value(B, T, i);
 }
 
+// gcr_score_models: values of the n caller models, written together with their counts and (optionally) packed masks
+// straight into page-locked host memory (device-mapped): the caller synchronises and reads, no device-to-host copies
+__global__ void k_score_out(Buffers B, Thresholds T, unsigned int n, double* __restrict__ h_score, unsigned int* __restrict__ h_cnt,
+                            unsigned int* __restrict__ h_masks)
+{
+    const unsigned int t = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
+    for (unsigned int i = t; i < n; i += stride)
+    {
+        cand_value(B, T, i);
+        h_score[i] = B.cand_score[i];
+        h_cnt[2 * i] = B.cand_cnt[2 * i];
+        h_cnt[2 * i + 1] = B.cand_cnt[2 * i + 1];
+    }
+    if (h_masks)
+    {
+        const size_t words = static_cast<size_t>(n) * B.wmask;
+        for (size_t w = t; w < words; w += stride) h_masks[w] = B.cand_masks[w];
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // K4-K6 as phases of ONE cooperative kernel (k_tail): at small sizes (C2) six dependent launches of 4-7 us each cost
 // as much as the scoring kernel; grid-wide barriers between the phases cost ~1-2 us.
