@@ -263,6 +263,13 @@ Thresholds make_thresholds_uncached(const double thr_in[2], int problem)
             if (fit_atan2_poly(zmax, T.pc, 3) > 5e-7) T.orient_all_exact = 1;
         }
     }
+    {
+        const int d = T.poly_deg == 2 ? 2 : 3;
+        T.pc_lead = T.pc[d];
+        for (int i = 0; i < d; i++) T.pm[i] = static_cast<float>(static_cast<double>(T.pc[d - 1 - i]) / static_cast<double>(T.pc[d]));
+        if (d == 2) T.pm[2] = 0.f;
+        if (!(std::fabs(T.pc_lead) > 1e-12f)) T.orient_all_exact = 1; // degenerate fit: no monic form
+    }
     // rounding of tanT to float + rcp (1 ulp) + two multiplies + polynomial-free compare
     T.t_band0 = static_cast<float>(26.0 * kU + 4.0 * kU * T.tanT);
     T.t_lo0 = std::nextafter(T.tanT - T.t_band0, -1.0f);

@@ -80,6 +80,8 @@ struct Thresholds
     float t_lo0, t_hi0; // tanT -/+ t_band0 (rounded outwards)
     int poly_deg;    // 2 or 3: degree of the r^2 polynomial that meets the fit tolerance
     float pc[4];     // r^2 = z (pc0 + z (pc1 + z (pc2 + z pc3))), z = tan^2
+    float pm[3];     // monic form: P(z) = pc_lead * Q(z), Q = ((z + pm0) z + pm1) z + pm2 (degree 3) or (z + pm0) z + pm1 (degree 2):
+    float pc_lead;   // every step has ONE constant operand (no register copies of constants in the hot loop); lead factor applied per chunk
     float scale_unit; // (3 ln 2)^2: converts sum of d^2 (log2 units) into sum of r^2
     int orient_all_exact; // orientation threshold outside the fast path's range -> every hypothesis exact
     int problem;          // 0 hybrid (two_sift), 1 scale-only (three_sift), 2 scale-only "original" (three_sift_original)

@@ -72,8 +72,9 @@ __device__ __forceinline__ Verdict orient_verdict_cs(float c1, float s1, const H
     e.in = t <= fmaf(-H.dpr, ri, T.t_lo0);               // tanT - band0 - dpr / max
     e.unc = (t <= fmaf(H.dpr, ri, T.t_hi0)) && !e.in;   // tanT + band0 + dpr / max
     z = t * t;
-    if (T.poly_deg == 2) p = fmaf(z, fmaf(z, T.pc[2], T.pc[1]), T.pc[0]); // uniform branch (kernel parameter)
-    else p = fmaf(z, fmaf(z, fmaf(z, T.pc[3], T.pc[2]), T.pc[1]), T.pc[0]);
+    // p = Q(z) of the monic form (Thresholds::pm): r^2 = pc_lead * z * Q(z); the lead factor is applied once per chunk
+    if (T.poly_deg == 2) p = fmaf(z + T.pm[0], z, T.pm[1]); // uniform branch (kernel parameter)
+    else p = fmaf(fmaf(z + T.pm[0], z, T.pm[1]), z, T.pm[2]);
     return e;
 }
 
@@ -198,14 +199,12 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
                             const float2 lo = __ffma2_rn(make_float2(-H[j].dpr, -H[j].dpr), ri, make_float2(T.t_lo0, T.t_lo0));
                             const float2 hi = __ffma2_rn(make_float2(H[j].dpr, H[j].dpr), ri, make_float2(T.t_hi0, T.t_hi0));
                             const float2 z = __fmul2_rn(t, t);
-                            float2 pl;
+                            float2 pl; // Q(z) of the monic form, as in orient_verdict_cs
+                            const float2 z0 = make_float2(z.x + T.pm[0], z.y + T.pm[0]);
                             if (T.poly_deg == 2)
-                                pl = __ffma2_rn(z, __ffma2_rn(z, make_float2(T.pc[2], T.pc[2]), make_float2(T.pc[1], T.pc[1])),
-                                                make_float2(T.pc[0], T.pc[0]));
+                                pl = __ffma2_rn(z0, z, make_float2(T.pm[1], T.pm[1]));
                             else
-                                pl = __ffma2_rn(z, __ffma2_rn(z, __ffma2_rn(z, make_float2(T.pc[3], T.pc[3]), make_float2(T.pc[2], T.pc[2])),
-                                                              make_float2(T.pc[1], T.pc[1])),
-                                                make_float2(T.pc[0], T.pc[0]));
+                                pl = __ffma2_rn(__ffma2_rn(z0, z, make_float2(T.pm[1], T.pm[1])), z, make_float2(T.pm[2], T.pm[2]));
                             pk0[e] = z.x; pk0[e + 1] = z.y;
                             pk1[e] = pl.x; pk1[e + 1] = pl.y;
                             pv[e].in = t.x <= lo.x;
@@ -302,7 +301,7 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
         }
         else
         {
-            H[j].sum_o += static_cast<double>(acc[j]);
+            H[j].sum_o += static_cast<double>(acc[j]) * static_cast<double>(T.pc_lead);
             H[j].cnt_o += static_cast<unsigned int>(cntf[j]);
         }
     }
