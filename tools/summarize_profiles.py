@@ -45,6 +45,8 @@ tot = sum(sum(v) for k, v in agg.items() if "gcr::" in k[0])
 with open(f"profiles/{OUT}_launch_list_c2.txt", "w") as f:
     f.write("# ncu --metrics gpu__time_duration.sum --clock-control none python bench.py --steps 5 --warmup 3 (config C2)\n")
     f.write("# per-launch times are cold-cache and serialised: compare SHARES, not absolutes\n")
+    f.write("# the list covers every loop of bench.py: device-resident steps, the kernel-timing pass and the host-buffer (e2e) steps,\n")
+    f.write("# in which k_sample_solve reads the replayed samples in place over PCIe (about twice its device-resident duration)\n")
     f.write(f"{'kernel':60s} {'grid':>16s} {'block':>14s} {'launches':>9s} {'mean_us':>9s} {'share_of_gcr':>12s}\n")
     for (n, g, b), v in agg.items():
         share = sum(v) / tot if "gcr::" in n else float("nan")
