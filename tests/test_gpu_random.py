@@ -95,3 +95,83 @@ def test_estimator_result_is_consistent_with_the_oracle(port):
         assert np.allclose(np.asarray(H).ravel()[[6, 7, 8]], [model.h7, model.h8, 1.0], rtol=1e-12), case  # model.h:211-226, identity normaliser
         err = np.hypot(model.h7 - sc.model[0], model.h8 - sc.model[1]) / np.hypot(sc.model[0], sc.model[1])
         assert err < 0.05, (case, err)
+
+
+def test_engine_reuse_across_sizes_problems_and_modes(port):
+    """One engine handle driven through growing / shrinking feature sets, batch sizes, problem modes and run modes in a
+    shuffled order: buffer re-allocation, counter reset and stale state must never leak into a result."""
+    import gcr_capi
+    import gcr_scenes as gs
+    e = gcr_capi.Engine(0)
+    rng = np.random.Generator(np.random.PCG64(31415))
+    for step in range(40):
+        problem = int(rng.choice([0, 0, 0, 1, 2]))
+        ns, no = int(rng.integers(3, 3000)), int(rng.integers(2, 900))
+        H = int(rng.choice([1, 7, 129, 1000, 5000, 20000]))
+        sc = gs.make_scene(ns, no, float(rng.choice([0.2, 0.6])), 100 + step)
+        mode = int(rng.choice([0, gcr_capi.RUN_KEEP_PER_HYP, gcr_capi.RUN_EMIT_MASKS, gcr_capi.RUN_ALL_EXACT]))
+        e.set_problem(problem)
+        if problem == 0:
+            e.set_features(sc.scale, sc.orient)
+            smp = gs.draw_samples(H, ns, no, step)
+            ora = port.replay(sc.scale, sc.orient, smp, sc.thr, nthreads=0)
+            thr = sc.thr
+        else:
+            e.set_features(sc.scale)
+            smp = gs.draw_samples_scale3(H, ns, step)
+            ora = port.replay_scale(sc.scale, smp, sc.thr[0], original=problem == 2, nthreads=0)
+            thr = [sc.thr[0], 0.0]
+        res = e.run(H, thr, samples=smp, flags=mode)
+        want = port.select_best(ora["score"], ora["flags"])
+        label = f"step {step}: problem {problem}, {ns}+{no} features, H={H}, mode {mode}"
+        assert res.n_solved == int(((ora["flags"] & 2) > 0).sum()), label
+        if want < 0:
+            assert res.best_index == -1, label
+            continue
+        ties = np.isclose(ora["score"], ora["score"][want], rtol=1e-12) & ((ora["flags"] & 4) > 0)
+        if ties.sum() == 1:
+            assert res.best_index == want, label
+        assert res.best_score == pytest.approx(ora["score"][want], rel=1e-9), label
+        b = e.best()
+        if ties.sum() == 1:
+            assert np.array_equal(np.concatenate([b["scale_words"], b["orient_words"]]), ora["masks"][want]), label
+            assert tuple(b["n_inl"]) == tuple(ora["n_inl"][want]), label
+        if mode & (gcr_capi.RUN_KEEP_PER_HYP | gcr_capi.RUN_EMIT_MASKS):
+            dev = e.fetch(masks=bool(mode & gcr_capi.RUN_EMIT_MASKS))
+            assert np.array_equal(dev["n_inl"], ora["n_inl"]), label
+            if mode & gcr_capi.RUN_EMIT_MASKS:
+                assert np.array_equal(dev["masks"], ora["masks"]), label
+    e.close()
+
+
+def test_engines_in_concurrent_threads(port):
+    """Four engines driven from four host threads at once (one stream each): results equal the single-threaded ones."""
+    import threading
+    import gcr_capi
+    import gcr_scenes as gs
+    scenes = [gs.make_scene(900 + 50 * i, 300 + 10 * i, 0.3, 40 + i) for i in range(4)]
+    want, got, errs = [], [None] * 4, []
+    e0 = gcr_capi.Engine(0)
+    for sc in scenes:
+        e0.set_features(sc.scale, sc.orient)
+        r = e0.run(30000, sc.thr, seed=5)
+        want.append((r.best_index, r.best_score, tuple(r.best_n_inl)))
+    e0.close()
+
+    def work(i):
+        try:
+            e = gcr_capi.Engine(0)
+            for _ in range(5):
+                e.set_features(scenes[i].scale, scenes[i].orient)
+                r = e.run(30000, scenes[i].thr, seed=5)
+                got[i] = (r.best_index, r.best_score, tuple(r.best_n_inl))
+                assert got[i] == want[i]
+            e.close()
+        except Exception as ex:  # surfaced in the main thread
+            errs.append((i, repr(ex)))
+
+    ts = [threading.Thread(target=work, args=(i,)) for i in range(4)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    assert not errs, errs
+    assert got == want
