@@ -79,6 +79,12 @@ struct gcr_engine_s
     int n_sm = 148;
     int problem = 0; // GCR_PROBLEM_*
     int score_grid[2] = {148, 148};
+    bool pdl = true;            // programmatic dependent launch of the scoring kernel and the tail (GCR_PDL=0: plain launches)
+    bool resident_ok = true;    // k_score_resident usable (GCR_RESIDENT=0 forces the ring kernel: A/B runs)
+    long long resident_max_hyp = 262144; // ... for batches up to this many slots (GCR_RESIDENT_MAX_HYP); measured on B200 against the
+                                         // ring kernel: step 59.8 -> 47.4 us at C1 (5k slots), 86.7 -> 85.4 us at C2 (100k), kernel +4 % at C5 (1M)
+    int resident_cost_o = 27;   // cost model of k_score_resident's static partition: orientation block (scale block = 10) ...
+    int resident_cost_p = 20;   // ... and a precise tile relative to an FP32 tile (x 10); GCR_COST_O / GCR_COST_P for tuning runs
     int tail_grid = 148;
     cudaStream_t own_stream = nullptr, stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, evk0 = nullptr, evk1 = nullptr;
@@ -459,6 +465,16 @@ int gcr_create(int device, gcr_handle* out)
         e = cudaFuncSetAttribute(k_score_fast<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ScoreSmem));
     if (e == cudaSuccess)
         e = cudaFuncSetAttribute(k_score_fast<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ScoreSmem));
+    const int resident_smem = kResidentMaxChunks * kChunkBytes + 64;
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(k_score_resident<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, resident_smem);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(k_score_resident<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, resident_smem);
+    if (const char* v = std::getenv("GCR_RESIDENT")) h->resident_ok = std::atoi(v) != 0;
+    if (const char* v = std::getenv("GCR_PDL")) h->pdl = std::atoi(v) != 0;
+    if (const char* v = std::getenv("GCR_RESIDENT_MAX_HYP")) h->resident_max_hyp = std::atoll(v);
+    if (const char* v = std::getenv("GCR_COST_O")) h->resident_cost_o = std::max(1, std::atoi(v));
+    if (const char* v = std::getenv("GCR_COST_P")) h->resident_cost_p = std::max(1, std::atoi(v));
     for (int m = 0; m < 2 && e == cudaSuccess; m++)
     {
         int per_sm = 1;
@@ -519,6 +535,19 @@ int gcr_destroy(gcr_handle h)
     delete h;
     return GCR_OK;
 }
+
+#ifdef GCR_TRACE
+// diagnostic builds only (tools/trace_score.py): copies the scoring kernels' timeline rows and clears them
+int gcr_debug_read_trace(void* dst, size_t bytes)
+{
+    cudaDeviceSynchronize();
+    if (cudaMemcpyFromSymbol(dst, gcr::g_trace, std::min(bytes, sizeof(gcr::g_trace))) != cudaSuccess) return -1;
+    void* p = nullptr;
+    cudaGetSymbolAddress(&p, gcr::g_trace);
+    cudaMemset(p, 0, sizeof(gcr::g_trace));
+    return 0;
+}
+#endif
 
 const char* gcr_last_error(gcr_handle h) { return h ? h->err.c_str() : "null handle"; }
 
@@ -844,14 +873,39 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
     k_sample_solve<<<hb, 128, 0, s>>>(B, T, all_exact);
     {
         const int grid = h->score_grid[h->have_masks ? 1 : 0]; // persistent: one CTA per resident slot
+        // small feature sets (both working sets fit in one SM's shared memory): resident kernel, one CTA per SM
+        const int chunks = B.ncs + B.nco + B.ncsd + B.ncod;
+        const bool resident = h->resident_ok && chunks <= kResidentMaxChunks && n_hyp <= h->resident_max_hyp;
+        const size_t rsmem = static_cast<size_t>(chunks) * kChunkBytes + 64;
+        // chained launches: the scoring kernel and the tail start launching while their predecessor runs and wait for its
+        // results on the device (griddepcontrol.wait); not when the scoring kernel is bracketed by timing events
+        const bool pdl = h->pdl && !time_kernels;
+        cudaLaunchAttribute at[2];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        at[1].id = cudaLaunchAttributeCooperative;
+        at[1].val.cooperative = 1;
+        cudaLaunchConfig_t cfg = {};
+        cfg.stream = s;
+        cfg.attrs = at;
+        cfg.numAttrs = pdl ? 1 : 0;
         if (time_kernels) GCR_CUDA(cudaEventRecord(h->evk0, s));
-        if (h->have_masks)
-            k_score_fast<true><<<grid, kScoreThreads, sizeof(ScoreSmem), s>>>(B, T);
+        if (resident)
+        {
+            cfg.gridDim = dim3(h->n_sm);
+            cfg.blockDim = dim3(kResidentThreads);
+            cfg.dynamicSmemBytes = rsmem;
+            GCR_CUDA(cudaLaunchKernelEx(&cfg, h->have_masks ? k_score_resident<true> : k_score_resident<false>, B, T, h->resident_cost_o,
+                                        h->resident_cost_p));
+        }
         else
-            k_score_fast<false><<<grid, kScoreThreads, sizeof(ScoreSmem), s>>>(B, T);
+        {
+            cfg.gridDim = dim3(grid);
+            cfg.blockDim = dim3(kScoreThreads);
+            cfg.dynamicSmemBytes = sizeof(ScoreSmem);
+            GCR_CUDA(cudaLaunchKernelEx(&cfg, h->have_masks ? k_score_fast<true> : k_score_fast<false>, B, T));
+        }
         if (time_kernels) GCR_CUDA(cudaEventRecord(h->evk1, s));
-    }
-    {
         // Candidate window: hypotheses whose FP32-path value is within rel_tol of the best one are re-scored in FP64.
         // The FP32 value error per inlier is ~ 2 (delta d) / T' (scale: MUFU.LG2 + roundings, delta d ~ 4e-7) and
         // ~ 2 (delta t) / sqrt(tsq) (orientation), i.e. it grows as the thresholds tighten; 4e-5 was validated at the
@@ -859,8 +913,17 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
         double rel_tol = 2.0 * std::max(2e-5, 4e-5 * 0.096 / static_cast<double>(T.Tp));
         if (h->problem == 0) rel_tol = std::max(rel_tol, 2.0 * 4e-5 * 0.0785 / std::sqrt(T.tsq[1]));
         rel_tol = std::min(rel_tol, 0.05);
-        void* args[] = {&B, const_cast<Thresholds*>(&T), &rel_tol};
-        GCR_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(k_tail), dim3(h->tail_grid), dim3(kExactThreads), args, 0, s));
+        cfg.gridDim = dim3(h->tail_grid);
+        cfg.blockDim = dim3(kExactThreads);
+        cfg.dynamicSmemBytes = 0;
+        if (pdl)
+            cfg.numAttrs = 2; // cooperative + programmatic
+        else
+        {
+            cfg.attrs = at + 1; // cooperative only
+            cfg.numAttrs = 1;
+        }
+        GCR_CUDA(cudaLaunchKernelEx(&cfg, k_tail, B, T, rel_tol));
     }
     if (time_kernels) GCR_CUDA(cudaEventRecord(h->ev1, s));
     if (flags & (GCR_RUN_KEEP_PER_HYP | GCR_RUN_EMIT_MASKS))

@@ -175,6 +175,7 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
 {
     const int h = blockIdx.x * blockDim.x + threadIdx.x;
     const unsigned lane = threadIdx.x & 31;
+    pdl_launch_dependents(); // the scoring kernel may set up (barriers, feature staging) while this one runs
     if (h == 0) B.phase_ns[6] = global_ns(); // diagnostics: start of the stage as seen by the first CTA
     bool solved = false, hard = false, sample_valid = false, sens_s = false, sens_o = false;
     Model4 m = {0.0, 0.0, 0.0, 0.0};
@@ -909,6 +910,7 @@ __global__ void __launch_bounds__(kExactThreads) k_tail(const __grid_constant__ 
 {
     cooperative_groups::grid_group grid = cooperative_groups::this_grid();
     const bool stamp = blockIdx.x == 0 && threadIdx.x == 0; // phase boundaries as seen by CTA 0 (diagnostics, ns)
+    pdl_wait(); // results of the scoring kernel
     if (stamp) B.phase_ns[0] = global_ns();
     fixup_phase(B, T);
     exact_items_phase(B, T, 0, 0u);

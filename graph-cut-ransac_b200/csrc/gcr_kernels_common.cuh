@@ -219,6 +219,13 @@ __device__ __forceinline__ double from_ordered_bits(unsigned long long b)
 }
 
 
+// Programmatic dependent launch (the three kernels of gcr_run are chained with
+// cudaLaunchAttributeProgrammaticStreamSerialization): a kernel lets its successor start launching at once, and the successor
+// runs its prologue (barrier set-up, feature staging) under the predecessor's tail, then waits here for the predecessor's
+// results.  Both are no-ops in a plain launch.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 __device__ __forceinline__ unsigned long long global_ns()
 {
     unsigned long long t;

@@ -19,6 +19,41 @@
 namespace gcr
 {
 
+// Diagnostic timeline (builds with -DGCR_TRACE only; tools/trace_score.py): per CTA (ring kernel) or per warp (resident
+// kernel) a row of kTraceCols %globaltimer stamps: [0] = SM id, [1] = kernel entry, [2] = plan ready, then per work item
+// (claimed, first features ready, done), 0-terminated.
+#ifdef GCR_TRACE
+constexpr int kTraceRows = 8192, kTraceCols = 64;
+__device__ unsigned long long g_trace[kTraceRows * kTraceCols];
+struct Tracer
+{
+    unsigned long long* row;
+    int n;
+    __device__ __forceinline__ Tracer(int r, bool on) : row(on && r < kTraceRows ? g_trace + static_cast<size_t>(r) * kTraceCols : nullptr), n(0)
+    {
+        if (row)
+        {
+            unsigned int smid;
+            asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
+            row[n++] = smid;
+        }
+    }
+    __device__ __forceinline__ void stamp()
+    {
+        if (row && n < kTraceCols - 1)
+        {
+            row[n++] = global_ns();
+            row[n] = 0;
+        }
+    }
+};
+#define GCR_TRACER(name, r, on) Tracer name(r, on)
+#define GCR_STAMP(name) name.stamp()
+#else
+#define GCR_TRACER(name, r, on)
+#define GCR_STAMP(name)
+#endif
+
 struct HypRegs
 {
     float nh7, nh8, A, Tin, Tout, cphi, sphi, dpr;
@@ -94,10 +129,12 @@ __device__ __forceinline__ void worklist_push(const Buffers& B, unsigned int hyp
 
 // One chunk of one class for the kHB hypotheses of this thread.  CLS 0 = scale, 1 = orientation.
 // FP32 chunk: 512 features, groups of 4 (float4 per plane).  Precise chunk: 256 features, groups of 2 (double2).
-template <bool MASKS, bool PRECISE, int CLS>
+// RANGE: only the groups [g0r, g1r) of the chunk (the resident kernel's segments; both multiples of kScoreUnroll).
+template <bool MASKS, bool PRECISE, int CLS, bool RANGE = false>
 __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& T, const float* stage, int fbase,
-                                            HypRegs (&H)[kHB])
+                                            HypRegs (&H)[kHB], int g0r = 0, int g1r = 0)
 {
+    static_assert(kScoreUnroll % kVoteGroups == 0, "the vote window must divide the unroll factor");
     constexpr int G = PRECISE ? 2 : 4;             // features per group
     constexpr int NF = PRECISE ? kChunk / 2 : kChunk; // features per chunk
     float acc[kHB], cntf[kHB]; // per-chunk FP32 partials; counts are exact integers (< 2^24)
@@ -111,9 +148,12 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
     bool unc_j[kHB]; // hypothesis j had an evaluation of the last kVoteGroups groups inside the band (per thread)
 #pragma unroll
     for (int j = 0; j < kHB; j++) unc_j[j] = false;
-#pragma unroll kScoreUnroll
-    for (int g = 0; g < NF / G; g++)
+    const int g0 = RANGE ? g0r : 0, g1 = RANGE ? g1r : NF / G;
+    for (int gb = g0; gb < g1; gb += kScoreUnroll)
+#pragma unroll
+    for (int u = 0; u < kScoreUnroll; u++)
     {
+        const int g = gb + u;
         float fa[G], fb[G], fc[G];   // FP32 planes
         double da[G], db[G], dc[G];  // FP64 planes (precise tiles)
         if constexpr (PRECISE)
@@ -245,7 +285,7 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
             }
         }
         // the band check is voted once per kVoteGroups groups (the vote + branch cost ~5 issue slots)
-        if (g % kVoteGroups == kVoteGroups - 1)
+        if (u % kVoteGroups == kVoteGroups - 1)
         {
             bool any_unc = false;
 #pragma unroll
@@ -307,37 +347,16 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
     }
 }
 
-// One work item: all chunks [c_begin, c_end) of this tile flavour's chunk list, scale class first.
-template <bool MASKS, bool PRECISE>
-__device__ __forceinline__ void score_item(const Buffers& B, const Thresholds& T, ScoreSmem& S, uint32_t& ring,
-                                           int first_compact, int n_list, bool from_back, int c_begin, int c_end,
-                                           bool single_split)
+// Hypothesis parameters of the kHB hypotheses of a thread: compact index first_compact + j * stride + lane_in_tile of the FP32
+// list (from the front of the compact arrays) or of the precise list (from the back).
+template <bool PRECISE>
+__device__ __forceinline__ void load_hyps(const Buffers& B, HypRegs (&H)[kHB], int first_compact, int stride, int t, int n_list,
+                                          bool from_back)
 {
-    const int tid = threadIdx.x, lane = tid & 31;
-    const int ncs = PRECISE ? B.ncsd : B.ncs;
-    const float* base_s = PRECISE ? reinterpret_cast<const float*>(B.fsd) : B.fs;
-    const float* base_o = PRECISE ? reinterpret_cast<const float*>(B.fod) : B.fo;
-    constexpr int NF = PRECISE ? kChunk / 2 : kChunk;
-    const int nch = c_end - c_begin;
-
-    auto issue = [&](uint32_t n, int chunk) {
-        if (tid == 0)
-        {
-            const uint32_t st = n % kStages;
-            if (n >= kStages) mbar_wait(&S.empty[st], ((n / kStages) - 1) & 1);
-            const float* src = chunk < ncs ? base_s + static_cast<size_t>(chunk) * kChunkFloats
-                                           : base_o + static_cast<size_t>(chunk - ncs) * kChunkFloats;
-            mbar_expect_tx(&S.full[st], kChunkBytes);
-            tma_load_1d(S.stage[st], src, kChunkBytes, &S.full[st]);
-        }
-    };
-    for (int p = 0; p < min(kStages - 1, nch); p++) issue(ring + p, c_begin + p);
-
-    HypRegs H[kHB];
 #pragma unroll
     for (int j = 0; j < kHB; j++)
     {
-        const int k = first_compact + j * kScoreThreads + tid;
+        const int k = first_compact + j * stride + t;
         H[j].active = k < n_list;
         const int c = from_back ? B.n_hyp - 1 - k : k;
         // inactive lanes: parameters for which every comparison is false
@@ -356,21 +375,12 @@ __device__ __forceinline__ void score_item(const Buffers& B, const Thresholds& T
         H[j].sum_s = H[j].sum_o = 0.0;
         H[j].cnt_s = H[j].cnt_o = 0u;
     }
+}
 
-    for (int i = 0; i < nch; i++)
-    {
-        if (i + kStages - 1 < nch) issue(ring + i + kStages - 1, c_begin + i + kStages - 1);
-        const uint32_t n = ring + i;
-        const uint32_t st = n % kStages;
-        mbar_wait(&S.full[st], (n / kStages) & 1);
-        const int chunk = c_begin + i;
-        if (chunk < ncs) score_chunk<MASKS, PRECISE, 0>(B, T, S.stage[st], chunk * NF, H);
-        else score_chunk<MASKS, PRECISE, 1>(B, T, S.stage[st], (chunk - ncs) * NF, H);
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&S.empty[st]);
-    }
-    ring += nch;
-
+// Partial sums / counts of a thread's hypotheses into the per-hypothesis arrays: plain stores when this item covered every
+// feature, atomics when the feature range is split over several items.
+__device__ __forceinline__ void flush_hyps(const Buffers& B, const Thresholds& T, HypRegs (&H)[kHB], bool single_split)
+{
 #pragma unroll
     for (int j = 0; j < kHB; j++)
     {
@@ -400,6 +410,52 @@ __device__ __forceinline__ void score_item(const Buffers& B, const Thresholds& T
     }
 }
 
+// One work item: all chunks [c_begin, c_end) of this tile flavour's chunk list, scale class first.
+template <bool MASKS, bool PRECISE>
+__device__ __forceinline__ void score_item(const Buffers& B, const Thresholds& T, ScoreSmem& S, uint32_t& ring,
+                                           int first_compact, int n_list, bool from_back, int c_begin, int c_end,
+                                           bool single_split)
+{
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int ncs = PRECISE ? B.ncsd : B.ncs;
+    const float* base_s = PRECISE ? reinterpret_cast<const float*>(B.fsd) : B.fs;
+    const float* base_o = PRECISE ? reinterpret_cast<const float*>(B.fod) : B.fo;
+    constexpr int NF = PRECISE ? kChunk / 2 : kChunk;
+    const int nch = c_end - c_begin;
+
+    auto issue = [&](uint32_t n, int chunk) {
+        if (tid == 0)
+        {
+            const uint32_t st = n % kStages;
+            if (n >= kStages) mbar_wait(&S.empty[st], ((n / kStages) - 1) & 1);
+            const float* src = chunk < ncs ? base_s + static_cast<size_t>(chunk) * kChunkFloats
+                                           : base_o + static_cast<size_t>(chunk - ncs) * kChunkFloats;
+            mbar_expect_tx(&S.full[st], kChunkBytes);
+            tma_load_1d(S.stage[st], src, kChunkBytes, &S.full[st]);
+        }
+    };
+    for (int p = 0; p < min(kStages - 1, nch); p++) issue(ring + p, c_begin + p);
+
+    HypRegs H[kHB];
+    load_hyps<PRECISE>(B, H, first_compact, kScoreThreads, tid, n_list, from_back);
+
+    for (int i = 0; i < nch; i++)
+    {
+        if (i + kStages - 1 < nch) issue(ring + i + kStages - 1, c_begin + i + kStages - 1);
+        const uint32_t n = ring + i;
+        const uint32_t st = n % kStages;
+        mbar_wait(&S.full[st], (n / kStages) & 1);
+        const int chunk = c_begin + i;
+        if (chunk < ncs) score_chunk<MASKS, PRECISE, 0>(B, T, S.stage[st], chunk * NF, H);
+        else score_chunk<MASKS, PRECISE, 1>(B, T, S.stage[st], (chunk - ncs) * NF, H);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&S.empty[st]);
+    }
+    ring += nch;
+
+    flush_hyps(B, T, H, single_split);
+}
+
 template <bool MASKS>
 __global__ void __launch_bounds__(kScoreThreads, GCR_MINB) k_score_fast(const __grid_constant__ Buffers B,
                                                               const __grid_constant__ Thresholds T)
@@ -416,7 +472,11 @@ __global__ void __launch_bounds__(kScoreThreads, GCR_MINB) k_score_fast(const __
         }
         fence_barrier_init();
     }
+    GCR_TRACER(tr, blockIdx.x, threadIdx.x == 0);
+    GCR_STAMP(tr);
+    pdl_launch_dependents();
     __syncthreads();
+    pdl_wait(); // compact lists and counters of k_sample_solve
 
     const int n_fast = static_cast<int>(B.ctr->n_fast), n_sens = static_cast<int>(B.ctr->n_sens);
     const int tiles_a = (n_fast + kTileHyps - 1) / kTileHyps, tiles_b = (n_sens + kTileHyps - 1) / kTileHyps;
@@ -434,6 +494,7 @@ __global__ void __launch_bounds__(kScoreThreads, GCR_MINB) k_score_fast(const __
     const int splits_b = (chunks_b + cps_b - 1) / cps_b;
     const int items_b = tiles_b * splits_b, n_items = items_b + tiles_a * splits_a;
 
+    GCR_STAMP(tr);
     __shared__ int s_item;
     uint32_t ring = 0; // chunks issued / consumed so far by this CTA (ring position, same in every thread)
     for (;;)
@@ -443,6 +504,7 @@ __global__ void __launch_bounds__(kScoreThreads, GCR_MINB) k_score_fast(const __
         const int item = s_item;
         __syncthreads();
         if (item >= n_items) break;
+        GCR_STAMP(tr);
         if (item >= items_b)
         {
             const int k = item - items_b;
@@ -456,7 +518,145 @@ __global__ void __launch_bounds__(kScoreThreads, GCR_MINB) k_score_fast(const __
             score_item<MASKS, true>(B, T, S, ring, tile * kTileHyps, n_sens, true, split * cps_b,
                                     min(chunks_b, (split + 1) * cps_b), splits_b == 1);
         }
+        GCR_STAMP(tr);
     }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Resident form of the scoring kernel, for feature sets whose FP32 and FP64 working sets fit in one SM's shared
+// memory together (<= kResidentMaxChunks chunks of 3 KB: ~5 000 features; configs C1, C2, C4).  One CTA of 1024
+// threads per SM copies the whole working set into shared memory once (four TMA bulk copies on three mbarriers:
+// FP32 scale, FP32 orientation, FP64 planes) and every WARP then works on its own, with no block barrier, ring
+// protocol or work counter after the prologue.  The work is partitioned STATICALLY and by cost: hypotheses in tiles
+// of 32 (precise tiles first), each tile a line of feature blocks (32 features) measured in cost units (scale block
+// 10, orientation block cost_o, everything times cost_p / 10 in a precise tile); the lines of all tiles, laid end to
+// end, are cut into one piece of equal cost per resident warp, so a warp scores at most a tail of one tile, some
+// whole tiles and a head of another, and all warps finish together (the dynamic items of the ring kernel leave a
+// 10 us drain at C2 because its costliest items last 30 of the kernel's 40 us).  Arithmetic, verdicts, worklist and
+// mask emission are score_chunk's, i.e. bit-identical to the ring kernel.
+constexpr int kResidentThreads = 1024;
+constexpr int kResidentMaxChunks = 75; // 75 x 3 KB + barriers <= 227 KB
+constexpr int kCostS = 10, kMinPieceCost = 40;
+
+struct ResidentPlan // identical in every warp (pure function of the counters and the feature counts)
+{
+    int nbs, nbo;       // blocks of 32 features per class
+    int cost_o;         // cost of an orientation block (scale block = kCostS)
+    int total;          // cost of the feature line of one FP32 tile
+    __device__ __forceinline__ int block_at(long long c) const // cost offset inside a tile's line -> block (monotone, onto)
+    {
+        const int cs = kCostS * nbs;
+        return c <= cs ? static_cast<int>((c + kCostS / 2) / kCostS) : nbs + static_cast<int>((c - cs + cost_o / 2) / cost_o);
+    }
+};
+
+template <bool MASKS, bool PRECISE>
+__device__ __forceinline__ void resident_task(const Buffers& B, const Thresholds& T, const float* sm_s, const float* sm_o,
+                                              const ResidentPlan& P, int tile, int b0, int b1, int n_list, bool single,
+                                              uint64_t* bar_s, uint64_t* bar_o)
+{
+    constexpr int NF = PRECISE ? kChunk / 2 : kChunk; // features per chunk
+    constexpr int G = PRECISE ? 2 : 4;
+    constexpr int BPC = NF / 32, GPB = 32 / G;         // blocks per chunk, groups per block
+    HypRegs H[kHB];
+    load_hyps<PRECISE>(B, H, tile * 32 * kHB, 32, threadIdx.x & 31, n_list, PRECISE);
+    const int s1 = min(b1, P.nbs);
+    if (b0 < s1)
+    {
+        mbar_wait(bar_s, 0);
+        for (int b = b0; b < s1;)
+        {
+            const int chunk = b / BPC, be = min(s1, (chunk + 1) * BPC);
+            score_chunk<MASKS, PRECISE, 0, true>(B, T, sm_s + chunk * kChunkFloats, chunk * NF, H, (b - chunk * BPC) * GPB,
+                                                 (be - chunk * BPC) * GPB);
+            b = be;
+        }
+    }
+    const int o0 = max(b0, P.nbs) - P.nbs, o1 = b1 - P.nbs;
+    if (o0 < o1)
+    {
+        mbar_wait(bar_o, 0);
+        for (int b = o0; b < o1;)
+        {
+            const int chunk = b / BPC, be = min(o1, (chunk + 1) * BPC);
+            score_chunk<MASKS, PRECISE, 1, true>(B, T, sm_o + chunk * kChunkFloats, chunk * NF, H, (b - chunk * BPC) * GPB,
+                                                 (be - chunk * BPC) * GPB);
+            b = be;
+        }
+    }
+    flush_hyps(B, T, H, single);
+}
+
+template <bool MASKS>
+__global__ void __launch_bounds__(kResidentThreads, 1) k_score_resident(const __grid_constant__ Buffers B,
+                                                                        const __grid_constant__ Thresholds T,
+                                                                        const int cost_o, const int cost_p)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    float* sm_fs = reinterpret_cast<float*>(smem_raw);
+    float* sm_fo = sm_fs + B.ncs * kChunkFloats;
+    float* sm_fsd = sm_fo + B.nco * kChunkFloats;
+    float* sm_fod = sm_fsd + B.ncsd * kChunkFloats;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sm_fod + B.ncod * kChunkFloats); // [0] FP32 scale [1] FP32 orientation [2] FP64
+    if (threadIdx.x == 0)
+    {
+        if (blockIdx.x == 0) B.phase_ns[7] = global_ns(); // diagnostics
+        for (int i = 0; i < 3; i++) mbar_init(&bars[i], 1);
+        fence_barrier_init();
+        const uint32_t b_fs = B.ncs * kChunkBytes, b_fo = B.nco * kChunkBytes, b_fsd = B.ncsd * kChunkBytes,
+                       b_fod = B.ncod * kChunkBytes;
+        mbar_expect_tx(&bars[0], b_fs);
+        if (b_fs) tma_load_1d(sm_fs, B.fs, b_fs, &bars[0]);
+        mbar_expect_tx(&bars[1], b_fo);
+        if (b_fo) tma_load_1d(sm_fo, B.fo, b_fo, &bars[1]);
+        mbar_expect_tx(&bars[2], b_fsd + b_fod);
+        if (b_fsd) tma_load_1d(sm_fsd, B.fsd, b_fsd, &bars[2]);
+        if (b_fod) tma_load_1d(sm_fod, B.fod, b_fod, &bars[2]);
+    }
+    GCR_TRACER(tr, (threadIdx.x >> 5) * gridDim.x + blockIdx.x, (threadIdx.x & 31) == 0);
+    GCR_STAMP(tr);
+    pdl_launch_dependents();
+    __syncthreads();
+    pdl_wait(); // compact lists and counters of k_sample_solve (the features staged above are older than that kernel)
+
+    ResidentPlan P;
+    const int n_fast = static_cast<int>(B.ctr->n_fast), n_sens = static_cast<int>(B.ctr->n_sens);
+    P.nbs = (B.ns + 31) / 32;
+    P.nbo = (B.no + 31) / 32;
+    P.cost_o = cost_o;
+    P.total = kCostS * P.nbs + cost_o * P.nbo;
+    const int tiles_a = (n_fast + 32 * kHB - 1) / (32 * kHB), tiles_b = (n_sens + 32 * kHB - 1) / (32 * kHB);
+    // the line of all tiles in units of 1/10 cost: a precise tile is cost_p * total long, an FP32 tile 10 * total
+    const long long len_b = static_cast<long long>(cost_p) * P.total, len_a = 10ll * P.total;
+    const long long end_b = len_b * tiles_b, end_all = end_b + len_a * tiles_a;
+    const int n_warps = static_cast<int>(gridDim.x) * (kResidentThreads / 32);
+    const long long piece = max((end_all + n_warps - 1) / n_warps, 10ll * kMinPieceCost);
+    // consecutive pieces go to different SMs
+    const int w = static_cast<int>(threadIdx.x >> 5) * static_cast<int>(gridDim.x) + static_cast<int>(blockIdx.x);
+    long long pos = piece * w;
+    const long long pos_end = min(pos + piece, end_all);
+    GCR_STAMP(tr);
+    while (pos < pos_end)
+    {
+        GCR_STAMP(tr);
+        const bool precise = pos < end_b;
+        const long long len = precise ? len_b : len_a, rel = precise ? pos : pos - end_b;
+        const int tile = static_cast<int>(rel / len);
+        const long long off0 = rel - len * tile, off1 = min(len, off0 + (pos_end - pos));
+        // offsets in a tile's line -> blocks; the same rounding on both sides of a cut, so the pieces tile the line exactly
+        const int b0 = P.block_at(off0 * P.total / len), b1 = P.block_at(off1 * P.total / len);
+        const bool whole = b0 == 0 && b1 == P.nbs + P.nbo;
+        if (b0 < b1)
+        {
+            if (precise) resident_task<MASKS, true>(B, T, sm_fsd, sm_fod, P, tile, b0, b1, n_sens, whole, &bars[2], &bars[2]);
+            else resident_task<MASKS, false>(B, T, sm_fs, sm_fo, P, tile, b0, b1, n_fast, whole, &bars[0], &bars[1]);
+        }
+        pos += off1 - off0;
+        GCR_STAMP(tr);
+    }
+    // no CTA may retire while its bulk copies are in flight (a CTA without work gets here at once)
+    if (threadIdx.x == 0)
+        for (int i = 0; i < 3; i++) mbar_wait(&bars[i], 0);
 }
 
 } // namespace gcr
