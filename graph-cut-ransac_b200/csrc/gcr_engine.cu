@@ -488,6 +488,7 @@ int gcr_create(int device, gcr_handle* out)
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_tail, kExactThreads, 0);
         if (e == cudaSuccess) e = cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device);
         h->tail_grid = h->n_sm * std::max(1, std::min(per_sm, 2));
+        if (const char* v = std::getenv("GCR_TAIL_GRID")) h->tail_grid = std::max(1, std::min(std::atoi(v), h->n_sm * std::max(1, per_sm)));
         if (e == cudaSuccess && !coop)
         {
             h->err = "device does not support cooperative launches";
@@ -870,7 +871,20 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
     if (time_kernels) GCR_CUDA(cudaEventRecord(h->ev0, s));
     if (h->have_masks) GCR_CUDA(cudaMemsetAsync(h->d_masks.p, 0, sizeof(unsigned int) * H * W, s));
     const int hb = static_cast<int>((H + 127) / 128);
-    k_sample_solve<<<hb, 128, 0, s>>>(B, T, all_exact);
+    {
+        // chained to the kernel before it: behind k_prep_features (gcr_set_features + gcr_run back to back) the sample fetch, over
+        // PCIe for pinned replay arrays, runs under the feature preparation; behind any other kernel it is a plain launch
+        cudaLaunchAttribute at;
+        at.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at.val.programmaticStreamSerializationAllowed = 1;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(hb);
+        cfg.blockDim = dim3(128);
+        cfg.stream = s;
+        cfg.attrs = &at;
+        cfg.numAttrs = h->pdl && !time_kernels && !h->have_masks ? 1 : 0;
+        GCR_CUDA(cudaLaunchKernelEx(&cfg, k_sample_solve, B, T, all_exact));
+    }
     {
         const int grid = h->score_grid[h->have_masks ? 1 : 0]; // persistent: one CTA per resident slot
         // small feature sets (both working sets fit in one SM's shared memory): resident kernel, one CTA per SM

@@ -38,6 +38,7 @@ __global__ void k_prep_features(const double* __restrict__ scale, int ns, const 
 {
     constexpr int kCD = kChunk / 2; // features per FP64 chunk (same byte size as an FP32 chunk)
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    pdl_launch_dependents(); // a following k_sample_solve may fetch its samples (replay: over PCIe) while this kernel runs
     const float inf = __int_as_float(0x7f800000);
     const double dinf = __longlong_as_double(0x7ff0000000000000ll), dnan = __longlong_as_double(0x7ff8000000000000ll);
     if (i < ncs * kChunk)
@@ -209,6 +210,7 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
                 draw_pair(c[2], c[3], static_cast<uint32_t>(B.no), o0, o1);
             if (B.samples) reinterpret_cast<int4*>(B.samples)[h] = make_int4(s0, s1, o0, o1);
         }
+        pdl_wait(); // features and their per-feature columns: k_prep_features, when it is the kernel just before this one
         const unsigned n_third = static_cast<unsigned>(scale_only ? B.ns : B.no);
         const bool in_range = static_cast<unsigned>(s0) < static_cast<unsigned>(B.ns) &&
                               static_cast<unsigned>(s1) < static_cast<unsigned>(B.ns) &&
@@ -447,7 +449,10 @@ __device__ __forceinline__ void exact_items_phase(const Buffers& B, const Thresh
     const unsigned int upi = ups + upo;
     const unsigned long long n_units = static_cast<unsigned long long>(n_items) * upi;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (unsigned long long unit = blockIdx.x; unit < n_units; unit += gridDim.x)
+    // mode 0 runs in the tail's first phase behind the fix-up pairs, which fill the CTAs from the front: units from the back,
+    // so that no CTA has both chains (each one FP64 residual long, ~3.5 us) to run one after the other
+    const unsigned int first_cta = mode == 0 ? gridDim.x - 1u - blockIdx.x : blockIdx.x;
+    for (unsigned long long unit = first_cta; unit < n_units; unit += gridDim.x)
     {
         const unsigned int it = static_cast<unsigned int>(unit / upi), u = static_cast<unsigned int>(unit % upi);
         const int cls = u >= ups;
@@ -625,7 +630,15 @@ __device__ __forceinline__ void finalize_phase(const Buffers& B, const Threshold
         const unsigned long long other = __shfl_xor_sync(0xffffffffu, key, o);
         key = other > key ? other : key;
     }
-    if ((threadIdx.x & 31) == 0 && key) atomicMax(&B.ctr->best_key, key);
+    // one atomic per CTA (2 368 warp leaders on one address serialise in L2 for ~1 us)
+    __shared__ unsigned long long s_key[kExactThreads / 32];
+    if ((threadIdx.x & 31) == 0) s_key[threadIdx.x >> 5] = key;
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        for (unsigned int w = 1; w < blockDim.x / 32; w++) key = s_key[w] > key ? s_key[w] : key;
+        if (key) atomicMax(&B.ctr->best_key, key);
+    }
 }
 
 // collect: hypotheses whose FP32-path score is within the path's error of the best one are re-scored in FP64
