@@ -241,11 +241,12 @@ def run_ours(args):
     # ---- dominant kernel (FP32 MSAC scoring) timed alone, same launches, synchronous result read-back
     res = eng.run(n_hyp, scene.thr, first_hyp=first_hyp, samples_ptr=d_samples.data_ptr(), sync=True)
     k_ms = []
-    for _ in range(5):
+    for _ in range(20 if n_hyp * nfeat < 1e10 else 5):
         flush.zero_()
         r = eng.run(n_hyp, scene.thr, first_hyp=first_hyp, samples_ptr=d_samples.data_ptr(), sync=True, flags=gcr_capi.RUN_TIME_KERNELS)
         k_ms.append(r.score_kernel_ms)
-    k_ms = float(np.median(k_ms))
+    k_ms = float(np.mean(k_ms))  # mean, not median: CUDA event stamps tick every ~2 us here, which a 45 us kernel only averages out
+    kernel_name = "k_score_resident" if r.score_kernel == 1 else "k_score_fast"
     n_fast = res.n_solved - res.n_exact_hyp
     flops = n_fast * (ns * FLOP_SCALE + no * FLOP_ORIENT)
     achieved = flops / (k_ms * 1e-3) / 1e12
@@ -254,11 +255,11 @@ def run_ours(args):
                 "frac": achieved / FP32_PEAK_TFLOPS, "traffic": None,
                 "note": "issue-bound FP32/SFU kernel (no dense contraction, HBM traffic negligible): peak = 148 SM x 128 lanes x 2 x "
                         "1.965 GHz nominal (not in MEASURED_PEAKS.json, which holds HBM and bf16-tensor peaks only)",
-                "kernel": "k_score_fast", "kernel_ms": k_ms, "kernel_evals": int(n_fast) * nfeat,
+                "kernel": kernel_name, "kernel_ms": k_ms, "kernel_evals": int(n_fast) * nfeat,
                 "kernel_evals_per_s": n_fast * nfeat / (k_ms * 1e-3),
                 "hbm": {"algorithmic_bytes": int(alg_bytes), "achieved_gbs": alg_bytes / (k_ms * 1e-3) / 1e9}}
     try:  # DRAM bytes of this kernel from the committed `ncu --set full` capture (tools/summarize_profiles.py)
-        tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))[args.config]["k_score_fast"]
+        tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))[args.config][kernel_name]
         roofline["traffic"] = tr["dram_bytes_per_launch"]
         roofline["traffic_source"] = tr["source"]
     except Exception:

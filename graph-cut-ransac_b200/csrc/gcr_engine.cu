@@ -80,6 +80,7 @@ struct gcr_engine_s
     int problem = 0; // GCR_PROBLEM_*
     int score_grid[2] = {148, 148};
     bool pdl = true;            // programmatic dependent launch of the scoring kernel and the tail (GCR_PDL=0: plain launches)
+    bool last_resident = false; // the last gcr_run used k_score_resident
     bool resident_ok = true;    // k_score_resident usable (GCR_RESIDENT=0 forces the ring kernel: A/B runs)
     long long resident_max_hyp = 262144; // ... for batches up to this many slots (GCR_RESIDENT_MAX_HYP); measured on B200 against the
                                          // ring kernel: step 59.8 -> 47.4 us at C1 (5k slots), 86.7 -> 85.4 us at C2 (100k), kernel +4 % at C5 (1M)
@@ -889,7 +890,7 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
         const int grid = h->score_grid[h->have_masks ? 1 : 0]; // persistent: one CTA per resident slot
         // small feature sets (both working sets fit in one SM's shared memory): resident kernel, one CTA per SM
         const int chunks = B.ncs + B.nco + B.ncsd + B.ncod;
-        const bool resident = h->resident_ok && chunks <= kResidentMaxChunks && n_hyp <= h->resident_max_hyp;
+        const bool resident = h->last_resident = h->resident_ok && chunks <= kResidentMaxChunks && n_hyp <= h->resident_max_hyp;
         const size_t rsmem = static_cast<size_t>(chunks) * kChunkBytes + 64;
         // chained launches: the scoring kernel and the tail start launching while their predecessor runs and wait for its
         // results on the device (griddepcontrol.wait); not when the scoring kernel is bracketed by timing events
@@ -986,6 +987,7 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
         out->stage_phase_us[0] = static_cast<float>(static_cast<double>(ph[7] - ph[6]) * 1e-3); // k_sample_solve start -> k_score_fast start
         out->stage_phase_us[1] = static_cast<float>(static_cast<double>(ph[5] - ph[6]) * 1e-3); // k_sample_solve start -> end of k_tail
         out->winner_rank = static_cast<int32_t>(r.reserved);
+        out->score_kernel = h->last_resident ? 1 : 0;
         if (c.xchg_timeout) return h->fail(GCR_ERR_STATE, "winner exchange timed out: a peer rank did not run the same collective call");
         if (c.n_bad_sample) return h->fail(GCR_ERR_INVALID, "replayed sample indices out of range");
         if (c.n_worklist_overflow) return h->fail(GCR_ERR_STATE, "guard-band worklist overflow");

@@ -35,7 +35,7 @@ class GcrResult(C.Structure):
         ("best_n_inl", C.c_uint32 * 2), ("pad_", C.c_uint32 * 2), ("n_hyp", C.c_int64),
         ("n_sample_valid", C.c_int64), ("n_solved", C.c_int64), ("n_rechecked", C.c_int64),
         ("n_exact_hyp", C.c_int64), ("n_candidates", C.c_int64), ("device_ms", C.c_float),
-        ("score_kernel_ms", C.c_float), ("winner_rank", C.c_int32), ("pad2_", C.c_int32),
+        ("score_kernel_ms", C.c_float), ("winner_rank", C.c_int32), ("score_kernel", C.c_int32),
         ("tail_phase_us", C.c_float * 6),
         ("stage_phase_us", C.c_float * 2),
     ]

@@ -73,7 +73,7 @@ typedef struct gcr_result
     float device_ms;        /* CUDA-event time of the whole hypothesis stage on the engine stream (GCR_RUN_TIME_KERNELS; else 0) */
     float score_kernel_ms;  /* CUDA-event time of the dominant FP32 scoring kernel alone (GCR_RUN_TIME_KERNELS; else 0) */
     int32_t winner_rank;    /* rank owning best_index (0 unless the run exchanged records with peers) */
-    int32_t pad2_;
+    int32_t score_kernel;   /* which scoring kernel ran: 0 = k_score_fast (TMA ring), 1 = k_score_resident (working set in shared memory) */
     float tail_phase_us[6]; /* diagnostics (device timer): fix-up+FP64 items | finalize | collect | candidate re-scoring | select | start of the scoring kernel -> start of the tail */
     float stage_phase_us[2]; /* diagnostics (device timer): start of the sampler/solver kernel -> start of the scoring kernel | -> end of the tail */
 } gcr_result;

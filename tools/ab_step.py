@@ -17,9 +17,11 @@ h_scale, h_orient, h_smp = (torch.from_numpy(a).pin_memory() for a in (sc.scale,
 stream = torch.cuda.Stream(); torch.cuda.set_stream(stream)
 d_rec = torch.zeros(8, dtype=torch.float64, device="cuda")
 engines = []
+DEFAULT_LIB = gcr_capi.LIB_PATH
 for st in settings:
     kv = [] if st == "-" else [x.split("=") for x in st.split(",")]
     for k, v in kv: os.environ[k] = v
+    gcr_capi.LIB_PATH = os.path.join(ROOT, os.environ["LIB"]) if "LIB" in os.environ else DEFAULT_LIB  # LIB=gpurun_variants/x.so: another build
     e = gcr_capi.Engine(0); e.set_stream(stream.cuda_stream); e.set_features(sc.scale, sc.orient)
     e2 = gcr_capi.Engine(0)
     engines.append((e, e2))

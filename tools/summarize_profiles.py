@@ -13,7 +13,7 @@ KEYS = ["gpu__time_duration.sum", "sm__cycles_elapsed.avg", "sm__cycles_active.a
 OUT = sys.argv[2] if len(sys.argv) > 2 else R
 import json
 TRAFFIC = {}
-for cfg, kern in (("c2", "k_score_fast"), ("c3", "k_score_fast"), ("c2", "k_sample_solve"), ("c2", "k_tail")):
+for cfg, kern in (("c2", "k_score_resident"), ("c2", "k_score_fast"), ("c3", "k_score_fast"), ("c2", "k_sample_solve"), ("c2", "k_tail")):
     rep = f"gpurun_out/prof_{cfg}_{kern}_{R}.ncu-rep"
     if not os.path.exists(rep):
         continue
@@ -35,7 +35,10 @@ for cfg, kern in (("c2", "k_score_fast"), ("c3", "k_score_fast"), ("c2", "k_samp
                     tr += float(v.replace(",", "")) * scale.get(u, 1.0)
             TRAFFIC.setdefault(cfg.upper(), {})[kern] = {"dram_bytes_per_launch": tr, "source": f"profiles/{OUT}_ncu_full_{kern}_{cfg}.txt"}
 if TRAFFIC:
-    json.dump(TRAFFIC, open("profiles/traffic.json", "w"), indent=1)
+    old = json.load(open("profiles/traffic.json")) if os.path.exists("profiles/traffic.json") else {}
+    for cfg, d in TRAFFIC.items():
+        old.setdefault(cfg, {}).update(d)
+    json.dump(old, open("profiles/traffic.json", "w"), indent=1)
 rows = [r for r in csv.reader(open(f"gpurun_out/launches_c2_{R}.csv")) if len(r) > 10 and r[0].isdigit()]
 agg = collections.OrderedDict()
 for r in rows:

@@ -21,6 +21,7 @@ for rep in range(4):
     r = e.run(c["n_hyp"], sc.thr, samples_ptr=smp.data_ptr(), flags=gcr_capi.RUN_TIME_KERNELS)
     lib.gcr_debug_read_trace(buf.ctypes.data_as(C.c_void_p), C.c_size_t(buf.nbytes))
 print(f"{name} {sys.argv[2:]} kernel {r.score_kernel_ms*1e3:.1f} us, stage {r.device_ms*1e3:.1f} us")
+if os.environ.get("TRACE_DUMP"): np.save(os.environ["TRACE_DUMP"], buf[:4736])
 rows = buf[buf[:, 1] > 0]
 t0 = rows[:, 1].min()
 T = (rows[:, 1:].astype(np.int64) - np.int64(t0)) / 1e3  # us
