@@ -108,6 +108,8 @@ def cpu_reference_leg(name: str, budget_hyp: int, nthreads: int = 0):
     from oracle_lib import Oracle, have_reference
     kind = "reference" if have_reference() else "port"
     o = Oracle(kind)
+    if nthreads <= 0:  # every host core this process may use (torchrun exports OMP_NUM_THREADS=1: do not inherit that)
+        nthreads = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     scene, samples, n_hyp = workload(name)
     smp = samples[:budget_hyp]
     nfeat = len(scene.scale) + len(scene.orient)
