@@ -82,9 +82,12 @@ struct gcr_engine_s
     bool pdl = true;            // programmatic dependent launch of the scoring kernel and the tail (GCR_PDL=0: plain launches)
     bool last_resident = false; // the last gcr_run used k_score_resident
     bool resident_ok = true;    // k_score_resident usable (GCR_RESIDENT=0 forces the ring kernel: A/B runs)
-    long long resident_max_hyp = 262144; // ... for batches up to this many slots (GCR_RESIDENT_MAX_HYP); measured on B200 against the
-                                         // ring kernel: step 59.8 -> 47.4 us at C1 (5k slots), 86.7 -> 85.4 us at C2 (100k), kernel +4 % at C5 (1M)
-    int resident_cost_o = 27;   // cost model of k_score_resident's static partition: orientation block (scale block = 10) ...
+    long long resident_max_hyp = 262144; // ... for batches up to this many slots (GCR_RESIDENT_MAX_HYP) and slots x features (GCR_RESIDENT_MAX_EVALS).
+    long long resident_max_evals = 300000000; // Measured on B200 against the ring kernel: step 59.8 -> 47.4 us at C1 (5k slots x 2 500 features),
+                                              // 86.7 -> 85.4 us at C2 (100k x 2 500), 117.8 -> 120.2 us at C4's image size (100k x 5 000), kernel + 4 %
+                                              // at C5 (1M x 2 500); with several engines in flight (C4 batches) the ring kernel's small CTAs interleave
+                                              // with the other engines' kernels and win by 10 %
+    int resident_cost_o = 20;   // cost model of k_score_resident's static partition: orientation block (scale block = 10) ...
     int resident_cost_p = 20;   // ... and a precise tile relative to an FP32 tile (x 10); GCR_COST_O / GCR_COST_P for tuning runs
     int tail_grid = 148;
     cudaStream_t own_stream = nullptr, stream = nullptr;
@@ -473,7 +476,8 @@ int gcr_create(int device, gcr_handle* out)
         e = cudaFuncSetAttribute(k_score_resident<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, resident_smem);
     if (const char* v = std::getenv("GCR_RESIDENT")) h->resident_ok = std::atoi(v) != 0;
     if (const char* v = std::getenv("GCR_PDL")) h->pdl = std::atoi(v) != 0;
-    if (const char* v = std::getenv("GCR_RESIDENT_MAX_HYP")) h->resident_max_hyp = std::atoll(v);
+    if (const char* v = std::getenv("GCR_RESIDENT_MAX_HYP")) h->resident_max_hyp = h->resident_max_evals = std::atoll(v);
+    if (const char* v = std::getenv("GCR_RESIDENT_MAX_EVALS")) h->resident_max_evals = std::atoll(v);
     if (const char* v = std::getenv("GCR_COST_O")) h->resident_cost_o = std::max(1, std::atoi(v));
     if (const char* v = std::getenv("GCR_COST_P")) h->resident_cost_p = std::max(1, std::atoi(v));
     for (int m = 0; m < 2 && e == cudaSuccess; m++)
@@ -890,7 +894,8 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
         const int grid = h->score_grid[h->have_masks ? 1 : 0]; // persistent: one CTA per resident slot
         // small feature sets (both working sets fit in one SM's shared memory): resident kernel, one CTA per SM
         const int chunks = B.ncs + B.nco + B.ncsd + B.ncod;
-        const bool resident = h->last_resident = h->resident_ok && chunks <= kResidentMaxChunks && n_hyp <= h->resident_max_hyp;
+        const bool resident = h->last_resident = h->resident_ok && chunks <= kResidentMaxChunks && n_hyp <= h->resident_max_hyp &&
+                                                   n_hyp * (static_cast<long long>(B.ns) + B.no) <= h->resident_max_evals;
         const size_t rsmem = static_cast<size_t>(chunks) * kChunkBytes + 64;
         // chained launches: the scoring kernel and the tail start launching while their predecessor runs and wait for its
         // results on the device (griddepcontrol.wait); not when the scoring kernel is bracketed by timing events

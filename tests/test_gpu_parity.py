@@ -346,9 +346,12 @@ def test_randomised_scenes_vs_oracle(eng, port):
     assert n_solved > 2000
 
 
-def test_thousands_of_tied_hypotheses_select_the_earliest(eng, port):
-    """More near-best hypotheses than the re-scoring pass holds at once (1024): a scene whose minimal samples all come from
-    a handful of exactly consistent features, so that thousands of hypotheses tie; the reference keeps the first (S11)."""
+@pytest.mark.parametrize("H, min_tied", [(6000, 2000), (1400, 600), (120, 50)])
+def test_thousands_of_tied_hypotheses_select_the_earliest(eng, port, H, min_tied):
+    """Many exactly tied near-best hypotheses: a scene whose minimal samples all come from a handful of exactly consistent
+    features; the reference keeps the first (S11).  6000 slots: more ties than the re-scoring pass holds at once (1024
+    candidate slots), i.e. several collect | re-score | select rounds of k_tail; 1400 and 120: hundreds / tens of candidates
+    in one round."""
     import gcr_scenes as gs
     sc = gs.make_scene(40, 30, 1.0, 77, thr_scale=0.2, thr_orient=math.radians(3.0))
     # noise-free inliers: regenerate the scale / orientation values exactly from the ground-truth model
@@ -356,19 +359,19 @@ def test_thousands_of_tied_hypotheses_select_the_earliest(eng, port):
     h7, h8, alpha, phi = sc.model
     w = 1.0 - h7 * scale[:, 0] - h8 * scale[:, 1]
     scale[:, 2] = (w / alpha) ** 3
-    H = 6000
-    smp = gs.draw_samples(H, 40, 30, 3)
+    smp = gs.draw_samples(6000, 40, 30, 3)[:H].copy()
     smp[:, :2] = smp[0, :2]  # every hypothesis uses the same two scale features ...
-    smp[:, 2:] = smp[np.arange(H) % 2, 2:]  # ... and one of 2 orientation pairs: 2 distinct models, 3000 copies each
+    smp[:, 2:] = smp[np.arange(H) % 2, 2:]  # ... and one of 2 orientation pairs: 2 distinct models, H / 2 copies each
     ora = port.replay(scale, orient, smp, sc.thr, nthreads=0)
     want = port.select_best(ora["score"], ora["flags"])
     assert want >= 0
     n_tied = int(np.sum(ora["score"] == ora["score"][want]))
-    assert n_tied > 2000  # more than the 1024 candidate slots of one re-scoring pass
+    assert n_tied > min_tied
     res, dev = _run_replay(eng, scale, orient, smp, sc.thr)
     _compare(dev, ora, 40, 30, label="ties")
     assert res.best_index == want, (res.best_index, want, n_tied, res.n_candidates)
     assert res.best_score == pytest.approx(ora["score"][want], rel=1e-12)
+    assert res.n_candidates >= n_tied
 
 
 def test_pinned_host_inputs_are_read_in_place_with_identical_results(eng, port):
