@@ -176,15 +176,14 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
 {
     const int h = blockIdx.x * blockDim.x + threadIdx.x;
     const unsigned lane = threadIdx.x & 31;
-    pdl_launch_dependents(); // the scoring kernel may set up (barriers, feature staging) while this one runs
     if (h == 0) B.phase_ns[6] = global_ns(); // diagnostics: start of the stage as seen by the first CTA
     bool solved = false, hard = false, sample_valid = false, sens_s = false, sens_o = false;
     Model4 m = {0.0, 0.0, 0.0, 0.0};
     float4 p0 = make_float4(0.f, 0.f, 0.f, 0.f), p1 = make_float4(0.f, 1.f, 0.f, 0.f);
+    int s0 = 0, s1 = 0, o0 = 0, o1 = 0; // scale-only problems: (s0, s1, o0) index the scale class, o1 is unused (-1)
+    const bool scale_only = T.problem != 0;
     if (h < B.n_hyp)
     {
-        int s0, s1, o0, o1; // scale-only problems: (s0, s1, o0) index the scale class, o1 is unused (-1)
-        const bool scale_only = T.problem != 0;
         if (B.have_samples)
         {
             const int4 s = reinterpret_cast<const int4*>(B.samples)[h];
@@ -210,7 +209,14 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
                 draw_pair(c[2], c[3], static_cast<uint32_t>(B.no), o0, o1);
             if (B.samples) reinterpret_cast<int4*>(B.samples)[h] = make_int4(s0, s1, o0, o1);
         }
-        pdl_wait(); // features and their per-feature columns: k_prep_features, when it is the kernel just before this one
+    }
+    // Every thread: wait for the kernel before this one (k_prep_features in the host-buffer path: the features and their per-feature
+    // columns), and only THEN let the scoring kernel start: its prologue stages the feature planes that k_prep_features writes, and a
+    // dependent's griddepcontrol.wait covers this kernel only, so the trigger must not fire while k_prep_features may still run.
+    pdl_wait();
+    pdl_launch_dependents();
+    if (h < B.n_hyp)
+    {
         const unsigned n_third = static_cast<unsigned>(scale_only ? B.ns : B.no);
         const bool in_range = static_cast<unsigned>(s0) < static_cast<unsigned>(B.ns) &&
                               static_cast<unsigned>(s1) < static_cast<unsigned>(B.ns) &&

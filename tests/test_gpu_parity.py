@@ -447,3 +447,36 @@ def test_ring_and_resident_scoring_kernels_agree(port):
     finally:
         for e in engines.values():
             e.close()
+
+
+def test_back_to_back_feature_changes_with_chained_launches(port):
+    """gcr_set_features + gcr_run back to back with page-locked inputs, alternating between two scenes of the same size on one
+    engine: the kernels are chained with programmatic dependent launches (each starts under its predecessor and waits on the
+    device for what it needs), so a kernel that read the feature planes before k_prep_features had finished would score the
+    PREVIOUS scene's features.  Small batches (few CTAs of k_sample_solve, most SMs free for an early scoring kernel) are
+    the exposed case; every run must reproduce its own scene's reference result."""
+    import ctypes as C
+    import torch
+    import gcr_capi
+    import gcr_scenes as gs
+    ns, no, n_hyp = 1500, 400, 2048
+    scenes = [gs.make_scene(ns, no, 0.3, 21), gs.make_scene(ns, no, 0.4, 22)]
+    smps = [gs.draw_samples(n_hyp, ns, no, 31), gs.draw_samples(n_hyp, ns, no, 32)]
+    want = []
+    for sc, smp in zip(scenes, smps):
+        ora = port.replay(sc.scale, sc.orient, smp, sc.thr, want_masks=False, nthreads=0)
+        want.append(port.select_best(ora["score"], ora["flags"]))
+    assert want[0] >= 0 and want[1] >= 0
+    pinned = [tuple(torch.from_numpy(a).pin_memory() for a in (sc.scale, sc.orient, smp)) for sc, smp in zip(scenes, smps)]
+    e = gcr_capi.Engine(0)
+    try:
+        out = gcr_capi.GcrResult()
+        for it in range(60):
+            k = it & 1
+            ps, po, pp = pinned[k]
+            thr_c = (C.c_double * 2)(*scenes[k].thr)
+            assert e.lib.gcr_set_features(e.h, C.c_void_p(ps.data_ptr()), ns, C.c_void_p(po.data_ptr()), no, 0) == 0
+            assert e.lib.gcr_run(e.h, n_hyp, 0, 0, C.c_void_p(pp.data_ptr()), thr_c, 0, None, C.byref(out)) == 0
+            assert out.best_index == want[k], (it, out.best_index, want)
+    finally:
+        e.close()
