@@ -54,12 +54,14 @@ struct Tracer
 #define GCR_STAMP(name)
 #endif
 
+constexpr unsigned int kNoHyp = 0xffffffffu;
 struct HypRegs
 {
     float nh7, nh8, A, Tin, Tout, cphi, sphi, dpr;
     double h7d, h8d; // precise tiles only
-    unsigned int hyp;
-    bool active;
+    unsigned int hyp; // resident kernel: kNoHyp marks an inactive lane (padding of the last tile) instead of `active`: one long-lived
+                      // predicate more made ptxas keep the band-check predicates in a GPR there (12 LOP3 per 16 scale evaluations)
+    bool active;      // ring kernel
     double sum_s, sum_o;
     unsigned int cnt_s, cnt_o;
 };
@@ -311,7 +313,7 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
                         }
                         else
                             r = verdict(j, stage[f], stage[NF + f], stage[2 * NF + f], 0.0, 0.0, 0.0, x0, x1);
-                        if (r.unc && H[j].active)
+                        if (r.unc && (RANGE ? H[j].hyp != kNoHyp : H[j].active))
                             worklist_push(B, H[j].hyp, (CLS ? 0x80000000u : 0u) | static_cast<unsigned>(fbase + f));
                     }
                 }
@@ -324,7 +326,7 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
 #pragma unroll
             for (int j = 0; j < kHB; j++)
             {
-                if (H[j].active && mword[j])
+                if ((RANGE ? H[j].hyp != kNoHyp : H[j].active) && mword[j])
                     atomicOr(&B.masks[static_cast<size_t>(H[j].hyp) * B.wmask + (CLS ? B.ws : 0) + ((fbase + g * G) >> 5)],
                              mword[j]);
                 mword[j] = 0u;
@@ -349,7 +351,7 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
 
 // Hypothesis parameters of the kHB hypotheses of a thread: compact index first_compact + j * stride + lane_in_tile of the FP32
 // list (from the front of the compact arrays) or of the precise list (from the back).
-template <bool PRECISE>
+template <bool PRECISE, bool SENTINEL = false>
 __device__ __forceinline__ void load_hyps(const Buffers& B, HypRegs (&H)[kHB], int first_compact, int stride, int t, int n_list,
                                           bool from_back)
 {
@@ -357,16 +359,17 @@ __device__ __forceinline__ void load_hyps(const Buffers& B, HypRegs (&H)[kHB], i
     for (int j = 0; j < kHB; j++)
     {
         const int k = first_compact + j * stride + t;
-        H[j].active = k < n_list;
+        const bool active = k < n_list;
         const int c = from_back ? B.n_hyp - 1 - k : k;
         // inactive lanes: parameters for which every comparison is false
-        const float4 p0 = H[j].active ? B.pf0[c] : make_float4(0.f, 0.f, 0.f, -1.f);
-        const float4 p1 = H[j].active ? B.pf1[c] : make_float4(-1.f, __int_as_float(0x7fc00000), 0.f, 0.f);
-        H[j].hyp = H[j].active ? B.fast_hyp[c] : 0u;
+        const float4 p0 = active ? B.pf0[c] : make_float4(0.f, 0.f, 0.f, -1.f);
+        const float4 p1 = active ? B.pf1[c] : make_float4(-1.f, __int_as_float(0x7fc00000), 0.f, 0.f);
+        H[j].hyp = active ? B.fast_hyp[c] : (SENTINEL ? kNoHyp : 0u);
+        H[j].active = SENTINEL ? true : active;
         H[j].nh7 = p0.x; H[j].nh8 = p0.y; H[j].A = p0.z; H[j].Tin = p0.w;
         H[j].Tout = p1.x; H[j].cphi = p1.y; H[j].sphi = p1.z; H[j].dpr = p1.w;
         H[j].h7d = H[j].h8d = 0.0;
-        if (PRECISE && H[j].active)
+        if (PRECISE && active)
         {
             const Model4 m = B.models[H[j].hyp];
             H[j].h7d = m.h7;
@@ -379,12 +382,13 @@ __device__ __forceinline__ void load_hyps(const Buffers& B, HypRegs (&H)[kHB], i
 
 // Partial sums / counts of a thread's hypotheses into the per-hypothesis arrays: plain stores when this item covered every
 // feature, atomics when the feature range is split over several items.
+template <bool SENTINEL = false>
 __device__ __forceinline__ void flush_hyps(const Buffers& B, const Thresholds& T, HypRegs (&H)[kHB], bool single_split)
 {
 #pragma unroll
     for (int j = 0; j < kHB; j++)
     {
-        if (!H[j].active) continue;
+        if (SENTINEL ? H[j].hyp == kNoHyp : !H[j].active) continue;
         const size_t h = H[j].hyp;
         const double ss = H[j].sum_s * static_cast<double>(T.scale_unit);
         if (single_split)
@@ -552,14 +556,14 @@ struct ResidentPlan // identical in every warp (pure function of the counters an
 
 template <bool MASKS, bool PRECISE>
 __device__ __forceinline__ void resident_task(const Buffers& B, const Thresholds& T, const float* sm_s, const float* sm_o,
-                                              const ResidentPlan& P, int tile, int b0, int b1, int n_list, bool single,
+                                              const ResidentPlan& P, int tile, int b0, int b1, int n_list,
                                               uint64_t* bar_s, uint64_t* bar_o)
 {
     constexpr int NF = PRECISE ? kChunk / 2 : kChunk; // features per chunk
     constexpr int G = PRECISE ? 2 : 4;
     constexpr int BPC = NF / 32, GPB = 32 / G;         // blocks per chunk, groups per block
     HypRegs H[kHB];
-    load_hyps<PRECISE>(B, H, tile * 32 * kHB, 32, threadIdx.x & 31, n_list, PRECISE);
+    load_hyps<PRECISE, true>(B, H, tile * 32 * kHB, 32, threadIdx.x & 31, n_list, PRECISE);
     const int s1 = min(b1, P.nbs);
     if (b0 < s1)
     {
@@ -584,7 +588,7 @@ __device__ __forceinline__ void resident_task(const Buffers& B, const Thresholds
             b = be;
         }
     }
-    flush_hyps(B, T, H, single);
+    flush_hyps<true>(B, T, H, b0 == 0 && b1 == P.nbs + P.nbo); // plain stores when this warp covered the whole tile
 }
 
 template <bool MASKS>
@@ -645,11 +649,10 @@ __global__ void __launch_bounds__(kResidentThreads, 1) k_score_resident(const __
         const long long off0 = rel - len * tile, off1 = min(len, off0 + (pos_end - pos));
         // offsets in a tile's line -> blocks; the same rounding on both sides of a cut, so the pieces tile the line exactly
         const int b0 = P.block_at(off0 * P.total / len), b1 = P.block_at(off1 * P.total / len);
-        const bool whole = b0 == 0 && b1 == P.nbs + P.nbo;
         if (b0 < b1)
         {
-            if (precise) resident_task<MASKS, true>(B, T, sm_fsd, sm_fod, P, tile, b0, b1, n_sens, whole, &bars[2], &bars[2]);
-            else resident_task<MASKS, false>(B, T, sm_fs, sm_fo, P, tile, b0, b1, n_fast, whole, &bars[0], &bars[1]);
+            if (precise) resident_task<MASKS, true>(B, T, sm_fsd, sm_fod, P, tile, b0, b1, n_sens, &bars[2], &bars[2]);
+            else resident_task<MASKS, false>(B, T, sm_fs, sm_fo, P, tile, b0, b1, n_fast, &bars[0], &bars[1]);
         }
         pos += off1 - off0;
         GCR_STAMP(tr);
