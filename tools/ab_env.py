@@ -1,6 +1,7 @@
-"""Interleaved timing of engine settings read at gcr_create (GPU box): python tools/ab_env.py C2 GCR_RESIDENT=0 GCR_TPW=2 GCR_TPW=4 ...
+"""Interleaved timing of engine settings read at gcr_create (GPU box): python tools/ab_env.py C2 - GCR_RESIDENT=0 GCR_COST_O=27 ...
 One engine per setting ("-" = defaults), rounds alternate between them so that clock / thermal drift cancels; FLUSH=1 flushes
-L2 before every run as bench.py does.  The winners of all settings must agree."""
+L2 before every run as bench.py does.  The winners of all settings must agree.  Times are the engine's event brackets
+(GCR_RUN_TIME_KERNELS: chained launches off, event clock ticks every ~2 us); tools/ab_step.py measures whole steps as bench.py does."""
 import os, sys
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
