@@ -446,6 +446,24 @@ static int finish_features(gcr_handle h)
     return ensure_common(h);
 }
 
+
+// Launch of a kernel that follows another kernel of the same call: programmatic stream serialisation, the kernel waits at its top
+// (griddepcontrol.wait) for its predecessor, so only the launch latency overlaps.  Kernels launched this way touch nothing before the wait.
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_chained(gcr_engine_s* h, void (*kernel)(KArgs...), dim3 grid, dim3 block, cudaStream_t s, Args... args)
+{
+    cudaLaunchAttribute at;
+    at.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at.val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.stream = s;
+    cfg.attrs = &at;
+    cfg.numAttrs = h->pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 extern "C"
 {
 
@@ -1099,10 +1117,10 @@ int gcr_score_models(gcr_handle h, const double* models, int64_t n, const double
         unsigned char* d = static_cast<unsigned char*>(dp);
         std::memcpy(h->h_score_io.p, models, sizeof(Model4) * n);
         k_set_models<<<(un + 127) / 128, 128, 0, s>>>(B, reinterpret_cast<const Model4*>(d), un);
-        k_exact_items<<<grid, kExactThreads, 0, s>>>(B, T, 2, un);
-        k_score_out<<<std::max(1, std::min<int>(h->n_sm, static_cast<int>((W * n + 255) / 256))), 256, 0, s>>>(
-            B, T, un, reinterpret_cast<double*>(d + off_score), reinterpret_cast<unsigned int*>(d + off_cnt),
-            mask_words ? reinterpret_cast<unsigned int*>(d + off_masks) : nullptr);
+        GCR_CUDA(launch_chained(h, k_exact_items, dim3(grid), dim3(kExactThreads), s, B, T, 2, un));
+        GCR_CUDA(launch_chained(h, k_score_out, dim3(std::max(1, std::min<int>(h->n_sm, static_cast<int>((W * n + 255) / 256)))), dim3(256), s, B, T,
+                                un, reinterpret_cast<double*>(d + off_score), reinterpret_cast<unsigned int*>(d + off_cnt),
+                                mask_words ? reinterpret_cast<unsigned int*>(d + off_masks) : nullptr));
         GCR_CUDA(cudaGetLastError());
         GCR_CUDA(cudaStreamSynchronize(s));
         if (score) std::memcpy(score, h->h_score_io.p + off_score, sizeof(double) * n);
@@ -1113,8 +1131,8 @@ int gcr_score_models(gcr_handle h, const double* models, int64_t n, const double
     cudaGetLastError();
     GCR_CUDA(cudaMemcpyAsync(h->d_user_models.p, models, sizeof(Model4) * n, cudaMemcpyHostToDevice, s));
     k_set_models<<<(un + 127) / 128, 128, 0, s>>>(B, h->d_user_models.p, un);
-    k_exact_items<<<grid, kExactThreads, 0, s>>>(B, T, 2, un);
-    k_cand_value<<<(un + 127) / 128, 128, 0, s>>>(B, T, un);
+    GCR_CUDA(launch_chained(h, k_exact_items, dim3(grid), dim3(kExactThreads), s, B, T, 2, un));
+    GCR_CUDA(launch_chained(h, k_cand_value, dim3((un + 127) / 128), dim3(128), s, B, T, un));
     GCR_CUDA(cudaGetLastError());
     if (score) GCR_CUDA(cudaMemcpyAsync(score, h->d_cand_score.p, sizeof(double) * n, cudaMemcpyDeviceToHost, s));
     if (n_inl) GCR_CUDA(cudaMemcpyAsync(n_inl, h->d_cand_cnt.p, 2 * sizeof(unsigned int) * n, cudaMemcpyDeviceToHost, s));
@@ -1197,9 +1215,10 @@ int gcr_fit_models(gcr_handle h, int64_t n_fits, const uint32_t* scale_idx, cons
     F.n_lines = static_cast<long long>(O);
     F.problem = h->problem;
     if (O) k_fit_lines<<<static_cast<unsigned int>((O + kFitThreads - 1) / kFitThreads), kFitThreads, 0, s>>>(F);
-    k_fit_rows<<<F.n_units, kFitThreads, 0, s>>>(F);
-    k_fit_solve<<<static_cast<unsigned int>(K), 32, 0, s>>>(F);
-    if (hybrid) k_fit_phi<<<static_cast<unsigned int>(K), kFitThreads, 0, s>>>(F);
+    if (O) GCR_CUDA(launch_chained(h, k_fit_rows, dim3(F.n_units), dim3(kFitThreads), s, F));
+    else k_fit_rows<<<F.n_units, kFitThreads, 0, s>>>(F); // first kernel of the call: behind the input copy, plain
+    GCR_CUDA(launch_chained(h, k_fit_solve, dim3(static_cast<unsigned int>(K)), dim3(32), s, F));
+    if (hybrid) GCR_CUDA(launch_chained(h, k_fit_phi, dim3(static_cast<unsigned int>(K)), dim3(kFitThreads), s, F));
     GCR_CUDA(cudaGetLastError());
     GCR_CUDA(cudaMemcpyAsync(h->h_fit_out.p, h->d_fit_out.p, out_bytes, cudaMemcpyDeviceToHost, s));
     GCR_CUDA(cudaStreamSynchronize(s));

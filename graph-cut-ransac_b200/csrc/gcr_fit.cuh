@@ -124,6 +124,8 @@ struct FitBuffers
 // lineFromPointAndAngle (math_utils.hpp:104-109) of every listed orientation feature
 __global__ void __launch_bounds__(kFitThreads) k_fit_lines(FitBuffers F)
 {
+    pdl_launch_dependents(); // chained launch: the next kernel of the call may start launching now; it waits at its own top
+    pdl_wait();
     const long long i = static_cast<long long>(blockIdx.x) * kFitThreads + threadIdx.x;
     if (i >= F.n_lines) return;
     const double* f = F.orient + 3 * static_cast<size_t>(F.idx_o[i]);
@@ -150,6 +152,8 @@ __device__ __forceinline__ int fit_of_unit(const FitBuffers& F, unsigned int u)
 // lexicographic order.  A thread walks rows r0 + tid, + kFitThreads, ...; consecutive threads take consecutive b.
 __global__ void __launch_bounds__(kFitThreads) k_fit_rows(FitBuffers F)
 {
+    pdl_launch_dependents(); // chained launch: the next kernel of the call may start launching now; it waits at its own top
+    pdl_wait();
     __shared__ double s_red[kFitThreads / 32][2 * kFitGram];
     const unsigned int u = blockIdx.x;
     const int k = fit_of_unit(F, u);
@@ -285,6 +289,8 @@ __device__ inline bool solve_normal3(const dd g[kFitGram], double x[3])
 // One warp per fit: units of the fit summed in a fixed order, then the solve.
 __global__ void __launch_bounds__(32) k_fit_solve(FitBuffers F)
 {
+    pdl_launch_dependents(); // chained launch: the next kernel of the call may start launching now; it waits at its own top
+    pdl_wait();
     const int k = blockIdx.x, lane = threadIdx.x;
     const FitDesc D = F.desc[k];
     const unsigned int u_end = k + 1 < F.n_fits ? F.desc[k + 1].unit_first : F.n_units;
@@ -328,6 +334,8 @@ __global__ void __launch_bounds__(32) k_fit_solve(FitBuffers F)
 // appearance to resolve equal counts exactly as the reference's unordered_map does; emitted here in that order.
 __global__ void __launch_bounds__(kFitThreads) k_fit_phi(FitBuffers F)
 {
+    pdl_launch_dependents(); // chained launch: the next kernel of the call may start launching now; it waits at its own top
+    pdl_wait();
     __shared__ unsigned int s_count[kPhiBins], s_first[kPhiBins];
     __shared__ unsigned long long s_moment[kPhiBins];
     const int k = blockIdx.x;

@@ -514,6 +514,8 @@ __device__ __forceinline__ void exact_items_phase(const Buffers& B, const Thresh
 
 __global__ void __launch_bounds__(kExactThreads) k_exact_items(Buffers B, Thresholds T, int mode, unsigned int n_direct = 1u)
 {
+    pdl_launch_dependents(); // chained launch: the next kernel of the call may start launching now; it waits at its own top
+    pdl_wait();
     exact_items_phase(B, T, mode, n_direct);
 }
 
@@ -528,6 +530,8 @@ __device__ __forceinline__ void cand_value(const Buffers& B, const Thresholds& T
 }
 __global__ void k_cand_value(Buffers B, Thresholds T, unsigned int n)
 {
+    pdl_launch_dependents(); // chained launch: the next kernel of the call may start launching now; it waits at its own top
+    pdl_wait();
     const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) cand_value(B, T, i);
 }
@@ -537,6 +541,8 @@ __global__ void k_cand_value(Buffers B, Thresholds T, unsigned int n)
 __global__ void k_score_out(Buffers B, Thresholds T, unsigned int n, double* __restrict__ h_score, unsigned int* __restrict__ h_cnt,
                             unsigned int* __restrict__ h_masks)
 {
+    pdl_launch_dependents(); // chained launch: the next kernel of the call may start launching now; it waits at its own top
+    pdl_wait();
     const unsigned int t = blockIdx.x * blockDim.x + threadIdx.x, stride = gridDim.x * blockDim.x;
     for (unsigned int i = t; i < n; i += stride)
     {
@@ -1007,6 +1013,8 @@ __global__ void k_refine_done(Buffers B) { B.ctr->n_hard = 0u; }
 // caller-supplied models -> candidate slots [0, n) (gcr_score_model / gcr_score_models)
 __global__ void k_set_models(Buffers B, const Model4* __restrict__ m, unsigned int n)
 {
+    pdl_launch_dependents(); // chained launch: the next kernel of the call may start launching now; it waits at its own top
+    pdl_wait();
     const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     B.cand_model[i] = m[i];
