@@ -36,6 +36,24 @@ def test_version_and_struct_layout(lib):
     assert gcr_capi.RECORD_DTYPE.itemsize == 64
 
 
+def test_ctypes_mirror_matches_the_header_as_compiled(tmp_path):
+    """gcr_result as gcc lays it out from include/gcr_b200.h == the ctypes mirror in gcr_capi (size and every field offset)."""
+    import subprocess
+    import gcr_capi
+    fields = [name for name, _ in gcr_capi.GcrResult._fields_]
+    src = tmp_path / "layout.c"
+    src.write_text("#include <stdio.h>\n#include <stddef.h>\n#include \"gcr_b200.h\"\nint main(void) {\n"
+                   "  printf(\"%zu\\n\", sizeof(gcr_result));\n"
+                   + "".join(f"  printf(\"%zu\\n\", offsetof(gcr_result, {f}));\n" for f in fields)
+                   + "  printf(\"%zu\\n\", sizeof(gcr_record));\n  return 0;\n}\n")
+    exe = tmp_path / "layout"
+    subprocess.check_call(["gcc", "-std=c99", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
+    out = [int(x) for x in subprocess.check_output([str(exe)]).split()]
+    assert out[0] == ctypes.sizeof(gcr_capi.GcrResult)
+    assert out[1:-1] == [getattr(gcr_capi.GcrResult, f).offset for f in fields]
+    assert out[-1] == gcr_capi.RECORD_DTYPE.itemsize
+
+
 def test_null_handle_is_an_error_not_a_crash(lib):
     assert lib.gcr_destroy(None) == -1
     assert lib.gcr_set_features(None, None, 0, None, 0, 0) == -1
