@@ -999,6 +999,7 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
         out->n_solved = c.n_solved;
         out->n_rechecked = c.n_worklist;
         out->n_exact_hyp = c.n_hard;
+        out->n_scored = static_cast<int64_t>(c.n_fast) + c.n_sens + c.n_hard;
         out->n_candidates = c.n_candidates;
         if (time_kernels)
         {

@@ -38,6 +38,7 @@ class GcrResult(C.Structure):
         ("score_kernel_ms", C.c_float), ("winner_rank", C.c_int32), ("score_kernel", C.c_int32),
         ("tail_phase_us", C.c_float * 6),
         ("stage_phase_us", C.c_float * 2),
+        ("n_scored", C.c_int64),
     ]
 
 

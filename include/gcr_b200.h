@@ -76,6 +76,8 @@ typedef struct gcr_result
     int32_t score_kernel;   /* which scoring kernel ran: 0 = k_score_fast (TMA ring), 1 = k_score_resident (working set in shared memory) */
     float tail_phase_us[6]; /* diagnostics (device timer): fix-up+FP64 items | finalize | collect | candidate re-scoring | select | start of the scoring kernel -> start of the tail */
     float stage_phase_us[2]; /* diagnostics (device timer): start of the sampler/solver kernel -> start of the scoring kernel | -> end of the tail */
+    int64_t n_scored;       /* hypotheses scored against every feature (FP32 tiles + precise tiles + FP64 list); == n_solved in the reporting
+                             * modes, fewer in winner-only runs, which skip models that isValidModel rejects (they can never be selected) */
 } gcr_result;
 
 /* Winner record written to device memory by the last kernel of gcr_run when `d_record` is given:

@@ -1,122 +1,230 @@
-// Pipe-throughput microbenchmarks for the B200 (sm_100a) non-tensor datapath: the denominators of the
-// hybrid-MSAC kernel's issue-bound roofline.  Prints warp-instructions per clock per SM for each op mix.
-//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o ubench ubench.cu && ./ubench
+// Issue-rate microbenchmarks of the B200 (sm_100a) non-tensor datapath: the measured denominators of the hybrid-MSAC scoring
+// kernels' roofline (bench.py reads the JSON this prints; SURVEY 8d asks for the nominal FP32 peak AND an FMA measurement).
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o tools/ubench tools/ubench.cu && tools/ubench [--json profiles/x.json]
+//
+// Method: one CTA of 1024 threads per SM (8 warps per scheduler), every thread runs kIters iterations of kIlp INDEPENDENT dependency
+// chains; every instruction is its own `asm volatile` with a read-write operand, so nothing can be folded, hoisted or removed.
+// Cycles = SM clock (clock64) from the first warp's start to the last warp's end inside each CTA, averaged over the CTAs, so the
+// rates are per SM clock and do not depend on the frequency the box happens to run at; the same launch is also timed with CUDA
+// events (-> instructions per second at the clock the box actually sustained, which is what a roofline denominator is).
+// A rate above 4 warp-instructions / clock / SM (the issue limit of 4 schedulers) would mean a broken measurement: asserted.
 #include <cstdio>
-#include <cstdint>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+#include <algorithm>
 #include <cuda_runtime.h>
 
-#define ITERS 2048
-#define NACC 8
+constexpr int kIlp = 8;
+constexpr int kThreads = 1024;
+
+enum Kind
+{
+    K_FFMA, K_FFMA_ACC, K_FADD, K_FMUL, K_FFMA2, K_FSETP_PFFMA, K_FMNMX, K_LOP3, K_IADD, K_MUFU_LG2, K_MUFU_RCP, K_LDS128,
+    K_MIX_SCALE, K_MIX_ORIENT, K_FFMA_MUFU_7_1, K_FFMA_FMNMX_1_1, K_COUNT
+};
+
+struct Desc { const char* name; int instr_per_step; int flops_per_step; const char* note; };
+static const Desc kDesc[K_COUNT] = {
+    {"FFMA  d = a*b + d (3 distinct registers)", 1, 2, "the FP32 peak denominator"},
+    {"FFMA  d = d*b + c (chain form)", 1, 2, ""},
+    {"FADD", 1, 1, ""},
+    {"FMUL", 1, 1, ""},
+    {"FFMA2 (fma.rn.f32x2: two FMAs per instruction)", 1, 4, "packed FP32 pair"},
+    {"FSETP + predicated FFMA", 2, 3, "verdict + accumulate pattern"},
+    {"FMNMX", 1, 1, "alu pipe"},
+    {"LOP3", 1, 0, "alu pipe"},
+    {"IADD3", 1, 0, "alu pipe"},
+    {"MUFU.LG2", 1, 1, "xu pipe"},
+    {"MUFU.RCP", 1, 1, "xu pipe"},
+    {"LDS.128 broadcast", 1, 0, "shared-memory feature read of the scoring kernels"},
+    {"scale-evaluation mix: 2 FFMA + MUFU.LG2 + FADD + 2 FSETP + pred FFMA + 2 pred FADD", 9, 11, "one scale evaluation as issued (no loads)"},
+    {"orientation-evaluation mix: 8 FFMA + 4 FMUL + 3 FADD + FMNMX + FMNMX3 + MUFU.RCP + 2 FSETP", 20, 30, "one orientation evaluation as issued (no loads)"},
+    {"7 FFMA : 1 MUFU.LG2", 8, 14, "xu co-issue"},
+    {"1 FFMA : 1 FMNMX", 2, 3, "fma + alu co-issue"},
+};
 
 template <int KIND>
-__global__ void __launch_bounds__(256) k_bench(float* out, unsigned long long* cycles, float s0, float s1, float s2)
+__global__ void __launch_bounds__(kThreads, 1) k_bench(float* out, unsigned long long* cycles, int iters, float s0, float s1, float s2)
 {
-    float a[NACC];
-    float b = s0 + threadIdx.x * 1e-9f, c = s1, d = s2;
-    unsigned int ia[NACC];
-    unsigned long long pa[NACC];
+    __shared__ unsigned long long t_first, t_last;
+    __shared__ float4 sh[256];
+    if (threadIdx.x == 0) { t_first = ~0ull; t_last = 0ull; }
+    if (threadIdx.x < 256) sh[threadIdx.x] = make_float4(s0, s1, s2, s0);
+    float a[kIlp], acc[kIlp];
+    unsigned int ia[kIlp];
+    unsigned long long pa[kIlp];
+    const float b = s0 + threadIdx.x * 1e-9f, c = s1, d = s2;
+    const unsigned long long pb = (static_cast<unsigned long long>(__float_as_uint(s1)) << 32) | __float_as_uint(s1);
+    const unsigned long long pc = (static_cast<unsigned long long>(__float_as_uint(s2)) << 32) | __float_as_uint(s2);
 #pragma unroll
-    for (int i = 0; i < NACC; i++) { a[i] = s0 * i + threadIdx.x; ia[i] = threadIdx.x + i; pa[i] = threadIdx.x * 0x100000001ull + i; }
-    __shared__ float4 sh[64];
-    if (threadIdx.x < 64) sh[threadIdx.x] = make_float4(s0, s1, s2, s0);
+    for (int i = 0; i < kIlp; i++)
+    {
+        a[i] = 1.0f + 1e-3f * (i + threadIdx.x);
+        acc[i] = 0.f;
+        ia[i] = threadIdx.x * 17 + i;
+        pa[i] = (static_cast<unsigned long long>(__float_as_uint(a[i])) << 32) | __float_as_uint(a[i]);
+    }
+    const unsigned sh_base = static_cast<unsigned>(__cvta_generic_to_shared(sh));
     __syncthreads();
     const unsigned long long t0 = clock64();
-    for (int it = 0; it < ITERS; it++)
+    for (int it = 0; it < iters; it++)
     {
 #pragma unroll
-        for (int i = 0; i < NACC; i++)
+        for (int i = 0; i < kIlp; i++)
         {
-            if (KIND == 0) asm volatile("fma.rn.f32 %0, %1, %2, %0;" : "+f"(a[i]) : "f"(b), "f"(c));                       // FFMA, 2 distinct + acc
-            if (KIND == 1) asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(a[i]) : "f"(c), "f"(d));                       // FFMA chain form
-            if (KIND == 2) asm volatile("add.rn.f32 %0, %0, %1;" : "+f"(a[i]) : "f"(c));                                   // FADD
-            if (KIND == 3) asm volatile("mul.rn.f32 %0, %0, %1;" : "+f"(a[i]) : "f"(c));                                   // FMUL
-            if (KIND == 4) asm volatile("{.reg .pred p; setp.le.f32 p, %0, %1; @p add.s32 %2, %2, 1;}" : "+f"(a[i]) : "f"(c), "r"(ia[i])); // FSETP + pred IADD (not chained)
-            if (KIND == 5) asm volatile("min.f32 %0, %0, %1;" : "+f"(a[i]) : "f"(c));                                      // FMNMX
-            if (KIND == 6) asm volatile("add.s32 %0, %0, %1;" : "+r"(ia[i]) : "r"(ia[(i + 1) % NACC]));                    // IADD
-            if (KIND == 7) asm volatile("lg2.approx.f32 %0, %0;" : "+f"(a[i]));                                            // MUFU.LG2
-            if (KIND == 8) asm volatile("rcp.approx.f32 %0, %0;" : "+f"(a[i]));                                            // MUFU.RCP
-            if (KIND == 9) asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(pa[i]) : "l"(pa[(i + 1) % NACC]), "l"(pa[(i + 2) % NACC])); // FFMA2
-            if (KIND == 10) { asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(a[i]) : "f"(c), "f"(d));                     // 1 FFMA : 1 FMNMX
-                              asm volatile("min.f32 %0, %0, %1;" : "+f"(a[i]) : "f"(b)); }
-            if (KIND == 11) { asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(a[i]) : "f"(c), "f"(d));                     // 2 FFMA : 1 FMNMX
-                              asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(a[i]) : "f"(d), "f"(c));
-                              asm volatile("min.f32 %0, %0, %1;" : "+f"(a[i]) : "f"(b)); }
-            if (KIND == 12) { asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(a[i]) : "f"(c), "f"(d));                     // 4 FFMA : 1 MUFU
-                              asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(a[i]) : "f"(d), "f"(c));
-                              asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(a[i]) : "f"(c), "f"(d));
-                              asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(a[i]) : "f"(d), "f"(c));
-                              asm volatile("lg2.approx.f32 %0, %0;" : "+f"(a[i])); }
-            if (KIND == 13) { float4 v = sh[(it + i) & 63]; a[i] += v.x + v.y + v.z + v.w; }                                // LDS.128 broadcast + 4 FADD
-            if (KIND == 14) { asm volatile("{.reg .pred p; setp.le.f32 p, %0, %1; @p fma.rn.f32 %2, %0, %0, %2;}" : "+f"(a[i]) : "f"(c), "f"(d)); } // FSETP + pred FFMA
-            if (KIND == 15) asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(ia[i]) : "r"(ia[(i + 1) % NACC]), "r"(ia[(i + 2) % NACC])); // LOP3
-            if (KIND == 16) { asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(pa[i]) : "l"(pa[(i + 1) % NACC]), "l"(pa[(i + 2) % NACC])); // FFMA2 : FMNMX 1:1
-                              asm volatile("min.f32 %0, %0, %1;" : "+f"(a[i]) : "f"(b)); }
-            if (KIND == 17) { asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(pa[i]) : "l"(pa[(i + 1) % NACC]), "l"(pa[(i + 2) % NACC])); // FFMA2 : MUFU 2:1
-                              asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(pa[i]) : "l"(pa[(i + 2) % NACC]), "l"(pa[(i + 1) % NACC]));
-                              asm volatile("lg2.approx.f32 %0, %0;" : "+f"(a[i])); }
+            if (KIND == K_FFMA) asm volatile("fma.rn.f32 %0, %1, %2, %0;" : "+f"(a[i]) : "f"(b), "f"(c));
+            if (KIND == K_FFMA_ACC) asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(a[i]) : "f"(c), "f"(d));
+            if (KIND == K_FADD) asm volatile("add.rn.f32 %0, %0, %1;" : "+f"(a[i]) : "f"(c));
+            if (KIND == K_FMUL) asm volatile("mul.rn.f32 %0, %0, %1;" : "+f"(a[i]) : "f"(c));
+            if (KIND == K_FFMA2) asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(pa[i]) : "l"(pb), "l"(pc));
+            if (KIND == K_FSETP_PFFMA)
+                // the compared value changes every step (ptxas optimises the PTX it is given: a loop-invariant setp would be hoisted)
+                asm volatile("{.reg .pred p; setp.le.f32 p, %1, %2; @p fma.rn.f32 %1, %0, %3, %1;}" : "+f"(a[i]), "+f"(acc[i]) : "f"(1e30f), "f"(d));
+            if (KIND == K_FMNMX) asm volatile("min.f32 %0, %0, %1;" : "+f"(a[i]) : "f"(c));
+            if (KIND == K_LOP3) asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(ia[i]) : "r"(ia[(i + 1) % kIlp]), "r"(ia[(i + 2) % kIlp]));
+            if (KIND == K_IADD) asm volatile("add.s32 %0, %0, %1;" : "+r"(ia[i]) : "r"(ia[(i + 1) % kIlp]));
+            if (KIND == K_MUFU_LG2) asm volatile("lg2.approx.ftz.f32 %0, %0;" : "+f"(a[i]));
+            if (KIND == K_MUFU_RCP) asm volatile("rcp.approx.ftz.f32 %0, %0;" : "+f"(a[i]));
+            if (KIND == K_LDS128)
+            {
+                float x, y, z, w;
+                asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(x), "=f"(y), "=f"(z), "=f"(w) : "r"(sh_base + 16u * ((it * kIlp + i) & 255)));
+                asm volatile("" ::"f"(x), "f"(y), "f"(z), "f"(w));
+                if (it == iters + 1) a[i] += x + y + z + w; // never true: keeps the destination registers live without extra instructions
+            }
+            if (KIND == K_MIX_SCALE)
+            {
+                // v = fma(h8, y, fma(h7, x, iq)); L = lg2 v; dd = A - L; in = |dd| <= Tin; unc = |dd| <= Tout; @in acc += dd*dd; @in cnt += 1
+                float v, L;
+                asm volatile("fma.rn.f32 %0, %1, %2, %3;" : "=f"(v) : "f"(b), "f"(a[i]), "f"(c));
+                asm volatile("fma.rn.f32 %0, %1, %2, %0;" : "+f"(v) : "f"(d), "f"(a[i]));
+                asm volatile("lg2.approx.ftz.f32 %0, %1;" : "=f"(L) : "f"(v));
+                asm volatile("sub.rn.f32 %0, %1, %0;" : "+f"(L) : "f"(c));
+                asm volatile("{.reg .pred p, q; .reg .f32 m; abs.f32 m, %2; setp.le.f32 p, m, %3; setp.le.f32 q, m, %4; @p fma.rn.f32 %0, %2, %2, %0; @p add.rn.f32 %1, %1, 0f3F800000; @q add.rn.f32 %1, %1, 0f00000000;}"
+                             : "+f"(acc[i]), "+f"(a[i]) : "f"(L), "f"(d), "f"(b));
+            }
+            if (KIND == K_MIX_ORIENT)
+            {
+                float n, dd, c1, s1v, mn, mx, ri, t, lo, hi, z, p;
+                asm volatile("fma.rn.f32 %0, %1, %2, %3;" : "=f"(n) : "f"(a[i]), "f"(b), "f"(c));
+                asm volatile("fma.rn.f32 %0, %1, %2, %3;" : "=f"(dd) : "f"(a[i]), "f"(d), "f"(c));
+                asm volatile("mul.rn.f32 %0, %1, %2;" : "=f"(c1) : "f"(dd), "f"(c));
+                asm volatile("fma.rn.f32 %0, %1, %2, %0;" : "+f"(c1) : "f"(n), "f"(d));
+                asm volatile("mul.rn.f32 %0, %1, %2;" : "=f"(s1v) : "f"(dd), "f"(d));
+                asm volatile("fma.rn.f32 %0, %1, %2, %0;" : "+f"(s1v) : "f"(n), "f"(c));
+                asm volatile("{.reg .f32 m, n; abs.f32 m, %2; abs.f32 n, %3; min.f32 %0, m, n; max.f32 %1, m, n;}" : "=f"(mn), "=f"(mx) : "f"(c1), "f"(s1v));
+                asm volatile("max.f32 %0, %0, 0f0DA24260;" : "+f"(mx));
+                asm volatile("rcp.approx.ftz.f32 %0, %1;" : "=f"(ri) : "f"(mx));
+                asm volatile("mul.rn.f32 %0, %1, %2;" : "=f"(t) : "f"(mn), "f"(ri));
+                asm volatile("fma.rn.f32 %0, %1, %2, %3;" : "=f"(lo) : "f"(b), "f"(ri), "f"(c));
+                asm volatile("fma.rn.f32 %0, %1, %2, %3;" : "=f"(hi) : "f"(d), "f"(ri), "f"(c));
+                asm volatile("mul.rn.f32 %0, %1, %1;" : "=f"(z) : "f"(t));
+                asm volatile("add.rn.f32 %0, %1, %2;" : "=f"(p) : "f"(z), "f"(c));
+                asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(p) : "f"(z), "f"(d));
+                asm volatile("{.reg .pred p, q; setp.le.f32 p, %2, %4; setp.le.f32 q, %2, %5; @p fma.rn.f32 %0, %3, %6, %0; @p add.rn.f32 %1, %1, 0f3F800000; @q add.rn.f32 %1, %1, 0f00000000;}"
+                             : "+f"(acc[i]), "+f"(a[i]) : "f"(t), "f"(z), "f"(lo), "f"(hi), "f"(p));
+            }
+            if (KIND == K_FFMA_MUFU_7_1)
+            {
+#pragma unroll
+                for (int r = 0; r < 7; r++) asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(a[i]) : "f"(c), "f"(d));
+                asm volatile("lg2.approx.ftz.f32 %0, %0;" : "+f"(acc[i]));
+            }
+            if (KIND == K_FFMA_FMNMX_1_1)
+            {
+                asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(a[i]) : "f"(c), "f"(d));
+                asm volatile("min.f32 %0, %0, %1;" : "+f"(acc[i]) : "f"(b));
+            }
         }
     }
     const unsigned long long t1 = clock64();
+    atomicMin(&t_first, t0);
+    atomicMax(&t_last, t1);
     float s = 0.f;
 #pragma unroll
-    for (int i = 0; i < NACC; i++) s += a[i] + (float)ia[i] + (float)(pa[i] & 0xffff);
-    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
-    if (threadIdx.x == 0) cycles[blockIdx.x] = t1 - t0;
+    for (int i = 0; i < kIlp; i++) s += a[i] + acc[i] + static_cast<float>(ia[i]) + static_cast<float>(pa[i] & 0xffff);
+    if (s == 123.456f) out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) cycles[blockIdx.x] = t_last - t_first;
 }
 
 template <int KIND>
-void run(const char* name, int instr_per_slot, int blocks_per_sm, int nsm, float* out, unsigned long long* cyc)
+static void launch(int grid, float* out, unsigned long long* cyc, int iters, cudaStream_t s)
 {
-    const int grid = nsm * blocks_per_sm;
+    k_bench<KIND><<<grid, kThreads, 0, s>>>(out, cyc, iters, 1.0000001f, 0.9999999f, 1e-7f);
+}
+typedef void (*launch_fn)(int, float*, unsigned long long*, int, cudaStream_t);
+template <int K> struct Table { static void fill(launch_fn* t) { t[K] = launch<K>; Table<K + 1>::fill(t); } };
+template <> struct Table<K_COUNT> { static void fill(launch_fn*) {} };
+
+int main(int argc, char** argv)
+{
+    const char* json_path = nullptr;
+    for (int i = 1; i + 1 < argc; i++) if (!std::strcmp(argv[i], "--json")) json_path = argv[i + 1];
+    int dev = 0, n_sm = 0, clock_khz = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+    cudaDeviceGetAttribute(&clock_khz, cudaDevAttrClockRate, dev);
+    float* out; unsigned long long* cyc;
+    cudaMalloc(&out, sizeof(float) * n_sm * kThreads);
+    cudaMalloc(&cyc, sizeof(unsigned long long) * n_sm);
+    launch_fn table[K_COUNT];
+    Table<0>::fill(table);
     cudaEvent_t e0, e1;
     cudaEventCreate(&e0); cudaEventCreate(&e1);
-    k_bench<KIND><<<grid, 256>>>(out, cyc, 1.0001f, 0.9999f, 1e-3f);
-    cudaDeviceSynchronize();
-    cudaEventRecord(e0);
-    k_bench<KIND><<<grid, 256>>>(out, cyc, 1.0001f, 0.9999f, 1e-3f);
-    cudaEventRecord(e1);
-    cudaDeviceSynchronize();
-    float ms; cudaEventElapsedTime(&ms, e0, e1);
-    unsigned long long* h = new unsigned long long[grid];
-    cudaMemcpy(h, cyc, grid * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
-    double avg = 0; for (int i = 0; i < grid; i++) avg += (double)h[i]; avg /= grid;
-    // warp-instructions per SM: blocks_per_sm * 8 warps * ITERS * NACC * instr_per_slot, all resident concurrently
-    const double winstr = (double)blocks_per_sm * 8.0 * ITERS * NACC * instr_per_slot;
-    printf("%-34s bps=%d  cycles=%9.0f  warp-instr/clk/SM=%6.3f  lane-ops/clk/SM=%7.1f  kernel=%.3f ms  eff.clock=%.0f MHz\n", name,
-           blocks_per_sm, avg, winstr / avg, 32.0 * winstr / avg, ms, avg / (ms * 1e3));
-    delete[] h;
-    cudaError_t e = cudaGetLastError();
-    if (e != cudaSuccess) printf("CUDA error: %s\n", cudaGetErrorString(e));
-}
-
-int main()
-{
-    int nsm = 0; cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, 0);
-    int clk = 0; cudaDeviceGetAttribute(&clk, cudaDevAttrClockRate, 0);
-    printf("SMs=%d  clockRate attr=%d kHz\n", nsm, clk);
-    float* out; unsigned long long* cyc;
-    cudaMalloc(&out, sizeof(float) * nsm * 8 * 256);
-    cudaMalloc(&cyc, sizeof(unsigned long long) * nsm * 8);
-    for (int bps : {2, 4})
+    std::string json = "{\"n_sm\": " + std::to_string(n_sm) + ", \"max_clock_mhz\": " + std::to_string(clock_khz / 1000) + ", \"ops\": {";
+    std::printf("SMs=%d  max SM clock=%d MHz  (%d threads/SM, %d independent chains per thread)\n", n_sm, clock_khz / 1000, kThreads, kIlp);
+    double ffma_tflops_burst = 0, ffma_tflops_sustained = 0, ffma_rate = 0;
+    bool broken = false;
+    for (int k = 0; k < K_COUNT; k++)
     {
-        run<0>("FFMA acc=b*c+acc", 1, bps, nsm, out, cyc);
-        run<1>("FFMA acc=acc*c+d", 1, bps, nsm, out, cyc);
-        run<2>("FADD", 1, bps, nsm, out, cyc);
-        run<3>("FMUL", 1, bps, nsm, out, cyc);
-        run<4>("FSETP + @p IADD", 2, bps, nsm, out, cyc);
-        run<5>("FMNMX", 1, bps, nsm, out, cyc);
-        run<6>("IADD", 1, bps, nsm, out, cyc);
-        run<15>("LOP3", 1, bps, nsm, out, cyc);
-        run<7>("MUFU.LG2", 1, bps, nsm, out, cyc);
-        run<8>("MUFU.RCP", 1, bps, nsm, out, cyc);
-        run<9>("FFMA2 (f32x2)", 1, bps, nsm, out, cyc);
-        run<10>("FFMA:FMNMX 1:1", 2, bps, nsm, out, cyc);
-        run<11>("FFMA:FMNMX 2:1", 3, bps, nsm, out, cyc);
-        run<12>("FFMA:MUFU 4:1", 5, bps, nsm, out, cyc);
-        run<13>("LDS.128 bcast + 4 FADD", 5, bps, nsm, out, cyc);
-        run<14>("FSETP + @p FFMA", 2, bps, nsm, out, cyc);
-        run<16>("FFMA2:FMNMX 1:1", 2, bps, nsm, out, cyc);
-        run<17>("FFMA2:MUFU 2:1", 3, bps, nsm, out, cyc);
+        const int iters = (k == K_MUFU_LG2 || k == K_MUFU_RCP) ? 4096 : 16384;
+        table[k](n_sm, out, cyc, 256, 0); // warm-up (instruction cache, clocks)
+        cudaDeviceSynchronize();
+        // burst: one launch (~1 ms); sustained: back-to-back launches for ~0.5 s, the last one timed
+        float ms_burst = 0.f, ms_sus = 0.f;
+        cudaEventRecord(e0); table[k](n_sm, out, cyc, iters, 0); cudaEventRecord(e1);
+        cudaEventSynchronize(e1);
+        cudaEventElapsedTime(&ms_burst, e0, e1);
+        std::vector<unsigned long long> h(n_sm);
+        cudaMemcpy(h.data(), cyc, sizeof(unsigned long long) * n_sm, cudaMemcpyDeviceToHost);
+        const int reps = std::max(4, static_cast<int>(500.0f / std::max(ms_burst, 0.05f)));
+        for (int r = 0; r < reps; r++) table[k](n_sm, out, cyc, iters, 0);
+        cudaEventRecord(e0); table[k](n_sm, out, cyc, iters, 0); cudaEventRecord(e1);
+        cudaEventSynchronize(e1);
+        cudaEventElapsedTime(&ms_sus, e0, e1);
+        if (cudaGetLastError() != cudaSuccess) { std::printf("CUDA error\n"); return 1; }
+        double cyc_avg = 0;
+        for (auto v : h) cyc_avg += static_cast<double>(v);
+        cyc_avg /= n_sm;
+        const double instr_per_warp = static_cast<double>(iters) * kIlp * kDesc[k].instr_per_step;
+        const double rate = (kThreads / 32) * instr_per_warp / cyc_avg; // warp-instructions / clock / SM
+        const double total_instr = instr_per_warp * (kThreads / 32) * n_sm;
+        const double flops = static_cast<double>(iters) * kIlp * kDesc[k].flops_per_step * kThreads * n_sm;
+        const double tf_burst = flops / (ms_burst * 1e-3) / 1e12, tf_sus = flops / (ms_sus * 1e-3) / 1e12;
+        const double eff_mhz = total_instr / n_sm / rate / (ms_burst * 1e-3) / 1e6;
+        std::printf("%-64.64s  %6.3f warp-instr/clk/SM  %7.2f lane-ops/clk/SM  burst %6.3f ms (%6.1f Tflop/s, eff. clock %4.0f MHz)  sustained %6.3f ms (%6.1f Tflop/s)\n",
+                    kDesc[k].name, rate, rate * 32.0, ms_burst, tf_burst, eff_mhz, ms_sus, tf_sus);
+        if (rate > 4.05) { std::printf("BROKEN MEASUREMENT above: more than 4 warp-instructions per clock per SM\n"); broken = true; }
+        if (k == K_FFMA) { ffma_tflops_burst = tf_burst; ffma_tflops_sustained = tf_sus; ffma_rate = rate; }
+        char buf[512];
+        std::snprintf(buf, sizeof(buf), "%s\"%d\": {\"name\": \"%s\", \"warp_instr_per_clk_per_sm\": %.4f, \"burst_ms\": %.4f, \"sustained_ms\": %.4f, "
+                      "\"tflops_burst\": %.3f, \"tflops_sustained\": %.3f, \"effective_clock_mhz\": %.0f}", k ? ", " : "", k, kDesc[k].name, rate, ms_burst,
+                      ms_sus, tf_burst, tf_sus, eff_mhz);
+        json += buf;
     }
-    return 0;
+    char tail[512];
+    std::snprintf(tail, sizeof(tail), "}, \"fp32_ffma_tflops_burst\": %.3f, \"fp32_ffma_tflops_sustained\": %.3f, \"ffma_warp_instr_per_clk_per_sm\": %.4f, "
+                  "\"fp32_nominal_tflops\": %.3f}", ffma_tflops_burst, ffma_tflops_sustained, ffma_rate, n_sm * 128.0 * 2.0 * clock_khz * 1e3 / 1e12);
+    json += tail;
+    std::printf("FP32 FFMA measured: burst %.2f Tflop/s, sustained %.2f Tflop/s (nominal %d SM x 128 x 2 x %.3f GHz = %.2f)\n", ffma_tflops_burst,
+                ffma_tflops_sustained, n_sm, clock_khz / 1e6, n_sm * 128.0 * 2.0 * clock_khz * 1e3 / 1e12);
+    if (json_path && !broken)
+    {
+        FILE* f = std::fopen(json_path, "w");
+        if (f) { std::fputs(json.c_str(), f); std::fputs("\n", f); std::fclose(f); }
+    }
+    return broken ? 2 : 0;
 }
