@@ -78,7 +78,7 @@ struct gcr_engine_s
     int device = 0;
     int n_sm = 148;
     int problem = 0; // GCR_PROBLEM_*
-    int score_grid[2] = {148, 148};
+    int score_grid[3] = {148, 148, 148}; // per scoring mode: winner-only, per-hypothesis counts, + masks
     bool pdl = true;            // programmatic dependent launch of the scoring kernel and the tail (GCR_PDL=0: plain launches)
     bool last_resident = false; // the last gcr_run used k_score_resident
     bool resident_ok = true;    // k_score_resident usable (GCR_RESIDENT=0 forces the ring kernel: A/B runs)
@@ -90,6 +90,7 @@ struct gcr_engine_s
     int resident_cost_o = 20;   // cost model of k_score_resident's static partition: orientation block (scale block = 10) ...
     int resident_cost_p = 20;   // ... and a precise tile relative to an FP32 tile (x 10); GCR_COST_O / GCR_COST_P for tuning runs
     int tail_grid = 148;
+    unsigned int worklist_cap_override = 0; // GCR_WORKLIST_CAP (tests of the overflow report)
     cudaStream_t own_stream = nullptr, stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, evk0 = nullptr, evk1 = nullptr;
     std::string err;
@@ -104,6 +105,7 @@ struct gcr_engine_s
     DevBuf<float> d_fs, d_fo;
     DevBuf<double> d_fsd, d_fod; // FP64 SoA for the precise tiles
     DevBuf<double> d_aux_s, d_aux_o; // per-feature inputs of the minimal solvers (k_prep_features)
+    std::vector<double> h_aux_s, h_aux_o; // GCR_FEATURES_HOST_LIBM: the same columns evaluated by the host's C library
     int ncsd = 0, ncod = 0;
     DevBuf<unsigned int> d_irr_s, d_irr_o;
     DevBuf<Scene> d_scene;
@@ -119,6 +121,12 @@ struct gcr_engine_s
     DevBuf<double> d_sums, d_score;
     DevBuf<unsigned int> d_cnts, d_ninl, d_masks, d_fast_hyp, d_hard_hyp;
     DevBuf<float4> d_pf0, d_pf1;
+    DevBuf<ContPar> d_cont_par; // winner-only runs: contenders of the selection cascade (k_tail)
+    DevBuf<unsigned long long> d_cont_q;
+    DevBuf<unsigned int> d_cont_n;
+    DevBuf<double> d_cont_val;
+    DevBuf<TailState> d_ts;
+    DevBuf<float2> d_err_ab; // winner-only runs: per-hypothesis error bound of the FP32 class values (k_sample_solve -> k_tail)
     DevBuf<uint2> d_worklist;
     DevBuf<unsigned int> d_cand_hyp, d_cand_cnt, d_cand_masks;
     DevBuf<Model4> d_cand_model;
@@ -167,6 +175,26 @@ struct gcr_engine_s
         return GCR_ERR_CUDA;
     }
 };
+
+// Every ABI entry point works on the engine's device and leaves the caller's current device as it found it (a torch process reads
+// the thread's current device with cudaGetDevice: an engine on device 1 must not move later torch allocations there).
+struct DeviceGuard
+{
+    int prev = -1, dev;
+    cudaError_t err;
+    explicit DeviceGuard(int d) : dev(d)
+    {
+        err = cudaGetDevice(&prev);
+        if (err == cudaSuccess && prev != dev) err = cudaSetDevice(dev);
+    }
+    ~DeviceGuard()
+    {
+        if (prev >= 0 && prev != dev) cudaSetDevice(prev);
+    }
+};
+#define GCR_DEVICE(h)                                                      \
+    DeviceGuard device_guard_((h)->device);                                \
+    if (device_guard_.err != cudaSuccess) return (h)->cuda_fail(device_guard_.err, "cudaSetDevice")
 
 #define GCR_CUDA(call)                                             \
     do                                                             \
@@ -284,6 +312,21 @@ Thresholds make_thresholds_uncached(const double thr_in[2], int problem)
     T.t_band0 = static_cast<float>(26.0 * kU + 4.0 * kU * T.tanT);
     T.t_lo0 = std::nextafter(T.tanT - T.t_band0, -1.0f);
     T.t_hi0 = std::nextafter(T.tanT + T.t_band0, 2.0f);
+    // winner-only runs (score_chunk_w): dq = (A - lg2 v) / Tp and r^2 / tsq1 = z (pn0 + z (pn1 + z (pn2 + z pn3)))
+    T.inv_Tp = static_cast<float>(1.0 / static_cast<double>(T.Tp));
+    T.sqrt_tsq1 = static_cast<float>(tr1);
+    for (int i = 0; i < 4; i++) T.pn[i] = T.tsq[1] > 0.0 ? static_cast<float>(static_cast<double>(T.pc[i]) / T.tsq[1]) : 0.f;
+    if (problem == 0 && !T.orient_all_exact)
+    {
+        // beyond the fitted range the polynomial only has to keep the term at zero: z P(z) / tsq >= 1 for every tan^2 up to 1
+        const double tt = static_cast<double>(T.tanT) * 1.01 + 1e-6, z0 = tt * tt;
+        for (int i = 0; i <= 4000 && !T.orient_all_exact; i++)
+        {
+            const double z = z0 + (1.0 - z0) * i / 4000.0;
+            const double hz = ((static_cast<double>(T.pn[3]) * z + T.pn[2]) * z + T.pn[1]) * z + T.pn[0];
+            if (!(z * hz >= 1.0 + 1e-3)) T.orient_all_exact = 1;
+        }
+    }
     return T;
 }
 
@@ -328,6 +371,7 @@ Buffers make_buffers(gcr_engine_s* h, unsigned long long seed, bool have_samples
     B.hard_hyp = h->d_hard_hyp.p;
     B.worklist = h->d_worklist.p;
     B.worklist_cap = static_cast<unsigned int>(std::min<size_t>(h->d_worklist.cap, 0x7fffffffu));
+    if (h->worklist_cap_override) B.worklist_cap = std::min(B.worklist_cap, h->worklist_cap_override); // tests: force an overflow
     B.cand_hyp = h->d_cand_hyp.p;
     B.cand_model = h->d_cand_model.p;
     B.cand_score = h->d_cand_score.p;
@@ -341,6 +385,12 @@ Buffers make_buffers(gcr_engine_s* h, unsigned long long seed, bool have_samples
     B.phase_ns = reinterpret_cast<unsigned long long*>(h->d_best.p + 32);
     B.record_user = record_user;
     B.best_masks = h->d_best.p + kResultHeaderWords;
+    B.err_ab = h->d_err_ab.p;
+    B.cont_par = h->d_cont_par.p;
+    B.cont_q = h->d_cont_q.p;
+    B.cont_n = h->d_cont_n.p;
+    B.cont_val = h->d_cont_val.p;
+    B.ts = h->d_ts.p;
     B.host_block = nullptr;
     for (int p = 0; p < kMaxPeers; p++) B.xchg_peer[p] = static_cast<unsigned long long*>(h->peer_ptr[p]);
     B.xchg_world = 0; // set by gcr_run for exchanging runs
@@ -358,6 +408,15 @@ int ensure_common(gcr_engine_s* h)
         GCR_CUDA(h->d_ctr.ensure(1));
         GCR_CUDA(cudaMemset(h->d_ctr.p, 0, sizeof(Counters)));
     }
+    if (h->d_ts.cap < 1)
+    {
+        GCR_CUDA(h->d_ts.ensure(1));
+        GCR_CUDA(cudaMemset(h->d_ts.p, 0, sizeof(TailState)));
+    }
+    GCR_CUDA(h->d_cont_par.ensure(kContCap));
+    GCR_CUDA(h->d_cont_q.ensure(2 * kContCap));
+    GCR_CUDA(h->d_cont_n.ensure(2 * kContCap));
+    GCR_CUDA(h->d_cont_val.ensure(2 * kContCap));
     GCR_CUDA(h->d_cand_hyp.ensure(kCandCap));
     GCR_CUDA(h->d_cand_model.ensure(kCandCap));
     GCR_CUDA(h->d_cand_score.ensure(kCandCap));
@@ -397,7 +456,7 @@ static int peer_buffer(gcr_engine_s* h)
 {
     if (!h->d_xchg.p)
     {
-        GCR_CUDA(cudaSetDevice(h->device));
+        GCR_DEVICE(h);
         GCR_CUDA(h->d_xchg.ensure(kXchgWords));
         GCR_CUDA(cudaMemset(h->d_xchg.p, 0, sizeof(unsigned long long) * kXchgWords));
     }
@@ -464,6 +523,17 @@ static cudaError_t launch_chained(gcr_engine_s* h, void (*kernel)(KArgs...), dim
     return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
+// Device-side failures of the last run, from the counter snapshot its last kernel wrote into the result block.  The reference throws
+// rather than continue on bad input (GCRANSAC.h:222-228); an asynchronous caller (gcr_run with out == NULL) learns of them from
+// gcr_best / gcr_fetch.
+static int check_run_counters(gcr_engine_s* h, const Counters& c)
+{
+    if (c.xchg_timeout) return h->fail(GCR_ERR_STATE, "winner exchange timed out: a peer rank did not run the same collective call");
+    if (c.n_bad_sample) return h->fail(GCR_ERR_INVALID, "replayed sample indices out of range");
+    if (c.n_worklist_overflow) return h->fail(GCR_ERR_STATE, "guard-band worklist overflow: masks / counts of this run are incomplete");
+    return GCR_OK;
+}
+
 extern "C"
 {
 
@@ -476,33 +546,34 @@ int gcr_create(int device, gcr_handle* out)
     gcr_engine_s* h = new (std::nothrow) gcr_engine_s();
     if (!h) return GCR_ERR_NOMEM;
     h->device = device;
-    cudaError_t e = cudaSetDevice(device);
+    DeviceGuard device_guard_(device);
+    cudaError_t e = device_guard_.err;
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreate(&h->ev0);
     if (e == cudaSuccess) e = cudaEventCreate(&h->ev1);
     if (e == cudaSuccess) e = cudaEventCreate(&h->evk0);
     if (e == cudaSuccess) e = cudaEventCreate(&h->evk1);
     if (e == cudaSuccess) e = cudaDeviceGetAttribute(&h->n_sm, cudaDevAttrMultiProcessorCount, device);
-    if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(k_score_fast<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ScoreSmem));
-    if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(k_score_fast<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ScoreSmem));
     const int resident_smem = kResidentMaxChunks * kChunkBytes + 64;
-    if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(k_score_resident<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, resident_smem);
-    if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(k_score_resident<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, resident_smem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_score_fast<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ScoreSmem));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_score_fast<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ScoreSmem));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_score_fast<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ScoreSmem));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_score_resident<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, resident_smem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_score_resident<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, resident_smem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_score_resident<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, resident_smem);
     if (const char* v = std::getenv("GCR_RESIDENT")) h->resident_ok = std::atoi(v) != 0;
     if (const char* v = std::getenv("GCR_PDL")) h->pdl = std::atoi(v) != 0;
+    if (const char* v = std::getenv("GCR_WORKLIST_CAP")) h->worklist_cap_override = static_cast<unsigned int>(std::max(1, std::atoi(v)));
     if (const char* v = std::getenv("GCR_RESIDENT_MAX_HYP")) h->resident_max_hyp = h->resident_max_evals = std::atoll(v);
     if (const char* v = std::getenv("GCR_RESIDENT_MAX_EVALS")) h->resident_max_evals = std::atoll(v);
     if (const char* v = std::getenv("GCR_COST_O")) h->resident_cost_o = std::max(1, std::atoi(v));
     if (const char* v = std::getenv("GCR_COST_P")) h->resident_cost_p = std::max(1, std::atoi(v));
-    for (int m = 0; m < 2 && e == cudaSuccess; m++)
+    for (int m = 0; m < 3 && e == cudaSuccess; m++)
     {
         int per_sm = 1;
-        e = m ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_score_fast<true>, kScoreThreads, sizeof(ScoreSmem))
-              : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_score_fast<false>, kScoreThreads, sizeof(ScoreSmem));
+        e = m == 0 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_score_fast<0>, kScoreThreads, sizeof(ScoreSmem))
+                   : (m == 1 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_score_fast<1>, kScoreThreads, sizeof(ScoreSmem))
+                             : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_score_fast<2>, kScoreThreads, sizeof(ScoreSmem)));
         h->score_grid[m] = h->n_sm * std::max(1, per_sm);
     }
     if (e == cudaSuccess)
@@ -534,7 +605,7 @@ int gcr_create(int device, gcr_handle* out)
 int gcr_destroy(gcr_handle h)
 {
     if (!h) return GCR_ERR_INVALID;
-    cudaSetDevice(h->device);
+    DeviceGuard device_guard_(h->device);
     if (h->own_stream) cudaStreamSynchronize(h->own_stream);
     peer_release(h);
     h->d_xchg.release();
@@ -543,7 +614,8 @@ int gcr_destroy(gcr_handle h)
     h->d_irr_s.release(); h->d_irr_o.release(); h->d_scene.release(); h->d_samples.release();
     h->d_models.release(); h->d_flags.release(); h->d_sums.release(); h->d_score.release();
     h->d_cnts.release(); h->d_ninl.release(); h->d_masks.release(); h->d_fast_hyp.release();
-    h->d_hard_hyp.release(); h->d_pf0.release(); h->d_pf1.release(); h->d_worklist.release();
+    h->d_hard_hyp.release(); h->d_pf0.release(); h->d_pf1.release(); h->d_err_ab.release(); h->d_cont_par.release(); h->d_cont_q.release(); h->d_cont_n.release();
+    h->d_cont_val.release(); h->d_ts.release(); h->d_worklist.release();
     h->d_cand_hyp.release(); h->d_cand_cnt.release(); h->d_cand_masks.release(); h->d_best.release();
     if (h->h_best) cudaFreeHost(h->h_best);
     h->d_cand_model.release(); h->d_cand_score.release(); h->d_cand_qsum.release(); h->d_cand_rawcnt.release(); h->d_ctr.release();
@@ -582,9 +654,11 @@ int gcr_set_stream(gcr_handle h, void* cuda_stream)
     return GCR_OK;
 }
 
-int gcr_set_features(gcr_handle h, const double* scale, int64_t ns, const double* orient, int64_t no, int on_device)
+int gcr_set_features(gcr_handle h, const double* scale, int64_t ns, const double* orient, int64_t no, int where)
 {
     if (!h) return GCR_ERR_INVALID;
+    const bool on_device = (where & GCR_FEATURES_ON_DEVICE) != 0, host_libm = (where & GCR_FEATURES_HOST_LIBM) != 0;
+    if (on_device && host_libm) return h->fail(GCR_ERR_INVALID, "GCR_FEATURES_HOST_LIBM needs host arrays");
     if (!h->stream) return h->fail(GCR_ERR_STATE, "engine was not created successfully");
     if (h->problem == 0)
     {
@@ -601,7 +675,7 @@ int gcr_set_features(gcr_handle h, const double* scale, int64_t ns, const double
         orient = nullptr;
     }
     if (ns > (1ll << 30) || no > (1ll << 30)) return h->fail(GCR_ERR_INVALID, "feature count too large");
-    GCR_CUDA(cudaSetDevice(h->device));
+    GCR_DEVICE(h);
     h->ns = static_cast<int>(ns);
     h->no = static_cast<int>(no);
     if (on_device)
@@ -630,7 +704,26 @@ int gcr_set_features(gcr_handle h, const double* scale, int64_t ns, const double
     h->fetch_orient = h->orient_ptr;
     h->fetch_ns = h->ns;
     h->fetch_no = h->no;
-    return finish_features(h);
+    const int rc = finish_features(h);
+    if (rc != GCR_OK || !host_libm) return rc;
+    // Bit-exact replay mode: the solvers' per-FEATURE transcendental columns -- pow(s, 1/3) of two_sift.hpp:288-299 (three_sift.hpp:153-160,
+    // three_sift_original.hpp: pow(s, -1/3)) and the sine / cosine of lineFromPointAndAngle (math_utils.hpp:104-109) -- evaluated by the host's
+    // C library, i.e. by the very functions the reference calls, and written over the device-evaluated columns.  isValidSample and the
+    // 3 x 4 system are then IEEE-basic operations on identical inputs: flags are the reference's bit for bit also where the vanishing point
+    // sits on a vertex of the sample hull (the knife edge that is the last ulp of sin / cos).
+    h->h_aux_s.resize(static_cast<size_t>(ns));
+    h->h_aux_o.resize(2 * static_cast<size_t>(no));
+    for (int64_t i = 0; i < ns; ++i) h->h_aux_s[i] = h->problem == 2 ? std::pow(scale[3 * i + 2], -1.0 / 3.0) : std::pow(scale[3 * i + 2], 1.0 / 3.0);
+    for (int64_t i = 0; i < no; ++i)
+    {
+        const double t = orient[3 * i + 2];
+        h->h_aux_o[2 * i] = std::sin(t);
+        h->h_aux_o[2 * i + 1] = std::cos(t);
+    }
+    GCR_CUDA(cudaMemcpyAsync(h->d_aux_s.p, h->h_aux_s.data(), sizeof(double) * ns, cudaMemcpyHostToDevice, h->stream));
+    if (no > 0) GCR_CUDA(cudaMemcpyAsync(h->d_aux_o.p, h->h_aux_o.data(), sizeof(double) * 2 * no, cudaMemcpyHostToDevice, h->stream));
+    GCR_CUDA(cudaStreamSynchronize(h->stream)); // pageable staging: the vectors may be reused by the next call
+    return GCR_OK;
 }
 
 int gcr_set_keypoints(gcr_handle h, const void* keypoints, int64_t n, int is_f32, int on_device, int64_t* n_scale,
@@ -639,7 +732,7 @@ int gcr_set_keypoints(gcr_handle h, const void* keypoints, int64_t n, int is_f32
     if (!h) return GCR_ERR_INVALID;
     if (!h->stream) return h->fail(GCR_ERR_STATE, "engine was not created successfully");
     if (!keypoints || n < 1 || n > (1ll << 30)) return h->fail(GCR_ERR_INVALID, "gcr_set_keypoints: 1 <= n <= 2^30 rows of (x, y, size, angle)");
-    GCR_CUDA(cudaSetDevice(h->device));
+    GCR_DEVICE(h);
     const size_t row_bytes = is_f32 ? 16 : 32;
     const void* d_kp = keypoints;
     cudaStream_t s = h->stream;
@@ -742,7 +835,7 @@ int gcr_peer_attach_ptrs(gcr_handle h, void* const* peer_buffers, int world, int
     int rc = peer_buffer(h);
     if (rc != GCR_OK) return rc;
     peer_release(h);
-    GCR_CUDA(cudaSetDevice(h->device));
+    GCR_DEVICE(h);
     GCR_CUDA(cudaStreamSynchronize(h->stream));
     GCR_CUDA(cudaMemset(h->d_xchg.p, 0, sizeof(unsigned long long) * kXchgWords));
     for (int p = 0; p < world; p++) h->peer_ptr[p] = p == rank ? static_cast<void*>(h->d_xchg.p) : peer_buffers[p];
@@ -758,7 +851,7 @@ int gcr_peer_attach(gcr_handle h, const void* ipc_handles, int world, int rank)
     int rc = peer_buffer(h);
     if (rc != GCR_OK) return rc;
     peer_release(h);
-    GCR_CUDA(cudaSetDevice(h->device));
+    GCR_DEVICE(h);
     GCR_CUDA(cudaStreamSynchronize(h->stream));
     GCR_CUDA(cudaMemset(h->d_xchg.p, 0, sizeof(unsigned long long) * kXchgWords));
     for (int p = 0; p < world; p++)
@@ -788,7 +881,7 @@ int gcr_peer_attach(gcr_handle h, const void* ipc_handles, int world, int rank)
 int gcr_peer_detach(gcr_handle h)
 {
     if (!h) return GCR_ERR_INVALID;
-    cudaSetDevice(h->device);
+    DeviceGuard device_guard_(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     return peer_release(h);
 }
@@ -797,7 +890,7 @@ int gcr_get_features(gcr_handle h, double* scale, double* orient)
 {
     if (!h) return GCR_ERR_INVALID;
     if (!h->fetch_scale) return h->fail(GCR_ERR_STATE, "gcr_get_features before gcr_set_features / gcr_set_keypoints");
-    GCR_CUDA(cudaSetDevice(h->device));
+    GCR_DEVICE(h);
     if (scale && h->fetch_ns > 0)
         GCR_CUDA(cudaMemcpyAsync(scale, h->fetch_scale, sizeof(double) * 3 * h->fetch_ns, cudaMemcpyDeviceToHost, h->stream));
     if (orient && h->fetch_no > 0 && h->fetch_orient)
@@ -815,7 +908,7 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
     if (n_hyp < 1 || n_hyp > (1ll << 30)) return h->fail(GCR_ERR_INVALID, "n_hyp out of range");
     if (!thr || !(thr[0] >= 0.0) || !std::isfinite(thr[0]) || (h->problem == 0 && (!(thr[1] >= 0.0) || !std::isfinite(thr[1]))))
         return h->fail(GCR_ERR_INVALID, "thresholds must be finite and non-negative");
-    GCR_CUDA(cudaSetDevice(h->device));
+    GCR_DEVICE(h);
     const size_t H = static_cast<size_t>(n_hyp);
     const size_t W = static_cast<size_t>((h->ns + 31) / 32 + (h->no + 31) / 32);
     h->n_hyp = static_cast<int>(n_hyp);
@@ -832,6 +925,7 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
     GCR_CUDA(h->d_hard_hyp.ensure(H));
     GCR_CUDA(h->d_pf0.ensure(H));
     GCR_CUDA(h->d_pf1.ensure(H));
+    GCR_CUDA(h->d_err_ab.ensure(H));
     GCR_CUDA(h->d_worklist.ensure(std::max<size_t>(1u << 16, 4 * H)));
     if (h->have_masks) GCR_CUDA(h->d_masks.ensure(H * W));
     int rc = ensure_common(h);
@@ -909,7 +1003,8 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
         GCR_CUDA(cudaLaunchKernelEx(&cfg, k_sample_solve, B, T, all_exact));
     }
     {
-        const int grid = h->score_grid[h->have_masks ? 1 : 0]; // persistent: one CTA per resident slot
+        const int mode = h->have_masks ? 2 : (h->have_per_hyp ? 1 : 0); // scoring mode: winner-only | per-hypothesis counts | + masks
+        const int grid = h->score_grid[mode]; // persistent: one CTA per resident slot
         // small feature sets (both working sets fit in one SM's shared memory): resident kernel, one CTA per SM
         const int chunks = B.ncs + B.nco + B.ncsd + B.ncod;
         const bool resident = h->last_resident = h->resident_ok && chunks <= kResidentMaxChunks && n_hyp <= h->resident_max_hyp &&
@@ -933,15 +1028,15 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
             cfg.gridDim = dim3(h->n_sm);
             cfg.blockDim = dim3(kResidentThreads);
             cfg.dynamicSmemBytes = rsmem;
-            GCR_CUDA(cudaLaunchKernelEx(&cfg, h->have_masks ? k_score_resident<true> : k_score_resident<false>, B, T, h->resident_cost_o,
-                                        h->resident_cost_p));
+            GCR_CUDA(cudaLaunchKernelEx(&cfg, mode == 2 ? k_score_resident<2> : (mode == 1 ? k_score_resident<1> : k_score_resident<0>), B, T,
+                                        h->resident_cost_o, h->resident_cost_p));
         }
         else
         {
             cfg.gridDim = dim3(grid);
             cfg.blockDim = dim3(kScoreThreads);
             cfg.dynamicSmemBytes = sizeof(ScoreSmem);
-            GCR_CUDA(cudaLaunchKernelEx(&cfg, h->have_masks ? k_score_fast<true> : k_score_fast<false>, B, T));
+            GCR_CUDA(cudaLaunchKernelEx(&cfg, mode == 2 ? k_score_fast<2> : (mode == 1 ? k_score_fast<1> : k_score_fast<0>), B, T));
         }
         if (time_kernels) GCR_CUDA(cudaEventRecord(h->evk1, s));
         // Candidate window: hypotheses whose FP32-path value is within rel_tol of the best one are re-scored in FP64.
@@ -999,6 +1094,7 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
         out->n_solved = c.n_solved;
         out->n_rechecked = c.n_worklist;
         out->n_exact_hyp = c.n_hard;
+        out->n_refined = c.n_refined;
         out->n_scored = static_cast<int64_t>(c.n_fast) + c.n_sens + c.n_hard;
         out->n_candidates = c.n_candidates;
         if (time_kernels)
@@ -1012,9 +1108,7 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
         out->stage_phase_us[1] = static_cast<float>(static_cast<double>(ph[5] - ph[6]) * 1e-3); // k_sample_solve start -> end of k_tail
         out->winner_rank = static_cast<int32_t>(r.reserved);
         out->score_kernel = h->last_resident ? 1 : 0;
-        if (c.xchg_timeout) return h->fail(GCR_ERR_STATE, "winner exchange timed out: a peer rank did not run the same collective call");
-        if (c.n_bad_sample) return h->fail(GCR_ERR_INVALID, "replayed sample indices out of range");
-        if (c.n_worklist_overflow) return h->fail(GCR_ERR_STATE, "guard-band worklist overflow");
+        return check_run_counters(h, c);
     }
     return GCR_OK;
 }
@@ -1028,14 +1122,20 @@ int gcr_best(gcr_handle h, double model[4], double* score, uint32_t n_inl[2], ui
     const bool want_masks = scale_mask_words || orient_mask_words;
     if (!h->last_run_mirrored)
     {
-        GCR_CUDA(cudaSetDevice(h->device));
-        GCR_CUDA(cudaMemcpyAsync(h->h_best, h->d_best.p, sizeof(unsigned int) * (want_masks ? kResultHeaderWords + ws + wo : 16),
+        GCR_DEVICE(h);
+        GCR_CUDA(cudaMemcpyAsync(h->h_best, h->d_best.p, sizeof(unsigned int) * (want_masks ? kResultHeaderWords + ws + wo : 32),
                                  cudaMemcpyDeviceToHost, h->stream));
         GCR_CUDA(cudaStreamSynchronize(h->stream));
     }
     // (a mirrored run was synchronous: the staging block is complete and the stream idle)
     Record r;
     std::memcpy(&r, h->h_best, sizeof(r));
+    {
+        Counters c;
+        std::memcpy(&c, h->h_best + 16, sizeof(c));
+        const int rc = check_run_counters(h, c);
+        if (rc != GCR_OK) return rc;
+    }
     if (model) for (int i = 0; i < 4; i++) model[i] = r.model[i];
     if (score) *score = r.score;
     if (n_inl) { n_inl[0] = r.n_inl[0]; n_inl[1] = r.n_inl[1]; }
@@ -1061,8 +1161,15 @@ int gcr_fetch(gcr_handle h, uint8_t* flags, double* models, double* score, uint3
 {
     if (!h) return GCR_ERR_INVALID;
     if (!h->have_run) return h->fail(GCR_ERR_STATE, "gcr_fetch before gcr_run");
-    GCR_CUDA(cudaSetDevice(h->device));
+    GCR_DEVICE(h);
+    if (!h->last_run_mirrored) GCR_CUDA(cudaMemcpyAsync(h->h_best, h->d_best.p, sizeof(unsigned int) * 32, cudaMemcpyDeviceToHost, h->stream));
     GCR_CUDA(cudaStreamSynchronize(h->stream));
+    {
+        Counters c;
+        std::memcpy(&c, h->h_best + 16, sizeof(c));
+        const int rc = check_run_counters(h, c);
+        if (rc != GCR_OK) return rc;
+    }
     const size_t H = static_cast<size_t>(h->n_hyp);
     const size_t W = static_cast<size_t>((h->ns + 31) / 32 + (h->no + 31) / 32);
     if ((score || n_inl) && !h->have_per_hyp)
@@ -1088,7 +1195,7 @@ int gcr_score_models(gcr_handle h, const double* models, int64_t n, const double
     if (n < 1 || n > kCandCap) return h->fail(GCR_ERR_INVALID, "gcr_score_models: 1 <= n <= 1024 models per call");
     if (!(thr[0] >= 0.0) || !std::isfinite(thr[0]) || (h->problem == 0 && (!(thr[1] >= 0.0) || !std::isfinite(thr[1]))))
         return h->fail(GCR_ERR_INVALID, "thresholds must be finite and non-negative");
-    GCR_CUDA(cudaSetDevice(h->device));
+    GCR_DEVICE(h);
     int rc = ensure_common(h);
     if (rc != GCR_OK) return rc;
     GCR_CUDA(h->d_user_models.ensure(kCandCap));
@@ -1161,7 +1268,7 @@ int gcr_fit_models(gcr_handle h, int64_t n_fits, const uint32_t* scale_idx, cons
         if (scale_idx[i] >= static_cast<uint32_t>(h->ns)) return h->fail(GCR_ERR_INVALID, "gcr_fit_models: scale index out of range");
     for (size_t i = 0; i < O; ++i)
         if (orient_idx[i] >= static_cast<uint32_t>(h->no)) return h->fail(GCR_ERR_INVALID, "gcr_fit_models: orientation index out of range");
-    GCR_CUDA(cudaSetDevice(h->device));
+    GCR_DEVICE(h);
 
     auto align16 = [](size_t x) { return (x + 15) & ~static_cast<size_t>(15); };
     const size_t in_desc = 0, in_s = align16(K * sizeof(FitDesc)), in_o = align16(in_s + 4 * S), in_bytes = align16(in_o + 4 * O);
@@ -1274,7 +1381,7 @@ int gcr_debug_eval(gcr_handle h, int which, const double* in, int64_t n, const d
 {
     if (!h || !in || !out || n < 1 || which < 0 || which > 4) return GCR_ERR_INVALID;
     if (!h->stream) return h->fail(GCR_ERR_STATE, "engine was not created successfully");
-    GCR_CUDA(cudaSetDevice(h->device));
+    GCR_DEVICE(h);
     GCR_CUDA(h->d_dbg_in.ensure(3 * static_cast<size_t>(n)));
     GCR_CUDA(h->d_dbg_out.ensure(static_cast<size_t>(n)));
     Model4 m = {0, 0, 1, 0};

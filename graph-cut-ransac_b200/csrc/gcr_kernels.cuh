@@ -41,10 +41,12 @@ __global__ void k_prep_features(const double* __restrict__ scale, int ns, const 
     pdl_launch_dependents(); // a following k_sample_solve may fetch its samples (replay: over PCIe) while this kernel runs
     const float inf = __int_as_float(0x7f800000);
     const double dinf = __longlong_as_double(0x7ff0000000000000ll), dnan = __longlong_as_double(0x7ff8000000000000ll);
-    if (i < ncs * kChunk)
+    if (i < ncs * kChunk) // (whole warps: the bound is a multiple of the block size)
     {
         float a = 0.f, b = 0.f, c = inf; // pad: v = +inf -> never an inlier, never in the band
         double ad = 0.0, bd = 0.0, cd = dinf;
+        double xa = 0.0, ya = 0.0, ia = 0.0;
+        bool ok = false;
         if (i < ns)
         {
             const double x = scale[3 * i], y = scale[3 * i + 1], s = scale[3 * i + 2];
@@ -58,10 +60,16 @@ __global__ void k_prep_features(const double* __restrict__ scale, int ns, const 
             // a per-FEATURE value, evaluated here once with the very function the solver would call per hypothesis
             aux_s[i] = problem == 2 ? pow(s, -1.0 / 3.0) : pow(s, 1.0 / 3.0);
             const double q = cbrt(s);
-            const double xa = x / q, ya = y / q, ia = 1.0 / q;
-            const bool ok = isfinite(xa) && isfinite(ya) && isfinite(ia) && fabs(xa) < 1e12 && fabs(ya) < 1e12 &&
-                            fabs(ia) < 1e12 && fabs(ia) > 1e-12;
-            if (ok)
+            xa = x / q; ya = y / q; ia = 1.0 / q;
+            ok = isfinite(xa) && isfinite(ya) && isfinite(ia) && fabs(xa) < 1e12 && fabs(ya) < 1e12 && fabs(ia) < 1e12 && fabs(ia) > 1e-12;
+        }
+        // Features leave the FP32 / FP64 planes in aligned PAIRS (2j, 2j + 1): an irregular feature takes its partner along, and so does the
+        // padding behind the last feature of an odd count.  The winner-only scoring loop shares one reciprocal between the two features of a
+        // pair (score_chunk_w): a NaN sentinel must never meet a real feature there.
+        const bool pair_ok = ok && __shfl_xor_sync(0xffffffffu, ok, 1);
+        if (i < ns)
+        {
+            if (pair_ok)
             {
                 a = static_cast<float>(xa);
                 b = static_cast<float>(ya);
@@ -93,7 +101,8 @@ __global__ void k_prep_features(const double* __restrict__ scale, int ns, const 
     {
         float a = 0.f, b = 0.f, c = 0.f;
         double ad = 0.0, bd = dnan, cd = 0.0; // pad: NaN sine
-        bool pad = true;
+        bool pad = true, ok = false;
+        double k = 0.0, st = 0.0, ct = 0.0;
         if (i < no)
         {
             const double x = orient[3 * i], y = orient[3 * i + 1], t = orient[3 * i + 2];
@@ -103,13 +112,16 @@ __global__ void k_prep_features(const double* __restrict__ scale, int ns, const 
                 orient_copy[3 * i + 1] = y;
                 orient_copy[3 * i + 2] = t;
             }
-            double st, ct;
             sincos(t, &st, &ct);
             aux_o[2 * i] = st; // lineFromPointAndAngle's sine / cosine (math_utils.hpp:104-109), per feature
             aux_o[2 * i + 1] = ct;
-            const double k = x * st - y * ct;
-            const bool ok = isfinite(k) && isfinite(st) && isfinite(ct) && fabs(k) < 1e12;
-            if (ok)
+            k = x * st - y * ct;
+            ok = isfinite(k) && isfinite(st) && isfinite(ct) && fabs(k) < 1e12;
+        }
+        const bool pair_ok = ok && __shfl_xor_sync(0xffffffffu, ok, 1); // aligned pairs, as for the scale class
+        if (i < no)
+        {
+            if (pair_ok)
             {
                 a = static_cast<float>(k);
                 b = static_cast<float>(st);
@@ -172,12 +184,50 @@ __device__ __forceinline__ void draw_pair(uint32_t u0, uint32_t u1, uint32_t n, 
     b = static_cast<int>(i1);
 }
 
+// Error bands of the FP32 path for one model: |delta (A - lg2 v)| <= drho / 2 and |delta t| <= dprime / max + t_band0 in the
+// FP32 tiles (v, numer, denom from FP32 features and FP32 h7, h8), and the same with the three cancelling FMAs done in FP64 and rounded
+// once (precise tiles, and the mid-precision refinement of the contenders in k_tail).
+struct PathBands
+{
+    double A;                 // log2 of the (effective) alpha
+    double drho32, dprime32;  // FP32 tiles
+    double drho64, dprime64;  // FP64 front end
+    bool ok32, ok64, common_ok;
+};
+__device__ __forceinline__ PathBands path_bands(const Model4& m, const Scene& sc, const Thresholds& T, bool all_exact)
+{
+    PathBands r;
+    const double ah7 = fabs(m.h7), ah8 = fabs(m.h8);
+    const double mag = ah7 * sc.xq_max + ah8 * sc.yq_max + sc.iq_max; // bound of the terms of v
+    // scale-only "original": residual |log(rectified / alpha^3)| = 3 ln2 |-lg2 alpha - lg2 v|: alpha enters reciprocally
+    const double alpha_eff = T.problem == 2 ? 1.0 / m.alpha : m.alpha;
+    r.A = log2(alpha_eff);
+    const double Tp = T.Tp;
+    const double v_lo = alpha_eff * T.exp2_neg_Tp, v_hi = alpha_eff * T.exp2_pos_Tp; // hypothesis-independent factors from the host
+    const double kh = sc.k_max * (ah7 + ah8);
+    const double eps_lg = 2.384185791015625e-7 + 3.0 * kU * (fabs(r.A) + Tp + 1.0); // MUFU.LG2 + roundings of A, d
+    const double dv = 8.0 * kU * mag;
+    r.drho32 = 2.0 * (dv / ((v_lo - dv) * kLn2) + eps_lg);
+    r.dprime32 = 6.0 * kU * (2.0 + 3.0 * kh) * 1.0001;
+    r.ok32 = isfinite(dv) && (v_lo > 4.0 * dv) && (r.drho32 < 1e-3 * Tp) && (r.dprime32 < 1e-3 * T.tanT);
+    const double kU64 = 1.1102230246251565e-16;
+    const double dv64 = 8.0 * kU64 * mag;
+    r.drho64 = 2.0 * (dv64 / ((v_lo - dv64) * kLn2) + 1.5 * kU / kLn2 + eps_lg);
+    r.dprime64 = 6.0 * kU64 * (2.0 + 3.0 * kh) * 1.0001;
+    r.ok64 = isfinite(dv64) && (v_lo > 4.0 * dv64) && (r.drho64 < 1e-3 * Tp);
+    r.common_ok = !all_exact && !T.orient_all_exact && !sc.irr_overflow && isfinite(r.A) && (v_hi * 1.01 < 1000.0) && (kh < 1e6) &&
+                  (ah7 < 1e6) && (ah8 < 1e6);
+    return r;
+}
+
 __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, int all_exact)
 {
     const int h = blockIdx.x * blockDim.x + threadIdx.x;
     const unsigned lane = threadIdx.x & 31;
     if (h == 0) B.phase_ns[6] = global_ns(); // diagnostics: start of the stage as seen by the first CTA
     bool solved = false, hard = false, sample_valid = false, sens_s = false, sens_o = false;
+    bool scored = false; // goes to one of the three scoring lists (winner-only runs leave out the models isValidModel rejects)
+    const bool winner = !B.per_hyp;
     Model4 m = {0.0, 0.0, 0.0, 0.0};
     float4 p0 = make_float4(0.f, 0.f, 0.f, 0.f), p1 = make_float4(0.f, 1.f, 0.f, 0.f);
     int s0 = 0, s1 = 0, o0 = 0, o1 = 0; // scale-only problems: (s0, s1, o0) index the scale class, o1 is unused (-1)
@@ -261,48 +311,53 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
         {
             f |= 2;
             // consulted at selection time, GCRANSAC.h:440-446; the scale-only solvers keep SolverEngine's default (always valid)
-            if (T.problem != 0 || is_valid_model(m)) f |= 4;
+            const bool model_valid = T.problem != 0 || is_valid_model(m);
+            if (model_valid) f |= 4;
+            // The reference scores every model and consults isValidModel only when it would become the best one (GCRANSAC.h:440-446):
+            // a rejected model can never be selected, so a winner-only run does not score it (its slot reports flags without bit 4)
+            scored = model_valid || !winner;
             // ---- scoring-path parameters and their proven error bands (DESIGN.md "error budget")
-            const Scene sc = *B.scene;
-            const double ah7 = fabs(m.h7), ah8 = fabs(m.h8);
-            const double mag = ah7 * sc.xq_max + ah8 * sc.yq_max + sc.iq_max; // bound of the terms of v
-            // scale-only "original": residual |log(rectified / alpha^3)| = 3 ln2 |-lg2 alpha - lg2 v|: alpha enters reciprocally
-            const double alpha_eff = T.problem == 2 ? 1.0 / m.alpha : m.alpha;
-            const double A = log2(alpha_eff);
-            const double Tp = T.Tp;
-            const double v_lo = alpha_eff * T.exp2_neg_Tp, v_hi = alpha_eff * T.exp2_pos_Tp; // hypothesis-independent factors from the host
-            const double kh = sc.k_max * (ah7 + ah8);
-            const double eps_lg = 2.384185791015625e-7 + 3.0 * kU * (fabs(A) + Tp + 1.0); // MUFU.LG2 + roundings of A, d
-            // FP32 tiles: v, numer, denom from FP32 features and FP32 (h7, h8)
-            const double dv = 8.0 * kU * mag;
-            double drho = 2.0 * (dv / ((v_lo - dv) * kLn2) + eps_lg);
-            double dprime = 6.0 * kU * (2.0 + 3.0 * kh) * 1.0001;
-            const bool ok32 = isfinite(dv) && (v_lo > 4.0 * dv) && (drho < 1e-3 * Tp) && (dprime < 1e-3 * T.tanT);
-            // precise tiles: the same three FMAs in FP64, rounded once to FP32 (relative error u)
-            const double kU64 = 1.1102230246251565e-16;
-            const double dv64 = 8.0 * kU64 * mag;
-            const double drho64 = 2.0 * (dv64 / ((v_lo - dv64) * kLn2) + 1.5 * kU / kLn2 + eps_lg);
-            const bool ok64 = isfinite(dv64) && (v_lo > 4.0 * dv64) && (drho64 < 1e-3 * Tp);
-            const bool common_ok = !all_exact && !T.orient_all_exact && !sc.irr_overflow && isfinite(A) &&
-                                   (v_hi * 1.01 < 1000.0) && (kh < 1e6) && (ah7 < 1e6) && (ah8 < 1e6);
+            const PathBands pb = path_bands(m, *B.scene, T, all_exact != 0);
+            const double A = pb.A, Tp = T.Tp;
+            double drho = pb.drho32, dprime = pb.dprime32;
             // The 1e-3 caps keep the FP32 residuals of the inliers within the 1e-5 score bar; hypotheses that
             // miss them in FP32 (tiny alpha: cancellation in v; large |h|: angle noise) go to the precise tiles,
             // the rest (out of any proven range) to the FP64 reference-order kernel.
-            if (common_ok && ok32) { }
-            else if (common_ok && ok64)
+            if (pb.common_ok && pb.ok32) { }
+            else if (pb.common_ok && pb.ok64)
             {
                 sens_s = true;
-                drho = drho64;
-                dprime = 6.0 * kU64 * (2.0 + 3.0 * kh) * 1.0001;
+                drho = pb.drho64;
+                dprime = pb.dprime64;
             }
             else hard = true;
-            if (hard) f |= 8;
+            if (hard && scored) f |= 8;
             double sphi, cphi;
             sincos(m.phi, &sphi, &cphi);
-            p0 = make_float4(static_cast<float>(-m.h7), static_cast<float>(-m.h8), static_cast<float>(A),
-                             __double2float_rd(Tp - drho));
-            p1 = make_float4(__double2float_ru(Tp + drho), static_cast<float>(cphi), static_cast<float>(sphi),
-                             __double2float_ru(dprime));
+            if (winner)
+            {
+                // score_chunk_w: dq = A/Tp - lg2(v)/Tp; the class values carry an error of at most err_ab.x + err_ab.y * (sum of 1/mx over the orientation evaluations) + 8e-6 value
+                // (DESIGN.md 5b): |delta dq| <= |delta (A - lg2 v)| / Tp + roundings of A/Tp and of the FMA (drho is twice its own bound of
+                // |delta (A - lg2 v)|; that safety factor is left out here, the 8u of dv already doubles the first-order 4u); a feature near or
+                // inside the threshold moves its term 1 - dq^2 by <= 2.1 |delta dq| + 2u.  Orientation: the term 1 - r^2/tsq moves by
+                // <= 2.1 (delta t) / sqrt(tsq), delta t <= dprime / mx + t_band0, + 2.5e-6 (polynomial fit 5e-7, Horner and FFMA.SAT roundings,
+                // the two extra roundings of the shared reciprocal)
+                const double ddq = 0.5 * drho / Tp + 2.0 * kU * (fabs(A) / Tp + 2.0);
+                const double e_s = 2.1 * ddq + 2.0 * kU;
+                const double e_o0 = 2.1 * static_cast<double>(T.t_band0) / static_cast<double>(T.sqrt_tsq1) + 2.5e-6;
+                const double e_o1 = 2.1 * dprime / static_cast<double>(T.sqrt_tsq1);
+                const double no_eff = T.problem == 0 ? static_cast<double>(B.no) : 0.0;
+                B.err_ab[h] = make_float2(__double2float_ru(static_cast<double>(B.ns) * e_s + no_eff * e_o0), __double2float_ru(1.001 * e_o1));
+                p0 = make_float4(static_cast<float>(-m.h7), static_cast<float>(-m.h8), static_cast<float>(A / Tp), 0.f);
+                p1 = make_float4(0.f, static_cast<float>(cphi), static_cast<float>(sphi), 0.f);
+            }
+            else
+            {
+                p0 = make_float4(static_cast<float>(-m.h7), static_cast<float>(-m.h8), static_cast<float>(A),
+                                 __double2float_rd(Tp - drho));
+                p1 = make_float4(__double2float_ru(Tp + drho), static_cast<float>(cphi), static_cast<float>(sphi),
+                                 __double2float_ru(dprime));
+            }
         }
         B.flags[h] = f;
         B.models[h] = m;
@@ -314,20 +369,22 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
     // block-aggregated compaction of solved hypotheses into the fast / precise / exact lists: warp ballots, a prefix over
     // the block's warps in shared memory, ONE returning atomic per list and block (per-warp atomics on the same three
     // counters serialise in L2 and were half of this kernel's time)
-    __shared__ unsigned int s_cnt[4][4];  // [list][warp]: fast, sens, hard, sample_valid
+    __shared__ unsigned int s_cnt[5][4];  // [list][warp]: fast, sens, hard, sample_valid, solved
     __shared__ unsigned int s_base[3];
     const unsigned warp = threadIdx.x >> 5;
     const bool sens = sens_s || sens_o;
     const unsigned m_valid = __ballot_sync(0xffffffffu, sample_valid);
-    const unsigned m_fast = __ballot_sync(0xffffffffu, solved && !hard && !sens);
-    const unsigned m_sens = __ballot_sync(0xffffffffu, solved && !hard && sens);
-    const unsigned m_hard = __ballot_sync(0xffffffffu, solved && hard);
+    const unsigned m_fast = __ballot_sync(0xffffffffu, scored && !hard && !sens);
+    const unsigned m_sens = __ballot_sync(0xffffffffu, scored && !hard && sens);
+    const unsigned m_hard = __ballot_sync(0xffffffffu, scored && hard);
+    const unsigned m_solved = __ballot_sync(0xffffffffu, solved);
     if (lane == 0)
     {
         s_cnt[0][warp] = __popc(m_fast);
         s_cnt[1][warp] = __popc(m_sens);
         s_cnt[2][warp] = __popc(m_hard);
         s_cnt[3][warp] = __popc(m_valid);
+        s_cnt[4][warp] = __popc(m_solved);
     }
     __syncthreads();
     if (threadIdx.x < 3)
@@ -339,9 +396,7 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
     else if (threadIdx.x == 32)
     {
         const unsigned int nv = s_cnt[3][0] + s_cnt[3][1] + s_cnt[3][2] + s_cnt[3][3];
-        unsigned int ns = 0;
-#pragma unroll
-        for (int l = 0; l < 3; l++) ns += s_cnt[l][0] + s_cnt[l][1] + s_cnt[l][2] + s_cnt[l][3];
+        const unsigned int ns = s_cnt[4][0] + s_cnt[4][1] + s_cnt[4][2] + s_cnt[4][3];
         if (nv) atomicAdd(&B.ctr->n_sample_valid, nv);
         if (ns) atomicAdd(&B.ctr->n_solved, ns);
     }
@@ -354,7 +409,7 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
         base_hard += s_cnt[2][w];
     }
     const unsigned below = (1u << lane) - 1u;
-    if (solved && !hard)
+    if (scored && !hard)
     {
         // normal hypotheses fill the compact arrays from the front, score-sensitive ones from the back, so
         // that the rare-path traffic of the latter stays in their own warps
@@ -364,7 +419,7 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
         B.pf1[c] = p1;
         B.fast_hyp[c] = h;
     }
-    if (solved && hard) B.hard_hyp[base_hard + __popc(m_hard & below)] = h;
+    if (scored && hard) B.hard_hyp[base_hard + __popc(m_hard & below)] = h;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -410,6 +465,11 @@ __device__ __forceinline__ void fixup_phase(const Buffers& B, const Thresholds& 
         const double r2 = r * r;
         if (r2 <= T.tsq[cls])
         {
+            if (!B.per_hyp) // winner-only run: the accumulators are class values sum max(0, 1 - r^2 / tsq)
+            {
+                if (T.tsq[cls] > 0.0) atomicAdd(&B.sums[2 * h + cls], 1.0 - r2 / T.tsq[cls]);
+                continue;
+            }
             atomicAdd(&B.sums[2 * h + cls], r2);
             atomicAdd(&B.cnts[2 * h + cls], 1u);
             if (B.masks) atomicOr(&B.masks[static_cast<size_t>(h) * B.wmask + (cls ? B.ws : 0) + (f >> 5)], 1u << (f & 31));
@@ -446,11 +506,12 @@ __device__ __forceinline__ double msac_value(const Thresholds& T, double s0, dou
     return v0 + (-s1 / T.tsq[1] + static_cast<double>(c1));
 }
 
-__device__ __forceinline__ void exact_items_phase(const Buffers& B, const Thresholds& T, int mode, unsigned int n_direct)
+__device__ __forceinline__ void exact_items_phase(const Buffers& B, const Thresholds& T, int mode, unsigned int n_direct,
+                                                  unsigned int hard_first = 0u, unsigned int hard_count = 0xffffffffu)
 {
     __shared__ unsigned long long red[kExactThreads / 32];
     __shared__ unsigned int redc[kExactThreads / 32];
-    const unsigned int n_items = mode == 0 ? __ldcg(&B.ctr->n_hard) : (mode == 1 ? min(__ldcg(&B.ctr->n_candidates) - n_direct, static_cast<unsigned>(kCandCap)) : n_direct);
+    const unsigned int n_items = mode == 0 ? (hard_count != 0xffffffffu ? hard_count : __ldcg(&B.ctr->n_hard)) : (mode == 1 ? min(__ldcg(&B.ctr->n_candidates) - n_direct, static_cast<unsigned>(kCandCap)) : n_direct);
     const unsigned int ups = (B.ns + kExactThreads - 1) / kExactThreads, upo = (B.no + kExactThreads - 1) / kExactThreads;
     const unsigned int upi = ups + upo;
     const unsigned long long n_units = static_cast<unsigned long long>(n_items) * upi;
@@ -465,7 +526,7 @@ __device__ __forceinline__ void exact_items_phase(const Buffers& B, const Thresh
         const int f = static_cast<int>((cls ? u - ups : u) * kExactThreads) + tid;
         const int n = cls ? B.no : B.ns;
         const double* F = cls ? B.orient : B.scale;
-        const unsigned int h = mode == 0 ? B.hard_hyp[it] : 0u;
+        const unsigned int h = mode == 0 ? B.hard_hyp[hard_first + it] : 0u;
         const Model4 m = mode == 0 ? B.models[h] : B.cand_model[it];
         unsigned int* mask_out = mode == 0 ? (B.masks ? B.masks + static_cast<size_t>(h) * B.wmask : nullptr)
                                            : B.cand_masks + static_cast<size_t>(it) * B.wmask;
@@ -714,6 +775,329 @@ __device__ __forceinline__ void collect_phase(const Buffers& B, const Thresholds
     }
 }
 
+// ---- winner-only runs (Buffers::per_hyp == 0): a three-level cascade.
+//  1. The scoring kernels leave per class the truncated-quadratic value S_i = sum_f max(0, 1 - r^2/tsq_i) in sums[2h + i] and the largest
+//     1/mx of the orientation evaluations in cnts[2h + 1]; the FP32 evaluation error of S_0 + S_1 is bounded per hypothesis by
+//     err = err_ab.x + err_ab.y * (sum of 1/mx, bounded chunk by chunk) + 8e-6 value (k_sample_solve).  That bound is a sum over ALL features (which of them
+//     sit near the threshold is not known), i.e. loose: ~1e-3 of the value for 70 000 features.
+//  2. CONTENDERS -- hypotheses whose upper bound reaches the best lower bound -- are re-scored by refine_phase in mid precision with exact
+//     inlier decisions (FP64 front end, FP32 MUFU, a guard band of a few ulps decided by the FP64 reference-order residuals): exact counts,
+//     hence the zero-reset rule S3, and a value whose error is bounded over the INLIERS only (~1e-6 of the value).
+//  3. The few contenders whose refined upper bound reaches the best refined lower bound are scored in FP64 reference order (candidates),
+//     and the selection rule (GCRANSAC.h:440-446, strict '<', earliest wins) sees the reference's own values.
+// Value and loose error bound of a scored, model-valid hypothesis (level 1).
+__device__ __forceinline__ double hyp_value_w(const Buffers& B, const Thresholds& T, unsigned int h, unsigned char f, double& err)
+{
+    err = 0.0;
+    if (f & 8) // scored by the FP64 reference-order kernel: exact, zero-reset rule applied
+    {
+        unsigned int n0, n1;
+        return hyp_value(B, T, h, f, n0, n1);
+    }
+    const double s0 = B.sums[2 * h], s1 = T.problem == 0 ? B.sums[2 * h + 1] : 0.0;
+    const float2 ab = B.err_ab[h];
+    const double v = s0 + s1;
+    err = static_cast<double>(ab.x) + static_cast<double>(ab.y) * static_cast<double>(__uint_as_float(B.cnts[2 * h + 1])) + 8e-6 * v + 1e-9;
+    return v;
+}
+
+// Calls fn(h, flags) for every scored, model-valid hypothesis of the run, grid-strided (directly over the slots for small batches,
+// through the compact lists for big ones, as finalize_phase does).
+template <typename F>
+__device__ __forceinline__ void for_each_scored_valid(const Buffers& B, F fn)
+{
+    if (tail_direct(B))
+    {
+        for (int h = blockIdx.x * blockDim.x + threadIdx.x; h < B.n_hyp; h += gridDim.x * blockDim.x)
+        {
+            const unsigned char f = B.flags[h];
+            if ((f & 6) == 6) fn(static_cast<unsigned int>(h), f);
+        }
+        return;
+    }
+    const unsigned int n_fast = __ldcg(&B.ctr->n_fast), n_sens = __ldcg(&B.ctr->n_sens), n_hard = __ldcg(&B.ctr->n_hard);
+    const unsigned int total = n_fast + n_sens + n_hard;
+    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x)
+    {
+        const unsigned int h = scored_hyp(B, i, n_fast, n_sens);
+        const unsigned char f = B.flags[h];
+        if (f & 4) fn(h, f);
+    }
+}
+
+// block-wide maximum of an ordered key, one atomic per CTA
+__device__ __forceinline__ void publish_key(unsigned long long* dst, unsigned long long key)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        const unsigned long long other = __shfl_xor_sync(0xffffffffu, key, o);
+        key = other > key ? other : key;
+    }
+    __shared__ unsigned long long s_keyw[kExactThreads / 32];
+    if ((threadIdx.x & 31) == 0) s_keyw[threadIdx.x >> 5] = key;
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        for (unsigned int w = 1; w < blockDim.x / 32; w++) key = s_keyw[w] > key ? s_keyw[w] : key;
+        if (key) atomicMax(dst, key);
+    }
+    __syncthreads();
+}
+
+// level 1: best LOWER bound over the hypotheses that may have a positive score (S11: a model needs one)
+__device__ __forceinline__ void finalize_phase_w(const Buffers& B, const Thresholds& T)
+{
+    unsigned long long key = 0ull;
+    for_each_scored_valid(B, [&](unsigned int h, unsigned char f) {
+        double err;
+        const double v = hyp_value_w(B, T, h, f, err);
+        if (v + err > 0.0)
+        {
+            const unsigned long long k = ordered_bits(v - err);
+            key = k > key ? k : key;
+        }
+    });
+    publish_key(&B.ctr->best_key, key);
+}
+
+// level 2, collection: every not yet refined hypothesis whose upper bound reaches `floor_v` takes a contender slot; the collecting thread
+// derives the refinement's parameters (FP64 model, FP32 band limits of the FP64-front arithmetic).  Slots beyond kContCap: the overflow flag
+// sends the stragglers straight to level 3.
+__device__ __forceinline__ void contender_collect_phase(const Buffers& B, const Thresholds& T, double floor_v)
+{
+    for_each_scored_valid(B, [&](unsigned int h, unsigned char f) {
+        if (f & 32) return; // already a contender
+        double err;
+        const double v = hyp_value_w(B, T, h, f, err);
+        if (!(v + err > 0.0) || v + err < floor_v) return;
+        const unsigned int slot = atomicAdd(&B.ts->n_cont, 1u);
+        if (slot >= kContCap)
+        {
+            B.ts->cont_overflow = 1u;
+            return;
+        }
+        B.flags[h] = f | 32;
+        // class values that prove the minimal inlier counts by themselves (every term is <= 1): this contender cannot lose its score to the
+        // zero-reset rule, its lower bound is a valid one
+        if (!(f & 8))
+        {
+            const double s0 = B.sums[2 * h], s1 = B.sums[2 * h + 1];
+            if (!(s0 - err > static_cast<double>(T.min_inl[0]) - 1.0) || (T.problem == 0 && !(s1 - err > static_cast<double>(T.min_inl[1]) - 1.0)))
+                B.ts->unproven = 1u;
+        }
+        ContPar P;
+        const Model4 m = B.models[h];
+        P.hyp = h;
+        P.exact = (f & 8) ? 1u : 0u;
+        P.h7 = m.h7;
+        P.h8 = m.h8;
+        sincos(m.phi, &P.sphi, &P.cphi);
+        const PathBands pb = path_bands(m, *B.scene, T, false);
+        const double Tp = T.Tp;
+        P.A = static_cast<float>(pb.A);
+        P.Tin = __double2float_rd(Tp - pb.drho64);
+        P.Tout = __double2float_ru(Tp + pb.drho64);
+        P.dpr = __double2float_ru(pb.dprime64);
+        // error of a CERTAIN inlier's term r^2/tsq in this arithmetic (band evaluations are decided and valued in FP64):
+        //   scale        |delta d| <= drho64 / 2  ->  delta (d/Tp)^2 <= 1.05 drho64 / Tp (+ the FP32 rounding of d^2's factor)
+        //   orientation  |delta t| <= 2 band0r (evaluations whose dprime64 / mx exceeds band0r are sent to FP64)  ->  2.1 * 2 band0r / sqrt(tsq),
+        //                + 1.2e-6 for the polynomial fit (5e-7) and its FP32 evaluation
+        const double band0r = 8.0 * kU * static_cast<double>(T.tanT) + 1e-12;
+        P.e_s = __double2float_ru(1.05 * pb.drho64 / Tp + 4.0 * kU);
+        P.e_o = __double2float_ru(4.2 * band0r / static_cast<double>(T.sqrt_tsq1) + 1.2e-6);
+        P.ri_cap = __double2float_rd(band0r / fmax(pb.dprime64, 1e-300));
+        P.band0r = __double2float_ru(band0r);
+        B.cont_par[slot] = P;
+        B.cont_q[2 * slot] = B.cont_q[2 * slot + 1] = 0ull;
+        B.cont_n[2 * slot] = B.cont_n[2 * slot + 1] = 0u;
+    });
+}
+
+// level 2, evaluation: unit = (contender, 256 consecutive features of one class), thread <-> feature.  The three cancelling FMAs
+// (v = 1/q - h7 x/q - h8 y/q; numer, denom) and the rotation by -phi in FP64 from the FP64 planes, rounded once; MUFU.LG2 / MUFU.RCP
+// and the threshold tests in FP32 against band limits that bound what is left (2^-22 of lg2 + roundings; a few ulps of t): certainly
+// in -> r^2 from the FP32 value, certainly out -> nothing, in between (a few 1e-5 of the evaluations) and irregular features -> the
+// FP64 reference-order residual decides and gives r^2.  Sums of r^2/tsq in 64-bit fixed point (order-independent), exact counts.
+constexpr int kRefineFW = 64;  // features per warp and unit
+constexpr int kRefineIlp = 4;  // independent evaluations in flight per thread
+__device__ __forceinline__ void refine_phase(const Buffers& B, const Thresholds& T, unsigned int c_first, unsigned int c_end)
+{
+    constexpr int kCD = kChunk / 2;
+    constexpr int kFB = kRefineFW * (kExactThreads / 32); // features per unit (one CTA)
+    if (c_end <= c_first) return;
+    // The mapping of the scoring kernels: one LANE per contender (its parameters and sums in registers, no reduction), the features read as
+    // warp-uniform loads of the FP64 planes; unit = (32 contenders) x (kFB features of one class), each warp of the CTA a kRefineFW slice.
+    const unsigned int n_groups = (c_end - c_first + 31) / 32;
+    const unsigned int bs = (B.ns + kFB - 1) / kFB, bo = (B.no + kFB - 1) / kFB, fbk = bs + bo;
+    const unsigned int n_units = n_groups * fbk;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const double unit_s = static_cast<double>(T.scale_unit);
+    __shared__ double s_pl[3][kFB]; // the unit's block of the three FP64 planes (12 KB), staged once per unit
+    for (unsigned int unit = blockIdx.x; unit < n_units; unit += gridDim.x)
+    {
+        const unsigned int g = unit / fbk, u = unit % fbk;
+        const int cls = u >= bs;
+        const int n = cls ? B.no : B.ns;
+        const int blk0 = static_cast<int>((cls ? u - bs : u) * kFB);
+        const double* planes = cls ? B.fod : B.fsd;
+        __syncthreads(); // the previous unit's readers are done
+        for (int i = threadIdx.x; i < kFB; i += blockDim.x)
+        {
+            const int f = min(blk0 + i, n - 1); // (slots past the end repeat the last feature and are not counted)
+            const double* pl = planes + static_cast<size_t>(f / kCD) * (3 * kCD) + (f % kCD);
+            s_pl[0][i] = pl[0];
+            s_pl[1][i] = pl[kCD];
+            s_pl[2][i] = pl[2 * kCD];
+        }
+        __syncthreads();
+        const int f_begin = blk0 + warp * kRefineFW;
+        const int f_end = min(n, f_begin + kRefineFW);
+        const unsigned int c = c_first + g * 32 + lane;
+        ContPar P;
+        P.exact = 1u;
+        if (c < c_end) P = B.cont_par[c];
+        const bool active = !P.exact; // (a contender the FP64 kernel scored already needs no refinement)
+        unsigned long long q = 0ull;
+        unsigned int cnt = 0u;
+        for (int fb = f_begin; fb < f_end; fb += kRefineIlp)
+        {
+            float x0[kRefineIlp], x1[kRefineIlp]; // scale: d; orientation: t, 1/mx.  The arithmetic of all features first (independent chains)
+            bool bad[kRefineIlp];                 // irregular feature (sentinel plane value): FP64 decides
+#pragma unroll
+            for (int j = 0; j < kRefineIlp; j++)
+            {
+                const int i = fb + j - blk0; // (< kFB: kRefineFW is a multiple of kRefineIlp)
+                const double pa = s_pl[0][i], pb = s_pl[1][i], pc = s_pl[2][i];
+                if (cls == 0)
+                {
+                    const float v = static_cast<float>(fma(-P.h8, pb, fma(-P.h7, pa, pc)));
+                    x0[j] = P.A - lg2_approx(v);
+                    x1[j] = 0.f;
+                    bad[j] = !(pc < 1e300);
+                }
+                else
+                {
+                    const double nn = fma(pa, -P.h7, pb), dd = fma(pa, P.h8, pc);
+                    const double c1 = fma(nn, P.sphi, dd * P.cphi), s1 = fma(nn, P.cphi, -(dd * P.sphi));
+                    const float a1 = static_cast<float>(fabs(c1)), a2 = static_cast<float>(fabs(s1));
+                    const float mn = fminf(a1, a2), mx = fmaxf(fmaxf(a1, a2), 1e-30f);
+                    x1[j] = rcp_approx(mx);
+                    x0[j] = mn * x1[j];
+                    bad[j] = pb != pb;
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < kRefineIlp; j++)
+            {
+                const int f = fb + j;
+                if (f >= f_end || !active) continue;
+                bool in, fallback;
+                double r2;
+                if (cls == 0)
+                {
+                    const float d = x0[j];
+                    in = fabsf(d) <= P.Tin;
+                    fallback = (!in && fabsf(d) <= P.Tout) || bad[j]; // guard band, or an irregular feature
+                    r2 = static_cast<double>(d) * static_cast<double>(d) * unit_s;
+                }
+                else
+                {
+                    const float t = x0[j], ri = x1[j];
+                    const float band = fmaf(P.dpr, ri, P.band0r);
+                    const bool wide = !(ri <= P.ri_cap); // the FP64 part of the band is no longer negligible: decide in FP64
+                    in = !wide && t <= T.tanT - band;
+                    fallback = (!in && t <= T.tanT + band) || bad[j];
+                    const float z = t * t;
+                    r2 = static_cast<double>(z * fmaf(fmaf(fmaf(T.pc[3], z, T.pc[2]), z, T.pc[1]), z, T.pc[0]));
+                }
+                if (fallback)
+                {
+                    const Model4 m = B.models[P.hyp];
+                    const double* F = cls ? B.orient : B.scale;
+                    const double r = cls ? orientation_residual(F[3 * f], F[3 * f + 1], F[3 * f + 2], m)
+                                         : scale_residual(F[3 * f], F[3 * f + 1], F[3 * f + 2], m, T.problem == 2);
+                    r2 = r * r;
+                    in = r2 <= T.tsq[cls]; // S1
+                }
+                if (in)
+                {
+                    q += static_cast<unsigned long long>(fmin(r2 / T.tsq[cls], 1.0) * kFix + 0.5);
+                    cnt++;
+                }
+            }
+        }
+        if (active && cnt) // fixed point: the order of the additions does not matter
+        {
+            atomicAdd(&B.cont_q[2 * c + cls], q);
+            atomicAdd(&B.cont_n[2 * c + cls], cnt);
+        }
+    }
+}
+
+// level 2, values: refined value (exact counts: zero-reset rule S3 applied) and its error bound per contender; best refined lower bound
+__device__ __forceinline__ void contender_value_phase(const Buffers& B, const Thresholds& T, unsigned int c_first, unsigned int c_end)
+{
+    unsigned long long key = 0ull;
+    for (unsigned int c = c_first + blockIdx.x * blockDim.x + threadIdx.x; c < c_end; c += gridDim.x * blockDim.x)
+    {
+        const ContPar P = B.cont_par[c];
+        double v, err = 0.0;
+        unsigned int n0, n1;
+        if (P.exact) v = hyp_value(B, T, P.hyp, B.flags[P.hyp], n0, n1);
+        else
+        {
+            v = msac_value(T, fix_to_double(B.cont_q[2 * c], T.tsq[0]), fix_to_double(B.cont_q[2 * c + 1], T.tsq[1]), B.cont_n[2 * c],
+                           B.cont_n[2 * c + 1], n0, n1);
+            err = static_cast<double>(n0) * P.e_s + static_cast<double>(n1) * P.e_o + 1e-12 * static_cast<double>(n0 + n1) + 1e-12;
+        }
+        B.cont_val[2 * c] = v;
+        B.cont_val[2 * c + 1] = err;
+        if (v > 0.0) // (a reset or inlier-free contender has no score)
+        {
+            const unsigned long long k = ordered_bits(v - err);
+            key = k > key ? k : key;
+        }
+    }
+    publish_key(&B.ts->lb_ref_key, key);
+}
+
+// level 3, collection: contenders whose refined upper bound reaches the best refined lower bound (the reference's winner, and everything
+// tied with it, is among them: its true value is >= every other true value >= every lower bound); after a contender overflow also every
+// hypothesis that found no slot, by its loose bound.  Later rounds: the deferred ones (more than kCandCap candidates: massive ties).
+constexpr unsigned int kDirectCand = 16;
+__device__ __forceinline__ void collect_phase_w(const Buffers& B, const Thresholds& T, int round, unsigned int base, unsigned int n_cont,
+                                                double floor_loose, bool direct)
+{
+    if (round > 0)
+    {
+        for (int h = blockIdx.x * blockDim.x + threadIdx.x; h < B.n_hyp; h += gridDim.x * blockDim.x)
+        {
+            const unsigned char f = B.flags[h];
+            if ((f & 6) == 6 && (f & 16)) collect_candidate(B, h, base, f);
+        }
+        return;
+    }
+    const unsigned long long lk = __ldcg(&B.ts->lb_ref_key);
+    const double best_lb = lk ? from_ordered_bits(lk) : 0.0;
+    for (unsigned int c = blockIdx.x * blockDim.x + threadIdx.x; c < n_cont; c += gridDim.x * blockDim.x)
+    {
+        const double v = B.cont_val[2 * c], err = B.cont_val[2 * c + 1];
+        if (direct || (v > 0.0 && v + err >= best_lb))
+        {
+            const unsigned int h = B.cont_par[c].hyp;
+            collect_candidate(B, h, base, B.flags[h]);
+        }
+    }
+    if (__ldcg(&B.ts->cont_overflow))
+        for_each_scored_valid(B, [&](unsigned int h, unsigned char f) {
+            if (f & 32) return;
+            double err;
+            const double v = hyp_value_w(B, T, h, f, err);
+            if (v + err > 0.0 && v + err >= fmin(floor_loose, best_lb)) collect_candidate(B, h, base, f);
+        });
+}
+
 struct Record // mirrors gcr_record
 {
     double score;
@@ -903,10 +1287,14 @@ __device__ __forceinline__ void select_phase(const Buffers& B, const Thresholds&
             }
             if (final)
             {
+                B.ctr->n_refined = min(B.ts->n_cont, static_cast<unsigned int>(kContCap));
                 *B.ctr_snap = B.ctr[0];
                 Counters z;
                 memset(&z, 0, sizeof(z));
                 B.ctr[0] = z;
+                TailState tz;
+                memset(&tz, 0, sizeof(tz));
+                B.ts[0] = tz;
             }
         }
     }
@@ -937,25 +1325,84 @@ __global__ void __launch_bounds__(kExactThreads) k_tail(const __grid_constant__ 
     const bool stamp = blockIdx.x == 0 && threadIdx.x == 0; // phase boundaries as seen by CTA 0 (diagnostics, ns)
     pdl_wait(); // results of the scoring kernel
     if (stamp) B.phase_ns[0] = global_ns();
+    const bool winner = !B.per_hyp;
     fixup_phase(B, T);
     exact_items_phase(B, T, 0, 0u);
     grid.sync();
     if (stamp) B.phase_ns[1] = global_ns();
-    finalize_phase(B, T);
-    grid.sync();
+    unsigned int n_cont = 0u;
+    double floor_loose = 0.0;
+    bool direct = false;
+    if (winner)
+    {
+        finalize_phase_w(B, T);
+        grid.sync();
+#ifdef GCR_TAIL_DEBUG
+        if (stamp) B.phase_ns[2] = global_ns();
+#endif
+        // Contender rounds: one, unless the refinement lowers the bar (the loosely best hypothesis lost its score to the zero-reset rule, or
+        // its refined lower bound falls below its loose one) or the slots run out.  Every CTA reads the same counters after each barrier.
+        const unsigned long long k0 = __ldcg(&B.ctr->best_key);
+        if (k0)
+        {
+            floor_loose = from_ordered_bits(k0);
+            for (;;)
+            {
+                contender_collect_phase(B, T, floor_loose);
+                grid.sync();
+#ifdef GCR_TAIL_DEBUG
+                if (stamp) B.phase_ns[3] = global_ns();
+#endif
+                const unsigned int n_now = min(__ldcg(&B.ts->n_cont), static_cast<unsigned int>(kContCap));
+                const bool overflow = __ldcg(&B.ts->cont_overflow) != 0u;
+                if (n_cont == 0u && n_now <= kDirectCand && !overflow && !__ldcg(&B.ts->unproven))
+                {
+                    // a handful of contenders whose scores cannot be reset (small scenes: the loose bound is already tight): their FP64
+                    // scoring is cheaper than the refinement round and its two barriers
+                    n_cont = n_now;
+                    direct = true;
+                    break;
+                }
+                refine_phase(B, T, n_cont, n_now);
+                grid.sync();
+#ifdef GCR_TAIL_DEBUG
+                if (stamp) B.phase_ns[4] = global_ns();
+#endif
+                contender_value_phase(B, T, n_cont, n_now);
+                grid.sync();
+                n_cont = n_now;
+                const unsigned long long lk = __ldcg(&B.ts->lb_ref_key);
+                const double lb_ref = lk ? from_ordered_bits(lk) : -1.0; // no refined contender has a score yet: everything positive stays in play
+                if (overflow || lb_ref >= floor_loose) break;
+                floor_loose = lb_ref;
+            }
+        }
+    }
+    else
+    {
+        finalize_phase(B, T);
+        grid.sync();
+    }
+#ifndef GCR_TAIL_DEBUG
     if (stamp) B.phase_ns[2] = global_ns();
+#endif
     // Candidate rounds: one, unless more than kCandCap hypotheses sit inside the window (massive ties).  The candidate
     // counters are cumulative; every CTA tracks the bases of the current round in registers (the counters are stable
     // between the barrier after a collect phase and the next collect phase, so all CTAs read the same values).
     unsigned int cand_base = 0u, ovf_base = 0u;
     for (int round = 0;; round++)
     {
-        collect_phase(B, T, rel_tol, round, cand_base);
+        if (winner) collect_phase_w(B, T, round, cand_base, n_cont, floor_loose, direct);
+        else collect_phase(B, T, rel_tol, round, cand_base);
         grid.sync();
+#ifndef GCR_TAIL_DEBUG
         if (stamp && round == 0) B.phase_ns[3] = global_ns();
+#endif
         exact_items_phase(B, T, 1, cand_base);
         grid.sync();
+#ifndef GCR_TAIL_DEBUG
         if (stamp && round == 0) B.phase_ns[4] = global_ns();
+#endif
         // '>' (not '!='): in the last round the selecting CTA zeroes the counters while slower CTAs may still be reading
         const unsigned int cand_now = __ldcg(&B.ctr->n_candidates), ovf_now = __ldcg(&B.ctr->n_cand_overflow);
         const bool more = ovf_now > ovf_base;

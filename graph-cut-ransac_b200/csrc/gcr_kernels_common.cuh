@@ -59,8 +59,25 @@ struct Counters
     unsigned int n_sample_valid, n_solved, n_fast, n_hard;
     unsigned int n_worklist, n_worklist_overflow, n_candidates, n_cand_overflow;
     unsigned int n_bad_sample, next_item, xchg_timeout, n_sens;
-    unsigned long long best_key; // ordered bits of the best fast score among model-valid hypotheses
-    unsigned long long pad1;
+    unsigned long long best_key; // ordered bits of the best fast score among model-valid hypotheses (winner-only runs: of the best LOWER bound)
+    unsigned int n_refined;      // winner-only runs: contenders re-scored in mid precision with exact inlier decisions (k_tail)
+    unsigned int pad1;
+};
+
+constexpr int kContCap = 4096; // winner-only runs: contenders refined in mid precision per run (k_tail)
+struct ContPar // one contender: parameters of its refinement (gcr_kernels.cuh, refine_phase)
+{
+    double h7, h8, cphi, sphi;
+    float A, Tin, Tout, dpr;       // log2 alpha; |A - lg2 v| certainly in / possibly in; FP64 part of the orientation band (x 1/mx)
+    float e_s, e_o, ri_cap, band0r; // error per certain inlier's term (scale, orientation); 1/mx beyond which FP64 decides; FP32 part of the band
+    unsigned int hyp, exact;        // hypothesis; 1 = scored by the FP64 kernel already
+    unsigned int pad_[2];
+};
+struct TailState // winner-only runs: state of the contender rounds (cleared with the run counters by the last kernel)
+{
+    unsigned long long lb_ref_key; // ordered bits of the best refined lower bound
+    unsigned int n_cont, cont_overflow;
+    unsigned int unproven, pad_;   // a contender whose class values do not prove the minimal inlier counts by themselves
 };
 
 struct Scene // written by k_prep_features
@@ -87,6 +104,10 @@ struct Thresholds
     int problem;          // 0 hybrid (two_sift), 1 scale-only (three_sift), 2 scale-only "original" (three_sift_original)
     int strict;           // gcr_score_models only: inlier iff r^2 < tsq
     unsigned int min_inl[2]; // minimal sample size per class: fewer inliers than this resets the score to zero (S3)
+    // winner-only runs (gcr_score.cuh, score_chunk_w): MSAC as the truncated quadratic sum_f max(0, 1 - r_f^2 / tsq)
+    float inv_Tp;    // 1 / Tp: dq = (A - lg2 v) / Tp, scale inlier <=> |dq| <= 1
+    float pn[4];     // orientation: r^2 / tsq = z (pn0 + z (pn1 + z (pn2 + z pn3))), z = tan^2 (= pc / tsq1)
+    float sqrt_tsq1; // sqrt(tsq[1]) (error bound of the orientation class value)
 };
 
 struct Buffers
@@ -94,7 +115,9 @@ struct Buffers
     // features
     const double* scale;
     const double* orient;
-    int per_hyp;         // reporting mode: per-hypothesis scores / inlier counts are outputs (GCR_RUN_KEEP_PER_HYP / EMIT_MASKS)
+    int per_hyp;         // reporting mode: per-hypothesis scores / inlier counts are outputs (GCR_RUN_KEEP_PER_HYP / EMIT_MASKS);
+                         // 0 = winner-only run: truncated-quadratic class values, no counts / bands / worklist, invalid models unscored
+    float2* err_ab;      // winner-only runs, [H]: error bound of the FP32 class values = err_ab.x + err_ab.y * (sum of 1/mx over the orientation evaluations, cnts[2h+1] as float) + 8e-6 value
     const double* aux_s; // [ns] pow(s, 1/3) (scale-only original: pow(s, -1/3)): the solvers' per-feature column
     const double* aux_o; // [no,2] (sin, cos) of the orientation
     int ns, no;
@@ -135,6 +158,11 @@ struct Buffers
     unsigned long long* cand_qsum; // [kCandCap,2] fixed-point sums of r^2 (units of tsq 2^-44)
     unsigned int* cand_rawcnt;     // [kCandCap,2]
     unsigned int* cand_masks; // [kCandCap, W]
+    ContPar* cont_par;              // [kContCap] winner-only runs: contenders
+    unsigned long long* cont_q;     // [kContCap,2] fixed-point sums of r^2/tsq
+    unsigned int* cont_n;           // [kContCap,2] exact inlier counts
+    double* cont_val;               // [kContCap,2] refined value, error bound
+    TailState* ts;
     Counters* ctr;      // live counters of the run in flight
     Counters* ctr_snap; // snapshot for the host, written by the last kernel
     unsigned long long* phase_ns; // [8] %globaltimer at the phase boundaries of k_tail

@@ -64,6 +64,8 @@ struct HypRegs
     bool active;      // ring kernel
     double sum_s, sum_o;
     unsigned int cnt_s, cnt_o;
+    float rimax; // winner-only runs: sum over the orientation chunks of (largest 1 / max(|c'|, |s'|) of the chunk's evaluations) x (features of a
+                 // chunk), an upper bound of the sum of 1 / max over all orientation evaluations (scales the class value's error bound)
 };
 
 struct Verdict
@@ -349,6 +351,162 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Winner-only runs (no per-hypothesis outputs asked for): the class value of MSAC is evaluated as the truncated quadratic
+//     value_i = n_i - sum_inl r^2 / tsq_i = sum_f max(0, 1 - r_f^2 / tsq_i)          (MSAC_scoring_function.hpp:22-51,93-125)
+// which is CONTINUOUS at the threshold: no inlier decision is taken here, so there is no guard band, no worklist and no count; an
+// FP32 evaluation error moves the value by at most 2.1 (delta r) / sqrt(tsq) per feature near or inside the threshold (bound per
+// hypothesis in k_sample_solve + the largest 1 / max met here).  The selection then re-scores every hypothesis whose
+// upper bound reaches the best lower bound in FP64 reference order (counts, masks and the reference's value come from there), so the
+// selected model is the reference's.  Per evaluation: scale 2 FFMA + MUFU.LG2 + FFMA + FFMA.SAT + 1/2 FADD2, orientation 6 FFMA/FMUL
+// + FMNMX + FMNMX3.NAN + MUFU.RCP + 2 FMUL + 2-3 FFMA + FFMA.SAT + 1/2 FADD2 + 1/2 FMNMX3 (the FP32 tiles' scale FMAs as FFMA2 pairs).
+__device__ __forceinline__ float fma_sat(float a, float b, float c) // saturating FMA: clamps to [0, 1], NaN -> 0 (SASS FFMA.SAT)
+{
+    float r;
+    asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+    return r;
+}
+__device__ __forceinline__ float fmax_nan(float a, float b) // NaN-propagating maximum (SASS FMNMX[3].NAN)
+{
+    float r;
+    asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+    return r;
+}
+
+#ifndef GCR_RCP2
+#define GCR_RCP2 1
+#endif
+template <bool PRECISE, int CLS, bool RANGE = false>
+__device__ __forceinline__ void score_chunk_w(const Thresholds& T, const float* stage, HypRegs (&H)[kHB], int g0r = 0, int g1r = 0)
+{
+    constexpr int G = PRECISE ? 2 : 4;               // features per group
+    constexpr int NF = PRECISE ? kChunk / 2 : kChunk; // features per chunk
+    float2 acc[kHB];                                  // two FP32 partial sums per hypothesis (even / odd features), flushed per chunk
+    float rim[kHB];                                   // largest 1 / max of this chunk's orientation evaluations
+#pragma unroll
+    for (int j = 0; j < kHB; j++)
+    {
+        acc[j] = make_float2(0.f, 0.f);
+        rim[j] = 0.f;
+    }
+    const int g0 = RANGE ? g0r : 0, g1 = RANGE ? g1r : NF / G;
+    for (int gb = g0; gb < g1; gb += kScoreUnroll)
+#pragma unroll
+    for (int u = 0; u < kScoreUnroll; u++)
+    {
+        const int g = gb + u;
+        float fa[4], fb[4], fc[4]; // the group's three plane values as FP32 (precise tiles: filled below, per hypothesis)
+        double da[2], db[2], dc[2];
+        if constexpr (PRECISE)
+        {
+            const double2 a = reinterpret_cast<const double2*>(stage)[g];
+            const double2 b = reinterpret_cast<const double2*>(stage + 2 * NF)[g];
+            const double2 c = reinterpret_cast<const double2*>(stage + 4 * NF)[g];
+            da[0] = a.x; da[1] = a.y; db[0] = b.x; db[1] = b.y; dc[0] = c.x; dc[1] = c.y;
+        }
+        else
+        {
+            const float4 a = reinterpret_cast<const float4*>(stage)[g];
+            const float4 b = reinterpret_cast<const float4*>(stage + NF)[g];
+            const float4 c = reinterpret_cast<const float4*>(stage + 2 * NF)[g];
+            fa[0] = a.x; fa[1] = a.y; fa[2] = a.z; fa[3] = a.w;
+            fb[0] = b.x; fb[1] = b.y; fb[2] = b.z; fb[3] = b.w;
+            fc[0] = c.x; fc[1] = c.y; fc[2] = c.z; fc[3] = c.w;
+        }
+#pragma unroll
+        for (int j = 0; j < kHB; j++)
+        {
+#pragma unroll
+            for (int e = 0; e < G; e += 2)
+            {
+                float2 gq; // the pair's two contributions max(0, 1 - r^2 / tsq)
+                if constexpr (CLS == 0)
+                {
+                    float2 v;
+                    if constexpr (PRECISE)
+                        v = make_float2(static_cast<float>(fma(-H[j].h8d, db[e], fma(-H[j].h7d, da[e], dc[e]))),
+                                        static_cast<float>(fma(-H[j].h8d, db[e + 1], fma(-H[j].h7d, da[e + 1], dc[e + 1]))));
+                    else
+                        v = __ffma2_rn(make_float2(H[j].nh8, H[j].nh8), make_float2(fb[e], fb[e + 1]),
+                                       __ffma2_rn(make_float2(H[j].nh7, H[j].nh7), make_float2(fa[e], fa[e + 1]), make_float2(fc[e], fc[e + 1])));
+                    const float2 L = make_float2(lg2_approx(v.x), lg2_approx(v.y));
+                    // dq = (A - lg2 v) / Tp in one rounding: H.A holds A / Tp here (k_sample_solve)
+                    const float2 dq = __ffma2_rn(L, make_float2(-T.inv_Tp, -T.inv_Tp), make_float2(H[j].A, H[j].A));
+                    gq = make_float2(fma_sat(-dq.x, dq.x, 1.0f), fma_sat(-dq.y, dq.y, 1.0f));
+                }
+                else
+                {
+                    float n[2], d[2], ri[2];
+#pragma unroll
+                    for (int q = 0; q < 2; q++)
+                    {
+                        if constexpr (PRECISE)
+                        {
+                            n[q] = static_cast<float>(fma(da[e + q], -H[j].h7d, db[e + q])); // sin - k h7
+                            d[q] = static_cast<float>(fma(da[e + q], H[j].h8d, dc[e + q]));  // cos + k h8
+                        }
+                        else
+                        {
+                            n[q] = fmaf(fa[e + q], H[j].nh7, fb[e + q]);
+                            d[q] = fmaf(-fa[e + q], H[j].nh8, fc[e + q]);
+                        }
+                    }
+                    float gg[2], mn[2], mx[2];
+#pragma unroll
+                    for (int q = 0; q < 2; q++)
+                    {
+                        const float c1 = fmaf(n[q], H[j].sphi, d[q] * H[j].cphi);
+                        const float s1 = fmaf(n[q], H[j].cphi, -(d[q] * H[j].sphi));
+                        const float a1 = fabsf(c1), a2 = fabsf(s1);
+                        // NaN-propagating maximum: a padding / irregular feature (NaN sine) gives ri = NaN, which the value (FFMA.SAT: NaN -> 0) and
+                        // the running maximum below both ignore; an exact 0/0 of a real feature gives ri ~ 1e18, i.e. an unbounded error bound,
+                        // and the hypothesis is then re-scored in FP64 whatever its value
+                        mn[q] = fminf(a1, a2);
+                        mx[q] = fmax_nan(fmax_nan(a1, a2), 1e-18f);
+                    }
+                    if constexpr (GCR_RCP2 && !RANGE)
+                    {
+                    // ONE reciprocal for the pair: 1/mx0 = mx1 / (mx0 mx1), 1/mx1 = mx0 / (mx0 mx1): the XU pipe (16 lanes per clock and SM) is
+                    // what bounds this kernel, an FMUL is 8 times cheaper.  Padding / irregular features come in aligned pairs (k_prep_features),
+                    // so a NaN never reaches a real feature's reciprocal.  mx in [1e-18, 1e6]: the product stays inside the FP32 range.
+                    const float rp = rcp_approx(mx[0] * mx[1]);
+                    ri[0] = rp * mx[1];
+                    ri[1] = rp * mx[0];
+                    }
+                    else // the resident kernel (one 1024-thread CTA per SM, small scenes) measured 6 % faster at C2 with two reciprocals
+                    {
+                        ri[0] = rcp_approx(mx[0]);
+                        ri[1] = rcp_approx(mx[1]);
+                    }
+#pragma unroll
+                    for (int q = 0; q < 2; q++)
+                    {
+                        const float t = mn[q] * ri[q];
+                        const float z = t * t;
+                        float h;
+                        if (T.poly_deg == 2) h = fmaf(fmaf(T.pn[2], z, T.pn[1]), z, T.pn[0]); // uniform branch (kernel parameter)
+                        else h = fmaf(fmaf(fmaf(T.pn[3], z, T.pn[2]), z, T.pn[1]), z, T.pn[0]);
+                        gg[q] = fma_sat(-z, h, 1.0f);
+                    }
+                    gq = make_float2(gg[0], gg[1]);
+                    rim[j] = fmaxf(fmaxf(rim[j], ri[0]), ri[1]);
+                }
+                acc[j] = __fadd2_rn(acc[j], gq);
+            }
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < kHB; j++)
+    {
+        if (CLS == 0) H[j].sum_s += static_cast<double>(acc[j].x) + static_cast<double>(acc[j].y);
+        else
+        {
+            H[j].sum_o += static_cast<double>(acc[j].x) + static_cast<double>(acc[j].y);
+            H[j].rimax += rim[j] * static_cast<float>((g1 - g0) * G); // (round-off of this sum: 1e-7 relative, inside the bound's own margins)
+        }
+    }
+}
+
 // Hypothesis parameters of the kHB hypotheses of a thread: compact index first_compact + j * stride + lane_in_tile of the FP32
 // list (from the front of the compact arrays) or of the precise list (from the back).
 template <bool PRECISE, bool SENTINEL = false>
@@ -377,12 +535,13 @@ __device__ __forceinline__ void load_hyps(const Buffers& B, HypRegs (&H)[kHB], i
         }
         H[j].sum_s = H[j].sum_o = 0.0;
         H[j].cnt_s = H[j].cnt_o = 0u;
+        H[j].rimax = 0.f;
     }
 }
 
 // Partial sums / counts of a thread's hypotheses into the per-hypothesis arrays: plain stores when this item covered every
 // feature, atomics when the feature range is split over several items.
-template <bool SENTINEL = false>
+template <bool SENTINEL = false, bool WINNER = false>
 __device__ __forceinline__ void flush_hyps(const Buffers& B, const Thresholds& T, HypRegs (&H)[kHB], bool single_split)
 {
 #pragma unroll
@@ -390,6 +549,23 @@ __device__ __forceinline__ void flush_hyps(const Buffers& B, const Thresholds& T
     {
         if (SENTINEL ? H[j].hyp == kNoHyp : !H[j].active) continue;
         const size_t h = H[j].hyp;
+        if constexpr (WINNER)
+        {
+            // class values (sums) and the bound of the sum of 1 / max over the orientation evaluations (a float in cnts[2h + 1])
+            if (single_split)
+            {
+                B.sums[2 * h] = H[j].sum_s;
+                B.sums[2 * h + 1] = H[j].sum_o;
+                B.cnts[2 * h + 1] = __float_as_uint(H[j].rimax);
+            }
+            else
+            {
+                if (H[j].sum_s != 0.0) atomicAdd(&B.sums[2 * h], H[j].sum_s);
+                if (H[j].sum_o != 0.0) atomicAdd(&B.sums[2 * h + 1], H[j].sum_o);
+                if (H[j].rimax > 0.f) atomicAdd(reinterpret_cast<float*>(&B.cnts[2 * h + 1]), H[j].rimax);
+            }
+            continue;
+        }
         const double ss = H[j].sum_s * static_cast<double>(T.scale_unit);
         if (single_split)
         {
@@ -414,53 +590,105 @@ __device__ __forceinline__ void flush_hyps(const Buffers& B, const Thresholds& T
     }
 }
 
-// One work item: all chunks [c_begin, c_end) of this tile flavour's chunk list, scale class first.
-template <bool MASKS, bool PRECISE>
+// Position in a tile flavour's chunk list -> (class, chunk of that class).  GCR_INTERLEAVE=1 (default) spreads the orientation chunks evenly
+// among the scale chunks (Bresenham), so that every work item -- and, with items of many CTAs in flight, every SM at every moment -- carries
+// the scene's mix of the two evaluation kinds: the scale evaluation is bound by the XU pipe (one MUFU per ~5 issue slots), the orientation
+// evaluation by issue slots (one MUFU per ~16); side by side they fill both.  0: all scale chunks, then all orientation chunks.
+#ifndef GCR_INTERLEAVE
+#define GCR_INTERLEAVE 1
+#endif
+struct ChunkWalk // consecutive positions of the list, one division at the start (a 64-bit division per chunk cost ~10 % of a chunk's instructions)
+{
+    int ncs, nco, pos, o, acc; // o = floor(pos * nco / n), acc = (pos * nco) mod n
+    __device__ __forceinline__ ChunkWalk(int ncs_, int nco_, int p) : ncs(ncs_), nco(nco_), pos(p)
+    {
+        const unsigned long long t = static_cast<unsigned long long>(p) * static_cast<unsigned int>(nco_);
+        const unsigned int n = static_cast<unsigned int>(ncs_ + nco_);
+        o = static_cast<int>(t / n);
+        acc = static_cast<int>(t - static_cast<unsigned long long>(o) * n);
+    }
+    // class and chunk-of-class of the current position; advances
+    __device__ __forceinline__ int next(bool& orient)
+    {
+#if GCR_INTERLEAVE
+        acc += nco;
+        orient = acc >= ncs + nco;
+        const int ci = orient ? o : pos - o;
+        if (orient)
+        {
+            acc -= ncs + nco;
+            o++;
+        }
+        pos++;
+        return ci;
+#else
+        orient = pos >= ncs;
+        const int ci = orient ? pos - ncs : pos;
+        pos++;
+        return ci;
+#endif
+    }
+};
+
+// One work item: all chunks [c_begin, c_end) of this tile flavour's chunk list.
+// MODE: 0 winner-only (score_chunk_w), 1 per-hypothesis counts and sums (score_chunk), 2 as 1 + packed inlier masks of every hypothesis
+template <int MODE, bool PRECISE>
 __device__ __forceinline__ void score_item(const Buffers& B, const Thresholds& T, ScoreSmem& S, uint32_t& ring,
                                            int first_compact, int n_list, bool from_back, int c_begin, int c_end,
                                            bool single_split)
 {
     const int tid = threadIdx.x, lane = tid & 31;
-    const int ncs = PRECISE ? B.ncsd : B.ncs;
+    const int ncs = PRECISE ? B.ncsd : B.ncs, nco_list = PRECISE ? B.ncod : B.nco;
     const float* base_s = PRECISE ? reinterpret_cast<const float*>(B.fsd) : B.fs;
     const float* base_o = PRECISE ? reinterpret_cast<const float*>(B.fod) : B.fo;
     constexpr int NF = PRECISE ? kChunk / 2 : kChunk;
     const int nch = c_end - c_begin;
 
-    auto issue = [&](uint32_t n, int chunk) {
+    ChunkWalk produce(ncs, nco_list, c_begin), consume(ncs, nco_list, c_begin); // the producer runs kStages - 1 chunks ahead
+    auto issue = [&](uint32_t n) {
         if (tid == 0)
         {
             const uint32_t st = n % kStages;
             if (n >= kStages) mbar_wait(&S.empty[st], ((n / kStages) - 1) & 1);
-            const float* src = chunk < ncs ? base_s + static_cast<size_t>(chunk) * kChunkFloats
-                                           : base_o + static_cast<size_t>(chunk - ncs) * kChunkFloats;
+            bool orient;
+            const int ci = produce.next(orient);
+            const float* src = orient ? base_o + static_cast<size_t>(ci) * kChunkFloats : base_s + static_cast<size_t>(ci) * kChunkFloats;
             mbar_expect_tx(&S.full[st], kChunkBytes);
             tma_load_1d(S.stage[st], src, kChunkBytes, &S.full[st]);
         }
     };
-    for (int p = 0; p < min(kStages - 1, nch); p++) issue(ring + p, c_begin + p);
+    for (int p = 0; p < min(kStages - 1, nch); p++) issue(ring + p);
 
     HypRegs H[kHB];
     load_hyps<PRECISE>(B, H, first_compact, kScoreThreads, tid, n_list, from_back);
 
     for (int i = 0; i < nch; i++)
     {
-        if (i + kStages - 1 < nch) issue(ring + i + kStages - 1, c_begin + i + kStages - 1);
+        if (i + kStages - 1 < nch) issue(ring + i + kStages - 1);
         const uint32_t n = ring + i;
         const uint32_t st = n % kStages;
         mbar_wait(&S.full[st], (n / kStages) & 1);
-        const int chunk = c_begin + i;
-        if (chunk < ncs) score_chunk<MASKS, PRECISE, 0>(B, T, S.stage[st], chunk * NF, H);
-        else score_chunk<MASKS, PRECISE, 1>(B, T, S.stage[st], (chunk - ncs) * NF, H);
+        bool orient;
+        const int ci = consume.next(orient);
+        if constexpr (MODE == 0)
+        {
+            if (!orient) score_chunk_w<PRECISE, 0>(T, S.stage[st], H);
+            else score_chunk_w<PRECISE, 1>(T, S.stage[st], H);
+        }
+        else
+        {
+            if (!orient) score_chunk<MODE == 2, PRECISE, 0>(B, T, S.stage[st], ci * NF, H);
+            else score_chunk<MODE == 2, PRECISE, 1>(B, T, S.stage[st], ci * NF, H);
+        }
         __syncwarp();
         if (lane == 0) mbar_arrive(&S.empty[st]);
     }
     ring += nch;
 
-    flush_hyps(B, T, H, single_split);
+    flush_hyps<false, MODE == 0>(B, T, H, single_split);
 }
 
-template <bool MASKS>
+template <int MODE>
 __global__ void __launch_bounds__(kScoreThreads, GCR_MINB) k_score_fast(const __grid_constant__ Buffers B,
                                                               const __grid_constant__ Thresholds T)
 {
@@ -513,13 +741,13 @@ __global__ void __launch_bounds__(kScoreThreads, GCR_MINB) k_score_fast(const __
         {
             const int k = item - items_b;
             const int split = splits_a - 1 - k / tiles_a, tile = k % tiles_a;
-            score_item<MASKS, false>(B, T, S, ring, tile * kTileHyps, n_fast, false, split * cps_a,
+            score_item<MODE, false>(B, T, S, ring, tile * kTileHyps, n_fast, false, split * cps_a,
                                      min(chunks_a, (split + 1) * cps_a), splits_a == 1);
         }
         else
         {
             const int split = splits_b - 1 - item / tiles_b, tile = item % tiles_b;
-            score_item<MASKS, true>(B, T, S, ring, tile * kTileHyps, n_sens, true, split * cps_b,
+            score_item<MODE, true>(B, T, S, ring, tile * kTileHyps, n_sens, true, split * cps_b,
                                     min(chunks_b, (split + 1) * cps_b), splits_b == 1);
         }
         GCR_STAMP(tr);
@@ -554,7 +782,7 @@ struct ResidentPlan // identical in every warp (pure function of the counters an
     }
 };
 
-template <bool MASKS, bool PRECISE>
+template <int MODE, bool PRECISE>
 __device__ __forceinline__ void resident_task(const Buffers& B, const Thresholds& T, const float* sm_s, const float* sm_o,
                                               const ResidentPlan& P, int tile, int b0, int b1, int n_list,
                                               uint64_t* bar_s, uint64_t* bar_o)
@@ -571,8 +799,11 @@ __device__ __forceinline__ void resident_task(const Buffers& B, const Thresholds
         for (int b = b0; b < s1;)
         {
             const int chunk = b / BPC, be = min(s1, (chunk + 1) * BPC);
-            score_chunk<MASKS, PRECISE, 0, true>(B, T, sm_s + chunk * kChunkFloats, chunk * NF, H, (b - chunk * BPC) * GPB,
-                                                 (be - chunk * BPC) * GPB);
+            if constexpr (MODE == 0)
+                score_chunk_w<PRECISE, 0, true>(T, sm_s + chunk * kChunkFloats, H, (b - chunk * BPC) * GPB, (be - chunk * BPC) * GPB);
+            else
+                score_chunk<MODE == 2, PRECISE, 0, true>(B, T, sm_s + chunk * kChunkFloats, chunk * NF, H, (b - chunk * BPC) * GPB,
+                                                         (be - chunk * BPC) * GPB);
             b = be;
         }
     }
@@ -583,15 +814,18 @@ __device__ __forceinline__ void resident_task(const Buffers& B, const Thresholds
         for (int b = o0; b < o1;)
         {
             const int chunk = b / BPC, be = min(o1, (chunk + 1) * BPC);
-            score_chunk<MASKS, PRECISE, 1, true>(B, T, sm_o + chunk * kChunkFloats, chunk * NF, H, (b - chunk * BPC) * GPB,
-                                                 (be - chunk * BPC) * GPB);
+            if constexpr (MODE == 0)
+                score_chunk_w<PRECISE, 1, true>(T, sm_o + chunk * kChunkFloats, H, (b - chunk * BPC) * GPB, (be - chunk * BPC) * GPB);
+            else
+                score_chunk<MODE == 2, PRECISE, 1, true>(B, T, sm_o + chunk * kChunkFloats, chunk * NF, H, (b - chunk * BPC) * GPB,
+                                                         (be - chunk * BPC) * GPB);
             b = be;
         }
     }
-    flush_hyps<true>(B, T, H, b0 == 0 && b1 == P.nbs + P.nbo); // plain stores when this warp covered the whole tile
+    flush_hyps<true, MODE == 0>(B, T, H, b0 == 0 && b1 == P.nbs + P.nbo); // plain stores when this warp covered the whole tile
 }
 
-template <bool MASKS>
+template <int MODE>
 __global__ void __launch_bounds__(kResidentThreads, 1) k_score_resident(const __grid_constant__ Buffers B,
                                                                         const __grid_constant__ Thresholds T,
                                                                         const int cost_o, const int cost_p)
@@ -651,8 +885,8 @@ __global__ void __launch_bounds__(kResidentThreads, 1) k_score_resident(const __
         const int b0 = P.block_at(off0 * P.total / len), b1 = P.block_at(off1 * P.total / len);
         if (b0 < b1)
         {
-            if (precise) resident_task<MASKS, true>(B, T, sm_fsd, sm_fod, P, tile, b0, b1, n_sens, &bars[2], &bars[2]);
-            else resident_task<MASKS, false>(B, T, sm_fs, sm_fo, P, tile, b0, b1, n_fast, &bars[0], &bars[1]);
+            if (precise) resident_task<MODE, true>(B, T, sm_fsd, sm_fod, P, tile, b0, b1, n_sens, &bars[2], &bars[2]);
+            else resident_task<MODE, false>(B, T, sm_fs, sm_fo, P, tile, b0, b1, n_fast, &bars[0], &bars[1]);
         }
         pos += off1 - off0;
         GCR_STAMP(tr);

@@ -16,6 +16,7 @@ LIB_PATH = os.environ.get("GCR_B200_LIB", os.path.join(PKG_DIR, "libgcr_b200.so"
 
 FLAG_SAMPLE_VALID, FLAG_SOLVED, FLAG_MODEL_VALID, FLAG_EXACT = 1, 2, 4, 8
 RUN_EMIT_MASKS, RUN_SAMPLES_ON_DEVICE, RUN_KEEP_PER_HYP, RUN_ALL_EXACT, RUN_EXCHANGE, RUN_TIME_KERNELS = 1, 2, 4, 8, 16, 32
+FEATURES_ON_DEVICE, FEATURES_HOST_LIBM = 1, 2
 IPC_HANDLE_BYTES = 64
 PROBLEM_HYBRID, PROBLEM_SCALE_ONLY, PROBLEM_SCALE_ONLY_ORIGINAL = 0, 1, 2
 ERR_INVALID, ERR_CUDA, ERR_STATE, ERR_NOMEM = -1, -2, -3, -4
@@ -38,6 +39,7 @@ class GcrResult(C.Structure):
         ("score_kernel_ms", C.c_float), ("winner_rank", C.c_int32), ("score_kernel", C.c_int32),
         ("tail_phase_us", C.c_float * 6),
         ("stage_phase_us", C.c_float * 2),
+        ("n_refined", C.c_int64),
         ("n_scored", C.c_int64),
     ]
 
@@ -131,8 +133,9 @@ class Engine:
         self.problem = problem
         self.ns = self.no = 0
 
-    def set_features(self, scale: np.ndarray, orient: np.ndarray = None):
-        """Host float64 [N,3] arrays (copied to the device inside the call); orient=None for scale-only problems."""
+    def set_features(self, scale: np.ndarray, orient: np.ndarray = None, host_libm: bool = False):
+        """Host float64 [N,3] arrays (copied to the device inside the call); orient=None for scale-only problems.
+        host_libm: GCR_FEATURES_HOST_LIBM, the bit-exact replay mode (solver columns evaluated by the host's C library)."""
         scale = np.ascontiguousarray(scale, np.float64)
         if orient is None:
             orient = np.zeros((0, 3))
@@ -143,7 +146,7 @@ class Engine:
         self.ns, self.no = len(scale), len(orient)
         self.fetch_ns, self.fetch_no = self.ns, self.no
         self._check(self.lib.gcr_set_features(self.h, scale.ctypes.data, self.ns, orient.ctypes.data if self.no else None,
-                                              self.no, 0))
+                                              self.no, FEATURES_HOST_LIBM if host_libm else 0))
 
     def set_keypoints(self, keypoints=None, device_ptr: int = None, n: int = None, is_f32: bool = None, want_sizes=True):
         """Keypoint rows (x, y, size, angle_deg) -> resident scale / orientation features (examples/utils.py:5-49 on the

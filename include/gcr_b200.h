@@ -47,6 +47,7 @@ enum gcr_status
 #define GCR_FLAG_SOLVED 2u       /* estimateMinimalModel produced a model */
 #define GCR_FLAG_MODEL_VALID 4u  /* isValidModel (max(|h7|,|h8|) < 1e-3) */
 #define GCR_FLAG_EXACT 8u        /* scored entirely in FP64 (outside the FP32 fast path's proven range) */
+/* (bits 16 and 32 are internal to the selection: deferred candidate; contender of a winner-only run) */
 
 /* gcr_run flags */
 #define GCR_RUN_EMIT_MASKS 1u        /* keep the packed inlier mask of EVERY hypothesis (parity / replay mode) */
@@ -76,6 +77,8 @@ typedef struct gcr_result
     int32_t score_kernel;   /* which scoring kernel ran: 0 = k_score_fast (TMA ring), 1 = k_score_resident (working set in shared memory) */
     float tail_phase_us[6]; /* diagnostics (device timer): fix-up+FP64 items | finalize | collect | candidate re-scoring | select | start of the scoring kernel -> start of the tail */
     float stage_phase_us[2]; /* diagnostics (device timer): start of the sampler/solver kernel -> start of the scoring kernel | -> end of the tail */
+    int64_t n_refined;      /* winner-only runs: contenders (upper bound of the FP32 value >= best lower bound) re-scored in mid precision with
+                             * exact inlier decisions before the FP64 candidates were chosen; 0 in the reporting modes */
     int64_t n_scored;       /* hypotheses scored against every feature (FP32 tiles + precise tiles + FP64 list); == n_solved in the reporting
                              * modes, fewer in winner-only runs, which skip models that isValidModel rejects (they can never be selected) */
 } gcr_result;
@@ -128,10 +131,24 @@ int gcr_set_problem(gcr_handle h, int problem);
 /* Use `cuda_stream` (a cudaStream_t) for all subsequent work; NULL restores the engine's own stream. */
 int gcr_set_stream(gcr_handle h, void* cuda_stream);
 
-/* Upload (or adopt from device memory when on_device != 0) the two feature classes and build the
- * FP32 structure-of-arrays working set.  Replaces the cv::Mat construction of
- * gcransac_python.cpp:284-296.  Requires ns >= 2 and no >= 2 (bindings.cpp:199-224). */
-int gcr_set_features(gcr_handle h, const double* scale, int64_t ns, const double* orient, int64_t no, int on_device);
+/* Upload (or, with GCR_FEATURES_ON_DEVICE, adopt from device memory) the two feature classes and build the FP32
+ * structure-of-arrays working set.  Replaces the cv::Mat construction of gcransac_python.cpp:284-296.  Requires ns >= 2 and
+ * no >= 2 (bindings.cpp:199-224).  `where` is a flags word:
+ *   0                         host arrays.  Pageable memory is copied before the call returns.  PAGE-LOCKED (device-mapped) arrays are
+ *                             read IN PLACE by the preparation kernel after the call has returned: the caller must leave them untouched
+ *                             until the next synchronising call on this handle (gcr_run with out != NULL, gcr_best, gcr_fetch, ...),
+ *                             as with any cudaMemcpyAsync from pinned memory.  The same holds for pinned `samples` of gcr_run.
+ *   GCR_FEATURES_ON_DEVICE    device pointers (16-byte aligned), adopted without a copy: the caller keeps them alive and unchanged for
+ *                             as long as the engine runs on them, and orders their producer before this call on the engine's stream
+ *                             (gcr_set_stream) or by an event.
+ *   GCR_FEATURES_HOST_LIBM    host arrays only: bit-exact replay mode.  The minimal solvers' per-feature transcendental columns
+ *                             (pow(s, 1/3): two_sift.hpp:288-299; sin / cos of the orientation: math_utils.hpp:104-109) are evaluated by
+ *                             the host's C library -- the functions the reference itself calls -- instead of the device's, so that
+ *                             isValidSample's answer is the reference's bit for bit even where it hangs on the last ulp of sin / cos
+ *                             (two orientation samples at one position).  Costs ns + no host transcendentals; synchronises. */
+#define GCR_FEATURES_ON_DEVICE 1
+#define GCR_FEATURES_HOST_LIBM 2
+int gcr_set_features(gcr_handle h, const double* scale, int64_t ns, const double* orient, int64_t no, int where);
 
 /* ---- multi-GPU winner exchange over peer memory (NVLink / NVSwitch), one engine per GPU -----------------------------
  * The path's only exchange step is "which rank holds the best model" (the reference is single-process; this is its
@@ -169,7 +186,10 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
             const double thr[2], uint32_t flags, void* d_record, gcr_result* out);
 
 /* Selected model of the last gcr_run: model, score, counts and packed masks (any pointer may be NULL).
- * Synchronises the stream.  *hyp_index = -1 and zeroed outputs when no model was found. */
+ * Synchronises the stream.  *hyp_index = -1 and zeroed outputs when no model was found.
+ * Device-side failures of the run -- replayed sample indices out of range (GCR_ERR_INVALID), guard-band worklist overflow or a winner
+ * exchange that timed out (GCR_ERR_STATE) -- are reported here (and by gcr_fetch) also when the run itself was asynchronous
+ * (gcr_run with out == NULL), from the counter snapshot the run's last kernel leaves in the result block. */
 int gcr_best(gcr_handle h, double model[4], double* score, uint32_t n_inl[2], uint32_t* scale_mask_words,
              uint32_t* orient_mask_words, int64_t* hyp_index);
 

@@ -32,7 +32,7 @@ def test_header_symbols_are_exported(lib):
 def test_version_and_struct_layout(lib):
     import gcr_capi
     assert b"sm_100a" in lib.gcr_version()
-    assert ctypes.sizeof(gcr_capi.GcrResult) == 8 + 8 + 32 + 8 + 8 + 6 * 8 + 8 + 8 + 24 + 8 + 8
+    assert ctypes.sizeof(gcr_capi.GcrResult) == 8 + 8 + 32 + 8 + 8 + 6 * 8 + 8 + 8 + 24 + 8 + 8 + 8
     assert gcr_capi.RECORD_DTYPE.itemsize == 64
 
 

@@ -40,9 +40,9 @@ def _compare(dev, ora, ns, no, check_masks=True, label=""):
             f"{label}: masks differ in hypotheses {np.nonzero((dev['masks'] != ora['masks']).any(1))[0][:10]}")
 
 
-def _run_replay(eng, scale, orient, samples, thr, masks=True, extra_flags=0):
+def _run_replay(eng, scale, orient, samples, thr, masks=True, extra_flags=0, host_libm=False):
     import gcr_capi
-    eng.set_features(scale, orient)
+    eng.set_features(scale, orient, host_libm=host_libm)
     flags = (gcr_capi.RUN_EMIT_MASKS if masks else gcr_capi.RUN_KEEP_PER_HYP) | extra_flags
     res = eng.run(len(samples), thr, samples=samples, flags=flags)
     dev = eng.fetch(masks=masks)
@@ -109,6 +109,34 @@ def test_replay_matches_reference_golden(eng, golden_dir, name):
     _compare(dev, ora, len(g["scale"]), len(g["orient"]), label=name)
     if not tie[int(g["best"])]:
         assert res.best_index == int(g["best"])
+
+
+def test_edge_golden_bit_exact_replay_mode_no_skipped_slots(eng, golden_dir, port):
+    """GCR_FEATURES_HOST_LIBM (include/gcr_b200.h): the solvers' per-feature columns sin / cos (math_utils.hpp:104-109) and
+    pow(s, 1/3) (two_sift.hpp:288-299) come from the host's C library, so isValidSample (two_sift.hpp:141-215) runs on the reference's
+    own inputs: EVERY slot of the edge fixture is compared, including the ones whose two orientation samples share a position
+    (vanishing point on a vertex of the sample hull), and so is the selected hypothesis."""
+    g = np.load(os.path.join(golden_dir, "hyp_stage_edge.npz"))
+    res, dev = _run_replay(eng, g["scale"], g["orient"], g["samples"], g["thr"], host_libm=True)
+    ora = {k: g[k] for k in ("flags", "models", "score", "n_inl", "masks")}
+    o = g["orient"][g["samples"][:, 2:]]
+    tie = (o[:, 0, 0] == o[:, 1, 0]) & (o[:, 0, 1] == o[:, 1, 1])
+    assert tie.sum() >= 1  # the fixture does hold such slots
+    _compare(dev, ora, len(g["scale"]), len(g["orient"]), label="edge, host-libm columns")
+    assert res.best_index == int(g["best"])
+    # exactly-zero thresholds under the same mode: flags of every slot, and the models they yield
+    import gcr_scenes as gs
+    sc = gs.make_scene(100, 50, 0.5, 1)
+    smp = gs.draw_samples(64, 100, 50, 2)
+    smp[5, 3] = smp[5, 2] ^ 1  # plus a few slots with the knife edge planted: the second orientation sample moved onto the first one's position
+    orient = sc.orient.copy()
+    orient[smp[5, 3], :2] = orient[smp[5, 2], :2]
+    thr = np.array([0.0, 0.0])
+    ora = port.replay(sc.scale, orient, smp, thr)
+    _, dev = _run_replay(eng, sc.scale, orient, smp, thr, host_libm=True)
+    assert np.array_equal(dev["flags"] & 7, ora["flags"])
+    ok = (ora["flags"] & 2) > 0
+    assert np.allclose(dev["models"][ok], ora["models"][ok], rtol=MODEL_RTOL, atol=1e-12)
 
 
 def test_threshold_sweep_matches_reference_golden(eng, golden_dir):
@@ -250,6 +278,47 @@ def test_minimal_and_ragged_inputs(eng, port):
     ora = port.replay(sc.scale, sc.orient, smp, thr)
     _, dev = _run_replay(eng, sc.scale, sc.orient, smp, thr)
     _compare(dev, ora, 100, 50, label="loose thr")
+
+
+def test_asynchronous_runs_report_device_side_failures(port):
+    """gcr_run with out == NULL (asynchronous) cannot report what its kernels find; gcr_best / gcr_fetch must (GCRANSAC.h:222-228: the
+    reference throws rather than continue): a guard-band worklist overflow (forced with a one-slot worklist) and replayed sample
+    indices out of range."""
+    import gcr_capi
+    import gcr_scenes as gs
+    os.environ["GCR_WORKLIST_CAP"] = "1"
+    try:
+        e = gcr_capi.Engine(0)
+    finally:
+        del os.environ["GCR_WORKLIST_CAP"]
+    sc = gs.make_scene(2000, 500, 0.3, 3)
+    smp = gs.draw_samples(20_000, 2000, 500, 4)
+    e.set_features(sc.scale, sc.orient)
+    e.run(len(smp), sc.thr, samples=smp, flags=gcr_capi.RUN_EMIT_MASKS, sync=False)
+    with pytest.raises(gcr_capi.GcrError) as ei:
+        e.best()
+    assert ei.value.code == gcr_capi.ERR_STATE and "overflow" in str(ei.value)
+    e.run(len(smp), sc.thr, samples=smp, flags=gcr_capi.RUN_EMIT_MASKS, sync=False)
+    with pytest.raises(gcr_capi.GcrError):
+        e.fetch(masks=True)
+    with pytest.raises(gcr_capi.GcrError):  # the synchronous form reports it itself
+        e.run(len(smp), sc.thr, samples=smp, flags=gcr_capi.RUN_EMIT_MASKS)
+    # a winner-only run has no guard bands, hence no worklist to overflow
+    res = e.run(len(smp), sc.thr, samples=smp)
+    ora = port.replay(sc.scale, sc.orient, smp, sc.thr, want_masks=False, nthreads=0)
+    assert res.best_index == port.select_best(ora["score"], ora["flags"])
+    e.close()
+    e = gcr_capi.Engine(0)
+    e.set_features(sc.scale, sc.orient)
+    bad = smp[:1000].copy()
+    bad[17, 2] = 500
+    e.run(len(bad), sc.thr, samples=bad, sync=False)
+    with pytest.raises(gcr_capi.GcrError) as ei:
+        e.best()
+    assert ei.value.code == gcr_capi.ERR_INVALID
+    e.run(1000, sc.thr, samples=smp[:1000], sync=False)  # and the next run is clean again
+    assert e.best()["index"] >= 0
+    e.close()
 
 
 def test_error_conventions(eng):

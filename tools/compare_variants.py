@@ -13,13 +13,15 @@ for lib in libs:
     gcr_capi.LIB_PATH = os.path.join(ROOT, lib)
     e = gcr_capi.Engine(0); e.set_features(sc.scale, sc.orient); engines.append(e)
 res = {lib: ([], []) for lib in libs}
+win = {}
 flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda") if os.environ.get("FLUSH") else None  # > L2: cold caches per run, as bench.py
 for rnd in range(12):
     for lib, e in zip(libs, engines):
         if flush is not None: flush.zero_(); torch.cuda.synchronize()
         r = e.run(c["n_hyp"], sc.thr, samples_ptr=smp.data_ptr(), flags=gcr_capi.RUN_TIME_KERNELS)
+        win[lib] = (r.best_index, r.best_score, r.n_scored, r.n_candidates, r.n_exact_hyp)
         if rnd >= 2:
             res[lib][0].append(r.score_kernel_ms); res[lib][1].append(r.device_ms)
 for lib in libs:
     k, s = np.array(res[lib][0]), np.array(res[lib][1])
-    print(f"{name} {lib:34s} kernel ms median {np.median(k):.4f} min {k.min():.4f} | stage ms median {np.median(s):.4f} min {s.min():.4f}")
+    print(f"{name} {lib:28s} kernel ms median {np.median(k):.4f} min {k.min():.4f} | stage ms median {np.median(s):.4f} min {s.min():.4f} | winner {win[lib]}")

@@ -14,5 +14,5 @@ for name in sys.argv[1:] or ["C2"]:
     print(name, "stage_ms %.4f score_ms %.4f" % (np.median([r.device_ms for r in rs]), np.median([r.score_kernel_ms for r in rs])),
           "tail phases us (fix+exact | finalize | collect | rescoring | select):", np.round(ph[:5], 2), "sum %.2f" % ph[:5].sum(),
           "| ss->score %.2f score->tail %.2f ss->end %.2f |" % (ph[6] if len(ph) > 6 else 0, ph[5], ph[7] if len(ph) > 7 else 0),
-          "cands", rs[0].n_candidates, "gb", rs[0].n_rechecked, "exact", rs[0].n_exact_hyp)
+          "refined", rs[0].n_refined, "cands", rs[0].n_candidates, "gb", rs[0].n_rechecked, "exact", rs[0].n_exact_hyp)
     e.close()
