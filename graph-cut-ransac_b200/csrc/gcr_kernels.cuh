@@ -864,7 +864,8 @@ __device__ __forceinline__ void finalize_phase_w(const Buffers& B, const Thresho
 // level 2, collection: every not yet refined hypothesis whose upper bound reaches `floor_v` takes a contender slot; the collecting thread
 // derives the refinement's parameters (FP64 model, FP32 band limits of the FP64-front arithmetic).  Slots beyond kContCap: the overflow flag
 // sends the stragglers straight to level 3.
-__device__ __forceinline__ void contender_collect_phase(const Buffers& B, const Thresholds& T, double floor_v)
+constexpr unsigned int kDirectCand = 16;
+__device__ __forceinline__ void contender_collect_phase(const Buffers& B, const Thresholds& T, double floor_v, bool speculate)
 {
     for_each_scored_valid(B, [&](unsigned int h, unsigned char f) {
         if (f & 32) return; // already a contender
@@ -911,6 +912,9 @@ __device__ __forceinline__ void contender_collect_phase(const Buffers& B, const 
         B.cont_par[slot] = P;
         B.cont_q[2 * slot] = B.cont_q[2 * slot + 1] = 0ull;
         B.cont_n[2 * slot] = B.cont_n[2 * slot + 1] = 0u;
+        // first round: the first few contenders also take candidate slots at once; when they turn out to be all there is (and none can
+        // lose its score to the zero-reset rule) the FP64 level starts without a collection pass and its barrier
+        if (speculate && slot < kDirectCand) collect_candidate(B, h, 0u, f | 32);
     });
 }
 
@@ -1065,7 +1069,6 @@ __device__ __forceinline__ void contender_value_phase(const Buffers& B, const Th
 // level 3, collection: contenders whose refined upper bound reaches the best refined lower bound (the reference's winner, and everything
 // tied with it, is among them: its true value is >= every other true value >= every lower bound); after a contender overflow also every
 // hypothesis that found no slot, by its loose bound.  Later rounds: the deferred ones (more than kCandCap candidates: massive ties).
-constexpr unsigned int kDirectCand = 16;
 __device__ __forceinline__ void collect_phase_w(const Buffers& B, const Thresholds& T, int round, unsigned int base, unsigned int n_cont,
                                                 double floor_loose, bool direct)
 {
@@ -1326,11 +1329,15 @@ __global__ void __launch_bounds__(kExactThreads) k_tail(const __grid_constant__ 
     pdl_wait(); // results of the scoring kernel
     if (stamp) B.phase_ns[0] = global_ns();
     const bool winner = !B.per_hyp;
-    fixup_phase(B, T);
-    exact_items_phase(B, T, 0, 0u);
-    grid.sync();
+    // (every CTA reads the same counters: they were final when the scoring kernel ended)
+    if (__ldcg(&B.ctr->n_worklist) | __ldcg(&B.ctr->n_hard) | B.scene->n_irr_s | B.scene->n_irr_o)
+    {
+        fixup_phase(B, T);
+        exact_items_phase(B, T, 0, 0u);
+        grid.sync();
+    }
     if (stamp) B.phase_ns[1] = global_ns();
-    unsigned int n_cont = 0u;
+    unsigned int n_cont = 0u, spec_cands = 0u;
     double floor_loose = 0.0;
     bool direct = false;
     if (winner)
@@ -1348,13 +1355,14 @@ __global__ void __launch_bounds__(kExactThreads) k_tail(const __grid_constant__ 
             floor_loose = from_ordered_bits(k0);
             for (;;)
             {
-                contender_collect_phase(B, T, floor_loose);
+                contender_collect_phase(B, T, floor_loose, n_cont == 0u);
                 grid.sync();
 #ifdef GCR_TAIL_DEBUG
                 if (stamp) B.phase_ns[3] = global_ns();
 #endif
                 const unsigned int n_now = min(__ldcg(&B.ts->n_cont), static_cast<unsigned int>(kContCap));
                 const bool overflow = __ldcg(&B.ts->cont_overflow) != 0u;
+                if (n_cont == 0u) spec_cands = min(__ldcg(&B.ts->n_cont), kDirectCand);
                 if (n_cont == 0u && n_now <= kDirectCand && !overflow && !__ldcg(&B.ts->unproven))
                 {
                     // a handful of contenders whose scores cannot be reset (small scenes: the loose bound is already tight): their FP64
@@ -1389,12 +1397,15 @@ __global__ void __launch_bounds__(kExactThreads) k_tail(const __grid_constant__ 
     // Candidate rounds: one, unless more than kCandCap hypotheses sit inside the window (massive ties).  The candidate
     // counters are cumulative; every CTA tracks the bases of the current round in registers (the counters are stable
     // between the barrier after a collect phase and the next collect phase, so all CTAs read the same values).
-    unsigned int cand_base = 0u, ovf_base = 0u;
+    unsigned int cand_base = direct ? 0u : spec_cands, ovf_base = 0u; // (speculative slots that were not used: a spent round)
     for (int round = 0;; round++)
     {
-        if (winner) collect_phase_w(B, T, round, cand_base, n_cont, floor_loose, direct);
-        else collect_phase(B, T, rel_tol, round, cand_base);
-        grid.sync();
+        if (!(direct && round == 0)) // direct: the contenders took their candidate slots when they were collected
+        {
+            if (winner) collect_phase_w(B, T, round, cand_base, n_cont, floor_loose, direct);
+            else collect_phase(B, T, rel_tol, round, cand_base);
+            grid.sync();
+        }
 #ifndef GCR_TAIL_DEBUG
         if (stamp && round == 0) B.phase_ns[3] = global_ns();
 #endif

@@ -30,7 +30,7 @@ constexpr int kStages = 6;
 #endif
 constexpr int kResultHeaderWords = 48; // result block: record (16 words) + counters (16) + phase stamps (16), then the winner's masks
 #ifndef GCR_ITEMS
-#define GCR_ITEMS 16
+#define GCR_ITEMS 24
 #endif
 constexpr int kItemsPerCta = GCR_ITEMS; // work items per resident CTA the chunk lists are cut for (k_score_fast)
 #ifndef GCR_VOTE

@@ -6,7 +6,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [os.path.join(ROOT, "graph-cut-ransac_b200"), os.path.join(ROOT, "tests")]
 import torch, gcr_capi, gcr_scenes as gs
 name, libs = sys.argv[1], sys.argv[2:]
-c = gs.CONFIGS[name]; sc = gs.config_scene(name)
+c = dict(gs.CONFIGS[name]); sc = gs.config_scene(name)
+if os.environ.get("HYP"): c["n_hyp"] = int(os.environ["HYP"])
 smp = torch.from_numpy(gs.draw_samples(c["n_hyp"], c["n_scale"], c["n_orient"], gs.SAMPLE_SEED)).cuda()
 engines = []
 for lib in libs:

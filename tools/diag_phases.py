@@ -4,7 +4,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [os.path.join(ROOT, "graph-cut-ransac_b200"), os.path.join(ROOT, "tests")]
 import numpy as np, torch, gcr_capi, gcr_scenes as gs
 for name in sys.argv[1:] or ["C2"]:
-    c = gs.CONFIGS[name]; sc = gs.config_scene(name)
+    c = dict(gs.CONFIGS[name]); sc = gs.config_scene(name)
+    if os.environ.get("HYP"): c["n_hyp"] = int(os.environ["HYP"])  # e.g. one rank's shard of a sharded run
     smp = gs.draw_samples(c["n_hyp"], c["n_scale"], c["n_orient"], gs.SAMPLE_SEED)
     e = gcr_capi.Engine(0); e.set_features(sc.scale, sc.orient)
     d = torch.from_numpy(smp).cuda()
