@@ -1039,13 +1039,6 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
             GCR_CUDA(cudaLaunchKernelEx(&cfg, mode == 2 ? k_score_fast<2> : (mode == 1 ? k_score_fast<1> : k_score_fast<0>), B, T));
         }
         if (time_kernels) GCR_CUDA(cudaEventRecord(h->evk1, s));
-        // Candidate window: hypotheses whose FP32-path value is within rel_tol of the best one are re-scored in FP64.
-        // The FP32 value error per inlier is ~ 2 (delta d) / T' (scale: MUFU.LG2 + roundings, delta d ~ 4e-7) and
-        // ~ 2 (delta t) / sqrt(tsq) (orientation), i.e. it grows as the thresholds tighten; 4e-5 was validated at the
-        // default thresholds (T' = 0.096, sqrt(tsq_o) = 0.0785) and is scaled from there, with a factor 2 on top.
-        double rel_tol = 2.0 * std::max(2e-5, 4e-5 * 0.096 / static_cast<double>(T.Tp));
-        if (h->problem == 0) rel_tol = std::max(rel_tol, 2.0 * 4e-5 * 0.0785 / std::sqrt(T.tsq[1]));
-        rel_tol = std::min(rel_tol, 0.05);
         cfg.gridDim = dim3(h->tail_grid);
         cfg.blockDim = dim3(kExactThreads);
         cfg.dynamicSmemBytes = 0;
@@ -1056,7 +1049,7 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
             cfg.attrs = at + 1; // cooperative only
             cfg.numAttrs = 1;
         }
-        GCR_CUDA(cudaLaunchKernelEx(&cfg, k_tail, B, T, rel_tol));
+        GCR_CUDA(cudaLaunchKernelEx(&cfg, k_tail, B, T));
     }
     if (time_kernels) GCR_CUDA(cudaEventRecord(h->ev1, s));
     if (flags & (GCR_RUN_KEEP_PER_HYP | GCR_RUN_EMIT_MASKS))

@@ -353,6 +353,11 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
             }
             else
             {
+                // reporting modes: error of a CERTAIN inlier's term r^2/tsq (guard-band evaluations are re-done in FP64): scale
+                // delta (d/Tp)^2 <= 1.05 drho / Tp (|delta d| <= drho / 2, |d| <= Tp) + 4u; orientation 2.1 (delta t) / sqrt(tsq) with
+                // delta t <= dprime / max + t_band0, + 1.2e-6 for the polynomial (finalize_phase sums them over the counted inliers)
+                B.err_ab[h] = make_float2(__double2float_ru(1.05 * drho / Tp + 4.0 * kU),
+                                          __double2float_ru(2.1 * dprime / static_cast<double>(T.sqrt_tsq1)));
                 p0 = make_float4(static_cast<float>(-m.h7), static_cast<float>(-m.h8), static_cast<float>(A),
                                  __double2float_rd(Tp - drho));
                 p1 = make_float4(__double2float_ru(Tp + drho), static_cast<float>(cphi), static_cast<float>(sphi),
@@ -361,6 +366,7 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
         }
         B.flags[h] = f;
         B.models[h] = m;
+        if (!winner) B.score[h] = 0.0; // (its low word collects a float sum in the scoring kernels, see flush_hyps)
         B.sums[2 * h] = 0.0;
         B.sums[2 * h + 1] = 0.0;
         B.cnts[2 * h] = 0u;
@@ -654,47 +660,39 @@ __device__ __forceinline__ bool tail_direct(const Buffers& B)
 
 __device__ __forceinline__ void finalize_phase(const Buffers& B, const Thresholds& T)
 {
+    // reporting modes: value and inlier counts of EVERY slot are outputs; the selection works on proven bounds: counts are exact
+    // (guard-band pairs were decided in FP64), the FP32 sum of r^2/tsq over the n0 + n1 certain inliers is off by at most
+    //   err = n0 e_s + e_o1 (sum of 1/max over them) + n1 (2.1 t_band0 / sqrt(tsq) + 1.2e-6) + 8e-6 (n0 + n1)
+    // (k_sample_solve's per-hypothesis coefficients err_ab; the last term: FP32 accumulation inside a chunk), kept in err_ab.x for collect_phase
     unsigned long long key = 0ull;
-    if (tail_direct(B))
+    const double e_o0 = 2.1 * static_cast<double>(T.t_band0) / fmax(static_cast<double>(T.sqrt_tsq1), 1e-300) + 1.2e-6;
+    for (int base = blockIdx.x * blockDim.x; base < B.n_hyp; base += gridDim.x * blockDim.x)
     {
-        for (int base = blockIdx.x * blockDim.x; base < B.n_hyp; base += gridDim.x * blockDim.x)
+        const int h = base + threadIdx.x;
+        if (h >= B.n_hyp) continue;
+        const unsigned char f = B.flags[h];
+        unsigned int n0 = 0, n1 = 0;
+        double v = 0.0, err = 0.0;
+        if (f & 2)
         {
-            const int h = base + threadIdx.x;
-            if (h >= B.n_hyp) continue;
-            const unsigned char f = B.flags[h];
-            unsigned int n0 = 0, n1 = 0;
-            double v = 0.0;
-            if ((f & 2) && (B.per_hyp || (f & 4))) v = hyp_value(B, T, h, f, n0, n1);
-            if (B.per_hyp) // reporting modes: value and inlier counts of EVERY slot are outputs
+            const float risum = *reinterpret_cast<const float*>(B.score + h);
+            const unsigned int c0 = B.cnts[2 * h], c1 = B.cnts[2 * h + 1];
+            v = hyp_value(B, T, h, f, n0, n1);
+            if (!(f & 8))
             {
-                B.score[h] = v;
-                B.n_inl[2 * h] = n0;
-                B.n_inl[2 * h + 1] = n1;
+                const float2 ab = B.err_ab[h];
+                err = static_cast<double>(c0) * ab.x + static_cast<double>(ab.y) * risum + static_cast<double>(c1) * e_o0 +
+                      8e-6 * static_cast<double>(c0 + c1) + 1e-12;
             }
-            if ((f & 4) && v > 0.0) // S10 + S11 (initial best is 0, strict '<')
-            {
-                const unsigned long long k = ordered_bits(v);
-                key = k > key ? k : key;
-            }
+            B.err_ab[h].x = __double2float_ru(err);
         }
-    }
-    else
-    {
-        // winner only: the scored hypotheses through the compact lists, nothing written
-        const unsigned int n_fast = __ldcg(&B.ctr->n_fast), n_sens = __ldcg(&B.ctr->n_sens), n_hard = __ldcg(&B.ctr->n_hard);
-        const unsigned int total = n_fast + n_sens + n_hard;
-        for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x)
+        B.score[h] = v;
+        B.n_inl[2 * h] = n0;
+        B.n_inl[2 * h + 1] = n1;
+        if ((f & 4) && v > 0.0) // S10 + S11 (initial best is 0, strict '<'); counts are exact here, so v > 0 is the reference's own test
         {
-            const unsigned int h = scored_hyp(B, i, n_fast, n_sens);
-            const unsigned char f = B.flags[h];
-            if (!(f & 4)) continue; // S10: an invalid model is never selected
-            unsigned int n0, n1;
-            const double v = hyp_value(B, T, h, f, n0, n1);
-            if (v > 0.0)
-            {
-                const unsigned long long k = ordered_bits(v);
-                key = k > key ? k : key;
-            }
+            const unsigned long long k = ordered_bits(v - err);
+            key = k > key ? k : key;
         }
     }
 #pragma unroll
@@ -737,40 +735,22 @@ __device__ __forceinline__ void collect_candidate(const Buffers& B, unsigned int
 }
 
 // round 0: every model-valid hypothesis inside the window; later rounds: the deferred ones
-__device__ __forceinline__ void collect_phase(const Buffers& B, const Thresholds& T, double rel_tol, int round, unsigned int base)
+__device__ __forceinline__ void collect_phase(const Buffers& B, const Thresholds& T, int round, unsigned int base)
 {
     const unsigned long long bk = __ldcg(&B.ctr->best_key);
     if (bk == 0ull) return;
-    const double best = from_ordered_bits(bk);
-    const double floor_v = best - rel_tol * best;
-    if (tail_direct(B) || round > 0)
+    const double best_lb = from_ordered_bits(bk); // best LOWER bound (finalize_phase)
+    for (int h = blockIdx.x * blockDim.x + threadIdx.x; h < B.n_hyp; h += gridDim.x * blockDim.x)
     {
-        for (int h = blockIdx.x * blockDim.x + threadIdx.x; h < B.n_hyp; h += gridDim.x * blockDim.x)
-        {
-            const unsigned char f = B.flags[h];
-            if ((f & 6) != 6) continue; // solved and model-valid
-            if (round > 0)
-            {
-                if (f & 16) collect_candidate(B, h, base, f);
-                continue;
-            }
-            unsigned int n0, n1;
-            const double v = B.per_hyp ? B.score[h] : hyp_value(B, T, h, f, n0, n1);
-            if (!(v > 0.0) || v < floor_v) continue;
-            collect_candidate(B, h, base, f);
-        }
-        return;
-    }
-    const unsigned int n_fast = __ldcg(&B.ctr->n_fast), n_sens = __ldcg(&B.ctr->n_sens), n_hard = __ldcg(&B.ctr->n_hard);
-    const unsigned int total = n_fast + n_sens + n_hard;
-    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x)
-    {
-        const unsigned int h = scored_hyp(B, i, n_fast, n_sens);
         const unsigned char f = B.flags[h];
-        if (!(f & 4)) continue;
-        unsigned int n0, n1;
-        const double v = hyp_value(B, T, h, f, n0, n1); // the same arithmetic on the same inputs as in finalize
-        if (!(v > 0.0) || v < floor_v) continue;
+        if ((f & 6) != 6) continue; // solved and model-valid
+        if (round > 0)
+        {
+            if (f & 16) collect_candidate(B, h, base, f);
+            continue;
+        }
+        const double v = B.score[h];
+        if (!(v > 0.0) || v + static_cast<double>(B.err_ab[h].x) < best_lb) continue; // upper bound below the best lower bound: cannot win
         collect_candidate(B, h, base, f);
     }
 }
@@ -1321,8 +1301,7 @@ __device__ __forceinline__ void select_phase(const Buffers& B, const Thresholds&
 
 // The fused tail: fixup + whole-hypothesis FP64 items | finalize | collect | FP64 re-scoring of the candidates | select.
 // Cooperative launch (all CTAs co-resident), kExactThreads threads per CTA.
-__global__ void __launch_bounds__(kExactThreads) k_tail(const __grid_constant__ Buffers B, const __grid_constant__ Thresholds T,
-                                                        double rel_tol)
+__global__ void __launch_bounds__(kExactThreads) k_tail(const __grid_constant__ Buffers B, const __grid_constant__ Thresholds T)
 {
     cooperative_groups::grid_group grid = cooperative_groups::this_grid();
     const bool stamp = blockIdx.x == 0 && threadIdx.x == 0; // phase boundaries as seen by CTA 0 (diagnostics, ns)
@@ -1403,7 +1382,7 @@ __global__ void __launch_bounds__(kExactThreads) k_tail(const __grid_constant__ 
         if (!(direct && round == 0)) // direct: the contenders took their candidate slots when they were collected
         {
             if (winner) collect_phase_w(B, T, round, cand_base, n_cont, floor_loose, direct);
-            else collect_phase(B, T, rel_tol, round, cand_base);
+            else collect_phase(B, T, round, cand_base);
             grid.sync();
         }
 #ifndef GCR_TAIL_DEBUG

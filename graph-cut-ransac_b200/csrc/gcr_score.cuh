@@ -91,21 +91,22 @@ __device__ __forceinline__ Verdict scale_verdict(float v, const HypRegs& H, floa
 // (denom, numer) of rectifiedAngle (model.h:156-165) rotated by -phi; the residual (S5, two_sift.hpp:647-665)
 // is the angle of that vector to the nearest multiple of pi/2 = atan(min/max) of its absolute components;
 // r^2 = z p(z), z = tan^2, by an even polynomial.
-__device__ __forceinline__ Verdict orient_verdict_cs(float c1, float s1, const HypRegs& H, const Thresholds& T, float& z, float& p);
+__device__ __forceinline__ Verdict orient_verdict_cs(float c1, float s1, const HypRegs& H, const Thresholds& T, float& z, float& p, float& ri);
 __device__ __forceinline__ Verdict orient_verdict(float n, float d, const HypRegs& H, const Thresholds& T, float& z,
-                                                  float& p)
+                                                  float& p, float& ri)
 {
     const float c1 = fmaf(n, H.sphi, d * H.cphi);
     const float s1 = fmaf(n, H.cphi, -(d * H.sphi));
-    return orient_verdict_cs(c1, s1, H, T, z, p);
+    return orient_verdict_cs(c1, s1, H, T, z, p, ri);
 }
-__device__ __forceinline__ Verdict orient_verdict_cs(float c1, float s1, const HypRegs& H, const Thresholds& T, float& z, float& p)
+// ri: 1 / max(|c'|, |s'|), the factor of the hypothesis' FP64-derived band dprime in this evaluation's error of t
+__device__ __forceinline__ Verdict orient_verdict_cs(float c1, float s1, const HypRegs& H, const Thresholds& T, float& z, float& p, float& ri)
 {
     const float a1 = fabsf(c1), a2 = fabsf(s1);
     // the 1e-30 floor keeps an exact 0/0 (numer = denom = 0, where the reference evaluates atan2 of round-off)
     // finite: t = 0 with an enormous band -> worklist
     const float mn = fminf(a1, a2), mx = fmaxf(fmaxf(a1, a2), 1e-30f);
-    const float ri = rcp_approx(mx);
+    ri = rcp_approx(mx);
     const float t = mn * ri;
     Verdict e;
     e.in = t <= fmaf(-H.dpr, ri, T.t_lo0);               // tanT - band0 - dpr / max
@@ -142,11 +143,12 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
     constexpr int G = PRECISE ? 2 : 4;             // features per group
     constexpr int NF = PRECISE ? kChunk / 2 : kChunk; // features per chunk
     float acc[kHB], cntf[kHB]; // per-chunk FP32 partials; counts are exact integers (< 2^24)
+    float rsum[kHB];
     unsigned int mword[kHB];
 #pragma unroll
     for (int j = 0; j < kHB; j++)
     {
-        acc[j] = cntf[j] = 0.f;
+        acc[j] = cntf[j] = rsum[j] = 0.f;
         mword[j] = 0u;
     }
     bool unc_j[kHB]; // hypothesis j had an evaluation of the last kVoteGroups groups inside the band (per thread)
@@ -178,13 +180,13 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
         }
         // verdict of hypothesis j on one feature given its three plane values (FP32 or FP64 flavour)
         auto verdict = [&](int j, float a32, float b32, float c32, double a64, double b64, double c64, float& x0,
-                           float& x1) -> Verdict {
+                           float& x1, float& x2) -> Verdict {
             if constexpr (CLS == 0)
             {
                 float v;
                 if constexpr (PRECISE) v = static_cast<float>(fma(-H[j].h8d, b64, fma(-H[j].h7d, a64, c64)));
                 else v = fmaf(H[j].nh8, b32, fmaf(H[j].nh7, a32, c32));
-                x1 = 0.f;
+                x1 = x2 = 0.f;
                 return scale_verdict(v, H[j], x0);
             }
             else
@@ -200,7 +202,7 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
                     n = fmaf(a32, H[j].nh7, b32);
                     d = fmaf(-a32, H[j].nh8, c32);
                 }
-                return orient_verdict(n, d, H[j], T, x0, x1);
+                return orient_verdict(n, d, H[j], T, x0, x1, x2);
             }
         };
 #pragma unroll
@@ -208,7 +210,7 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
         {
             // FP32 tiles, packed form (GCR_F2): the FMAs that do not depend on a predicate are issued as f32x2 pairs
             // (FFMA2 / FMUL2: two IEEE operations per issue slot, bit-identical to the scalar form)
-            float pk0[G], pk1[G];
+            float pk0[G], pk1[G], pk2[G];
             Verdict pv[G];
             if constexpr (!PRECISE && kPacked<CLS>)
             {
@@ -224,6 +226,7 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
                         const float2 d = __ffma2_rn(L, make_float2(-1.f, -1.f), make_float2(H[j].A, H[j].A)); // A - L, one rounding
                         pk0[e] = d.x; pk0[e + 1] = d.y;
                         pk1[e] = pk1[e + 1] = 0.f;
+                        pk2[e] = pk2[e + 1] = 0.f;
                         pv[e] = scale_verdict_d(d.x, H[j]);
                         pv[e + 1] = scale_verdict_d(d.y, H[j]);
                     }
@@ -251,6 +254,7 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
                                 pl = __ffma2_rn(__ffma2_rn(z0, z, make_float2(T.pm[1], T.pm[1])), z, make_float2(T.pm[2], T.pm[2]));
                             pk0[e] = z.x; pk0[e + 1] = z.y;
                             pk1[e] = pl.x; pk1[e + 1] = pl.y;
+                            pk2[e] = ri.x; pk2[e + 1] = ri.y;
                             pv[e].in = t.x <= lo.x;
                             pv[e].unc = (t.x <= hi.x) && !pv[e].in;
                             pv[e + 1].in = t.y <= lo.y;
@@ -259,8 +263,8 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
                         else
                         {
                             // the rest of the evaluation stays scalar (see GCR_F2 in gcr_kernels_common.cuh)
-                            pv[e] = orient_verdict_cs(c1.x, s1.x, H[j], T, pk0[e], pk1[e]);
-                            pv[e + 1] = orient_verdict_cs(c1.y, s1.y, H[j], T, pk0[e + 1], pk1[e + 1]);
+                            pv[e] = orient_verdict_cs(c1.x, s1.x, H[j], T, pk0[e], pk1[e], pk2[e]);
+                            pv[e + 1] = orient_verdict_cs(c1.y, s1.y, H[j], T, pk0[e + 1], pk1[e + 1], pk2[e + 1]);
                         }
                     }
                 }
@@ -268,20 +272,22 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
 #pragma unroll
             for (int e = 0; e < G; e++)
             {
-                float x0, x1;
+                float x0, x1, x2;
                 Verdict r;
                 if constexpr (!PRECISE && kPacked<CLS>)
                 {
                     x0 = pk0[e];
                     x1 = pk1[e];
+                    x2 = pk2[e];
                     r = pv[e];
                 }
                 else
-                    r = PRECISE ? verdict(j, 0.f, 0.f, 0.f, da[e], db[e], dc[e], x0, x1)
-                                : verdict(j, fa[e], fb[e], fc[e], 0.0, 0.0, 0.0, x0, x1);
+                    r = PRECISE ? verdict(j, 0.f, 0.f, 0.f, da[e], db[e], dc[e], x0, x1, x2)
+                                : verdict(j, fa[e], fb[e], fc[e], 0.0, 0.0, 0.0, x0, x1, x2);
                 if (r.in)
                 {
                     acc[j] = CLS == 0 ? fmaf(x0, x0, acc[j]) : fmaf(x0, x1, acc[j]);
+                    if (CLS == 1) rsum[j] += x2; // sum of 1 / max over the certain inliers: scales the value's error bound (finalize_phase)
                     cntf[j] += 1.0f;
                     if (MASKS) mword[j] |= 1u << ((g * G + e) & 31);
                 }
@@ -306,15 +312,15 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
 #pragma unroll 1
                     for (int f = f0; f < f0 + kVoteGroups * G; f++)
                     {
-                        float x0, x1;
+                        float x0, x1, x2;
                         Verdict r;
                         if constexpr (PRECISE)
                         {
                             const double* sd = reinterpret_cast<const double*>(stage);
-                            r = verdict(j, 0.f, 0.f, 0.f, sd[f], sd[NF + f], sd[2 * NF + f], x0, x1);
+                            r = verdict(j, 0.f, 0.f, 0.f, sd[f], sd[NF + f], sd[2 * NF + f], x0, x1, x2);
                         }
                         else
-                            r = verdict(j, stage[f], stage[NF + f], stage[2 * NF + f], 0.0, 0.0, 0.0, x0, x1);
+                            r = verdict(j, stage[f], stage[NF + f], stage[2 * NF + f], 0.0, 0.0, 0.0, x0, x1, x2);
                         if (r.unc && (RANGE ? H[j].hyp != kNoHyp : H[j].active))
                             worklist_push(B, H[j].hyp, (CLS ? 0x80000000u : 0u) | static_cast<unsigned>(fbase + f));
                     }
@@ -347,6 +353,7 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
         {
             H[j].sum_o += static_cast<double>(acc[j]) * static_cast<double>(T.pc_lead);
             H[j].cnt_o += static_cast<unsigned int>(cntf[j]);
+            H[j].rimax += rsum[j];
         }
     }
 }
@@ -567,12 +574,16 @@ __device__ __forceinline__ void flush_hyps(const Buffers& B, const Thresholds& T
             continue;
         }
         const double ss = H[j].sum_s * static_cast<double>(T.scale_unit);
+        // (reporting modes: the sum of 1 / max over the certain orientation inliers travels in the low word of the hypothesis' score slot,
+        //  which k_sample_solve cleared and finalize_phase reads before it writes the score)
+        float* risum = reinterpret_cast<float*>(B.score + h);
         if (single_split)
         {
             B.sums[2 * h] = ss;
             B.sums[2 * h + 1] = H[j].sum_o;
             B.cnts[2 * h] = H[j].cnt_s;
             B.cnts[2 * h + 1] = H[j].cnt_o;
+            *risum = H[j].rimax;
         }
         else
         {
@@ -585,6 +596,7 @@ __device__ __forceinline__ void flush_hyps(const Buffers& B, const Thresholds& T
             {
                 atomicAdd(&B.sums[2 * h + 1], H[j].sum_o);
                 atomicAdd(&B.cnts[2 * h + 1], H[j].cnt_o);
+                atomicAdd(risum, H[j].rimax);
             }
         }
     }

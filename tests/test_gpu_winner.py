@@ -20,7 +20,7 @@ def eng():
     e.close()
 
 
-def _check_winner(eng, port, scale, orient, smp, thr, label="", libm_ties=False):
+def _check_winner(eng, port, scale, orient, smp, thr, label="", libm_ties=False, flags=0):
     """winner-only replay run vs oracle: index, score (1e-11: both FP64 reference order), counts, model, masks.
     libm_ties: where the oracle's scores of two hypotheses agree to 1e-13 relative their order is the last ulp of log / pow / atan2
     (glibc vs CUDA libm); either is accepted (thresholds of 1e-9, where only the minimal sample itself scores)."""
@@ -28,7 +28,7 @@ def _check_winner(eng, port, scale, orient, smp, thr, label="", libm_ties=False)
     ora = port.replay(scale, orient, smp, thr, nthreads=0)
     want = port.select_best(ora["score"], ora["flags"])
     eng.set_features(scale, orient)
-    res = eng.run(len(smp), thr, samples=smp)
+    res = eng.run(len(smp), thr, samples=smp, flags=flags)
     if libm_ties and want >= 0 and res.best_index >= 0 and res.best_index != want:
         got = res.best_index
         assert (ora["flags"][got] & 6) == 6 and abs(ora["score"][got] - ora["score"][want]) <= 1e-13 * abs(ora["score"][want]), label
@@ -44,11 +44,13 @@ def _check_winner(eng, port, scale, orient, smp, thr, label="", libm_ties=False)
     ws = (len(scale) + 31) // 32
     assert np.array_equal(b["scale_words"], ora["masks"][want][:ws]), label
     assert np.array_equal(b["orient_words"], ora["masks"][want][ws:]), label
-    # the slots of rejected models are reported (flags) but not scored
-    assert res.n_scored <= res.n_solved
-    assert res.n_scored == int(((ora["flags"] & 4) > 0).sum())
     assert res.n_solved == int(((ora["flags"] & 2) > 0).sum())
-    assert res.n_rechecked == 0
+    if flags == 0:
+        # the slots of rejected models are reported (flags) but not scored; no inlier decisions, hence no guard-band pairs
+        assert res.n_scored == int(((ora["flags"] & 4) > 0).sum())
+        assert res.n_rechecked == 0
+    else:
+        assert res.n_scored == res.n_solved
     return res
 
 
@@ -167,6 +169,11 @@ def test_winner_only_reversed_fp32_order_is_resolved_in_fp64(eng, port):
                 if not (1e-12 < gap < 1e-5):
                     continue  # a libm-level tie, or a pair the FP32 values already order
                 checked += 1
+                import gcr_capi
+                # the reporting modes select on proven bounds too (finalize_phase / collect_phase: exact counts, FP32 sums)
+                rep = _check_winner(eng, port, sc.scale, orient, smp, sc.thr, f"twins level {level} eps {eps} (reporting)",
+                                    flags=gcr_capi.RUN_KEEP_PER_HYP)
+                assert rep.n_candidates >= 2 or rep.n_exact_hyp > 0 or gap > 1e-7
                 res = _check_winner(eng, port, sc.scale, orient, smp, sc.thr, f"twins level {level} eps {eps}")
                 assert res.n_refined >= 2 or res.n_exact_hyp > 0  # (25 degrees: every hypothesis is scored in FP64 from the start) both went through the refinement (exact counts, error ~1e-6 of the value) before the FP64 level
     assert checked >= 8
