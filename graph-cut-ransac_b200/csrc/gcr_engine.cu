@@ -92,7 +92,7 @@ struct gcr_engine_s
     int tail_grid = 148;
     unsigned int worklist_cap_override = 0; // GCR_WORKLIST_CAP (tests of the overflow report)
     cudaStream_t own_stream = nullptr, stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr, evk0 = nullptr, evk1 = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, evk0 = nullptr, evk1 = nullptr, ev_wait = nullptr;
     std::string err;
 
     // features
@@ -553,6 +553,7 @@ int gcr_create(int device, gcr_handle* out)
     if (e == cudaSuccess) e = cudaEventCreate(&h->ev1);
     if (e == cudaSuccess) e = cudaEventCreate(&h->evk0);
     if (e == cudaSuccess) e = cudaEventCreate(&h->evk1);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_wait, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaDeviceGetAttribute(&h->n_sm, cudaDevAttrMultiProcessorCount, device);
     const int resident_smem = kResidentMaxChunks * kChunkBytes + 64;
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_score_fast<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ScoreSmem));
@@ -627,6 +628,7 @@ int gcr_destroy(gcr_handle h)
     if (h->ev1) cudaEventDestroy(h->ev1);
     if (h->evk0) cudaEventDestroy(h->evk0);
     if (h->evk1) cudaEventDestroy(h->evk1);
+    if (h->ev_wait) cudaEventDestroy(h->ev_wait);
     if (h->own_stream) cudaStreamDestroy(h->own_stream);
     delete h;
     return GCR_OK;
@@ -651,6 +653,18 @@ int gcr_set_stream(gcr_handle h, void* cuda_stream)
 {
     if (!h) return GCR_ERR_INVALID;
     h->stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : h->own_stream;
+    return GCR_OK;
+}
+
+int gcr_wait_stream(gcr_handle h, void* producer_stream)
+{
+    if (!h) return GCR_ERR_INVALID;
+    if (!h->stream) return h->fail(GCR_ERR_STATE, "engine was not created successfully");
+    GCR_DEVICE(h);
+    cudaStream_t p = static_cast<cudaStream_t>(producer_stream);
+    if (p == h->stream) return GCR_OK; // same stream: already ordered
+    GCR_CUDA(cudaEventRecord(h->ev_wait, p));
+    GCR_CUDA(cudaStreamWaitEvent(h->stream, h->ev_wait, 0));
     return GCR_OK;
 }
 

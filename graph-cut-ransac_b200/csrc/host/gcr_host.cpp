@@ -190,6 +190,8 @@ static int estimateImpl(int problem, const double* scale, size_t ns, const doubl
 
     Lease eng(opt.device);
     eng.check(gcr_set_problem(eng.h, problem), "gcr_set_problem");
+    // device tensors: the pooled engine runs on its own non-blocking stream; the kernels that wrote the features must come first
+    if (opt.features_on_device && opt.wait_producer) eng.check(gcr_wait_stream(eng.h, opt.producer_stream), "gcr_wait_stream");
     eng.check(gcr_set_features(eng.h, scale, static_cast<int64_t>(ns), orient, static_cast<int64_t>(no),
                                opt.features_on_device ? 1 : 0),
               "gcr_set_features");

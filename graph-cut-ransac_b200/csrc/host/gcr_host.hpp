@@ -24,6 +24,8 @@ struct Options
     const int32_t* samples = nullptr; // replay mode: int32[n_samples,4] = (scale0, scale1, orient0, orient1), host memory
     int64_t n_samples = 0;            // ... then exactly n_samples iterations are run
     bool features_on_device = false;  // scale/orient pointers are DEVICE pointers on `device` (zero-copy tensors)
+    bool wait_producer = false;       // ... written by work on `producer_stream`: the engine's stream is ordered after it (gcr_wait_stream)
+    void* producer_stream = nullptr;  //     (a cudaStream_t; nullptr = the legacy default stream)
     double confidence = 0.95;         // settings.h:60
     size_t max_graph_cut_number = 10; // settings.h:57
     size_t max_batch = size_t(1) << 22; // hypothesis slots per device call

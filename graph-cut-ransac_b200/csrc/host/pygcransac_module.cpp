@@ -81,6 +81,22 @@ FeatureArg parseFeatures(const py::object& obj, const char* what, size_t kNumMin
     return out;
 }
 
+// CUDA-tensor inputs: the stream whose work produced them.  `stream` = None: torch's current stream of that device (what a tensor written
+// by the preceding torch calls is ordered on); an int: a raw cudaStream_t; an object with .cuda_stream (torch.cuda.Stream).
+void setProducerStream(gcr_host::Options& opt, const py::object& stream, int device)
+{
+    uintptr_t raw = 0;
+    if (stream.is_none())
+    {
+        py::object cur = py::module_::import("torch").attr("cuda").attr("current_stream")(device);
+        raw = cur.attr("cuda_stream").cast<uintptr_t>();
+    }
+    else if (py::hasattr(stream, "cuda_stream")) raw = stream.attr("cuda_stream").cast<uintptr_t>();
+    else raw = stream.cast<uintptr_t>();
+    opt.wait_producer = true;
+    opt.producer_stream = reinterpret_cast<void*>(raw);
+}
+
 py::array_t<bool> toMask(const std::vector<bool>& v)
 {
     py::array_t<bool> out(static_cast<py::ssize_t>(v.size()));
@@ -120,7 +136,7 @@ py::tuple findRectifyingHomographySIFT(py::object scale_features, py::object ori
                                        double orientation_residual_thresh, double spatial_coherence_weight,
                                        size_t min_iteration_number, size_t max_iteration_number,
                                        size_t max_local_optimization_number, py::object seed, int device, py::object samples,
-                                       bool return_stats)
+                                       bool return_stats, py::object stream)
 {
     FeatureArg fs = parseFeatures(scale_features, "Scale");
     FeatureArg fo = parseFeatures(orientation_features, "Orientation");
@@ -133,6 +149,7 @@ py::tuple findRectifyingHomographySIFT(py::object scale_features, py::object ori
         if (fs.device != fo.device) throw std::invalid_argument("Feature tensors live on different devices.");
         opt.device = fs.device;
         opt.features_on_device = true;
+        setProducerStream(opt, stream, fs.device);
     }
     if (!seed.is_none())
     {
@@ -177,7 +194,7 @@ py::tuple findRectifyingHomographySIFT(py::object scale_features, py::object ori
 // findRectifyingHomographyScaleOnly / ...Original (bindings.cpp:19-179): (H, inliers, model) or (None, inliers)
 py::tuple scaleOnlyImpl(bool original, py::object features, double scale_residual_thresh, double spatial_coherence_weight,
                         size_t min_iteration_number, size_t max_iteration_number, size_t max_local_optimization_number,
-                        py::object seed, int device, py::object samples, bool return_stats)
+                        py::object seed, int device, py::object samples, bool return_stats, py::object stream)
 {
     FeatureArg f = parseFeatures(features, "", 3);
     gcr_host::Options opt;
@@ -186,6 +203,7 @@ py::tuple scaleOnlyImpl(bool original, py::object features, double scale_residua
     {
         opt.device = f.device;
         opt.features_on_device = true;
+        setProducerStream(opt, stream, f.device);
     }
     if (!seed.is_none())
     {
@@ -226,15 +244,16 @@ py::tuple scaleOnlyImpl(bool original, py::object features, double scale_residua
 }
 
 py::tuple findRectifyingHomographyScaleOnly(py::object features, double thr, double scw, size_t min_it, size_t max_it, size_t max_lo,
-                                            py::object seed, int device, py::object samples, bool return_stats)
+                                            py::object seed, int device, py::object samples, bool return_stats, py::object stream)
 {
-    return scaleOnlyImpl(false, features, thr, scw, min_it, max_it, max_lo, seed, device, samples, return_stats);
+    return scaleOnlyImpl(false, features, thr, scw, min_it, max_it, max_lo, seed, device, samples, return_stats, stream);
 }
 
 py::tuple findRectifyingHomographyScaleOnlyOriginal(py::object features, double thr, double scw, size_t min_it, size_t max_it,
-                                                    size_t max_lo, py::object seed, int device, py::object samples, bool return_stats)
+                                                    size_t max_lo, py::object seed, int device, py::object samples, bool return_stats,
+                                                    py::object stream)
 {
-    return scaleOnlyImpl(true, features, thr, scw, min_it, max_it, max_lo, seed, device, samples, return_stats);
+    return scaleOnlyImpl(true, features, thr, scw, min_it, max_it, max_lo, seed, device, samples, return_stats, stream);
 }
 
 // host-side non-minimal fit, exposed for the parity tests of the refit step (two_sift.hpp:423-579)
@@ -310,14 +329,14 @@ PYBIND11_MODULE(pygcransac, m)
           py::arg("features"), py::arg("scale_residual_thresh"), py::arg("spatial_coherence_weight") = 0.0,
           py::arg("min_iteration_number") = 10000, py::arg("max_iteration_number") = 10000,
           py::arg("max_local_optimization_number") = 50, py::kw_only(), py::arg("seed") = py::none(), py::arg("device") = 0,
-          py::arg("samples") = py::none(), py::arg("return_stats") = false);
+          py::arg("samples") = py::none(), py::arg("return_stats") = false, py::arg("stream") = py::none());
 
     m.def("findRectifyingHomographyScaleOnlyOriginal", &findRectifyingHomographyScaleOnlyOriginal,
           "The 'original' scale-only formulation (rows [x, y, -s^(-1/3)] = -1); hypothesis stage on the GPU.",
           py::arg("features"), py::arg("scale_residual_thresh"), py::arg("spatial_coherence_weight") = 0.0,
           py::arg("min_iteration_number") = 10000, py::arg("max_iteration_number") = 10000,
           py::arg("max_local_optimization_number") = 50, py::kw_only(), py::arg("seed") = py::none(), py::arg("device") = 0,
-          py::arg("samples") = py::none(), py::arg("return_stats") = false);
+          py::arg("samples") = py::none(), py::arg("return_stats") = false, py::arg("stream") = py::none());
 
     m.def("findRectifyingHomographySIFT", &findRectifyingHomographySIFT,
           "Hybrid (scale + orientation) rectifying-homography RANSAC; hypothesis stage on the GPU.",
@@ -325,7 +344,7 @@ PYBIND11_MODULE(pygcransac, m)
           py::arg("orientation_residual_thresh"), py::arg("spatial_coherence_weight") = 0.0,
           py::arg("min_iteration_number") = 10000, py::arg("max_iteration_number") = 10000,
           py::arg("max_local_optimization_number") = 50, py::kw_only(), py::arg("seed") = py::none(),
-          py::arg("device") = 0, py::arg("samples") = py::none(), py::arg("return_stats") = false);
+          py::arg("device") = 0, py::arg("samples") = py::none(), py::arg("return_stats") = false, py::arg("stream") = py::none());
 
     m.def(
         "_fit_non_minimal_scale",

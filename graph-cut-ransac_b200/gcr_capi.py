@@ -23,7 +23,7 @@ ERR_INVALID, ERR_CUDA, ERR_STATE, ERR_NOMEM = -1, -2, -3, -4
 SCORE_TRUNCATED_SQ, SCORE_STRICT = 1, 2
 
 EXPORTS = [
-    "gcr_create", "gcr_destroy", "gcr_last_error", "gcr_set_stream", "gcr_set_problem", "gcr_set_features", "gcr_get_features", "gcr_run",
+    "gcr_create", "gcr_destroy", "gcr_last_error", "gcr_set_stream", "gcr_wait_stream", "gcr_set_problem", "gcr_set_features", "gcr_get_features", "gcr_run",
     "gcr_best",
     "gcr_fetch", "gcr_score_model", "gcr_score_models", "gcr_fit_models", "gcr_set_keypoints", "gcr_debug_eval", "gcr_version", "gcr_peer_export",
     "gcr_peer_attach", "gcr_peer_buffer", "gcr_peer_attach_ptrs", "gcr_peer_detach",
@@ -66,6 +66,7 @@ def load_library() -> C.CDLL:
     lib.gcr_last_error.argtypes = [vp]
     lib.gcr_last_error.restype = C.c_char_p
     lib.gcr_set_stream.argtypes = [vp, vp]
+    lib.gcr_wait_stream.argtypes = [vp, vp]
     lib.gcr_set_problem.argtypes = [vp, C.c_int]
     lib.gcr_set_features.argtypes = [vp, vp, i64, vp, i64, C.c_int]
     lib.gcr_get_features.argtypes = [vp, vp, vp]
@@ -126,6 +127,10 @@ class Engine:
 
     def set_stream(self, cuda_stream: int):
         self._check(self.lib.gcr_set_stream(self.h, C.c_void_p(cuda_stream)))
+
+    def wait_stream(self, cuda_stream: int):
+        """The engine's stream waits for the work submitted so far to `cuda_stream` (0 = legacy default stream)."""
+        self._check(self.lib.gcr_wait_stream(self.h, C.c_void_p(cuda_stream)))
 
     def set_problem(self, problem: int):
         """PROBLEM_HYBRID (default), PROBLEM_SCALE_ONLY or PROBLEM_SCALE_ONLY_ORIGINAL; call before set_features."""

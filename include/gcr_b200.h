@@ -131,6 +131,12 @@ int gcr_set_problem(gcr_handle h, int problem);
 /* Use `cuda_stream` (a cudaStream_t) for all subsequent work; NULL restores the engine's own stream. */
 int gcr_set_stream(gcr_handle h, void* cuda_stream);
 
+/* Order the engine's stream after everything submitted so far to `producer_stream` (a cudaStream_t; NULL = the legacy default stream):
+ * an event is recorded there and the engine's stream waits for it.  For callers that hand over device arrays (GCR_FEATURES_ON_DEVICE,
+ * GCR_RUN_SAMPLES_ON_DEVICE) written by kernels of another stream -- e.g. a PyTorch tensor produced on torch's current stream -- and do
+ * not want to move the engine onto that stream with gcr_set_stream.  Does not synchronise the host. */
+int gcr_wait_stream(gcr_handle h, void* producer_stream);
+
 /* Upload (or, with GCR_FEATURES_ON_DEVICE, adopt from device memory) the two feature classes and build the FP32
  * structure-of-arrays working set.  Replaces the cv::Mat construction of gcransac_python.cpp:284-296.  Requires ns >= 2 and
  * no >= 2 (bindings.cpp:199-224).  `where` is a flags word:

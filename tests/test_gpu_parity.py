@@ -321,6 +321,31 @@ def test_asynchronous_runs_report_device_side_failures(port):
     e.close()
 
 
+def test_entry_points_leave_the_callers_current_device_alone(port):
+    """Every ABI entry point works on the engine's device and restores the caller's (a torch process reads the thread's current
+    device with cudaGetDevice: an engine on device 1 must not move later allocations there).  Needs two devices."""
+    import torch
+    import gcr_capi
+    import gcr_scenes as gs
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two CUDA devices")
+    torch.cuda.set_device(0)
+    sc = gs.make_scene(500, 200, 0.4, 8)
+    smp = gs.draw_samples(2000, 500, 200, 9)
+    e = gcr_capi.Engine(1)
+    assert torch.cuda.current_device() == 0
+    e.set_features(sc.scale, sc.orient)
+    res = e.run(len(smp), sc.thr, samples=smp)
+    b = e.best()
+    e.score_model(b["model"], sc.thr)
+    assert torch.cuda.current_device() == 0
+    assert torch.zeros(1, device="cuda").device.index == 0
+    ora = port.replay(sc.scale, sc.orient, smp, sc.thr, want_masks=False, nthreads=0)
+    assert res.best_index == port.select_best(ora["score"], ora["flags"])
+    e.close()
+    assert torch.cuda.current_device() == 0
+
+
 def test_error_conventions(eng):
     import gcr_capi
     with pytest.raises(gcr_capi.GcrError):

@@ -184,6 +184,43 @@ def test_device_tensors_zero_copy_and_none_result(pg):
 
 
 @pytest.mark.gpu
+def test_device_tensors_are_ordered_after_their_producer_stream(pg):
+    """Feature tensors written by an asynchronous torch kernel on a side stream (behind a long-running kernel, so that they do not
+    exist yet when the call is made): the pooled engine runs on its own non-blocking stream and must wait for the producer
+    (gcr_wait_stream; `stream=` defaults to torch's current stream, may be given explicitly, 0 = the legacy default stream)."""
+    import torch
+    import gcr_scenes as gs
+    sc = gs.make_scene(900, 300, 0.4, 78)
+    want = pg.findRectifyingHomographySIFT(sc.scale, sc.orient, sc.thr[0], sc.thr[1], min_iteration_number=3000,
+                                           max_iteration_number=3000, seed=9)
+    hs, ho = torch.from_numpy(sc.scale).pin_memory(), torch.from_numpy(sc.orient).pin_memory()
+    big = torch.empty(256 << 20, dtype=torch.float32, device="cuda")
+    side = torch.cuda.Stream()
+    for explicit in (False, True, "legacy"):
+        ts = torch.full((900, 3), float("nan"), dtype=torch.float64, device="cuda")
+        to = torch.full((300, 3), float("nan"), dtype=torch.float64, device="cuda")
+        torch.cuda.synchronize()
+        if explicit == "legacy":
+            for _ in range(20):
+                big.mul_(1.0001)  # ~ms of work on the default stream in front of the copies
+            ts.copy_(hs, non_blocking=True)
+            to.copy_(ho, non_blocking=True)
+            got = pg.findRectifyingHomographySIFT(ts, to, sc.thr[0], sc.thr[1], min_iteration_number=3000, max_iteration_number=3000,
+                                                  seed=9, stream=0)
+        else:
+            with torch.cuda.stream(side):
+                for _ in range(20):
+                    big.mul_(1.0001)
+                ts.copy_(hs, non_blocking=True)
+                to.copy_(ho, non_blocking=True)
+                kw = {"stream": side} if explicit else {}
+                got = pg.findRectifyingHomographySIFT(ts, to, sc.thr[0], sc.thr[1], min_iteration_number=3000,
+                                                      max_iteration_number=3000, seed=9, **kw)
+        assert got[0] is not None and np.array_equal(want[0], got[0]) and np.array_equal(want[1], got[1]) and np.array_equal(want[2], got[2])
+    torch.cuda.synchronize()
+
+
+@pytest.mark.gpu
 def test_adaptive_iteration_count(pg):
     """min < max: the loop stops at max(min, getIterationNumber(best inlier counts)) (GCRANSAC.h:286-287,480-483)."""
     import gcr_scenes as gs
