@@ -37,7 +37,7 @@ static const Desc kDesc[K_COUNT] = {
     {"LOP3", 1, 0, "alu pipe"},
     {"IADD3", 1, 0, "alu pipe"},
     {"MUFU.LG2", 1, 1, "xu pipe"},
-    {"MUFU.RCP", 1, 1, "xu pipe"},
+    {"MUFU.RCP + FADD (the FADD keeps ptxas from folding rcp(rcp(x)))", 2, 2, "xu pipe: expect 2 x 0.5"},
     {"LDS.128 broadcast", 1, 0, "shared-memory feature read of the scoring kernels"},
     {"scale-evaluation mix: 2 FFMA + MUFU.LG2 + FADD + 2 FSETP + pred FFMA + 2 pred FADD", 9, 11, "one scale evaluation as issued (no loads)"},
     {"orientation-evaluation mix: 8 FFMA + 4 FMUL + 3 FADD + FMNMX + FMNMX3 + MUFU.RCP + 2 FSETP", 20, 30, "one orientation evaluation as issued (no loads)"},
@@ -86,7 +86,11 @@ __global__ void __launch_bounds__(kThreads, 1) k_bench(float* out, unsigned long
             if (KIND == K_LOP3) asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(ia[i]) : "r"(ia[(i + 1) % kIlp]), "r"(ia[(i + 2) % kIlp]));
             if (KIND == K_IADD) asm volatile("add.s32 %0, %0, %1;" : "+r"(ia[i]) : "r"(ia[(i + 1) % kIlp]));
             if (KIND == K_MUFU_LG2) asm volatile("lg2.approx.ftz.f32 %0, %0;" : "+f"(a[i]));
-            if (KIND == K_MUFU_RCP) asm volatile("rcp.approx.ftz.f32 %0, %0;" : "+f"(a[i]));
+            if (KIND == K_MUFU_RCP) // (a chain of reciprocals alone is folded by ptxas: x -> 1/x -> x; the FADD keeps it, counted below)
+            {
+                asm volatile("rcp.approx.ftz.f32 %0, %0;" : "+f"(a[i]));
+                asm volatile("add.rn.f32 %0, %0, %1;" : "+f"(a[i]) : "f"(c));
+            }
             if (KIND == K_LDS128)
             {
                 float x, y, z, w;
