@@ -91,6 +91,8 @@ struct gcr_engine_s
     int resident_cost_p = 20;   // ... and a precise tile relative to an FP32 tile (x 10); GCR_COST_O / GCR_COST_P for tuning runs
     int tail_grid = 148;
     unsigned int worklist_cap_override = 0; // GCR_WORKLIST_CAP (tests of the overflow report)
+    unsigned int cont_cap_override = 0;     // GCR_CONT_CAP (tests of the contender-overflow path of the selection cascade)
+    double dbg_floor_bump = 0.0;            // GCR_DEBUG_FLOOR_BUMP (tests of the bar-lowering contender round)
     cudaStream_t own_stream = nullptr, stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, evk0 = nullptr, evk1 = nullptr, ev_wait = nullptr;
     std::string err;
@@ -391,6 +393,8 @@ Buffers make_buffers(gcr_engine_s* h, unsigned long long seed, bool have_samples
     B.cont_n = h->d_cont_n.p;
     B.cont_val = h->d_cont_val.p;
     B.ts = h->d_ts.p;
+    B.cont_cap = h->cont_cap_override ? std::min<unsigned int>(h->cont_cap_override, kContCap) : kContCap;
+    B.dbg_floor_bump = h->dbg_floor_bump;
     B.host_block = nullptr;
     for (int p = 0; p < kMaxPeers; p++) B.xchg_peer[p] = static_cast<unsigned long long*>(h->peer_ptr[p]);
     B.xchg_world = 0; // set by gcr_run for exchanging runs
@@ -564,6 +568,8 @@ int gcr_create(int device, gcr_handle* out)
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_score_resident<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, resident_smem);
     if (const char* v = std::getenv("GCR_RESIDENT")) h->resident_ok = std::atoi(v) != 0;
     if (const char* v = std::getenv("GCR_PDL")) h->pdl = std::atoi(v) != 0;
+    if (const char* v = std::getenv("GCR_CONT_CAP")) h->cont_cap_override = static_cast<unsigned int>(std::max(1, std::atoi(v)));
+    if (const char* v = std::getenv("GCR_DEBUG_FLOOR_BUMP")) h->dbg_floor_bump = std::atof(v);
     if (const char* v = std::getenv("GCR_WORKLIST_CAP")) h->worklist_cap_override = static_cast<unsigned int>(std::max(1, std::atoi(v)));
     if (const char* v = std::getenv("GCR_RESIDENT_MAX_HYP")) h->resident_max_hyp = h->resident_max_evals = std::atoll(v);
     if (const char* v = std::getenv("GCR_RESIDENT_MAX_EVALS")) h->resident_max_evals = std::atoll(v);

@@ -853,7 +853,7 @@ __device__ __forceinline__ void contender_collect_phase(const Buffers& B, const 
         const double v = hyp_value_w(B, T, h, f, err);
         if (!(v + err > 0.0) || v + err < floor_v) return;
         const unsigned int slot = atomicAdd(&B.ts->n_cont, 1u);
-        if (slot >= kContCap)
+        if (slot >= B.cont_cap)
         {
             B.ts->cont_overflow = 1u;
             return;
@@ -1270,7 +1270,7 @@ __device__ __forceinline__ void select_phase(const Buffers& B, const Thresholds&
             }
             if (final)
             {
-                B.ctr->n_refined = min(B.ts->n_cont, static_cast<unsigned int>(kContCap));
+                B.ctr->n_refined = min(B.ts->n_cont, B.cont_cap);
                 *B.ctr_snap = B.ctr[0];
                 Counters z;
                 memset(&z, 0, sizeof(z));
@@ -1331,7 +1331,7 @@ __global__ void __launch_bounds__(kExactThreads) k_tail(const __grid_constant__ 
         const unsigned long long k0 = __ldcg(&B.ctr->best_key);
         if (k0)
         {
-            floor_loose = from_ordered_bits(k0);
+            floor_loose = from_ordered_bits(k0) + B.dbg_floor_bump; // (tests raise the first bar to force a second contender round)
             for (;;)
             {
                 contender_collect_phase(B, T, floor_loose, n_cont == 0u);
@@ -1339,10 +1339,10 @@ __global__ void __launch_bounds__(kExactThreads) k_tail(const __grid_constant__ 
 #ifdef GCR_TAIL_DEBUG
                 if (stamp) B.phase_ns[3] = global_ns();
 #endif
-                const unsigned int n_now = min(__ldcg(&B.ts->n_cont), static_cast<unsigned int>(kContCap));
+                const unsigned int n_now = min(__ldcg(&B.ts->n_cont), B.cont_cap);
                 const bool overflow = __ldcg(&B.ts->cont_overflow) != 0u;
                 if (n_cont == 0u) spec_cands = min(__ldcg(&B.ts->n_cont), kDirectCand);
-                if (n_cont == 0u && n_now <= kDirectCand && !overflow && !__ldcg(&B.ts->unproven))
+                if (n_cont == 0u && n_now >= 1u && n_now <= kDirectCand && !overflow && !__ldcg(&B.ts->unproven))
                 {
                     // a handful of contenders whose scores cannot be reset (small scenes: the loose bound is already tight): their FP64
                     // scoring is cheaper than the refinement round and its two barriers

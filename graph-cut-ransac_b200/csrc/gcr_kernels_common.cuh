@@ -163,6 +163,8 @@ struct Buffers
     unsigned int* cont_n;           // [kContCap,2] exact inlier counts
     double* cont_val;               // [kContCap,2] refined value, error bound
     TailState* ts;
+    unsigned int cont_cap;          // contender slots in use (kContCap; tests lower it to force the overflow path)
+    double dbg_floor_bump;          // tests only: added to the first contender bar (forces the bar-lowering round); 0
     Counters* ctr;      // live counters of the run in flight
     Counters* ctr_snap; // snapshot for the host, written by the last kernel
     unsigned long long* phase_ns; // [8] %globaltimer at the phase boundaries of k_tail

@@ -197,3 +197,30 @@ def test_winner_only_scale_only_problems(eng, port):
         assert int(b["n_inl"][0]) == int(ora["n_inl"][want][0] if ora["n_inl"].ndim == 2 else ora["n_inl"][want])
         assert np.array_equal(b["scale_words"], ora["masks"][want][:len(b["scale_words"])])
         e.close()
+
+
+def test_selection_cascade_rare_paths(port):
+    """The paths of the winner-only selection that ordinary data rarely takes, forced through the engine's test switches: the
+    contender slots run out (GCR_CONT_CAP: the stragglers go straight to the FP64 level by their loose bound), and the first contender
+    bar turns out too high (GCR_DEBUG_FLOOR_BUMP: no contender above it, or a refined lower bound below it -> the bar is lowered and
+    the round repeats).  Same winner, score, counts and masks as the oracle every time."""
+    import os
+    import gcr_capi
+    import gcr_scenes as gs
+    sc = gs.make_scene(1500, 500, 0.3, 91)
+    smp = gs.draw_samples(30_000, 1500, 500, 92)
+    # near-duplicates of the best sample make a crowd of contenders
+    ora = port.replay(sc.scale, sc.orient, smp[:4000], sc.thr, want_masks=False, nthreads=0)
+    best = port.select_best(ora["score"], ora["flags"])
+    smp[10_000:10_200] = smp[best]
+    for env in ({"GCR_CONT_CAP": "3"}, {"GCR_CONT_CAP": "40"}, {"GCR_DEBUG_FLOOR_BUMP": "5.0"}, {"GCR_DEBUG_FLOOR_BUMP": "1e9"},
+                {"GCR_DEBUG_FLOOR_BUMP": "0.5", "GCR_CONT_CAP": "17"}):
+        os.environ.update(env)
+        try:
+            e = gcr_capi.Engine(0)
+        finally:
+            for k in env:
+                del os.environ[k]
+        for n in (len(smp), 12_000, 4000):
+            _check_winner(e, port, sc.scale, sc.orient, smp[:n], sc.thr, f"{env} n={n}")
+        e.close()

@@ -10,7 +10,11 @@ for name in sys.argv[1:] or ["C2"]:
     e = gcr_capi.Engine(0); e.set_features(sc.scale, sc.orient)
     d = torch.from_numpy(smp).cuda()
     for _ in range(3): r = e.run(c["n_hyp"], sc.thr, samples_ptr=d.data_ptr())
-    rs = [e.run(c["n_hyp"], sc.thr, samples_ptr=d.data_ptr(), flags=gcr_capi.RUN_TIME_KERNELS if os.environ.get("TIME_KERNELS") else 0) for _ in range(10)]  # the event bracket switches the chained (PDL) launches off
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda") if os.environ.get("FLUSH") else None  # cold L2 per run, as bench.py
+    rs = []
+    for _ in range(10):
+        if flush is not None: flush.zero_(); torch.cuda.synchronize()
+        rs.append(e.run(c["n_hyp"], sc.thr, samples_ptr=d.data_ptr(), flags=gcr_capi.RUN_TIME_KERNELS if os.environ.get("TIME_KERNELS") else 0))  # the event bracket switches the chained (PDL) launches off
     ph = np.median([list(r.tail_phase_us) + list(r.stage_phase_us) for r in rs], axis=0)
     print(name, "stage_ms %.4f score_ms %.4f" % (np.median([r.device_ms for r in rs]), np.median([r.score_kernel_ms for r in rs])),
           "tail phases us (fix+exact | finalize | collect | rescoring | select):", np.round(ph[:5], 2), "sum %.2f" % ph[:5].sum(),
