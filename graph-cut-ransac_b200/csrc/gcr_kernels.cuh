@@ -193,6 +193,7 @@ struct PathBands
     double drho32, dprime32;  // FP32 tiles
     double drho64, dprime64;  // FP64 front end
     bool ok32, ok64, common_ok;
+    bool ok32_bound; // the FP32 bands are VALID (finite, v stays positive over the inlier range) though possibly wide
 };
 __device__ __forceinline__ PathBands path_bands(const Model4& m, const Scene& sc, const Thresholds& T, bool all_exact)
 {
@@ -209,7 +210,8 @@ __device__ __forceinline__ PathBands path_bands(const Model4& m, const Scene& sc
     const double dv = 8.0 * kU * mag;
     r.drho32 = 2.0 * (dv / ((v_lo - dv) * kLn2) + eps_lg);
     r.dprime32 = 6.0 * kU * (2.0 + 3.0 * kh) * 1.0001;
-    r.ok32 = isfinite(dv) && (v_lo > 4.0 * dv) && (r.drho32 < 1e-3 * Tp) && (r.dprime32 < 1e-3 * T.tanT);
+    r.ok32_bound = isfinite(dv) && (v_lo > 4.0 * dv) && isfinite(r.drho32) && isfinite(r.dprime32);
+    r.ok32 = r.ok32_bound && (r.drho32 < 1e-3 * Tp) && (r.dprime32 < 1e-3 * T.tanT);
     const double kU64 = 1.1102230246251565e-16;
     const double dv64 = 8.0 * kU64 * mag;
     r.drho64 = 2.0 * (dv64 / ((v_lo - dv64) * kLn2) + 1.5 * kU / kLn2 + eps_lg);
@@ -323,7 +325,11 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
             // The 1e-3 caps keep the FP32 residuals of the inliers within the 1e-5 score bar; hypotheses that
             // miss them in FP32 (tiny alpha: cancellation in v; large |h|: angle noise) go to the precise tiles,
             // the rest (out of any proven range) to the FP64 reference-order kernel.
-            if (pb.common_ok && pb.ok32) { }
+            // (A winner-only run needs no narrow bands, only valid ones: a wide band widens that hypothesis' error bound -- such models, tiny
+            //  alpha or large |h|, score poorly and do not become contenders -- and the precise tiles, twice the cost per evaluation plus an
+            //  F2F conversion on the XU pipe, shrink from ~4 % of the hypotheses to the few whose FP32 v could change sign.  Same-box A/B:
+            //  C3 kernel 5.558 -> 5.384 ms, 125k-slot shard 0.724 -> 0.693 ms, C5 0.214 -> 0.208 ms, 11 instead of 1 contenders at C3.)
+            if (pb.common_ok && (winner ? pb.ok32_bound : pb.ok32)) { }
             else if (pb.common_ok && pb.ok64)
             {
                 sens_s = true;
@@ -1342,7 +1348,9 @@ __global__ void __launch_bounds__(kExactThreads) k_tail(const __grid_constant__ 
                 const unsigned int n_now = min(__ldcg(&B.ts->n_cont), B.cont_cap);
                 const bool overflow = __ldcg(&B.ts->cont_overflow) != 0u;
                 if (n_cont == 0u) spec_cands = min(__ldcg(&B.ts->n_cont), kDirectCand);
-                if (n_cont == 0u && n_now >= 1u && n_now <= kDirectCand && !overflow && !__ldcg(&B.ts->unproven))
+                // (... and whose FP64 scoring is at most one wave of the grid: one candidate of a 70 000-feature scene, sixteen of a 2 500-feature one)
+                if (n_cont == 0u && n_now >= 1u && n_now <= kDirectCand && !overflow && !__ldcg(&B.ts->unproven) &&
+                    static_cast<unsigned long long>(n_now) * static_cast<unsigned int>(B.ns + B.no) <= static_cast<unsigned long long>(gridDim.x) * blockDim.x)
                 {
                     // a handful of contenders whose scores cannot be reset (small scenes: the loose bound is already tight): their FP64
                     // scoring is cheaper than the refinement round and its two barriers

@@ -20,7 +20,7 @@ for rnd in range(12):
     for lib, e in zip(libs, engines):
         if flush is not None: flush.zero_(); torch.cuda.synchronize()
         r = e.run(c["n_hyp"], sc.thr, samples_ptr=smp.data_ptr(), flags=gcr_capi.RUN_TIME_KERNELS)
-        win[lib] = (r.best_index, r.best_score, r.n_scored, r.n_candidates, r.n_exact_hyp)
+        win[lib] = (r.best_index, r.best_score, r.n_scored, r.n_refined, r.n_candidates, r.n_exact_hyp)
         if rnd >= 2:
             res[lib][0].append(r.score_kernel_ms); res[lib][1].append(r.device_ms)
 for lib in libs:
