@@ -527,6 +527,37 @@ static cudaError_t launch_chained(gcr_engine_s* h, void (*kernel)(KArgs...), dim
     return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
+// ------------------------------------------------------------------------------------------------
+// gcr_score_models_static: scratch of the batched FP64 model scoring in a file-scope device array instead of engine-owned allocations
+// (callers that must not allocate: CUDA graph capture, tight serving loops).  1 MiB per GPU that loads the library, held until exit.
+// In HOST code the array's name is a host-side stand-in, not a device address: the address the kernels get comes from
+// cudaGetSymbolAddress, resolved once per device with that device current (static_scratch_address).
+constexpr size_t kStaticScratchBytes = size_t(1) << 20;
+constexpr int kStaticMaxModels = 1024;
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+// fixed part of the layout, for kStaticMaxModels models: [Model4 32 KB][hyp u32 4 KB][qsum u64 x2 16 KB][rawcnt u32 x2 8 KB]
+// [score f64 8 KB][cnt u32 x2 8 KB] = 76 KB; the rest holds the packed masks of the n models (n x W words)
+constexpr size_t kStaticOffModel = 0, kStaticOffHyp = kStaticOffModel + 32 * kStaticMaxModels, kStaticOffQsum = kStaticOffHyp + 4 * kStaticMaxModels,
+                 kStaticOffRaw = kStaticOffQsum + 16 * kStaticMaxModels, kStaticOffScore = kStaticOffRaw + 8 * kStaticMaxModels,
+                 kStaticOffCnt = kStaticOffScore + 8 * kStaticMaxModels, kStaticOffMasks = kStaticOffCnt + 8 * kStaticMaxModels;
+static_assert(kStaticOffMasks % 256 == 0 && kStaticOffMasks < kStaticScratchBytes, "static scratch layout");
+constexpr int kStaticMaxDevices = 64;
+static unsigned char* g_static_scratch_ptr[kStaticMaxDevices] = {};
+
+// device address of g_static_scratch on the CURRENT device (= `device`); no allocation
+static cudaError_t static_scratch_address(int device, unsigned char** out)
+{
+    if (!g_static_scratch_ptr[device])
+    {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess) return e;
+        g_static_scratch_ptr[device] = static_cast<unsigned char*>(p); // (racing first calls resolve the same address)
+    }
+    *out = g_static_scratch_ptr[device];
+    return cudaSuccess;
+}
+
 // Device-side failures of the last run, from the counter snapshot its last kernel wrote into the result block.  The reference throws
 // rather than continue on bad input (GCRANSAC.h:222-228); an asynchronous caller (gcr_run with out == NULL) learns of them from
 // gcr_best / gcr_fetch.
@@ -1405,6 +1436,78 @@ int gcr_debug_eval(gcr_handle h, int which, const double* in, int64_t n, const d
     GCR_CUDA(cudaGetLastError());
     GCR_CUDA(cudaMemcpyAsync(out, h->d_dbg_out.p, sizeof(double) * n, cudaMemcpyDeviceToHost, h->stream));
     GCR_CUDA(cudaStreamSynchronize(h->stream));
+    return GCR_OK;
+}
+
+int gcr_score_models_static(int device, const double* d_scale, int64_t ns, const double* d_orient, int64_t no, const double* d_models, int64_t n,
+                            const double thr[2], uint32_t flags, double* d_score, uint32_t* d_n_inl, uint32_t* d_mask_words, void* cuda_stream,
+                            char* err, size_t err_cap)
+{
+    auto fail = [&](int code, const char* msg) {
+        if (err && err_cap) std::snprintf(err, err_cap, "%s", msg);
+        return code;
+    };
+    if (err && err_cap) err[0] = 0;
+    if (!d_scale || !d_orient || !d_models || !thr) return fail(GCR_ERR_INVALID, "gcr_score_models_static: null input pointer");
+    if (device < 0 || device >= kStaticMaxDevices) return fail(GCR_ERR_INVALID, "gcr_score_models_static: device index out of range (0..63)");
+    if (ns < 2 || no < 2 || ns > (1ll << 30) || no > (1ll << 30))
+        return fail(GCR_ERR_INVALID, "gcr_score_models_static: each feature class needs 2 .. 2^30 rows (hybrid problem only)");
+    if (n < 1 || n > kStaticMaxModels) return fail(GCR_ERR_INVALID, "gcr_score_models_static: 1 <= n <= 1024 models per call");
+    if (!(thr[0] >= 0.0) || !std::isfinite(thr[0]) || !(thr[1] >= 0.0) || !std::isfinite(thr[1]))
+        return fail(GCR_ERR_INVALID, "gcr_score_models_static: thresholds must be finite and non-negative");
+    const size_t W = static_cast<size_t>((ns + 31) / 32 + (no + 31) / 32);
+    if (static_cast<size_t>(n) * W * 4 > kStaticScratchBytes - kStaticOffMasks)
+    {
+        char msg[256];
+        std::snprintf(msg, sizeof(msg), "gcr_score_models_static: n x mask words = %lld x %zu exceeds the static scratch (%zu words: 1 MiB array, 76 KB of it "
+                      "accumulators); score fewer models per call or use gcr_score_models", static_cast<long long>(n), W, (kStaticScratchBytes - kStaticOffMasks) / 4);
+        return fail(GCR_ERR_INVALID, msg);
+    }
+    DeviceGuard device_guard_(device);
+    if (device_guard_.err != cudaSuccess) return fail(GCR_ERR_CUDA, cudaGetErrorString(device_guard_.err));
+    unsigned char* sp = nullptr;
+    cudaError_t e = static_scratch_address(device, &sp);
+    if (e != cudaSuccess) return fail(GCR_ERR_CUDA, cudaGetErrorString(e));
+
+    Thresholds T = make_thresholds(thr, GCR_PROBLEM_HYBRID);
+    if (flags & GCR_SCORE_TRUNCATED_SQ)
+    {
+        T.tsq[0] = (1.5 * thr[0]) * (1.5 * thr[0]);
+        T.tsq[1] = (1.5 * thr[1]) * (1.5 * thr[1]);
+    }
+    T.strict = (flags & GCR_SCORE_STRICT) ? 1 : 0;
+    Buffers B;
+    std::memset(&B, 0, sizeof(B));
+    B.scale = d_scale;
+    B.orient = d_orient;
+    B.ns = static_cast<int>(ns);
+    B.no = static_cast<int>(no);
+    B.ws = (B.ns + 31) / 32;
+    B.wmask = static_cast<int>(W);
+    B.cand_model = reinterpret_cast<Model4*>(sp + kStaticOffModel);
+    B.cand_hyp = reinterpret_cast<unsigned int*>(sp + kStaticOffHyp);
+    B.cand_qsum = reinterpret_cast<unsigned long long*>(sp + kStaticOffQsum);
+    B.cand_rawcnt = reinterpret_cast<unsigned int*>(sp + kStaticOffRaw);
+    B.cand_score = reinterpret_cast<double*>(sp + kStaticOffScore);
+    B.cand_cnt = reinterpret_cast<unsigned int*>(sp + kStaticOffCnt);
+    B.cand_masks = reinterpret_cast<unsigned int*>(sp + kStaticOffMasks);
+
+    cudaStream_t s = static_cast<cudaStream_t>(cuda_stream);
+    const unsigned int un = static_cast<unsigned int>(n);
+    const unsigned long long units =
+        static_cast<unsigned long long>(un) * ((B.ns + kExactThreads - 1) / kExactThreads + (B.no + kExactThreads - 1) / kExactThreads);
+    int n_sm = 148;
+    cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, device);
+    const int grid = static_cast<int>(std::min<unsigned long long>(units, static_cast<unsigned long long>(n_sm) * 8));
+    // the same three kernels as gcr_score_models, plain launches in stream order: models -> scratch and cleared accumulators (the array keeps
+    // the last call's contents) | FP64 reference-order scoring (every mask word of every model is written) | values, counts, masks -> caller
+    k_set_models<<<(un + 127) / 128, 128, 0, s>>>(B, reinterpret_cast<const Model4*>(d_models), un);
+    k_exact_items<<<grid, kExactThreads, 0, s>>>(B, T, 2, un);
+    // (outputs the caller did not ask for land in the scratch's own value / count slots)
+    k_score_out<<<std::max(1, std::min<int>(n_sm, static_cast<int>((W * n + 255) / 256))), 256, 0, s>>>(
+        B, T, un, d_score ? d_score : B.cand_score, d_n_inl ? d_n_inl : B.cand_cnt, d_mask_words);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(GCR_ERR_CUDA, cudaGetErrorString(e));
     return GCR_OK;
 }
 

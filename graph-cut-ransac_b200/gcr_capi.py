@@ -26,7 +26,7 @@ EXPORTS = [
     "gcr_create", "gcr_destroy", "gcr_last_error", "gcr_set_stream", "gcr_wait_stream", "gcr_set_problem", "gcr_set_features", "gcr_get_features", "gcr_run",
     "gcr_best",
     "gcr_fetch", "gcr_score_model", "gcr_score_models", "gcr_fit_models", "gcr_set_keypoints", "gcr_debug_eval", "gcr_version", "gcr_peer_export",
-    "gcr_peer_attach", "gcr_peer_buffer", "gcr_peer_attach_ptrs", "gcr_peer_detach",
+    "gcr_peer_attach", "gcr_peer_buffer", "gcr_peer_attach_ptrs", "gcr_peer_detach", "gcr_score_models_static",
 ]
 
 
@@ -83,6 +83,7 @@ def load_library() -> C.CDLL:
     lib.gcr_peer_attach_ptrs.argtypes = [vp, C.POINTER(vp), C.c_int, C.c_int]
     lib.gcr_peer_detach.argtypes = [vp]
     lib.gcr_debug_eval.argtypes = [vp, C.c_int, vp, i64, vp, vp]
+    lib.gcr_score_models_static.argtypes = [C.c_int, vp, i64, vp, i64, vp, i64, C.POINTER(C.c_double), u32, vp, vp, vp, vp, C.c_char_p, C.c_size_t]
     lib.gcr_version.restype = C.c_char_p
     for name in EXPORTS:
         fn = getattr(lib, name)

@@ -25,6 +25,7 @@
 #ifndef GCR_B200_H
 #define GCR_B200_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -236,6 +237,27 @@ int gcr_score_models(gcr_handle h, const double* models, int64_t n, const double
  * model: too few constraints, non-finite solution, alpha < 1e-9).  Parity: model <= 1e-6 relative.  Synchronises. */
 int gcr_fit_models(gcr_handle h, int64_t n_fits, const uint32_t* scale_idx, const int64_t* scale_off,
                    const uint32_t* orient_idx, const int64_t* orient_off, double* models, int32_t* ok);
+
+/* Allocation-free batched model scoring.  NO COUNTERPART IN THE REFERENCE: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The same computation as
+ * gcr_score_models for the hybrid problem -- MSACScoringFunction::getScore of n caller-supplied models in FP64 reference order -- without an
+ * engine handle: the three kernels' scratch (model copies, fixed-point accumulators, counts, packed masks) lives in a file-scope
+ * `static __device__` array of 1 MiB that every GPU loading the library holds until exit; the call performs no cudaMalloc / cudaFree /
+ * allocating library call and does not synchronise.
+ *   device                      CUDA device index (0..63) the pointers live on; the caller's current device is restored
+ *   d_scale f64[ns,3], d_orient f64[no,3], d_models f64[n,4] = (h7, h8, alpha, phi)      DEVICE pointers, caller-owned inputs
+ *   thr, flags                  as gcr_score_models (GCR_SCORE_TRUNCATED_SQ, GCR_SCORE_STRICT)
+ *   d_score f64[n], d_n_inl u32[n,2] (after the zero-reset rule), d_mask_words u32[n, ceil(ns/32)+ceil(no/32)]
+ *                               DEVICE pointers, caller-owned outputs, any may be NULL; valid once `cuda_stream` has passed the call
+ *   cuda_stream                 a cudaStream_t (NULL = the legacy default stream): the kernels run there, in stream order
+ *   err, err_cap                optional buffer for a message when the call fails (this entry point has no handle to ask)
+ * Limits (GCR_ERR_INVALID with a message beyond them): 1 <= n <= 1024 models and n x (ceil(ns/32) + ceil(no/32)) <= 242 688 mask words
+ * (e.g. 1024 models x 7 500 features, 110 models x 70 000 features); ns, no >= 2.
+ * The array is SHARED by every call in the process on that GPU and keeps the last call's contents (the call clears what must start at
+ * zero): calls that overlap on the GPU -- issued to different streams without ordering between them -- race on it; serialise them. */
+int gcr_score_models_static(int device, const double* d_scale, int64_t ns, const double* d_orient, int64_t no, const double* d_models, int64_t n,
+                            const double thr[2], uint32_t flags, double* d_score, uint32_t* d_n_inl, uint32_t* d_mask_words, void* cuda_stream,
+                            char* err, size_t err_cap);
 
 /* Device-side helper math, evaluated on the GPU by the same __device__ functions the kernels use.
  * which: 0 clipAngle(a) 1 minAngleDiff(a,b) 2 linesAnglesDiff(a,b)
