@@ -42,6 +42,10 @@ def main():
             s_rows = np.vstack([s_rows, sc.scale[~sc.scale_is_inlier][:6]])
             o_rows = np.vstack([o_rows, sc.orient[~sc.orient_is_inlier][:3]])
         m = ref.fit_nonminimal(s_rows, o_rows)
+        # the reference's linear solve ran through oracle/shim's QR: cross-check every golden fit against LAPACK (tests/lsq_independent.py)
+        import lsq_independent
+        x = lsq_independent.fit(s_rows, o_rows)
+        assert (x is None) == (m is None) and (x is None or np.allclose(x, m[3:6], rtol=1e-10, atol=0.0)), (k, x, m)
         out[f"fit{k}_scale"] = s_rows
         out[f"fit{k}_orient"] = o_rows
         out[f"fit{k}_ok"] = np.int64(m is not None)
