@@ -349,9 +349,11 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
                 // <= 2.1 (delta t) / sqrt(tsq), delta t <= dprime / mx + t_band0, + 2.5e-6 (polynomial fit 5e-7, Horner and FFMA.SAT roundings,
                 // the two extra roundings of the shared reciprocal)
                 const double ddq = 0.5 * drho / Tp + 2.0 * kU * (fabs(A) / Tp + 2.0);
-                const double e_s = 2.1 * ddq + 2.0 * kU;
-                const double e_o0 = 2.1 * static_cast<double>(T.t_band0) / static_cast<double>(T.sqrt_tsq1) + 2.5e-6;
-                const double e_o1 = 2.1 * dprime / static_cast<double>(T.sqrt_tsq1);
+                // (a term 1 - x^2, |x| <= 1, moves by at most min(1, (2 + d) d) when x moves by d: exact for the per-hypothesis scale part; the
+                //  orientation part is a sum over features of a + b / mx_f, for which 2.5 (a + b / mx_f) >= min(1, 2 x + x^2) at EVERY x >= 0)
+                const double e_s = fmin(1.0, (2.0 + ddq) * ddq) + 2.0 * kU;
+                const double e_o0 = 2.5 * static_cast<double>(T.t_band0) / static_cast<double>(T.sqrt_tsq1) + 2.5e-6;
+                const double e_o1 = 2.5 * dprime / static_cast<double>(T.sqrt_tsq1);
                 const double no_eff = T.problem == 0 ? static_cast<double>(B.no) : 0.0;
                 B.err_ab[h] = make_float2(__double2float_ru(static_cast<double>(B.ns) * e_s + no_eff * e_o0), __double2float_ru(1.001 * e_o1));
                 p0 = make_float4(static_cast<float>(-m.h7), static_cast<float>(-m.h8), static_cast<float>(A / Tp), 0.f);
@@ -362,8 +364,9 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
                 // reporting modes: error of a CERTAIN inlier's term r^2/tsq (guard-band evaluations are re-done in FP64): scale
                 // delta (d/Tp)^2 <= 1.05 drho / Tp (|delta d| <= drho / 2, |d| <= Tp) + 4u; orientation 2.1 (delta t) / sqrt(tsq) with
                 // delta t <= dprime / max + t_band0, + 1.2e-6 for the polynomial (finalize_phase sums them over the counted inliers)
-                B.err_ab[h] = make_float2(__double2float_ru(1.05 * drho / Tp + 4.0 * kU),
-                                          __double2float_ru(2.1 * dprime / static_cast<double>(T.sqrt_tsq1)));
+                const double dd_rep = 0.5 * drho / Tp;
+                B.err_ab[h] = make_float2(__double2float_ru(fmin(1.0, (2.0 + dd_rep) * dd_rep) + 4.0 * kU),
+                                          __double2float_ru(2.5 * dprime / static_cast<double>(T.sqrt_tsq1)));
                 p0 = make_float4(static_cast<float>(-m.h7), static_cast<float>(-m.h8), static_cast<float>(A),
                                  __double2float_rd(Tp - drho));
                 p1 = make_float4(__double2float_ru(Tp + drho), static_cast<float>(cphi), static_cast<float>(sphi),
@@ -671,7 +674,7 @@ __device__ __forceinline__ void finalize_phase(const Buffers& B, const Threshold
     //   err = n0 e_s + e_o1 (sum of 1/max over them) + n1 (2.1 t_band0 / sqrt(tsq) + 1.2e-6) + 8e-6 (n0 + n1)
     // (k_sample_solve's per-hypothesis coefficients err_ab; the last term: FP32 accumulation inside a chunk), kept in err_ab.x for collect_phase
     unsigned long long key = 0ull;
-    const double e_o0 = 2.1 * static_cast<double>(T.t_band0) / fmax(static_cast<double>(T.sqrt_tsq1), 1e-300) + 1.2e-6;
+    const double e_o0 = 2.5 * static_cast<double>(T.t_band0) / fmax(static_cast<double>(T.sqrt_tsq1), 1e-300) + 1.2e-6;
     for (int base = blockIdx.x * blockDim.x; base < B.n_hyp; base += gridDim.x * blockDim.x)
     {
         const int h = base + threadIdx.x;
@@ -832,9 +835,21 @@ __device__ __forceinline__ void publish_key(unsigned long long* dst, unsigned lo
 }
 
 // level 1: best LOWER bound over the hypotheses that may have a positive score (S11: a model needs one)
-__device__ __forceinline__ void finalize_phase_w(const Buffers& B, const Thresholds& T)
+// What a thread met in finalize_phase_w, kept in registers across the barrier: (hypothesis, upper bound) of up to kUbCache hypotheses, so that
+// the first contender collection decides from registers instead of walking the lists and re-loading five arrays per hypothesis again.
+constexpr int kUbCache = 4;
+struct UbCache
+{
+    unsigned int h[kUbCache];
+    double ub[kUbCache];
+    int n;         // entries held
+    bool overflow; // this thread met more than kUbCache hypotheses: it walks its share of the lists again
+};
+__device__ __forceinline__ void finalize_phase_w(const Buffers& B, const Thresholds& T, UbCache& cache)
 {
     unsigned long long key = 0ull;
+    cache.n = 0;
+    cache.overflow = false;
     for_each_scored_valid(B, [&](unsigned int h, unsigned char f) {
         double err;
         const double v = hyp_value_w(B, T, h, f, err);
@@ -842,6 +857,19 @@ __device__ __forceinline__ void finalize_phase_w(const Buffers& B, const Thresho
         {
             const unsigned long long k = ordered_bits(v - err);
             key = k > key ? k : key;
+            if (cache.n < kUbCache)
+            {
+#pragma unroll
+                for (int i = 0; i < kUbCache; i++) // (static indices: the arrays stay in registers)
+                    if (i == cache.n)
+                    {
+                        cache.h[i] = h;
+                        cache.ub[i] = v + err;
+                    }
+                cache.n++;
+            }
+            else
+                cache.overflow = true;
         }
     });
     publish_key(&B.ctr->best_key, key);
@@ -851,9 +879,10 @@ __device__ __forceinline__ void finalize_phase_w(const Buffers& B, const Thresho
 // derives the refinement's parameters (FP64 model, FP32 band limits of the FP64-front arithmetic).  Slots beyond kContCap: the overflow flag
 // sends the stragglers straight to level 3.
 constexpr unsigned int kDirectCand = 16;
-__device__ __forceinline__ void contender_collect_phase(const Buffers& B, const Thresholds& T, double floor_v, bool speculate)
+__device__ __forceinline__ void contender_collect_phase(const Buffers& B, const Thresholds& T, double floor_v, bool speculate,
+                                                        const UbCache* cache = nullptr)
 {
-    for_each_scored_valid(B, [&](unsigned int h, unsigned char f) {
+    auto consider = [&](unsigned int h, unsigned char f) {
         if (f & 32) return; // already a contender
         double err;
         const double v = hyp_value_w(B, T, h, f, err);
@@ -891,8 +920,9 @@ __device__ __forceinline__ void contender_collect_phase(const Buffers& B, const 
         //   orientation  |delta t| <= 2 band0r (evaluations whose dprime64 / mx exceeds band0r are sent to FP64)  ->  2.1 * 2 band0r / sqrt(tsq),
         //                + 1.2e-6 for the polynomial fit (5e-7) and its FP32 evaluation
         const double band0r = 8.0 * kU * static_cast<double>(T.tanT) + 1e-12;
-        P.e_s = __double2float_ru(1.05 * pb.drho64 / Tp + 4.0 * kU);
-        P.e_o = __double2float_ru(4.2 * band0r / static_cast<double>(T.sqrt_tsq1) + 1.2e-6);
+        const double dd_ref = 0.5 * pb.drho64 / Tp;
+        P.e_s = __double2float_ru(fmin(1.0, (2.0 + dd_ref) * dd_ref) + 4.0 * kU);
+        P.e_o = __double2float_ru(5.0 * band0r / static_cast<double>(T.sqrt_tsq1) + 1.2e-6);
         P.ri_cap = __double2float_rd(band0r / fmax(pb.dprime64, 1e-300));
         P.band0r = __double2float_ru(band0r);
         B.cont_par[slot] = P;
@@ -901,7 +931,16 @@ __device__ __forceinline__ void contender_collect_phase(const Buffers& B, const 
         // first round: the first few contenders also take candidate slots at once; when they turn out to be all there is (and none can
         // lose its score to the zero-reset rule) the FP64 level starts without a collection pass and its barrier
         if (speculate && slot < kDirectCand) collect_candidate(B, h, 0u, f | 32);
-    });
+    };
+    if (cache && !cache->overflow)
+    {
+        // first round: this thread's hypotheses and their upper bounds are still in its registers (finalize_phase_w)
+#pragma unroll
+        for (int i = 0; i < kUbCache; i++)
+            if (i < cache->n && cache->ub[i] >= floor_v) consider(cache->h[i], B.flags[cache->h[i]]);
+        return;
+    }
+    for_each_scored_valid(B, consider);
 }
 
 // level 2, evaluation: unit = (contender, 256 consecutive features of one class), thread <-> feature.  The three cancelling FMAs
@@ -1025,6 +1064,87 @@ __device__ __forceinline__ void refine_phase(const Buffers& B, const Thresholds&
     }
 }
 
+// The same evaluation for a FEW contenders (<= kRefineFewMax): thread <-> feature, the unit's features held in registers while the contenders
+// pass over them, one warp reduction + one pair of atomics per warp and contender.  The lane-per-contender form above executes all 32 lanes'
+// worth of arithmetic per feature whatever the number of contenders (21-25 us at C3 for 3-12 of them); this one costs ~0.7 us per contender.
+constexpr unsigned int kRefineFewMax = 24;
+__device__ __forceinline__ void refine_phase_few(const Buffers& B, const Thresholds& T, unsigned int c_first, unsigned int c_end)
+{
+    constexpr int kCD = kChunk / 2;
+    if (c_end <= c_first) return;
+    const unsigned int fbs = (B.ns + kExactThreads - 1) / kExactThreads, fbo = (B.no + kExactThreads - 1) / kExactThreads, n_units = fbs + fbo;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const double unit_s = static_cast<double>(T.scale_unit);
+    for (unsigned int u = blockIdx.x; u < n_units; u += gridDim.x)
+    {
+        const int cls = u >= fbs;
+        const int f = static_cast<int>((cls ? u - fbs : u) * kExactThreads) + tid;
+        const int n = cls ? B.no : B.ns;
+        double pa = 0.0, pb = 0.0, pc = 0.0;
+        bool bad = false; // irregular feature (sentinel plane value): FP64 decides
+        if (f < n)
+        {
+            const double* pl = (cls ? B.fod : B.fsd) + static_cast<size_t>(f / kCD) * (3 * kCD) + (f % kCD);
+            pa = pl[0];
+            pb = pl[kCD];
+            pc = pl[2 * kCD];
+            bad = cls ? (pb != pb) : !(pc < 1e300);
+        }
+        for (unsigned int c = c_first; c < c_end; c++)
+        {
+            const ContPar P = B.cont_par[c];
+            if (P.exact) continue; // (uniform) already scored in FP64
+            bool in = false, fallback = false;
+            double r2 = 0.0;
+            if (f < n)
+            {
+                if (cls == 0)
+                {
+                    const float v = static_cast<float>(fma(-P.h8, pb, fma(-P.h7, pa, pc)));
+                    const float d = P.A - lg2_approx(v);
+                    in = fabsf(d) <= P.Tin;
+                    fallback = (!in && fabsf(d) <= P.Tout) || bad;
+                    r2 = static_cast<double>(d) * static_cast<double>(d) * unit_s;
+                }
+                else
+                {
+                    const double nn = fma(pa, -P.h7, pb), dd = fma(pa, P.h8, pc);
+                    const double c1 = fma(nn, P.sphi, dd * P.cphi), s1 = fma(nn, P.cphi, -(dd * P.sphi));
+                    const float a1 = static_cast<float>(fabs(c1)), a2 = static_cast<float>(fabs(s1));
+                    const float mn = fminf(a1, a2), mx = fmaxf(fmaxf(a1, a2), 1e-30f);
+                    const float ri = rcp_approx(mx);
+                    const float t = mn * ri;
+                    const float band = fmaf(P.dpr, ri, P.band0r);
+                    const bool wide = !(ri <= P.ri_cap);
+                    in = !wide && t <= T.tanT - band;
+                    fallback = (!in && t <= T.tanT + band) || bad;
+                    const float z = t * t;
+                    r2 = static_cast<double>(z * fmaf(fmaf(fmaf(T.pc[3], z, T.pc[2]), z, T.pc[1]), z, T.pc[0]));
+                }
+                if (fallback)
+                {
+                    const Model4 m = B.models[P.hyp];
+                    const double* F = cls ? B.orient : B.scale;
+                    const double r = cls ? orientation_residual(F[3 * f], F[3 * f + 1], F[3 * f + 2], m)
+                                         : scale_residual(F[3 * f], F[3 * f + 1], F[3 * f + 2], m, T.problem == 2);
+                    r2 = r * r;
+                    in = r2 <= T.tsq[cls]; // S1
+                }
+            }
+            unsigned long long q = in ? static_cast<unsigned long long>(fmin(r2 / T.tsq[cls], 1.0) * kFix + 0.5) : 0ull;
+            const unsigned int cnt = __popc(__ballot_sync(0xffffffffu, in));
+            if (cnt == 0u) continue; // (warp-uniform)
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+            if (lane == 0)
+            {
+                atomicAdd(&B.cont_q[2 * c + cls], q);
+                atomicAdd(&B.cont_n[2 * c + cls], cnt);
+            }
+        }
+    }
+}
+
 // level 2, values: refined value (exact counts: zero-reset rule S3 applied) and its error bound per contender; best refined lower bound
 __device__ __forceinline__ void contender_value_phase(const Buffers& B, const Thresholds& T, unsigned int c_first, unsigned int c_end)
 {
@@ -1052,12 +1172,64 @@ __device__ __forceinline__ void contender_value_phase(const Buffers& B, const Th
     publish_key(&B.ts->lb_ref_key, key);
 }
 
+// level 2, values, FEW contenders (all of them fit one CTA's threads): every CTA computes every contender's refined value and the best refined
+// lower bound for itself (a few loads per thread and one block reduction: cheaper than a pass of the grid and its barrier); CTA 0 also records
+// them.  Thread c keeps contender c's value and bound for the collection that follows (collect_phase_w, few form).
+__device__ __forceinline__ double contender_value_local(const Buffers& B, const Thresholds& T, unsigned int n_cont, double& v_c, double& err_c)
+{
+    __shared__ unsigned long long s_lbk[kExactThreads / 32];
+    unsigned long long key = 0ull;
+    v_c = 0.0;
+    err_c = 0.0;
+    const unsigned int c = threadIdx.x;
+    if (c < n_cont)
+    {
+        const ContPar P = B.cont_par[c];
+        unsigned int n0, n1;
+        if (P.exact) v_c = hyp_value(B, T, P.hyp, B.flags[P.hyp], n0, n1);
+        else
+        {
+            v_c = msac_value(T, fix_to_double(__ldcg(&B.cont_q[2 * c]), T.tsq[0]), fix_to_double(__ldcg(&B.cont_q[2 * c + 1]), T.tsq[1]),
+                             __ldcg(&B.cont_n[2 * c]), __ldcg(&B.cont_n[2 * c + 1]), n0, n1);
+            err_c = static_cast<double>(n0) * P.e_s + static_cast<double>(n1) * P.e_o + 1e-12 * static_cast<double>(n0 + n1) + 1e-12;
+        }
+        if (blockIdx.x == 0)
+        {
+            B.cont_val[2 * c] = v_c;
+            B.cont_val[2 * c + 1] = err_c;
+        }
+        if (v_c > 0.0) key = ordered_bits(v_c - err_c);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        const unsigned long long other = __shfl_xor_sync(0xffffffffu, key, o);
+        key = other > key ? other : key;
+    }
+    __syncthreads(); // (s_lbk may still be read from an earlier round)
+    if ((threadIdx.x & 31) == 0) s_lbk[threadIdx.x >> 5] = key;
+    __syncthreads();
+    for (unsigned int w = 0; w < blockDim.x / 32; w++) key = s_lbk[w] > key ? s_lbk[w] : key;
+    if (blockIdx.x == 0 && threadIdx.x == 0 && key) atomicMax(&B.ts->lb_ref_key, key); // (for a later, crowded round's collection)
+    return key ? from_ordered_bits(key) : -1.0;
+}
+
 // level 3, collection: contenders whose refined upper bound reaches the best refined lower bound (the reference's winner, and everything
 // tied with it, is among them: its true value is >= every other true value >= every lower bound); after a contender overflow also every
 // hypothesis that found no slot, by its loose bound.  Later rounds: the deferred ones (more than kCandCap candidates: massive ties).
 __device__ __forceinline__ void collect_phase_w(const Buffers& B, const Thresholds& T, int round, unsigned int base, unsigned int n_cont,
-                                                double floor_loose, bool direct)
+                                                double floor_loose, bool direct, bool few, double v_c, double err_c, double lb_local)
 {
+    if (few && round == 0)
+    {
+        // thread c of CTA 0 holds contender c's refined value and bound (contender_value_local); no contender overflow in this form
+        if (blockIdx.x == 0 && threadIdx.x < n_cont && v_c > 0.0 && v_c + err_c >= lb_local)
+        {
+            const unsigned int h = B.cont_par[threadIdx.x].hyp;
+            collect_candidate(B, h, base, B.flags[h]);
+        }
+        return;
+    }
     if (round > 0)
     {
         for (int h = blockIdx.x * blockDim.x + threadIdx.x; h < B.n_hyp; h += gridDim.x * blockDim.x)
@@ -1323,11 +1495,12 @@ __global__ void __launch_bounds__(kExactThreads) k_tail(const __grid_constant__ 
     }
     if (stamp) B.phase_ns[1] = global_ns();
     unsigned int n_cont = 0u, spec_cands = 0u;
-    double floor_loose = 0.0;
-    bool direct = false;
+    double floor_loose = 0.0, v_c = 0.0, err_c = 0.0, lb_local = -1.0;
+    bool direct = false, few = false;
     if (winner)
     {
-        finalize_phase_w(B, T);
+        UbCache cache;
+        finalize_phase_w(B, T, cache);
         grid.sync();
 #ifdef GCR_TAIL_DEBUG
         if (stamp) B.phase_ns[2] = global_ns();
@@ -1340,7 +1513,7 @@ __global__ void __launch_bounds__(kExactThreads) k_tail(const __grid_constant__ 
             floor_loose = from_ordered_bits(k0) + B.dbg_floor_bump; // (tests raise the first bar to force a second contender round)
             for (;;)
             {
-                contender_collect_phase(B, T, floor_loose, n_cont == 0u);
+                contender_collect_phase(B, T, floor_loose, n_cont == 0u, n_cont == 0u ? &cache : nullptr);
                 grid.sync();
 #ifdef GCR_TAIL_DEBUG
                 if (stamp) B.phase_ns[3] = global_ns();
@@ -1358,16 +1531,23 @@ __global__ void __launch_bounds__(kExactThreads) k_tail(const __grid_constant__ 
                     direct = true;
                     break;
                 }
-                refine_phase(B, T, n_cont, n_now);
+                few = n_now - n_cont <= kRefineFewMax && n_now <= blockDim.x && !overflow;
+                if (few) refine_phase_few(B, T, n_cont, n_now);
+                else refine_phase(B, T, n_cont, n_now);
                 grid.sync();
 #ifdef GCR_TAIL_DEBUG
                 if (stamp) B.phase_ns[4] = global_ns();
 #endif
-                contender_value_phase(B, T, n_cont, n_now);
-                grid.sync();
+                double lb_ref;
+                if (few) lb_ref = lb_local = contender_value_local(B, T, n_now, v_c, err_c); // (no barrier: every CTA has the same numbers)
+                else
+                {
+                    contender_value_phase(B, T, n_cont, n_now);
+                    grid.sync();
+                    const unsigned long long lk = __ldcg(&B.ts->lb_ref_key);
+                    lb_ref = lk ? from_ordered_bits(lk) : -1.0; // no refined contender has a score yet: everything positive stays in play
+                }
                 n_cont = n_now;
-                const unsigned long long lk = __ldcg(&B.ts->lb_ref_key);
-                const double lb_ref = lk ? from_ordered_bits(lk) : -1.0; // no refined contender has a score yet: everything positive stays in play
                 if (overflow || lb_ref >= floor_loose) break;
                 floor_loose = lb_ref;
             }
@@ -1389,7 +1569,7 @@ __global__ void __launch_bounds__(kExactThreads) k_tail(const __grid_constant__ 
     {
         if (!(direct && round == 0)) // direct: the contenders took their candidate slots when they were collected
         {
-            if (winner) collect_phase_w(B, T, round, cand_base, n_cont, floor_loose, direct);
+            if (winner) collect_phase_w(B, T, round, cand_base, n_cont, floor_loose, direct, few, v_c, err_c, lb_local);
             else collect_phase(B, T, round, cand_base);
             grid.sync();
         }
