@@ -90,6 +90,7 @@ struct gcr_engine_s
     int resident_cost_o = 20;   // cost model of k_score_resident's static partition: orientation block (scale block = 10) ...
     int resident_cost_p = 20;   // ... and a precise tile relative to an FP32 tile (x 10); GCR_COST_O / GCR_COST_P for tuning runs
     int tail_grid = 148;
+    long long n_phi_fallbacks = 0;          // gcr_fit_score_models: fits whose device-side phi differed from the host's map replay (diagnostics)
     unsigned int worklist_cap_override = 0; // GCR_WORKLIST_CAP (tests of the overflow report)
     unsigned int cont_cap_override = 0;     // GCR_CONT_CAP (tests of the contender-overflow path of the selection cascade)
     double dbg_floor_bump = 0.0;            // GCR_DEBUG_FLOOR_BUMP (tests of the bar-lowering contender round)
@@ -1293,10 +1294,15 @@ int gcr_score_models(gcr_handle h, const double* models, int64_t n, const double
     return GCR_OK;
 }
 
-int gcr_fit_models(gcr_handle h, int64_t n_fits, const uint32_t* scale_idx, const int64_t* scale_off,
-                   const uint32_t* orient_idx, const int64_t* orient_off, double* models, int32_t* ok)
+// gcr_fit_models, and with `thr` the scoring of the fitted models in the same launch sequence (gcr_fit_score_models)
+static int fit_models_impl(gcr_handle h, int64_t n_fits, const uint32_t* scale_idx, const int64_t* scale_off, const uint32_t* orient_idx,
+                           const int64_t* orient_off, double* models, int32_t* ok, const double* thr, uint32_t score_flags, double* score,
+                           uint32_t* n_inl, uint32_t* mask_words)
 {
     if (!h || !scale_idx || !scale_off || !models || !ok) return GCR_ERR_INVALID;
+    const bool do_score = thr != nullptr;
+    if (do_score && (!(thr[0] >= 0.0) || !std::isfinite(thr[0]) || (h->problem == 0 && (!(thr[1] >= 0.0) || !std::isfinite(thr[1])))))
+        return h->fail(GCR_ERR_INVALID, "thresholds must be finite and non-negative");
     if (h->ns < 2) return h->fail(GCR_ERR_STATE, "gcr_fit_models before gcr_set_features");
     const bool hybrid = h->problem == 0;
     if (hybrid && (!orient_idx || !orient_off)) return h->fail(GCR_ERR_INVALID, "gcr_fit_models: the hybrid problem needs orientation index lists");
@@ -1341,8 +1347,16 @@ int gcr_fit_models(gcr_handle h, int64_t n_fits, const uint32_t* scale_idx, cons
     }
     std::memcpy(h->h_fit_in.p + in_s, scale_idx, 4 * S);
     if (O) std::memcpy(h->h_fit_in.p + in_o, orient_idx, 4 * O);
+    const size_t Wm = static_cast<size_t>((h->ns + 31) / 32 + (h->no + 31) / 32);
     const size_t out_models = 0, out_ok = align16(K * 32), out_nent = align16(out_ok + 4 * K), out_ent = align16(out_nent + 4 * K),
-                 out_bytes = align16(out_ent + entries * sizeof(FitEntry));
+                 out_score = align16(out_ent + entries * sizeof(FitEntry)), out_cnt = align16(out_score + (do_score ? 8 * K : 0)),
+                 out_masks = align16(out_cnt + (do_score ? 8 * K : 0)),
+                 out_bytes = align16(out_masks + (do_score && mask_words ? 4 * Wm * K : 0));
+    if (do_score)
+    {
+        const int rc = ensure_common(h);
+        if (rc != GCR_OK) return rc;
+    }
     GCR_CUDA(h->h_fit_out.ensure(out_bytes));
     GCR_CUDA(h->d_fit_out.ensure(out_bytes));
     GCR_CUDA(h->d_fit_lines.ensure(3 * std::max<size_t>(O, 1)));
@@ -1366,11 +1380,59 @@ int gcr_fit_models(gcr_handle h, int64_t n_fits, const uint32_t* scale_idx, cons
     F.n_units = static_cast<unsigned int>(units);
     F.n_lines = static_cast<long long>(O);
     F.problem = h->problem;
+    {
+        // the bucket counts the host's std::unordered_map<int, double> goes through while it grows to kPhiBins keys (k_fit_phi)
+        struct Sched { int n; int at[8], to[8]; };
+        static const Sched sched = [] {
+            Sched sc{0, {}, {}};
+            std::unordered_map<int, double> probe;
+            size_t last = probe.bucket_count();
+            for (int i = 0; i < kPhiBins; ++i)
+            {
+                probe[i] += 1.0;
+                if (probe.bucket_count() != last && sc.n < 8)
+                {
+                    last = probe.bucket_count();
+                    sc.at[sc.n] = i + 1;
+                    sc.to[sc.n++] = static_cast<int>(last);
+                }
+            }
+            return sc;
+        }();
+        F.n_rehash = sched.n;
+        for (int i = 0; i < 8; ++i)
+        {
+            F.rehash_at[i] = sched.at[i];
+            F.rehash_to[i] = sched.to[i];
+        }
+    }
     if (O) k_fit_lines<<<static_cast<unsigned int>((O + kFitThreads - 1) / kFitThreads), kFitThreads, 0, s>>>(F);
     if (O) GCR_CUDA(launch_chained(h, k_fit_rows, dim3(F.n_units), dim3(kFitThreads), s, F));
     else k_fit_rows<<<F.n_units, kFitThreads, 0, s>>>(F); // first kernel of the call: behind the input copy, plain
     GCR_CUDA(launch_chained(h, k_fit_solve, dim3(static_cast<unsigned int>(K)), dim3(32), s, F));
     if (hybrid) GCR_CUDA(launch_chained(h, k_fit_phi, dim3(static_cast<unsigned int>(K)), dim3(kFitThreads), s, F));
+    if (do_score)
+    {
+        // the fitted models (phi: the device's histogram mode) scored against every feature in the same stream, no round trip: the
+        // rescoring step of the local optimisation (GCRANSAC.h:1004-1046) and of the final refit (:645-661) behind their fits
+        Thresholds T = make_thresholds(thr, h->problem);
+        if (score_flags & GCR_SCORE_TRUNCATED_SQ)
+        {
+            T.tsq[0] = (1.5 * thr[0]) * (1.5 * thr[0]);
+            T.tsq[1] = (1.5 * thr[1]) * (1.5 * thr[1]);
+        }
+        T.strict = (score_flags & GCR_SCORE_STRICT) ? 1 : 0;
+        const Buffers B = make_buffers(h, 0, false, nullptr);
+        const unsigned int un = static_cast<unsigned int>(K);
+        const unsigned long long su =
+            static_cast<unsigned long long>(un) * ((h->ns + kExactThreads - 1) / kExactThreads + (h->no + kExactThreads - 1) / kExactThreads);
+        const int sgrid = static_cast<int>(std::min<unsigned long long>(su, static_cast<unsigned long long>(h->n_sm) * 8));
+        GCR_CUDA(launch_chained(h, k_set_models, dim3((un + 127) / 128), dim3(128), s, B, reinterpret_cast<const Model4*>(F.models), un));
+        GCR_CUDA(launch_chained(h, k_exact_items, dim3(sgrid), dim3(kExactThreads), s, B, T, 2, un));
+        GCR_CUDA(launch_chained(h, k_score_out, dim3(std::max(1, std::min<int>(h->n_sm, static_cast<int>((Wm * K + 255) / 256)))), dim3(256), s, B, T,
+                                un, reinterpret_cast<double*>(h->d_fit_out.p + out_score), reinterpret_cast<unsigned int*>(h->d_fit_out.p + out_cnt),
+                                mask_words ? reinterpret_cast<unsigned int*>(h->d_fit_out.p + out_masks) : nullptr));
+    }
     GCR_CUDA(cudaGetLastError());
     GCR_CUDA(cudaMemcpyAsync(h->h_fit_out.p, h->d_fit_out.p, out_bytes, cudaMemcpyDeviceToHost, s));
     GCR_CUDA(cudaStreamSynchronize(s));
@@ -1379,6 +1441,7 @@ int gcr_fit_models(gcr_handle h, int64_t n_fits, const uint32_t* scale_idx, cons
     const int* okd = reinterpret_cast<const int*>(h->h_fit_out.p + out_ok);
     const unsigned int* nent = reinterpret_cast<const unsigned int*>(h->h_fit_out.p + out_nent);
     const FitEntry* ent = reinterpret_cast<const FitEntry*>(h->h_fit_out.p + out_ent);
+    std::vector<size_t> phi_differs;
     for (size_t k = 0; k < K; ++k)
     {
         std::memcpy(models + 4 * k, m + 4 * k, 32);
@@ -1401,8 +1464,63 @@ int gcr_fit_models(gcr_handle h, int64_t n_fits, const uint32_t* scale_idx, cons
         for (unsigned int i = 0; i < nent[k]; ++i)
             if (e[i].bin == mode_bin) phi = static_cast<double>(e[i].moment) / kPhiFixedPoint / static_cast<double>(e[i].count);
         models[4 * k + 3] = phi;
+        if (do_score && phi != m[4 * k + 3]) phi_differs.push_back(k); // equally heavy bins, resolved differently: scored again below
+    }
+    if (do_score)
+    {
+        const double* sc = reinterpret_cast<const double*>(h->h_fit_out.p + out_score);
+        const uint32_t* cn = reinterpret_cast<const uint32_t*>(h->h_fit_out.p + out_cnt);
+        for (size_t k = 0; k < K; ++k)
+        {
+            if (score) score[k] = okd[k] ? sc[k] : 0.0;
+            if (n_inl)
+            {
+                n_inl[2 * k] = okd[k] ? cn[2 * k] : 0u;
+                n_inl[2 * k + 1] = okd[k] ? cn[2 * k + 1] : 0u;
+            }
+        }
+        if (mask_words) std::memcpy(mask_words, h->h_fit_out.p + out_masks, 4 * Wm * K);
+        h->n_phi_fallbacks += static_cast<long long>(phi_differs.size());
+        if (!phi_differs.empty())
+        {
+            // the device's restatement of the map order disagreed with the real map (another standard library's policy): those models are
+            // scored again with the host's phi, all of them in one pass
+            const size_t nd = phi_differs.size();
+            std::vector<double> mm(4 * nd), ss(nd);
+            std::vector<uint32_t> cc(2 * nd), ww(mask_words ? Wm * nd : 0);
+            for (size_t i = 0; i < nd; ++i) std::memcpy(&mm[4 * i], models + 4 * phi_differs[i], 32);
+            const int rc = gcr_score_models(h, mm.data(), static_cast<int64_t>(nd), thr, score_flags, ss.data(), cc.data(), mask_words ? ww.data() : nullptr);
+            if (rc != GCR_OK) return rc;
+            for (size_t i = 0; i < nd; ++i)
+            {
+                const size_t k = phi_differs[i];
+                if (score) score[k] = ss[i];
+                if (n_inl)
+                {
+                    n_inl[2 * k] = cc[2 * i];
+                    n_inl[2 * k + 1] = cc[2 * i + 1];
+                }
+                if (mask_words) std::memcpy(mask_words + Wm * k, &ww[Wm * i], 4 * Wm);
+            }
+        }
     }
     return GCR_OK;
+}
+
+int gcr_fit_models(gcr_handle h, int64_t n_fits, const uint32_t* scale_idx, const int64_t* scale_off,
+                   const uint32_t* orient_idx, const int64_t* orient_off, double* models, int32_t* ok)
+{
+    return fit_models_impl(h, n_fits, scale_idx, scale_off, orient_idx, orient_off, models, ok, nullptr, 0, nullptr, nullptr, nullptr);
+}
+
+long long gcr_debug_phi_fallbacks(gcr_handle h) { return h ? h->n_phi_fallbacks : -1; }
+
+int gcr_fit_score_models(gcr_handle h, int64_t n_fits, const uint32_t* scale_idx, const int64_t* scale_off, const uint32_t* orient_idx,
+                         const int64_t* orient_off, const double thr[2], uint32_t flags, double* models, int32_t* ok, double* score,
+                         uint32_t* n_inl, uint32_t* mask_words)
+{
+    if (!thr) return GCR_ERR_INVALID;
+    return fit_models_impl(h, n_fits, scale_idx, scale_off, orient_idx, orient_off, models, ok, thr, flags, score, n_inl, mask_words);
 }
 
 int gcr_score_model(gcr_handle h, const double model[4], const double thr[2], double* score, uint32_t n_inl[2],

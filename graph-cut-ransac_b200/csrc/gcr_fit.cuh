@@ -119,7 +119,12 @@ struct FitBuffers
     unsigned int n_units;
     long long n_lines;
     int problem;
+    // bucket-count schedule of the host's std::unordered_map<int, double> (probed once by the engine): the map rehashes to rehash_to[i]
+    // buckets while inserting its rehash_at[i]-th key (libstdc++: 13 at 1, 29 at 14, 59 at 30, 127 at 60, 257 at 128, 541 at 258)
+    int n_rehash;
+    int rehash_at[8], rehash_to[8];
 };
+constexpr int kPhiMaxBuckets = 1024;
 
 // lineFromPointAndAngle (math_utils.hpp:104-109) of every listed orientation feature
 __global__ void __launch_bounds__(kFitThreads) k_fit_lines(FitBuffers F)
@@ -338,6 +343,8 @@ __global__ void __launch_bounds__(kFitThreads) k_fit_phi(FitBuffers F)
     pdl_wait();
     __shared__ unsigned int s_count[kPhiBins], s_first[kPhiBins];
     __shared__ unsigned long long s_moment[kPhiBins];
+    __shared__ short s_key[kPhiBins], s_next[kPhiBins + 1], s_bucket[kPhiMaxBuckets];
+    __shared__ unsigned int s_total;
     const int k = blockIdx.x;
     if (!F.ok[k]) return;
     const FitDesc D = F.desc[k];
@@ -377,9 +384,82 @@ __global__ void __launch_bounds__(kFitThreads) k_fit_phi(FitBuffers F)
         e.count = s_count[b];
         e.moment = s_moment[b];
         F.ent[D.ent_off + rank] = e;
+        s_key[rank] = static_cast<short>(b);
         n_bins++;
     }
     if (n_bins) atomicAdd(&F.n_ent[k], n_bins);
+    // phi on the device too (so that the fitted models can be scored without a round trip: gcr_fit_score_models): the mean angle of the
+    // heaviest bin, and among equally heavy bins the one the REFERENCE meets first (two_sift.hpp:354-394: it walks an
+    // std::unordered_map<int, double> filled in order of first appearance and keeps the first strictly heavier entry).  Small index lists
+    // (14 orientations of a local-optimisation trial) have equally heavy bins as a rule, so the map's iteration order is restated here:
+    // libstdc++'s node list -- a new key whose bucket is empty goes to the FRONT of the list, otherwise behind its bucket's first node;
+    // a rehash re-links the nodes in list order by the same rule (hashtable.h: _M_insert_bucket_begin, _M_rehash_aux) -- with the bucket
+    // counts the host's own map goes through (FitBuffers::rehash_*).  The caller still replays the real map on the entries above and
+    // re-scores where the two disagree, so a library with another policy costs time, not correctness.
+    if (threadIdx.x == 0) s_total = 0u;
+    __syncthreads();
+    if (n_bins) atomicAdd(&s_total, n_bins);
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        constexpr short kNone = -2, kBB = kPhiBins; // no node / the list's before-begin sentinel
+        const int n = static_cast<int>(s_total);
+        int nb = 1, ri = 0;
+        s_next[kBB] = -1;
+        s_bucket[0] = kNone;
+        for (int i = 0; i < n; i++)
+        {
+            if (ri < F.n_rehash && i + 1 == F.rehash_at[ri])
+            {
+                nb = min(F.rehash_to[ri++], kPhiMaxBuckets);
+                for (int b = 0; b < nb; b++) s_bucket[b] = kNone;
+                short p = s_next[kBB];
+                s_next[kBB] = -1;
+                int bbegin_bkt = 0;
+                while (p >= 0)
+                {
+                    const short nx = s_next[p];
+                    const int b = s_key[p] % nb;
+                    if (s_bucket[b] == kNone)
+                    {
+                        s_next[p] = s_next[kBB];
+                        s_next[kBB] = p;
+                        s_bucket[b] = kBB;
+                        if (s_next[p] >= 0) s_bucket[bbegin_bkt] = p;
+                        bbegin_bkt = b;
+                    }
+                    else
+                    {
+                        s_next[p] = s_next[s_bucket[b]];
+                        s_next[s_bucket[b]] = p;
+                    }
+                    p = nx;
+                }
+            }
+            const int b = s_key[i] % nb;
+            if (s_bucket[b] != kNone)
+            {
+                s_next[i] = s_next[s_bucket[b]];
+                s_next[s_bucket[b]] = static_cast<short>(i);
+            }
+            else
+            {
+                s_next[i] = s_next[kBB];
+                s_next[kBB] = static_cast<short>(i);
+                if (s_next[i] >= 0) s_bucket[s_key[s_next[i]] % nb] = static_cast<short>(i);
+                s_bucket[b] = kBB;
+            }
+        }
+        unsigned int best = 0u;
+        int mode = -1;
+        for (short p = s_next[kBB]; p >= 0; p = s_next[p])
+            if (s_count[s_key[p]] > best)
+            {
+                best = s_count[s_key[p]];
+                mode = s_key[p];
+            }
+        if (mode >= 0) F.models[4 * k + 3] = static_cast<double>(s_moment[mode]) / kPhiFixedPoint / static_cast<double>(best);
+    }
 }
 
 } // namespace gcr

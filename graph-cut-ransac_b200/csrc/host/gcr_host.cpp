@@ -260,7 +260,7 @@ static int estimateImpl(int problem, const double* scale, size_t ns, const doubl
     // ---- local optimisation on the selected model (graphCutLocalOptimization for two classes, GCRANSAC.h:873-1062)
     SplitMix rng{st.seed ^ 0x6C6F63616C6F7074ull};
     std::vector<uint32_t> lab_words(W), in_s, in_o, smp_s, smp_o, scratch;
-    std::vector<double> trial_models, trial_scores;
+    std::vector<double> trial_scores;
     std::vector<uint32_t> trial_cnt, trial_words;
     // Non-minimal fits run on the device (gcr_fit_models), all trials of one inner RANSAC in one pass
     std::vector<uint32_t> fit_idx_s, fit_idx_o;
@@ -282,15 +282,19 @@ static int estimateImpl(int problem, const double* scale, size_t ns, const doubl
             fit_off_o.push_back(static_cast<int64_t>(fit_idx_o.size()));
         }
     };
-    auto fitRun = [&] {
+    auto fitScoreRun = [&](bool want_masks) {
         const size_t k = fit_off_s.size() - 1;
         fit_models.resize(4 * k);
         fit_ok.resize(k);
-        if (fit_idx_s.empty()) fit_idx_s.push_back(0u); // keep the pointers non-null for empty lists
+        trial_scores.resize(k);
+        trial_cnt.resize(2 * k);
+        if (want_masks) trial_words.resize(k * W);
+        if (fit_idx_s.empty()) fit_idx_s.push_back(0u);
         if (hybrid && fit_idx_o.empty()) fit_idx_o.push_back(0u);
-        eng.check(gcr_fit_models(eng.h, static_cast<int64_t>(k), fit_idx_s.data(), fit_off_s.data(), hybrid ? fit_idx_o.data() : nullptr,
-                                 hybrid ? fit_off_o.data() : nullptr, fit_models.data(), fit_ok.data()),
-                  "gcr_fit_models");
+        eng.check(gcr_fit_score_models(eng.h, static_cast<int64_t>(k), fit_idx_s.data(), fit_off_s.data(), hybrid ? fit_idx_o.data() : nullptr,
+                                       hybrid ? fit_off_o.data() : nullptr, thr, 0, fit_models.data(), fit_ok.data(), trial_scores.data(),
+                                       trial_cnt.data(), want_masks ? trial_words.data() : nullptr),
+                  "gcr_fit_score_models");
         return k;
     };
     // two classes: r^2 <= (1.5 t)^2 (GCRANSAC.h:931-937); one class: graph cut over the (empty) neighbourhood graph, which
@@ -311,7 +315,6 @@ static int estimateImpl(int problem, const double* scale, size_t ns, const doubl
             // inner RANSAC on the labelled inliers: min(7 x sample size, n) per class  (GCRANSAC.h:955-996)
             const size_t k_s = std::min(lim_s, in_s.size()), k_o = std::min(lim_o, in_o.size());
             if (in_s.size() <= min_s || (hybrid && in_o.size() <= min_o)) break; // sampling fails: neither a draw nor "use all" applies
-            trial_models.clear();
             fitBegin();
             for (size_t trial = 0; trial < std::min<size_t>(max_lo, 1024); ++trial) // one device pass holds 1024 fits / models
             {
@@ -319,29 +322,22 @@ static int estimateImpl(int problem, const double* scale, size_t ns, const doubl
                 if (k_o < in_o.size()) drawSubset(in_o, k_o, rng, scratch, smp_o); else smp_o = in_o;
                 fitAdd(smp_s, smp_o);
             }
-            const size_t n_fit = fitRun();
+            // all trial fits AND their scores in one device pass (gcr_fit_score_models): fit k's model goes through getScore on the device
+            // behind its fit, one synchronisation per inner RANSAC
+            const size_t n_fit = fitScoreRun(true);
             for (size_t t = 0; t < n_fit; ++t)
-                if (fit_ok[t]) trial_models.insert(trial_models.end(), &fit_models[4 * t], &fit_models[4 * t] + 4);
-            const size_t nt = trial_models.size() / 4;
-            if (nt > 0)
             {
-                trial_scores.resize(nt);
-                trial_cnt.resize(2 * nt);
-                trial_words.resize(nt * W);
-                eng.check(gcr_score_models(eng.h, trial_models.data(), static_cast<int64_t>(nt), thr, 0, trial_scores.data(),
-                                           trial_cnt.data(), trial_words.data()),
-                          "gcr_score_models(trials)");
-                st.lo_models_scored += static_cast<int>(nt);
-                for (size_t t = 0; t < nt; ++t)
-                    if (lo.score < trial_scores[t]) // strict, in trial order (GCRANSAC.h:1034)
-                    {
-                        updated = true;
-                        lo.score = trial_scores[t];
-                        std::memcpy(lo.model, &trial_models[4 * t], sizeof(lo.model));
-                        lo.n_inl[0] = trial_cnt[2 * t];
-                        lo.n_inl[1] = trial_cnt[2 * t + 1];
-                        lo.words.assign(trial_words.begin() + t * W, trial_words.begin() + (t + 1) * W);
-                    }
+                if (!fit_ok[t]) continue;
+                st.lo_models_scored += 1;
+                if (lo.score < trial_scores[t]) // strict, in trial order (GCRANSAC.h:1034)
+                {
+                    updated = true;
+                    lo.score = trial_scores[t];
+                    std::memcpy(lo.model, &fit_models[4 * t], sizeof(lo.model));
+                    lo.n_inl[0] = trial_cnt[2 * t];
+                    lo.n_inl[1] = trial_cnt[2 * t + 1];
+                    lo.words.assign(trial_words.begin() + t * W, trial_words.begin() + (t + 1) * W);
+                }
             }
             if (!updated) break;
         }
@@ -357,22 +353,15 @@ static int estimateImpl(int problem, const double* scale, size_t ns, const doubl
     {
         fitBegin();
         fitAdd(in_s, in_o);
-        fitRun();
-        if (fit_ok[0])
+        fitScoreRun(true); // the refit and its score in one device pass
+        if (fit_ok[0] && best.score < trial_scores[0])
         {
-            double a[4], sc = 0.0;
-            uint32_t cnt[2];
-            std::memcpy(a, fit_models.data(), sizeof(a));
-            eng.check(gcr_score_models(eng.h, a, 1, thr, 0, &sc, cnt, lab_words.data()), "gcr_score_models(refit)");
-            if (best.score < sc)
-            {
-                st.refit_accepted = true;
-                best.score = sc;
-                std::memcpy(best.model, a, sizeof(a));
-                best.n_inl[0] = cnt[0];
-                best.n_inl[1] = cnt[1];
-                best.words = lab_words;
-            }
+            st.refit_accepted = true;
+            best.score = trial_scores[0];
+            std::memcpy(best.model, fit_models.data(), sizeof(best.model));
+            best.n_inl[0] = trial_cnt[0];
+            best.n_inl[1] = trial_cnt[1];
+            best.words.assign(trial_words.begin(), trial_words.begin() + W);
         }
     }
     st.final_score = best.score;

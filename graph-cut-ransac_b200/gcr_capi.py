@@ -26,7 +26,7 @@ EXPORTS = [
     "gcr_create", "gcr_destroy", "gcr_last_error", "gcr_set_stream", "gcr_wait_stream", "gcr_set_problem", "gcr_set_features", "gcr_get_features", "gcr_run",
     "gcr_best",
     "gcr_fetch", "gcr_score_model", "gcr_score_models", "gcr_fit_models", "gcr_set_keypoints", "gcr_debug_eval", "gcr_version", "gcr_peer_export",
-    "gcr_peer_attach", "gcr_peer_buffer", "gcr_peer_attach_ptrs", "gcr_peer_detach", "gcr_score_models_static",
+    "gcr_peer_attach", "gcr_peer_buffer", "gcr_peer_attach_ptrs", "gcr_peer_detach", "gcr_score_models_static", "gcr_fit_score_models", "gcr_debug_phi_fallbacks",
 ]
 
 
@@ -76,6 +76,7 @@ def load_library() -> C.CDLL:
     lib.gcr_score_model.argtypes = [vp, vp, vp, vp, vp, vp, vp]
     lib.gcr_score_models.argtypes = [vp, vp, i64, vp, u32, vp, vp, vp]
     lib.gcr_fit_models.argtypes = [vp, i64, vp, vp, vp, vp, vp, vp]
+    lib.gcr_fit_score_models.argtypes = [vp, i64, vp, vp, vp, vp, vp, u32, vp, vp, vp, vp, vp]
     lib.gcr_set_keypoints.argtypes = [vp, vp, i64, C.c_int, C.c_int, vp, vp, vp]
     lib.gcr_peer_export.argtypes = [vp, vp]
     lib.gcr_peer_attach.argtypes = [vp, vp, C.c_int, C.c_int]
@@ -87,6 +88,9 @@ def load_library() -> C.CDLL:
     lib.gcr_version.restype = C.c_char_p
     for name in EXPORTS:
         fn = getattr(lib, name)
+        if name == "gcr_debug_phi_fallbacks":
+            fn.restype, fn.argtypes = C.c_longlong, [vp]
+            continue
         if name not in ("gcr_last_error", "gcr_version"):
             fn.restype = C.c_int
     return lib
@@ -290,6 +294,28 @@ class Engine:
                                             oi.ctypes.data if orient_lists is not None else None,
                                             oo.ctypes.data if orient_lists is not None else None, models.ctypes.data, ok.ctypes.data))
         return models, ok.astype(bool)
+
+    def fit_score_models(self, scale_lists, orient_lists, thr, truncated_sq=False, strict=False, masks=True):
+        """gcr_fit_score_models: fits from index lists and their scores in one device pass -> (models, ok, score, n_inl, mask words)."""
+        K = len(scale_lists)
+        def pack(lists):
+            off = np.zeros(K + 1, np.int64)
+            off[1:] = np.cumsum([len(l) for l in lists])
+            idx = np.ascontiguousarray(np.concatenate([np.asarray(l, np.uint32).ravel() for l in lists]) if off[-1] else np.zeros(1, np.uint32), np.uint32)
+            return idx, off
+        si, so = pack(scale_lists)
+        if orient_lists is not None:
+            oi, oo = pack(orient_lists)
+        thr = np.ascontiguousarray(thr, np.float64)
+        W = (self.ns + 31) // 32 + (self.no + 31) // 32
+        models, ok, score = np.zeros((K, 4)), np.zeros(K, np.int32), np.zeros(K)
+        n_inl = np.zeros((K, 2), np.uint32)
+        words = np.zeros((K, W), np.uint32) if masks else None
+        self._check(self.lib.gcr_fit_score_models(self.h, K, si.ctypes.data, so.ctypes.data, oi.ctypes.data if orient_lists is not None else None,
+                                                  oo.ctypes.data if orient_lists is not None else None, thr.ctypes.data,
+                                                  (1 if truncated_sq else 0) | (2 if strict else 0), models.ctypes.data, ok.ctypes.data,
+                                                  score.ctypes.data, n_inl.ctypes.data, words.ctypes.data if masks else None))
+        return models, ok.astype(bool), score, n_inl, words
 
     def debug_eval(self, which, abc, model=None):
         abc = np.ascontiguousarray(abc, np.float64).reshape(-1, 3)

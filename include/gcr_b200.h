@@ -238,6 +238,20 @@ int gcr_score_models(gcr_handle h, const double* models, int64_t n, const double
 int gcr_fit_models(gcr_handle h, int64_t n_fits, const uint32_t* scale_idx, const int64_t* scale_off,
                    const uint32_t* orient_idx, const int64_t* orient_off, double* models, int32_t* ok);
 
+/* gcr_fit_models followed, in the same launch sequence and with ONE synchronisation, by the scoring of the fitted models against every
+ * resident feature: "fit, then getScore" of one inner-RANSAC pass of the local optimisation (GCRANSAC.h:955-1046) and of the final refit
+ * (GCRANSAC.h:628-661).  Arguments as gcr_fit_models and gcr_score_models (thr, flags: GCR_SCORE_*); host outputs, any of score / n_inl /
+ * mask_words may be NULL: models f64[n_fits,4], ok i32[n_fits], score f64[n_fits], n_inl u32[n_fits,2] (after the zero-reset rule),
+ * mask_words u32[n_fits, ceil(Ns/32)+ceil(No/32)]; fits with ok = 0 report score 0 and no inliers.  Results are those of the two separate
+ * calls, bit for bit.  Synchronises. */
+int gcr_fit_score_models(gcr_handle h, int64_t n_fits, const uint32_t* scale_idx, const int64_t* scale_off, const uint32_t* orient_idx,
+                         const int64_t* orient_off, const double thr[2], uint32_t flags, double* models, int32_t* ok, double* score,
+                         uint32_t* n_inl, uint32_t* mask_words);
+
+/* Diagnostics: fits of gcr_fit_score_models calls on this handle whose device-side phi (histogram mode under the device's restatement of
+ * the reference's unordered_map order) differed from the host's replay of the real map and were scored a second time; 0 when the two agree. */
+long long gcr_debug_phi_fallbacks(gcr_handle h);
+
 /* Allocation-free batched model scoring.  NO COUNTERPART IN THE REFERENCE: added for callers that
  * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The same computation as
  * gcr_score_models for the hybrid problem -- MSACScoringFunction::getScore of n caller-supplied models in FP64 reference order -- without an

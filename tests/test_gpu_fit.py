@@ -125,3 +125,39 @@ def test_fit_argument_errors(eng):
         eng.fit_models([[0, 1, len(sc.scale)]], [[0, 1, 2]])  # index out of range
     with pytest.raises(gcr_capi.GcrError):
         eng.fit_models([[0, 1, 2]])  # the hybrid problem needs orientation lists
+
+
+def test_fit_score_models_equals_fit_then_score(eng):
+    """gcr_fit_score_models (fits and their scores in one device pass, one synchronisation: the local optimisation's inner RANSAC and the
+    final refit in csrc/host/gcr_host.cpp) == gcr_fit_models followed by gcr_score_models, bit for bit -- models (phi: the device's
+    histogram mode vs the host's replay of the reference's unordered_map order), ok flags, scores, counts, masks."""
+    import gcr_scenes as gs
+    sc = gs.make_scene(900, 300, 0.5, 61)
+    rng = np.random.default_rng(62)
+    si, oi = np.flatnonzero(sc.scale_is_inlier), np.flatnonzero(sc.orient_is_inlier)
+    s_lists = [rng.choice(si, int(rng.integers(2, 30)), replace=False) for _ in range(60)]
+    o_lists = [rng.choice(oi, int(rng.integers(2, 16)), replace=False) for _ in range(60)]
+    s_lists[5], o_lists[5] = s_lists[5][:2], o_lists[5][:2]      # exactly a minimal sample: declined (ok = 0)
+    s_lists[7], o_lists[7] = si, oi                                # the refit case: all inliers
+    o_lists[9] = np.concatenate([o_lists[9][:4], o_lists[9][:4]])  # duplicated rows: equally heavy histogram bins are likely
+    eng.set_features(sc.scale, sc.orient)
+    for truncated in (False, True):
+        m1, ok1 = eng.fit_models(s_lists, o_lists)
+        sc1, n1, w1 = eng.score_models(np.where(ok1[:, None], m1, 0.0), sc.thr, truncated_sq=truncated, masks=True)
+        m2, ok2, sc2, n2, w2 = eng.fit_score_models(s_lists, o_lists, sc.thr, truncated_sq=truncated)
+        assert np.array_equal(ok1, ok2) and not ok2[5] and ok2[7]
+        assert np.array_equal(m1[ok1], m2[ok2])
+        assert np.array_equal(sc1[ok1], sc2[ok2]) and np.array_equal(n1[ok1], n2[ok2]) and np.array_equal(w1[ok1], w2[ok2])
+        assert (sc2[~ok2] == 0).all() and (n2[~ok2] == 0).all()
+        assert sc2[7] > 0.5 * (len(si) + len(oi))
+    # scores only
+    m3, ok3, sc3, n3, w3 = eng.fit_score_models(s_lists, o_lists, sc.thr, masks=False)
+    assert w3 is None and np.array_equal(ok3, ok2)
+    # the device resolved equally heavy histogram bins as the host's std::unordered_map does (no fit needed the second scoring pass),
+    # also for histograms that grow through every rehash of the map (index lists of up to 300 orientation features)
+    all_o = np.arange(len(sc.orient))
+    big_lists = [rng.choice(all_o, n, replace=False) for n in (13, 14, 15, 29, 30, 31, 59, 60, 61, 127, 128, 129, 257, 258, 300)]
+    m4, ok4, sc4, _, _ = eng.fit_score_models([si] * len(big_lists), big_lists, sc.thr, masks=False)
+    m5, ok5 = eng.fit_models([si] * len(big_lists), big_lists)
+    assert np.array_equal(m4, m5) and ok4.all()
+    assert eng.lib.gcr_debug_phi_fallbacks(eng.h) == 0
