@@ -15,11 +15,15 @@ constexpr int kStages = 6;
 #ifndef GCR_THREADS
 #define GCR_THREADS 128
 #endif
+// Two hypotheses per thread, six 128-thread CTAs per SM (80 registers): every LDS.128 of the feature planes serves two hypotheses, which
+// relieves the MIO queue the MUFUs share.  Same-box A/B of the winner-only ring kernel at C3 (tools/compare_variants.py): 4.979 (1 hypothesis,
+// 8 CTAs) / 4.919 (2, 6 CTAs) / 5.003 (2, 5 CTAs, 96 registers) / 5.046 ms (2, 4 CTAs, 100 registers); C5 0.2018 -> 0.1935 ms.  (Round 1
+// measured the opposite for the reporting kernel, whose per-hypothesis state is twice as large.)
 #ifndef GCR_HB
-#define GCR_HB 1
+#define GCR_HB 2
 #endif
 #ifndef GCR_MINB
-#define GCR_MINB 8
+#define GCR_MINB 6
 #endif
 // Packed f32x2 arithmetic (FFMA2 / FMUL2: two IEEE operations per issue slot) in the FP32 tiles of the scoring kernel:
 // 0 none, 1 scale class, 2 + the six leading FMAs of an orientation evaluation, 3 + the rest of the orientation evaluation.
@@ -44,8 +48,6 @@ constexpr int kVoteGroups = GCR_VOTE; // groups of 4 (FP32) / 2 (precise) featur
 template <int CLS>
 constexpr bool kPacked = CLS == 0 ? (GCR_F2 >= 1) : (GCR_F2 >= 2);
 constexpr int kScoreThreads = GCR_THREADS;
-constexpr int kHB = GCR_HB; // hypotheses per thread in the fast kernel
-constexpr int kTileHyps = kScoreThreads * kHB;
 constexpr int kCandCap = 1024;
 constexpr int kIrrCap = 4096;
 constexpr int kMaxPeers = 16;

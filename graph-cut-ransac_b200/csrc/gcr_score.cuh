@@ -1,6 +1,6 @@
 // K3: the multi-class MSAC scoring kernel (the hot kernel of the engine).
 //
-// Work mapping: one thread <-> kHB hypotheses held in registers; the features of both classes stream
+// Work mapping: one thread <-> HB hypotheses held in registers; the features of both classes stream
 // through a shared-memory ring filled by 1-D TMA bulk copies (cp.async.bulk + mbarrier full/empty pairs)
 // and are read as broadcast 128-bit loads.  No reductions: every thread owns its hypotheses' partial sums.
 // A work item is (tile of kTileHyps hypotheses) x (range of feature chunks); items are strided over a
@@ -132,28 +132,28 @@ __device__ __forceinline__ void worklist_push(const Buffers& B, unsigned int hyp
     else atomicAdd(&B.ctr->n_worklist_overflow, 1u);
 }
 
-// One chunk of one class for the kHB hypotheses of this thread.  CLS 0 = scale, 1 = orientation.
+// One chunk of one class for the HB hypotheses of this thread.  CLS 0 = scale, 1 = orientation.
 // FP32 chunk: 512 features, groups of 4 (float4 per plane).  Precise chunk: 256 features, groups of 2 (double2).
 // RANGE: only the groups [g0r, g1r) of the chunk (the resident kernel's segments; both multiples of kScoreUnroll).
-template <bool MASKS, bool PRECISE, int CLS, bool RANGE = false>
+template <bool MASKS, bool PRECISE, int CLS, bool RANGE = false, int HB = 1>
 __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& T, const float* stage, int fbase,
-                                            HypRegs (&H)[kHB], int g0r = 0, int g1r = 0)
+                                            HypRegs (&H)[HB], int g0r = 0, int g1r = 0)
 {
     static_assert(kScoreUnroll % kVoteGroups == 0, "the vote window must divide the unroll factor");
     constexpr int G = PRECISE ? 2 : 4;             // features per group
     constexpr int NF = PRECISE ? kChunk / 2 : kChunk; // features per chunk
-    float acc[kHB], cntf[kHB]; // per-chunk FP32 partials; counts are exact integers (< 2^24)
-    float rsum[kHB];
-    unsigned int mword[kHB];
+    float acc[HB], cntf[HB]; // per-chunk FP32 partials; counts are exact integers (< 2^24)
+    float rsum[HB];
+    unsigned int mword[HB];
 #pragma unroll
-    for (int j = 0; j < kHB; j++)
+    for (int j = 0; j < HB; j++)
     {
         acc[j] = cntf[j] = rsum[j] = 0.f;
         mword[j] = 0u;
     }
-    bool unc_j[kHB]; // hypothesis j had an evaluation of the last kVoteGroups groups inside the band (per thread)
+    bool unc_j[HB]; // hypothesis j had an evaluation of the last kVoteGroups groups inside the band (per thread)
 #pragma unroll
-    for (int j = 0; j < kHB; j++) unc_j[j] = false;
+    for (int j = 0; j < HB; j++) unc_j[j] = false;
     const int g0 = RANGE ? g0r : 0, g1 = RANGE ? g1r : NF / G;
     for (int gb = g0; gb < g1; gb += kScoreUnroll)
 #pragma unroll
@@ -206,7 +206,7 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
             }
         };
 #pragma unroll
-        for (int j = 0; j < kHB; j++)
+        for (int j = 0; j < HB; j++)
         {
             // FP32 tiles, packed form (GCR_F2): the FMAs that do not depend on a predicate are issued as f32x2 pairs
             // (FFMA2 / FMUL2: two IEEE operations per issue slot, bit-identical to the scalar form)
@@ -299,14 +299,14 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
         {
             bool any_unc = false;
 #pragma unroll
-            for (int j = 0; j < kHB; j++) any_unc |= unc_j[j];
+            for (int j = 0; j < HB; j++) any_unc |= unc_j[j];
             if (__any_sync(0xffffffffu, any_unc))
             {
                 // rare: re-derive which pairs of these groups are inside the band (same instructions, same inputs,
                 // re-read from shared memory so that this path stays a small rolled loop out of the hot stream)
                 const int f0 = (g - (kVoteGroups - 1)) * G;
 #pragma unroll
-                for (int j = 0; j < kHB; j++)
+                for (int j = 0; j < HB; j++)
                 {
                     if (!unc_j[j]) continue; // usually one hypothesis of one lane
 #pragma unroll 1
@@ -327,12 +327,12 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
                 }
             }
 #pragma unroll
-            for (int j = 0; j < kHB; j++) unc_j[j] = false;
+            for (int j = 0; j < HB; j++) unc_j[j] = false;
         }
         if (MASKS && ((g + 1) * G) % 32 == 0)
         {
 #pragma unroll
-            for (int j = 0; j < kHB; j++)
+            for (int j = 0; j < HB; j++)
             {
                 if ((RANGE ? H[j].hyp != kNoHyp : H[j].active) && mword[j])
                     atomicOr(&B.masks[static_cast<size_t>(H[j].hyp) * B.wmask + (CLS ? B.ws : 0) + ((fbase + g * G) >> 5)],
@@ -342,7 +342,7 @@ __device__ __forceinline__ void score_chunk(const Buffers& B, const Thresholds& 
         }
     }
 #pragma unroll
-    for (int j = 0; j < kHB; j++)
+    for (int j = 0; j < HB; j++)
     {
         if (CLS == 0)
         {
@@ -380,18 +380,28 @@ __device__ __forceinline__ float fmax_nan(float a, float b) // NaN-propagating m
     return r;
 }
 
+// (GCR_RCP2=1: ONE reciprocal per pair of orientation evaluations, 1/a = b rcp(ab).  It paid while the XU pipe was the tightest unit
+//  (C3 5.60 -> 5.575 ms); with the pair arithmetic packed (GCR_WF2) the FMA pipe is, and the 1.5 extra multiplies cost more than half a
+//  MUFU: 5.117 -> 4.976 ms with two reciprocals.)
 #ifndef GCR_RCP2
-#define GCR_RCP2 1
+#define GCR_RCP2 0
 #endif
-template <bool PRECISE, int CLS, bool RANGE = false>
-__device__ __forceinline__ void score_chunk_w(const Thresholds& T, const float* stage, HypRegs (&H)[kHB], int g0r = 0, int g1r = 0)
+// Packed f32x2 arithmetic in the winner-only orientation evaluation: 0 none, 1 numer / denom / rotation of a PAIR of features as
+// FFMA2 / FMUL2, 2 + t, z and the polynomial.  Same IEEE results, one issue slot for two features: 17.5 -> 12 issue slots per orientation
+// evaluation; C3 kernel 5.371 / 5.181 / 5.109 ms for levels 0 / 1 / 2 (same box, interleaved), C2 28.7 -> 26.6 us.  (Round 1 found the pair
+// forms useless in the reporting kernel, whose FMA pipe was the tighter unit; this loop is issue-bound.)
+#ifndef GCR_WF2
+#define GCR_WF2 2
+#endif
+template <bool PRECISE, int CLS, bool RANGE = false, int HB = 1>
+__device__ __forceinline__ void score_chunk_w(const Thresholds& T, const float* stage, HypRegs (&H)[HB], int g0r = 0, int g1r = 0)
 {
     constexpr int G = PRECISE ? 2 : 4;               // features per group
     constexpr int NF = PRECISE ? kChunk / 2 : kChunk; // features per chunk
-    float2 acc[kHB];                                  // two FP32 partial sums per hypothesis (even / odd features), flushed per chunk
-    float rim[kHB];                                   // largest 1 / max of this chunk's orientation evaluations
+    float2 acc[HB];                                  // two FP32 partial sums per hypothesis (even / odd features), flushed per chunk
+    float rim[HB];                                   // largest 1 / max of this chunk's orientation evaluations
 #pragma unroll
-    for (int j = 0; j < kHB; j++)
+    for (int j = 0; j < HB; j++)
     {
         acc[j] = make_float2(0.f, 0.f);
         rim[j] = 0.f;
@@ -421,7 +431,7 @@ __device__ __forceinline__ void score_chunk_w(const Thresholds& T, const float* 
             fc[0] = c.x; fc[1] = c.y; fc[2] = c.z; fc[3] = c.w;
         }
 #pragma unroll
-        for (int j = 0; j < kHB; j++)
+        for (int j = 0; j < HB; j++)
         {
 #pragma unroll
             for (int e = 0; e < G; e += 2)
@@ -459,11 +469,31 @@ __device__ __forceinline__ void score_chunk_w(const Thresholds& T, const float* 
                         }
                     }
                     float gg[2], mn[2], mx[2];
+                    float c1v[2], s1v[2];
+                    if constexpr (GCR_WF2 && !PRECISE)
+                    {
+                        // numer, denom and the rotation by -phi of the PAIR as f32x2 operations (FFMA2 / FMUL2: same IEEE results, one issue
+                        // slot for two features; the kernel is issue-bound, its FMA pipe has the cycles)
+                        const float2 a2 = make_float2(fa[e], fa[e + 1]);
+                        const float2 n2 = __ffma2_rn(a2, make_float2(H[j].nh7, H[j].nh7), make_float2(fb[e], fb[e + 1]));
+                        const float2 d2 = __ffma2_rn(a2, make_float2(-H[j].nh8, -H[j].nh8), make_float2(fc[e], fc[e + 1]));
+                        const float2 c2 = __ffma2_rn(n2, make_float2(H[j].sphi, H[j].sphi), __fmul2_rn(d2, make_float2(H[j].cphi, H[j].cphi)));
+                        const float2 s2 = __ffma2_rn(n2, make_float2(H[j].cphi, H[j].cphi), __fmul2_rn(d2, make_float2(-H[j].sphi, -H[j].sphi)));
+                        c1v[0] = c2.x; c1v[1] = c2.y; s1v[0] = s2.x; s1v[1] = s2.y;
+                    }
+                    else
+                    {
+#pragma unroll
+                        for (int q = 0; q < 2; q++)
+                        {
+                            c1v[q] = fmaf(n[q], H[j].sphi, d[q] * H[j].cphi);
+                            s1v[q] = fmaf(n[q], H[j].cphi, -(d[q] * H[j].sphi));
+                        }
+                    }
 #pragma unroll
                     for (int q = 0; q < 2; q++)
                     {
-                        const float c1 = fmaf(n[q], H[j].sphi, d[q] * H[j].cphi);
-                        const float s1 = fmaf(n[q], H[j].cphi, -(d[q] * H[j].sphi));
+                        const float c1 = c1v[q], s1 = s1v[q];
                         const float a1 = fabsf(c1), a2 = fabsf(s1);
                         // NaN-propagating maximum: a padding / irregular feature (NaN sine) gives ri = NaN, which the value (FFMA.SAT: NaN -> 0) and
                         // the running maximum below both ignore; an exact 0/0 of a real feature gives ri ~ 1e18, i.e. an unbounded error bound,
@@ -477,23 +507,41 @@ __device__ __forceinline__ void score_chunk_w(const Thresholds& T, const float* 
                     // what bounds this kernel, an FMUL is 8 times cheaper.  Padding / irregular features come in aligned pairs (k_prep_features),
                     // so a NaN never reaches a real feature's reciprocal.  mx in [1e-18, 1e6]: the product stays inside the FP32 range.
                     const float rp = rcp_approx(mx[0] * mx[1]);
-                    ri[0] = rp * mx[1];
-                    ri[1] = rp * mx[0];
+                    const float2 r2 = __fmul2_rn(make_float2(rp, rp), make_float2(mx[1], mx[0]));
+                    ri[0] = r2.x;
+                    ri[1] = r2.y;
                     }
                     else // the resident kernel (one 1024-thread CTA per SM, small scenes) measured 6 % faster at C2 with two reciprocals
                     {
                         ri[0] = rcp_approx(mx[0]);
                         ri[1] = rcp_approx(mx[1]);
                     }
-#pragma unroll
-                    for (int q = 0; q < 2; q++)
+                    if constexpr (GCR_WF2 >= 2 && !PRECISE)
                     {
-                        const float t = mn[q] * ri[q];
-                        const float z = t * t;
-                        float h;
-                        if (T.poly_deg == 2) h = fmaf(fmaf(T.pn[2], z, T.pn[1]), z, T.pn[0]); // uniform branch (kernel parameter)
-                        else h = fmaf(fmaf(fmaf(T.pn[3], z, T.pn[2]), z, T.pn[1]), z, T.pn[0]);
-                        gg[q] = fma_sat(-z, h, 1.0f);
+                        // t, z = t^2 and the polynomial of the pair as f32x2 operations too
+                        const float2 t2 = __fmul2_rn(make_float2(mn[0], mn[1]), make_float2(ri[0], ri[1]));
+                        const float2 z2 = __fmul2_rn(t2, t2);
+                        float2 h2;
+                        if (T.poly_deg == 2) // uniform branch (kernel parameter)
+                            h2 = __ffma2_rn(__ffma2_rn(make_float2(T.pn[2], T.pn[2]), z2, make_float2(T.pn[1], T.pn[1])), z2, make_float2(T.pn[0], T.pn[0]));
+                        else
+                            h2 = __ffma2_rn(__ffma2_rn(__ffma2_rn(make_float2(T.pn[3], T.pn[3]), z2, make_float2(T.pn[2], T.pn[2])), z2,
+                                                       make_float2(T.pn[1], T.pn[1])), z2, make_float2(T.pn[0], T.pn[0]));
+                        gg[0] = fma_sat(-z2.x, h2.x, 1.0f);
+                        gg[1] = fma_sat(-z2.y, h2.y, 1.0f);
+                    }
+                    else
+                    {
+#pragma unroll
+                        for (int q = 0; q < 2; q++)
+                        {
+                            const float t = mn[q] * ri[q];
+                            const float z = t * t;
+                            float h;
+                            if (T.poly_deg == 2) h = fmaf(fmaf(T.pn[2], z, T.pn[1]), z, T.pn[0]); // uniform branch (kernel parameter)
+                            else h = fmaf(fmaf(fmaf(T.pn[3], z, T.pn[2]), z, T.pn[1]), z, T.pn[0]);
+                            gg[q] = fma_sat(-z, h, 1.0f);
+                        }
                     }
                     gq = make_float2(gg[0], gg[1]);
                     rim[j] = fmaxf(fmaxf(rim[j], ri[0]), ri[1]);
@@ -503,7 +551,7 @@ __device__ __forceinline__ void score_chunk_w(const Thresholds& T, const float* 
         }
     }
 #pragma unroll
-    for (int j = 0; j < kHB; j++)
+    for (int j = 0; j < HB; j++)
     {
         if (CLS == 0) H[j].sum_s += static_cast<double>(acc[j].x) + static_cast<double>(acc[j].y);
         else
@@ -514,14 +562,14 @@ __device__ __forceinline__ void score_chunk_w(const Thresholds& T, const float* 
     }
 }
 
-// Hypothesis parameters of the kHB hypotheses of a thread: compact index first_compact + j * stride + lane_in_tile of the FP32
+// Hypothesis parameters of the HB hypotheses of a thread: compact index first_compact + j * stride + lane_in_tile of the FP32
 // list (from the front of the compact arrays) or of the precise list (from the back).
-template <bool PRECISE, bool SENTINEL = false>
-__device__ __forceinline__ void load_hyps(const Buffers& B, HypRegs (&H)[kHB], int first_compact, int stride, int t, int n_list,
+template <bool PRECISE, bool SENTINEL = false, int HB = 1>
+__device__ __forceinline__ void load_hyps(const Buffers& B, HypRegs (&H)[HB], int first_compact, int stride, int t, int n_list,
                                           bool from_back)
 {
 #pragma unroll
-    for (int j = 0; j < kHB; j++)
+    for (int j = 0; j < HB; j++)
     {
         const int k = first_compact + j * stride + t;
         const bool active = k < n_list;
@@ -548,11 +596,11 @@ __device__ __forceinline__ void load_hyps(const Buffers& B, HypRegs (&H)[kHB], i
 
 // Partial sums / counts of a thread's hypotheses into the per-hypothesis arrays: plain stores when this item covered every
 // feature, atomics when the feature range is split over several items.
-template <bool SENTINEL = false, bool WINNER = false>
-__device__ __forceinline__ void flush_hyps(const Buffers& B, const Thresholds& T, HypRegs (&H)[kHB], bool single_split)
+template <bool SENTINEL = false, bool WINNER = false, int HB = 1>
+__device__ __forceinline__ void flush_hyps(const Buffers& B, const Thresholds& T, HypRegs (&H)[HB], bool single_split)
 {
 #pragma unroll
-    for (int j = 0; j < kHB; j++)
+    for (int j = 0; j < HB; j++)
     {
         if (SENTINEL ? H[j].hyp == kNoHyp : !H[j].active) continue;
         const size_t h = H[j].hyp;
@@ -644,7 +692,7 @@ struct ChunkWalk // consecutive positions of the list, one division at the start
 
 // One work item: all chunks [c_begin, c_end) of this tile flavour's chunk list.
 // MODE: 0 winner-only (score_chunk_w), 1 per-hypothesis counts and sums (score_chunk), 2 as 1 + packed inlier masks of every hypothesis
-template <int MODE, bool PRECISE>
+template <int MODE, bool PRECISE, int HB>
 __device__ __forceinline__ void score_item(const Buffers& B, const Thresholds& T, ScoreSmem& S, uint32_t& ring,
                                            int first_compact, int n_list, bool from_back, int c_begin, int c_end,
                                            bool single_split)
@@ -671,8 +719,8 @@ __device__ __forceinline__ void score_item(const Buffers& B, const Thresholds& T
     };
     for (int p = 0; p < min(kStages - 1, nch); p++) issue(ring + p);
 
-    HypRegs H[kHB];
-    load_hyps<PRECISE>(B, H, first_compact, kScoreThreads, tid, n_list, from_back);
+    HypRegs H[HB];
+    load_hyps<PRECISE, false, HB>(B, H, first_compact, kScoreThreads, tid, n_list, from_back);
 
     for (int i = 0; i < nch; i++)
     {
@@ -684,24 +732,27 @@ __device__ __forceinline__ void score_item(const Buffers& B, const Thresholds& T
         const int ci = consume.next(orient);
         if constexpr (MODE == 0)
         {
-            if (!orient) score_chunk_w<PRECISE, 0>(T, S.stage[st], H);
-            else score_chunk_w<PRECISE, 1>(T, S.stage[st], H);
+            if (!orient) score_chunk_w<PRECISE, 0, false, HB>(T, S.stage[st], H);
+            else score_chunk_w<PRECISE, 1, false, HB>(T, S.stage[st], H);
         }
         else
         {
-            if (!orient) score_chunk<MODE == 2, PRECISE, 0>(B, T, S.stage[st], ci * NF, H);
-            else score_chunk<MODE == 2, PRECISE, 1>(B, T, S.stage[st], ci * NF, H);
+            if (!orient) score_chunk<MODE == 2, PRECISE, 0, false, HB>(B, T, S.stage[st], ci * NF, H);
+            else score_chunk<MODE == 2, PRECISE, 1, false, HB>(B, T, S.stage[st], ci * NF, H);
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&S.empty[st]);
     }
     ring += nch;
 
-    flush_hyps<false, MODE == 0>(B, T, H, single_split);
+    flush_hyps<false, MODE == 0, HB>(B, T, H, single_split);
 }
 
+// hypotheses per thread / CTAs per SM of the ring kernel: 2 / GCR_MINB (6) in winner-only runs, 1 / 8 in the reporting modes
+template <int MODE> constexpr int kRingHB = MODE == 0 ? GCR_HB : 1;
+template <int MODE> constexpr int kRingMinB = MODE == 0 ? GCR_MINB : 8;
 template <int MODE>
-__global__ void __launch_bounds__(kScoreThreads, GCR_MINB) k_score_fast(const __grid_constant__ Buffers B,
+__global__ void __launch_bounds__(kScoreThreads, kRingMinB<MODE>) k_score_fast(const __grid_constant__ Buffers B,
                                                               const __grid_constant__ Thresholds T)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -723,6 +774,7 @@ __global__ void __launch_bounds__(kScoreThreads, GCR_MINB) k_score_fast(const __
     pdl_wait(); // compact lists and counters of k_sample_solve
 
     const int n_fast = static_cast<int>(B.ctr->n_fast), n_sens = static_cast<int>(B.ctr->n_sens);
+    constexpr int HB = kRingHB<MODE>, kTileHyps = kScoreThreads * HB;
     const int tiles_a = (n_fast + kTileHyps - 1) / kTileHyps, tiles_b = (n_sens + kTileHyps - 1) / kTileHyps;
     const int chunks_a = B.ncs + B.nco, chunks_b = B.ncsd + B.ncod;
     // Work decomposition, identical in every CTA: the chunk lists are cut so that there are ~8 items per resident
@@ -753,13 +805,13 @@ __global__ void __launch_bounds__(kScoreThreads, GCR_MINB) k_score_fast(const __
         {
             const int k = item - items_b;
             const int split = splits_a - 1 - k / tiles_a, tile = k % tiles_a;
-            score_item<MODE, false>(B, T, S, ring, tile * kTileHyps, n_fast, false, split * cps_a,
+            score_item<MODE, false, HB>(B, T, S, ring, tile * kTileHyps, n_fast, false, split * cps_a,
                                      min(chunks_a, (split + 1) * cps_a), splits_a == 1);
         }
         else
         {
             const int split = splits_b - 1 - item / tiles_b, tile = item % tiles_b;
-            score_item<MODE, true>(B, T, S, ring, tile * kTileHyps, n_sens, true, split * cps_b,
+            score_item<MODE, true, HB>(B, T, S, ring, tile * kTileHyps, n_sens, true, split * cps_b,
                                     min(chunks_b, (split + 1) * cps_b), splits_b == 1);
         }
         GCR_STAMP(tr);
@@ -802,8 +854,9 @@ __device__ __forceinline__ void resident_task(const Buffers& B, const Thresholds
     constexpr int NF = PRECISE ? kChunk / 2 : kChunk; // features per chunk
     constexpr int G = PRECISE ? 2 : 4;
     constexpr int BPC = NF / 32, GPB = 32 / G;         // blocks per chunk, groups per block
-    HypRegs H[kHB];
-    load_hyps<PRECISE, true>(B, H, tile * 32 * kHB, 32, threadIdx.x & 31, n_list, PRECISE);
+    constexpr int HB = 1; // (one hypothesis per thread: 1024-thread CTAs leave 64 registers)
+    HypRegs H[HB];
+    load_hyps<PRECISE, true, HB>(B, H, tile * 32 * HB, 32, threadIdx.x & 31, n_list, PRECISE);
     const int s1 = min(b1, P.nbs);
     if (b0 < s1)
     {
@@ -834,7 +887,7 @@ __device__ __forceinline__ void resident_task(const Buffers& B, const Thresholds
             b = be;
         }
     }
-    flush_hyps<true, MODE == 0>(B, T, H, b0 == 0 && b1 == P.nbs + P.nbo); // plain stores when this warp covered the whole tile
+    flush_hyps<true, MODE == 0, HB>(B, T, H, b0 == 0 && b1 == P.nbs + P.nbo); // plain stores when this warp covered the whole tile
 }
 
 template <int MODE>
@@ -875,7 +928,7 @@ __global__ void __launch_bounds__(kResidentThreads, 1) k_score_resident(const __
     P.nbo = (B.no + 31) / 32;
     P.cost_o = cost_o;
     P.total = kCostS * P.nbs + cost_o * P.nbo;
-    const int tiles_a = (n_fast + 32 * kHB - 1) / (32 * kHB), tiles_b = (n_sens + 32 * kHB - 1) / (32 * kHB);
+    const int tiles_a = (n_fast + 31) / 32, tiles_b = (n_sens + 31) / 32;
     // the line of all tiles in units of 1/10 cost: a precise tile is cost_p * total long, an FP32 tile 10 * total
     const long long len_b = static_cast<long long>(cost_p) * P.total, len_a = 10ll * P.total;
     const long long end_b = len_b * tiles_b, end_all = end_b + len_a * tiles_a;
