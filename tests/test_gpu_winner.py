@@ -224,3 +224,47 @@ def test_selection_cascade_rare_paths(port):
         for n in (len(smp), 12_000, 4000):
             _check_winner(e, port, sc.scale, sc.orient, smp[:n], sc.thr, f"{env} n={n}")
         e.close()
+
+
+def test_full_size_c3_properties(port):
+    """BASELINE config C3 at its full size (50 000 + 20 000 features, 1 000 000 Philox hypotheses) through the C ABI, by properties that do
+    not need the oracle to replay a million hypotheses: idempotence, shard invariance (two half ranges and eight eighths combined by the
+    selection rule == the whole run), the winner's score / counts / masks == the CPU oracle's MSAC of the winning model, the winning
+    hypothesis' minimal sample == the oracle's Philox twin of that slot and its model == the oracle's solve of that sample, and no
+    hypothesis of an oracle-replayed slice of 3 000 slots beats it."""
+    import gcr_capi
+    import gcr_parallel
+    import gcr_scenes as gs
+    sc = gs.config_scene("C3")
+    H, seed = 1_000_000, 2025
+    eng = gcr_capi.Engine(0)
+    eng.set_features(sc.scale, sc.orient)
+    r1 = eng.run(H, sc.thr, seed=seed)
+    b1 = eng.best()
+    r2 = eng.run(H, sc.thr, seed=seed)
+    b2 = eng.best()
+    assert (r1.best_index, r1.best_score) == (r2.best_index, r2.best_score) and np.array_equal(b1["scale_words"], b2["scale_words"])
+    assert r1.n_scored < r1.n_solved < r1.n_sample_valid < H and r1.n_rechecked == 0
+    for parts in (2, 8):
+        recs = np.zeros(parts, dtype=gcr_capi.RECORD_DTYPE)
+        for k in range(parts):
+            first, count = gcr_parallel.shard_range(H, k, parts)
+            r = eng.run(count, sc.thr, seed=seed, first_hyp=first)
+            recs[k]["index"], recs[k]["score"] = r.best_index, r.best_score
+        w = gcr_parallel.select_record(recs)
+        assert int(recs[w]["index"]) == r1.best_index and float(recs[w]["score"]) == r1.best_score, parts
+    # the winner against the CPU oracle
+    val, n_inl, sm, om = port.score_model(sc.scale, sc.orient, b1["model"], sc.thr)
+    assert np.array_equal(sm, b1["scale_mask"]) and np.array_equal(om, b1["orient_mask"])
+    assert np.array_equal(np.asarray(n_inl, np.uint32), b1["n_inl"]) and abs(val - b1["score"]) <= 1e-10 * val
+    smp = port.sample_philox(seed, r1.best_index, 1, len(sc.scale), len(sc.orient))
+    one = port.replay(sc.scale, sc.orient, smp, sc.thr)
+    assert (one["flags"][0] & 7) == 7 and np.allclose(one["models"][0], b1["model"], rtol=1e-6, atol=1e-12)
+    assert abs(one["score"][0] - b1["score"]) <= 1e-10 * val
+    # the planted plane is found, and nothing in an oracle-replayed slice beats the winner
+    assert np.allclose(b1["model"][:2], sc.model[:2], atol=5e-5)
+    sl = port.sample_philox(seed, 400_000, 3000, len(sc.scale), len(sc.orient))
+    ora = port.replay(sc.scale, sc.orient, sl, sc.thr, want_masks=False, nthreads=0)
+    ok = (ora["flags"] & 6) == 6
+    assert ora["score"][ok].max() <= b1["score"]
+    eng.close()
