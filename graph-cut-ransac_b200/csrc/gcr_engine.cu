@@ -147,6 +147,7 @@ struct gcr_engine_s
     // non-minimal fits (gcr_fit_models)
     DevBuf<unsigned char> d_fit_in, d_fit_out;
     DevBuf<double> d_fit_lines, d_fit_partial;
+    DevBuf<unsigned int> d_fit_done; // per-fit counters of k_fit_rows, zero between calls
     PinnedBuf h_fit_in, h_fit_out, h_score_io;
 
     // keypoint front end (gcr_set_keypoints)
@@ -659,7 +660,7 @@ int gcr_destroy(gcr_handle h)
     if (h->h_best) cudaFreeHost(h->h_best);
     h->d_cand_model.release(); h->d_cand_score.release(); h->d_cand_qsum.release(); h->d_cand_rawcnt.release(); h->d_ctr.release();
     h->d_dbg_in.release(); h->d_dbg_out.release(); h->d_user_models.release();
-    h->d_fit_in.release(); h->d_fit_out.release(); h->d_fit_lines.release(); h->d_fit_partial.release();
+    h->d_fit_in.release(); h->d_fit_out.release(); h->d_fit_lines.release(); h->d_fit_partial.release(); h->d_fit_done.release();
     h->h_fit_in.release(); h->h_fit_out.release(); h->h_score_io.release();
     h->d_kp.release(); h->d_front_table.release(); h->d_front_counts.release(); h->d_front_sizes.release();
     if (h->ev0) cudaEventDestroy(h->ev0);
@@ -1326,6 +1327,7 @@ static int fit_models_impl(gcr_handle h, int64_t n_fits, const uint32_t* scale_i
     GCR_CUDA(h->d_fit_in.ensure(in_bytes));
     FitDesc* desc = reinterpret_cast<FitDesc*>(h->h_fit_in.p + in_desc);
     unsigned long long units = 0, entries = 0;
+    int longest_o = 0;
     for (size_t k = 0; k < K; ++k)
     {
         FitDesc& D = desc[k];
@@ -1336,12 +1338,14 @@ static int fit_models_impl(gcr_handle h, int64_t n_fits, const uint32_t* scale_i
         // two_sift.hpp:431-447,603-609 / three_sift.hpp:203-211: fewer constraints than a minimal sample -> no model; exactly a
         // minimal sample belongs to the minimal solver, which neither the local optimisation nor the refit presents
         D.valid = hybrid ? ((D.ns >= 2 && D.no >= 2 && !(D.ns == 2 && D.no == 2)) ? 1 : 0) : (D.ns > 3 ? 1 : 0);
-        D.pad_ = 0;
+        longest_o = std::max(longest_o, D.no);
         const unsigned long long rows =
             static_cast<unsigned long long>(D.ns) + (hybrid ? static_cast<unsigned long long>(D.no) * (D.no > 0 ? D.no - 1 : 0) / 2 : 0);
         D.unit_first = static_cast<unsigned int>(units);
         D.ent_off = static_cast<unsigned int>(entries);
-        units += std::max<unsigned long long>(1, (rows + kFitUnitRows - 1) / kFitUnitRows);
+        D.unit_rows = 1024;
+        while (D.unit_rows < kFitUnitRows && (rows + D.unit_rows - 1) / D.unit_rows > static_cast<unsigned long long>(kFitUnitsAim)) D.unit_rows *= 2;
+        units += std::max<unsigned long long>(1, (rows + D.unit_rows - 1) / D.unit_rows);
         entries += static_cast<unsigned long long>(std::min(D.no, kPhiBins));
         if (units > 0x7fffffffull) return h->fail(GCR_ERR_INVALID, "gcr_fit_models: too many rows");
     }
@@ -1359,29 +1363,47 @@ static int fit_models_impl(gcr_handle h, int64_t n_fits, const uint32_t* scale_i
     }
     GCR_CUDA(h->h_fit_out.ensure(out_bytes));
     GCR_CUDA(h->d_fit_out.ensure(out_bytes));
-    GCR_CUDA(h->d_fit_lines.ensure(3 * std::max<size_t>(O, 1)));
+    const bool lines_in_smem = longest_o <= kFitSmemLines;
+    if (!lines_in_smem) GCR_CUDA(h->d_fit_lines.ensure(3 * std::max<size_t>(O, 1)));
+    if (!h->d_fit_done.p)
+    {
+        GCR_CUDA(h->d_fit_done.ensure(kCandCap));
+        GCR_CUDA(cudaMemsetAsync(h->d_fit_done.p, 0, sizeof(unsigned int) * kCandCap, h->stream));
+    }
     GCR_CUDA(h->d_fit_partial.ensure(static_cast<size_t>(units) * 2 * kFitGram));
 
     cudaStream_t s = h->stream;
+    // Small calls (a batch of local-optimisation fits, the refit) are chains of microsecond kernels: their results are written into the
+    // page-locked output block by the kernels that produce them (posted writes), larger ones go through the copy engine.  The INPUT
+    // always does: descriptors and index lists read in place over PCIe put a ~1.5 us round trip into every dependent access of the
+    // row kernel (binary search over the descriptors, index, feature) -- measured 5-10 us slower per call than the one copy.
+    constexpr size_t kFitInPlaceBytes = size_t(256) << 10;
+    const bool out_place = out_bytes <= kFitInPlaceBytes;
+    const unsigned char* in_base = h->d_fit_in.p;
     GCR_CUDA(cudaMemcpyAsync(h->d_fit_in.p, h->h_fit_in.p, in_bytes, cudaMemcpyHostToDevice, s));
     FitBuffers F;
     F.scale = h->scale_ptr;
     F.orient = h->orient_ptr;
-    F.desc = reinterpret_cast<const FitDesc*>(h->d_fit_in.p + in_desc);
-    F.idx_s = reinterpret_cast<const unsigned int*>(h->d_fit_in.p + in_s);
-    F.idx_o = reinterpret_cast<const unsigned int*>(h->d_fit_in.p + in_o);
-    F.lines = h->d_fit_lines.p;
+    F.desc = reinterpret_cast<const FitDesc*>(in_base + in_desc);
+    F.idx_s = reinterpret_cast<const unsigned int*>(in_base + in_s);
+    F.idx_o = reinterpret_cast<const unsigned int*>(in_base + in_o);
+    F.lines = lines_in_smem ? nullptr : h->d_fit_lines.p;
+    F.done = h->d_fit_done.p;
     F.partial = h->d_fit_partial.p;
     F.models = reinterpret_cast<double*>(h->d_fit_out.p + out_models);
     F.ok = reinterpret_cast<int*>(h->d_fit_out.p + out_ok);
     F.n_ent = reinterpret_cast<unsigned int*>(h->d_fit_out.p + out_nent);
     F.ent = reinterpret_cast<FitEntry*>(h->d_fit_out.p + out_ent);
+    F.h_models = out_place ? reinterpret_cast<double*>(h->h_fit_out.p + out_models) : nullptr;
+    F.h_ok = out_place ? reinterpret_cast<int*>(h->h_fit_out.p + out_ok) : nullptr;
+    F.h_n_ent = out_place ? reinterpret_cast<unsigned int*>(h->h_fit_out.p + out_nent) : nullptr;
+    F.h_ent = out_place ? reinterpret_cast<FitEntry*>(h->h_fit_out.p + out_ent) : nullptr;
     F.n_fits = static_cast<int>(K);
     F.n_units = static_cast<unsigned int>(units);
     F.n_lines = static_cast<long long>(O);
     F.problem = h->problem;
     {
-        // the bucket counts the host's std::unordered_map<int, double> goes through while it grows to kPhiBins keys (k_fit_phi)
+        // the bucket counts the host's std::unordered_map<int, double> goes through while it grows to kPhiBins keys (fit_phi_block)
         struct Sched { int n; int at[8], to[8]; };
         static const Sched sched = [] {
             Sched sc{0, {}, {}};
@@ -1406,11 +1428,18 @@ static int fit_models_impl(gcr_handle h, int64_t n_fits, const uint32_t* scale_i
             F.rehash_to[i] = sched.to[i];
         }
     }
-    if (O) k_fit_lines<<<static_cast<unsigned int>((O + kFitThreads - 1) / kFitThreads), kFitThreads, 0, s>>>(F);
-    if (O) GCR_CUDA(launch_chained(h, k_fit_rows, dim3(F.n_units), dim3(kFitThreads), s, F));
-    else k_fit_rows<<<F.n_units, kFitThreads, 0, s>>>(F); // first kernel of the call: behind the input copy, plain
-    GCR_CUDA(launch_chained(h, k_fit_solve, dim3(static_cast<unsigned int>(K)), dim3(32), s, F));
-    if (hybrid) GCR_CUDA(launch_chained(h, k_fit_phi, dim3(static_cast<unsigned int>(K)), dim3(kFitThreads), s, F));
+    FitSlots slots{nullptr, nullptr, nullptr, nullptr};
+    if (do_score)
+    {
+        const Buffers B0 = make_buffers(h, 0, false, nullptr);
+        slots = FitSlots{B0.cand_model, B0.cand_hyp, B0.cand_qsum, B0.cand_rawcnt};
+    }
+    if (!lines_in_smem)
+    {
+        k_fit_lines<<<static_cast<unsigned int>((O + kFitThreads - 1) / kFitThreads), kFitThreads, 0, s>>>(F);
+        GCR_CUDA(launch_chained(h, k_fit_rows, dim3(F.n_units), dim3(kFitThreads), s, F, slots));
+    }
+    else k_fit_rows<<<F.n_units, kFitThreads, 0, s>>>(F, slots); // first kernel of the call, behind the input copy: plain
     if (do_score)
     {
         // the fitted models (phi: the device's histogram mode) scored against every feature in the same stream, no round trip: the
@@ -1423,18 +1452,18 @@ static int fit_models_impl(gcr_handle h, int64_t n_fits, const uint32_t* scale_i
         }
         T.strict = (score_flags & GCR_SCORE_STRICT) ? 1 : 0;
         const Buffers B = make_buffers(h, 0, false, nullptr);
+        unsigned char* out_base = out_place ? h->h_fit_out.p : h->d_fit_out.p;
         const unsigned int un = static_cast<unsigned int>(K);
         const unsigned long long su =
             static_cast<unsigned long long>(un) * ((h->ns + kExactThreads - 1) / kExactThreads + (h->no + kExactThreads - 1) / kExactThreads);
         const int sgrid = static_cast<int>(std::min<unsigned long long>(su, static_cast<unsigned long long>(h->n_sm) * 8));
-        GCR_CUDA(launch_chained(h, k_set_models, dim3((un + 127) / 128), dim3(128), s, B, reinterpret_cast<const Model4*>(F.models), un));
-        GCR_CUDA(launch_chained(h, k_exact_items, dim3(sgrid), dim3(kExactThreads), s, B, T, 2, un));
+        GCR_CUDA(launch_chained(h, k_exact_items, dim3(sgrid), dim3(kExactThreads), s, B, T, 2, un)); // (slots set by k_fit_finish)
         GCR_CUDA(launch_chained(h, k_score_out, dim3(std::max(1, std::min<int>(h->n_sm, static_cast<int>((Wm * K + 255) / 256)))), dim3(256), s, B, T,
-                                un, reinterpret_cast<double*>(h->d_fit_out.p + out_score), reinterpret_cast<unsigned int*>(h->d_fit_out.p + out_cnt),
-                                mask_words ? reinterpret_cast<unsigned int*>(h->d_fit_out.p + out_masks) : nullptr));
+                                un, reinterpret_cast<double*>(out_base + out_score), reinterpret_cast<unsigned int*>(out_base + out_cnt),
+                                mask_words ? reinterpret_cast<unsigned int*>(out_base + out_masks) : nullptr));
     }
     GCR_CUDA(cudaGetLastError());
-    GCR_CUDA(cudaMemcpyAsync(h->h_fit_out.p, h->d_fit_out.p, out_bytes, cudaMemcpyDeviceToHost, s));
+    if (!out_place) GCR_CUDA(cudaMemcpyAsync(h->h_fit_out.p, h->d_fit_out.p, out_bytes, cudaMemcpyDeviceToHost, s));
     GCR_CUDA(cudaStreamSynchronize(s));
 
     const double* m = reinterpret_cast<const double*>(h->h_fit_out.p + out_models);
