@@ -1482,7 +1482,11 @@ __device__ __forceinline__ void select_phase(const Buffers& B, const Thresholds&
 __global__ void __launch_bounds__(kExactThreads) k_tail(const __grid_constant__ Buffers B, const __grid_constant__ Thresholds T)
 {
     cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+#ifdef GCR_NO_TAIL_STAMPS
+    const bool stamp = false; // (A/B build: what the phase stamps themselves cost)
+#else
     const bool stamp = blockIdx.x == 0 && threadIdx.x == 0; // phase boundaries as seen by CTA 0 (diagnostics, ns)
+#endif
     pdl_wait(); // results of the scoring kernel
     if (stamp) B.phase_ns[0] = global_ns();
     const bool winner = !B.per_hyp;
