@@ -566,7 +566,7 @@ __device__ __forceinline__ void fit_finish_block(const FitBuffers& F, const FitS
     if (F.h_models != nullptr)
     {
         // (entries and their count: written before the barriers of fit_phi_block; the model and its verdict: by this thread 0)
-        const unsigned int n_ent = F.n_ent[k];
+        const unsigned int n_ent = __ldcg(&F.n_ent[k]); // (accumulated by atomics of this CTA)
         const unsigned int e0 = F.desc[k].ent_off;
         for (unsigned int i = threadIdx.x; i < n_ent; i += kFitThreads) F.h_ent[e0 + i] = F.ent[e0 + i];
         if (threadIdx.x == 0)

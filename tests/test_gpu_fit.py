@@ -114,6 +114,21 @@ def test_large_refit_millions_of_pairs(eng, pg):
     assert abs(models[0, 3] - m.phi) < PHI_ATOL
     truth = sc.model
     assert np.allclose(models[0, :2], truth[:2], rtol=0.05)  # and it is the scene's plane
+    # whichever CTA stores the last of the 790 row units finishes the fit, the units summed in index order: the same bits every time;
+    # and fits of very different sizes (row units of 1 024 ... 8 192 rows, lines in shared or global memory) side by side in one call
+    for _ in range(3):
+        again, _ok = eng.fit_models([si], [oi])
+        assert np.array_equal(again, models)
+    rng = np.random.default_rng(4)
+    s_lists = [si, rng.choice(si, 14, replace=False), rng.choice(si, 600, replace=False), si[:3000], rng.choice(si, 40, replace=False)]
+    o_lists = [oi, rng.choice(oi, 14, replace=False), rng.choice(oi, 150, replace=False), oi[:1100], rng.choice(oi, 900, replace=False)]
+    mixed, ok = eng.fit_models(s_lists, o_lists)
+    assert ok.all() and np.array_equal(mixed[0], models[0])
+    for k in range(1, 5):
+        alone, _ok = eng.fit_models([s_lists[k]], [o_lists[k]])
+        assert np.array_equal(alone[0], mixed[k]), k
+        m = pg._fit_non_minimal(sc.scale[s_lists[k]], sc.orient[o_lists[k]])
+        assert np.allclose(mixed[k, :3], [m.h7, m.h8, m.alpha], rtol=MODEL_RTOL, atol=1e-12), k
 
 
 def test_fit_argument_errors(eng):
