@@ -2,6 +2,7 @@
 // include/gcr_b200.h.  Compiled for sm_100a only, with -fmad=false (see gcr_exact.cuh).
 #include "gcr_kernels.cuh"
 #include "gcr_fit.cuh"
+#include "gcr_lo.cuh"
 #include "gcr_front.cuh"
 #include "../../include/gcr_b200.h"
 
@@ -149,6 +150,10 @@ struct gcr_engine_s
     DevBuf<double> d_fit_lines, d_fit_partial;
     DevBuf<unsigned int> d_fit_done; // per-fit counters of k_fit_rows, zero between calls
     PinnedBuf h_fit_in, h_fit_out, h_score_io;
+    // one round of the local optimisation on the device (gcr_lo_round)
+    DevBuf<unsigned int> d_lo_in, d_lo_info, d_lo_idx;
+    DevBuf<FitDesc> d_lo_desc;
+    PinnedBuf h_lo_out;
 
     // keypoint front end (gcr_set_keypoints)
     DevBuf<unsigned char> d_kp;
@@ -662,6 +667,7 @@ int gcr_destroy(gcr_handle h)
     h->d_dbg_in.release(); h->d_dbg_out.release(); h->d_user_models.release();
     h->d_fit_in.release(); h->d_fit_out.release(); h->d_fit_lines.release(); h->d_fit_partial.release(); h->d_fit_done.release();
     h->h_fit_in.release(); h->h_fit_out.release(); h->h_score_io.release();
+    h->d_lo_in.release(); h->d_lo_info.release(); h->d_lo_idx.release(); h->d_lo_desc.release(); h->h_lo_out.release();
     h->d_kp.release(); h->d_front_table.release(); h->d_front_counts.release(); h->d_front_sizes.release();
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
@@ -1295,6 +1301,55 @@ int gcr_score_models(gcr_handle h, const double* models, int64_t n, const double
     return GCR_OK;
 }
 
+// findWeightedMode (two_sift.hpp:354-394) on the histogram entries a fit returned (bins in order of first appearance): the heaviest
+// bin, the first strictly heavier one in the iteration order of an unordered_map<int, double> filled in input order; with unit weights
+// the weight order is the count order.  The REAL map of this host: the check of the device's restatement of its order.
+static double replay_phi(const FitEntry* e, unsigned int n)
+{
+    std::unordered_map<int, double> bin_weight;
+    for (unsigned int i = 0; i < n; ++i) bin_weight[e[i].bin] += static_cast<double>(e[i].count);
+    int mode_bin = 0;
+    double heaviest = -1.0;
+    for (const auto& kv : bin_weight)
+        if (kv.second > heaviest)
+        {
+            heaviest = kv.second;
+            mode_bin = kv.first;
+        }
+    double phi = 0.0;
+    for (unsigned int i = 0; i < n; ++i)
+        if (e[i].bin == mode_bin) phi = static_cast<double>(e[i].moment) / kPhiFixedPoint / static_cast<double>(e[i].count);
+    return phi;
+}
+
+// bucket-count schedule of this host's std::unordered_map<int, double> while it grows to kPhiBins keys (fit_phi_block)
+static void fill_rehash_schedule(FitBuffers& F)
+{
+    struct Sched { int n; int at[8], to[8]; };
+    static const Sched sched = [] {
+        Sched sc{0, {}, {}};
+        std::unordered_map<int, double> probe;
+        size_t last = probe.bucket_count();
+        for (int i = 0; i < kPhiBins; ++i)
+        {
+            probe[i] += 1.0;
+            if (probe.bucket_count() != last && sc.n < 8)
+            {
+                last = probe.bucket_count();
+                sc.at[sc.n] = i + 1;
+                sc.to[sc.n++] = static_cast<int>(last);
+            }
+        }
+        return sc;
+    }();
+    F.n_rehash = sched.n;
+    for (int i = 0; i < 8; ++i)
+    {
+        F.rehash_at[i] = sched.at[i];
+        F.rehash_to[i] = sched.to[i];
+    }
+}
+
 // gcr_fit_models, and with `thr` the scoring of the fitted models in the same launch sequence (gcr_fit_score_models)
 static int fit_models_impl(gcr_handle h, int64_t n_fits, const uint32_t* scale_idx, const int64_t* scale_off, const uint32_t* orient_idx,
                            const int64_t* orient_off, double* models, int32_t* ok, const double* thr, uint32_t score_flags, double* score,
@@ -1402,32 +1457,7 @@ static int fit_models_impl(gcr_handle h, int64_t n_fits, const uint32_t* scale_i
     F.n_units = static_cast<unsigned int>(units);
     F.n_lines = static_cast<long long>(O);
     F.problem = h->problem;
-    {
-        // the bucket counts the host's std::unordered_map<int, double> goes through while it grows to kPhiBins keys (fit_phi_block)
-        struct Sched { int n; int at[8], to[8]; };
-        static const Sched sched = [] {
-            Sched sc{0, {}, {}};
-            std::unordered_map<int, double> probe;
-            size_t last = probe.bucket_count();
-            for (int i = 0; i < kPhiBins; ++i)
-            {
-                probe[i] += 1.0;
-                if (probe.bucket_count() != last && sc.n < 8)
-                {
-                    last = probe.bucket_count();
-                    sc.at[sc.n] = i + 1;
-                    sc.to[sc.n++] = static_cast<int>(last);
-                }
-            }
-            return sc;
-        }();
-        F.n_rehash = sched.n;
-        for (int i = 0; i < 8; ++i)
-        {
-            F.rehash_at[i] = sched.at[i];
-            F.rehash_to[i] = sched.to[i];
-        }
-    }
+    fill_rehash_schedule(F);
     FitSlots slots{nullptr, nullptr, nullptr, nullptr};
     if (do_score)
     {
@@ -1476,22 +1506,7 @@ static int fit_models_impl(gcr_handle h, int64_t n_fits, const uint32_t* scale_i
         std::memcpy(models + 4 * k, m + 4 * k, 32);
         ok[k] = okd[k];
         if (!hybrid || !okd[k]) continue;
-        // findWeightedMode (two_sift.hpp:354-394): heaviest bin, the first strictly heavier one in the iteration order
-        // of an unordered_map<int, double> filled in input order; with unit weights the weight order is the count order
-        std::unordered_map<int, double> bin_weight;
-        const FitEntry* e = ent + desc[k].ent_off;
-        for (unsigned int i = 0; i < nent[k]; ++i) bin_weight[e[i].bin] += static_cast<double>(e[i].count);
-        int mode_bin = 0;
-        double heaviest = -1.0;
-        for (const auto& kv : bin_weight)
-            if (kv.second > heaviest)
-            {
-                heaviest = kv.second;
-                mode_bin = kv.first;
-            }
-        double phi = 0.0;
-        for (unsigned int i = 0; i < nent[k]; ++i)
-            if (e[i].bin == mode_bin) phi = static_cast<double>(e[i].moment) / kPhiFixedPoint / static_cast<double>(e[i].count);
+        const double phi = replay_phi(ent + desc[k].ent_off, nent[k]);
         models[4 * k + 3] = phi;
         if (do_score && phi != m[4 * k + 3]) phi_differs.push_back(k); // equally heavy bins, resolved differently: scored again below
     }
@@ -1550,6 +1565,136 @@ int gcr_fit_score_models(gcr_handle h, int64_t n_fits, const uint32_t* scale_idx
 {
     if (!thr) return GCR_ERR_INVALID;
     return fit_models_impl(h, n_fits, scale_idx, scale_off, orient_idx, orient_off, models, ok, thr, flags, score, n_inl, mask_words);
+}
+
+int gcr_lo_round(gcr_handle h, gcr_lo_round_io* io, const double thr[2], uint32_t label_flags, int32_t n_trials, const int32_t lim[2],
+                 const int32_t min_inl[2], uint32_t* mask_words)
+{
+    if (!h || !io || !thr || !lim || !min_inl) return GCR_ERR_INVALID;
+    if (h->ns < 2) return h->fail(GCR_ERR_STATE, "gcr_lo_round before gcr_set_features");
+    const bool hybrid = h->problem == 0;
+    if (!(thr[0] >= 0.0) || !std::isfinite(thr[0]) || (hybrid && (!(thr[1] >= 0.0) || !std::isfinite(thr[1]))))
+        return h->fail(GCR_ERR_INVALID, "thresholds must be finite and non-negative");
+    if (n_trials < 1 || n_trials > kCandCap) return h->fail(GCR_ERR_INVALID, "gcr_lo_round: 1 <= n_trials <= 1024");
+    if (lim[0] < 1 || lim[0] > kLoMaxSubset || (hybrid && (lim[1] < 1 || lim[1] > kLoMaxSubset)) || min_inl[0] < 0 || min_inl[1] < 0)
+        return h->fail(GCR_ERR_INVALID, "gcr_lo_round: sub-sample sizes must be 1 ... 32 per class");
+    GCR_DEVICE(h);
+    const int rc = ensure_common(h);
+    if (rc != GCR_OK) return rc;
+    const size_t K = static_cast<size_t>(n_trials);
+    const size_t lim_s = static_cast<size_t>(lim[0]), lim_o = hybrid ? static_cast<size_t>(lim[1]) : 1;
+    const size_t Wm = static_cast<size_t>((h->ns + 31) / 32 + (h->no + 31) / 32);
+    auto align16 = [](size_t x) { return (x + 15) & ~static_cast<size_t>(15); };
+    const size_t ent_per_fit = hybrid ? std::min<size_t>(lim_o, kPhiBins) : 0;
+    const size_t out_models = 0, out_ok = align16(K * 32), out_nent = align16(out_ok + 4 * K), out_ent = align16(out_nent + 4 * K),
+                 out_bytes = align16(out_ent + K * ent_per_fit * sizeof(FitEntry));
+    GCR_CUDA(h->d_fit_out.ensure(out_bytes));
+    GCR_CUDA(h->h_fit_out.ensure(out_bytes));
+    GCR_CUDA(h->d_fit_partial.ensure(K * 2 * kFitGram));
+    GCR_CUDA(h->d_lo_in.ensure(static_cast<size_t>(h->ns) + static_cast<size_t>(std::max(h->no, 0)) + 1));
+    GCR_CUDA(h->d_lo_info.ensure(4));
+    GCR_CUDA(h->d_lo_idx.ensure(K * (lim_s + lim_o)));
+    GCR_CUDA(h->d_lo_desc.ensure(K));
+    const size_t lo_words = align16(sizeof(LoResult));
+    GCR_CUDA(h->h_lo_out.ensure(lo_words + 4 * Wm));
+    if (!h->d_fit_done.p)
+    {
+        GCR_CUDA(h->d_fit_done.ensure(kCandCap));
+        GCR_CUDA(cudaMemsetAsync(h->d_fit_done.p, 0, sizeof(unsigned int) * kCandCap, h->stream));
+    }
+    cudaStream_t s = h->stream;
+
+    LoRound R;
+    R.model = Model4{io->model[0], io->model[1], io->model[2], io->model[3]};
+    R.score = io->score;
+    R.rng_state = io->rng_state;
+    R.n_trials = n_trials;
+    R.lim[0] = lim[0];
+    R.lim[1] = hybrid ? lim[1] : 0;
+    R.min_inl[0] = min_inl[0];
+    R.min_inl[1] = min_inl[1];
+    R.hybrid = hybrid ? 1 : 0;
+    LoDevice L;
+    L.in_idx = h->d_lo_in.p;
+    L.info = h->d_lo_info.p;
+    L.desc = h->d_lo_desc.p;
+    L.idx_s = h->d_lo_idx.p;
+    L.idx_o = h->d_lo_idx.p + K * lim_s;
+    L.out = reinterpret_cast<LoResult*>(h->h_lo_out.p);
+    L.out_words = reinterpret_cast<unsigned int*>(h->h_lo_out.p + lo_words);
+
+    FitBuffers F;
+    F.scale = h->scale_ptr;
+    F.orient = h->orient_ptr;
+    F.desc = L.desc;
+    F.idx_s = L.idx_s;
+    F.idx_o = L.idx_o;
+    F.lines = nullptr; // (<= 32 orientation features per fit: lines in shared memory)
+    F.done = h->d_fit_done.p;
+    F.partial = h->d_fit_partial.p;
+    F.models = reinterpret_cast<double*>(h->d_fit_out.p + out_models);
+    F.ok = reinterpret_cast<int*>(h->d_fit_out.p + out_ok);
+    F.n_ent = reinterpret_cast<unsigned int*>(h->d_fit_out.p + out_nent);
+    F.ent = reinterpret_cast<FitEntry*>(h->d_fit_out.p + out_ent);
+    F.h_models = reinterpret_cast<double*>(h->h_fit_out.p + out_models);
+    F.h_ok = reinterpret_cast<int*>(h->h_fit_out.p + out_ok);
+    F.h_n_ent = reinterpret_cast<unsigned int*>(h->h_fit_out.p + out_nent);
+    F.h_ent = reinterpret_cast<FitEntry*>(h->h_fit_out.p + out_ent);
+    F.n_fits = n_trials;
+    F.n_units = static_cast<unsigned int>(K);
+    F.n_lines = 0;
+    F.problem = h->problem;
+    fill_rehash_schedule(F);
+
+    Thresholds T = make_thresholds(thr, h->problem), TL = T;
+    if (label_flags & GCR_SCORE_TRUNCATED_SQ)
+    {
+        TL.tsq[0] = (1.5 * thr[0]) * (1.5 * thr[0]);
+        TL.tsq[1] = (1.5 * thr[1]) * (1.5 * thr[1]);
+    }
+    TL.strict = (label_flags & GCR_SCORE_STRICT) ? 1 : 0;
+    const Buffers B = make_buffers(h, 0, false, nullptr);
+    const FitSlots slots{B.cand_model, B.cand_hyp, B.cand_qsum, B.cand_rawcnt};
+    const unsigned long long upi = (h->ns + kExactThreads - 1) / kExactThreads + (h->no + kExactThreads - 1) / kExactThreads;
+    const int grid1 = static_cast<int>(std::min<unsigned long long>(upi, static_cast<unsigned long long>(h->n_sm) * 8));
+    const int gridK = static_cast<int>(std::min<unsigned long long>(upi * K, static_cast<unsigned long long>(h->n_sm) * 8));
+    k_lo_label<<<grid1, kExactThreads, 0, s>>>(B, TL, R);
+    GCR_CUDA(launch_chained(h, k_lo_draw, dim3(1), dim3(kLoThreads), s, B, R, L));
+    GCR_CUDA(launch_chained(h, k_fit_rows, dim3(F.n_units), dim3(kFitThreads), s, F, slots));
+    GCR_CUDA(launch_chained(h, k_exact_items, dim3(gridK), dim3(kExactThreads), s, B, T, 2, static_cast<unsigned int>(K)));
+    GCR_CUDA(launch_chained(h, k_lo_select, dim3(1), dim3(256), s, B, T, R, L, static_cast<const double*>(F.models), static_cast<const int*>(F.ok)));
+    GCR_CUDA(cudaGetLastError());
+    GCR_CUDA(cudaStreamSynchronize(s));
+
+    const LoResult& r = *reinterpret_cast<const LoResult*>(h->h_lo_out.p);
+    io->phi_mismatch = 0;
+    if (hybrid && r.sampled)
+    {
+        // the device's restatement of the map order against this host's real map, on every trial's histogram entries
+        const double* m = reinterpret_cast<const double*>(h->h_fit_out.p + out_models);
+        const int* okd = reinterpret_cast<const int*>(h->h_fit_out.p + out_ok);
+        const unsigned int* nent = reinterpret_cast<const unsigned int*>(h->h_fit_out.p + out_nent);
+        const FitEntry* ent = reinterpret_cast<const FitEntry*>(h->h_fit_out.p + out_ent);
+        for (size_t k = 0; k < K; ++k)
+            if (okd[k] && replay_phi(ent + k * ent_per_fit, nent[k]) != m[4 * k + 3]) io->phi_mismatch += 1;
+        h->n_phi_fallbacks += io->phi_mismatch;
+    }
+    io->updated = r.updated;
+    io->sampled = r.sampled;
+    io->n_models_scored = r.n_models_scored;
+    io->n_labelled[0] = r.n_in[0];
+    io->n_labelled[1] = r.n_in[1];
+    if (io->phi_mismatch) return GCR_OK; // the caller repeats the round through gcr_score_models / gcr_fit_score_models; nothing else is reported
+    io->rng_state += r.draws * 0x9E3779B97F4A7C15ull;
+    if (r.updated)
+    {
+        std::memcpy(io->model, r.model, sizeof(io->model));
+        io->score = r.score;
+        io->n_inl[0] = r.n_inl[0];
+        io->n_inl[1] = r.n_inl[1];
+        if (mask_words) std::memcpy(mask_words, h->h_lo_out.p + lo_words, 4 * Wm);
+    }
+    return GCR_OK;
 }
 
 int gcr_score_model(gcr_handle h, const double model[4], const double thr[2], double* score, uint32_t n_inl[2],

@@ -95,17 +95,21 @@ struct SplitMix
 };
 
 // k distinct entries of `from`, uniformly (partial Fisher-Yates); the role of get_random_subset (GCRANSAC.h:53-80)
-void drawSubset(const std::vector<uint32_t>& from, size_t k, SplitMix& rng, std::vector<uint32_t>& scratch,
-                std::vector<uint32_t>& out)
+// (`scratch` holds a copy of the list the caller made once; the k swaps are undone before returning, so that the many draws from one
+// list -- 50 trials per inner RANSAC, 12 000 entries at C3 -- do not copy it each time)
+void drawSubset(size_t k, SplitMix& rng, std::vector<uint32_t>& scratch, std::vector<uint32_t>& out)
 {
-    scratch = from;
+    static thread_local std::vector<size_t> swapped;
+    swapped.resize(k);
     out.clear();
     for (size_t i = 0; i < k; ++i)
     {
         const size_t j = i + rng.below(static_cast<uint32_t>(scratch.size() - i));
         std::swap(scratch[i], scratch[j]);
+        swapped[i] = j;
         out.push_back(scratch[i]);
     }
+    for (size_t i = k; i-- > 0;) std::swap(scratch[i], scratch[swapped[i]]);
 }
 
 void wordsToIndices(const uint32_t* words, size_t n, std::vector<uint32_t>& out)
@@ -259,7 +263,7 @@ static int estimateImpl(int problem, const double* scale, size_t ns, const doubl
 
     // ---- local optimisation on the selected model (graphCutLocalOptimization for two classes, GCRANSAC.h:873-1062)
     SplitMix rng{st.seed ^ 0x6C6F63616C6F7074ull};
-    std::vector<uint32_t> lab_words(W), in_s, in_o, smp_s, smp_o, scratch;
+    std::vector<uint32_t> lab_words(W), in_s, in_o, smp_s, smp_o, scratch_s, scratch_o;
     std::vector<double> trial_scores;
     std::vector<uint32_t> trial_cnt, trial_words;
     // Non-minimal fits run on the device (gcr_fit_models), all trials of one inner RANSAC in one pass
@@ -304,9 +308,38 @@ static int estimateImpl(int problem, const double* scale, size_t ns, const doubl
     if (opt.do_local_optimization && max_lo > 0)
     {
         Best lo = best; // max_score / best_model / best_inliers of the reference
+        // One launch sequence and one synchronisation per pass (gcr_lo_round: labels, this generator's sub-samples drawn on the device,
+        // fits, scores, the strict-< update) where the sub-sample sizes allow; the two-call form below otherwise, and for a pass whose
+        // device-side histogram tie order disagreed with this host's std::unordered_map (never with libstdc++).
+        const bool device_rounds = lim_s <= 32 && (!hybrid || lim_o <= 32) && max_lo <= 1024;
         while (static_cast<size_t>(++st.graph_cut_number) < opt.max_graph_cut_number)
         {
             bool updated = false;
+            if (device_rounds)
+            {
+                gcr_lo_round_io io;
+                std::memset(&io, 0, sizeof(io));
+                std::memcpy(io.model, lo.model, sizeof(io.model));
+                io.score = lo.score;
+                io.rng_state = rng.s;
+                const int32_t lim[2] = {static_cast<int32_t>(lim_s), static_cast<int32_t>(lim_o)};
+                const int32_t mins[2] = {static_cast<int32_t>(min_s), static_cast<int32_t>(min_o)};
+                lab_words.resize(W);
+                eng.check(gcr_lo_round(eng.h, &io, thr, label_flags, static_cast<int32_t>(max_lo), lim, mins, lab_words.data()), "gcr_lo_round");
+                if (!io.phi_mismatch)
+                {
+                    if (!io.sampled) break; // sampling fails: neither a draw nor "use all" applies
+                    rng.s = io.rng_state;
+                    st.lo_models_scored += io.n_models_scored;
+                    if (!io.updated) break;
+                    lo.score = io.score;
+                    std::memcpy(lo.model, io.model, sizeof(lo.model));
+                    lo.n_inl[0] = io.n_inl[0];
+                    lo.n_inl[1] = io.n_inl[1];
+                    lo.words.assign(lab_words.begin(), lab_words.end());
+                    continue;
+                }
+            }
             // relabel every feature with the truncated threshold r^2 <= (1.5 t)^2   (GCRANSAC.h:931-937)
             eng.check(gcr_score_models(eng.h, lo.model, 1, thr, label_flags, nullptr, nullptr, lab_words.data()),
                       "gcr_score_models(label)");
@@ -316,10 +349,12 @@ static int estimateImpl(int problem, const double* scale, size_t ns, const doubl
             const size_t k_s = std::min(lim_s, in_s.size()), k_o = std::min(lim_o, in_o.size());
             if (in_s.size() <= min_s || (hybrid && in_o.size() <= min_o)) break; // sampling fails: neither a draw nor "use all" applies
             fitBegin();
+            scratch_s = in_s;
+            scratch_o = in_o;
             for (size_t trial = 0; trial < std::min<size_t>(max_lo, 1024); ++trial) // one device pass holds 1024 fits / models
             {
-                if (k_s < in_s.size()) drawSubset(in_s, k_s, rng, scratch, smp_s); else smp_s = in_s;
-                if (k_o < in_o.size()) drawSubset(in_o, k_o, rng, scratch, smp_o); else smp_o = in_o;
+                if (k_s < in_s.size()) drawSubset(k_s, rng, scratch_s, smp_s); else smp_s = in_s;
+                if (k_o < in_o.size()) drawSubset(k_o, rng, scratch_o, smp_o); else smp_o = in_o;
                 fitAdd(smp_s, smp_o);
             }
             // all trial fits AND their scores in one device pass (gcr_fit_score_models): fit k's model goes through getScore on the device

@@ -27,6 +27,7 @@ EXPORTS = [
     "gcr_best",
     "gcr_fetch", "gcr_score_model", "gcr_score_models", "gcr_fit_models", "gcr_set_keypoints", "gcr_debug_eval", "gcr_version", "gcr_peer_export",
     "gcr_peer_attach", "gcr_peer_buffer", "gcr_peer_attach_ptrs", "gcr_peer_detach", "gcr_score_models_static", "gcr_fit_score_models", "gcr_debug_phi_fallbacks",
+    "gcr_lo_round",
 ]
 
 
@@ -41,6 +42,14 @@ class GcrResult(C.Structure):
         ("stage_phase_us", C.c_float * 2),
         ("n_refined", C.c_int64),
         ("n_scored", C.c_int64),
+    ]
+
+
+class GcrLoRoundIo(C.Structure):  # gcr_lo_round_io
+    _fields_ = [
+        ("model", C.c_double * 4), ("score", C.c_double), ("n_inl", C.c_uint32 * 2), ("rng_state", C.c_uint64),
+        ("updated", C.c_uint32), ("sampled", C.c_uint32), ("n_models_scored", C.c_uint32), ("phi_mismatch", C.c_uint32),
+        ("n_labelled", C.c_uint32 * 2),
     ]
 
 
@@ -77,6 +86,7 @@ def load_library() -> C.CDLL:
     lib.gcr_score_models.argtypes = [vp, vp, i64, vp, u32, vp, vp, vp]
     lib.gcr_fit_models.argtypes = [vp, i64, vp, vp, vp, vp, vp, vp]
     lib.gcr_fit_score_models.argtypes = [vp, i64, vp, vp, vp, vp, vp, u32, vp, vp, vp, vp, vp]
+    lib.gcr_lo_round.argtypes = [vp, C.POINTER(GcrLoRoundIo), vp, u32, C.c_int32, vp, vp, vp]
     lib.gcr_set_keypoints.argtypes = [vp, vp, i64, C.c_int, C.c_int, vp, vp, vp]
     lib.gcr_peer_export.argtypes = [vp, vp]
     lib.gcr_peer_attach.argtypes = [vp, vp, C.c_int, C.c_int]
@@ -316,6 +326,19 @@ class Engine:
                                                   (1 if truncated_sq else 0) | (2 if strict else 0), models.ctypes.data, ok.ctypes.data,
                                                   score.ctypes.data, n_inl.ctypes.data, words.ctypes.data if masks else None))
         return models, ok.astype(bool), score, n_inl, words
+
+    def lo_round(self, model, score, rng_state, thr, n_trials, lim, min_inl, label_flags=SCORE_TRUNCATED_SQ):
+        """gcr_lo_round: one pass of the local optimisation's loop on the device -> (io struct, mask words of the new best or None)."""
+        io = GcrLoRoundIo()
+        for c in range(4):
+            io.model[c] = float(model[c])
+        io.score, io.rng_state = float(score), int(rng_state) & 0xFFFFFFFFFFFFFFFF
+        thr = np.ascontiguousarray(thr, np.float64)
+        lim_a, min_a = np.ascontiguousarray(lim, np.int32), np.ascontiguousarray(min_inl, np.int32)
+        words = np.zeros((self.ns + 31) // 32 + (self.no + 31) // 32, np.uint32)
+        self._check(self.lib.gcr_lo_round(self.h, C.byref(io), thr.ctypes.data, label_flags, int(n_trials), lim_a.ctypes.data, min_a.ctypes.data,
+                                          words.ctypes.data))
+        return io, (words if io.updated else None)
 
     def debug_eval(self, which, abc, model=None):
         abc = np.ascontiguousarray(abc, np.float64).reshape(-1, 3)

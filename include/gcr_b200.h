@@ -248,6 +248,37 @@ int gcr_fit_score_models(gcr_handle h, int64_t n_fits, const uint32_t* scale_idx
                          const int64_t* orient_off, const double thr[2], uint32_t flags, double* models, int32_t* ok, double* score,
                          uint32_t* n_inl, uint32_t* mask_words);
 
+/* One pass of the local optimisation's loop as ONE launch sequence with ONE synchronisation: GCRANSAC::graphCutLocalOptimization,
+ * GCRANSAC.h:873-1062 (two classes; one class: :759-870 over the empty neighbourhood graph) --
+ *   labels: every resident feature against io->model with the relabelling threshold (label_flags: GCR_SCORE_TRUNCATED_SQ, and
+ *     GCR_SCORE_STRICT for the one-class problems)                                                            GCRANSAC.h:931-937
+ *   inner RANSAC: n_trials times, min(lim[c], labelled inliers of class c) labelled inliers per class drawn without replacement
+ *     (a class no larger than lim[c] is taken whole), non-minimal fit, getScore with `thr`                    GCRANSAC.h:955-1046
+ *   update: the first trial that scores strictly higher than io->score and every trial before it              GCRANSAC.h:1034
+ * -- what gcr_score_models(labels) + host-side draws + gcr_fit_score_models did in two synchronous calls.  The draws are those of a
+ * SplitMix64 generator with state io->rng_state consumed in the order (trial, scale class, orientation class, draw): draw i of a
+ * sub-sample swaps positions i and i + floor(u * (n - i) / 2^32) of the ascending list of labelled inliers (u = upper 32 bits of the
+ * generator's next output) and takes the new entry at i -- a partial Fisher-Yates shuffle, the role of the reference's
+ * get_random_subset (GCRANSAC.h:53-80); the reference's own sampler is seeded from std::random_device and cannot be replayed.
+ * In: io->model, io->score (the so-far-best), io->rng_state.  Out: io->sampled = 0 if a class has no more than min_inl[c] labelled
+ * inliers (the reference's sampling fails: the optimisation ends; nothing else changes); else io->n_models_scored trials produced a
+ * model, io->rng_state is advanced by the draws, and if io->updated the model, score, n_inl (after the zero-reset rule) and mask_words
+ * (u32[ceil(Ns/32)+ceil(No/32)], may be NULL) are the winning trial's.  io->phi_mismatch != 0 (never with libstdc++, see
+ * gcr_debug_phi_fallbacks): the device's tie order of the orientation histogram differed from this host's std::unordered_map for that
+ * many trials; io is otherwise unchanged and the caller runs the round through the two-call path.  lim[c] <= 32, n_trials <= 1024.
+ * No counterpart as a single function in the reference: it is the body of its LO loop. */
+typedef struct gcr_lo_round_io
+{
+    double model[4];
+    double score;
+    uint32_t n_inl[2];
+    uint64_t rng_state;
+    uint32_t updated, sampled, n_models_scored, phi_mismatch;
+    uint32_t n_labelled[2]; /* out: labelled inliers per class */
+} gcr_lo_round_io;
+int gcr_lo_round(gcr_handle h, gcr_lo_round_io* io, const double thr[2], uint32_t label_flags, int32_t n_trials, const int32_t lim[2],
+                 const int32_t min_inl[2], uint32_t* mask_words);
+
 /* Diagnostics: fits of gcr_fit_score_models calls on this handle whose device-side phi (histogram mode under the device's restatement of
  * the reference's unordered_map order) differed from the host's replay of the real map and were scored a second time; 0 when the two agree. */
 long long gcr_debug_phi_fallbacks(gcr_handle h);

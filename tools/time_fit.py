@@ -40,4 +40,14 @@ for name in (sys.argv[1:] or ["C1", "C3"]):
     print(f"{name}: LO batch shape (50 fits of 14+14, no masks): median {med:.1f} us, min {mn:.1f} us")
     med, mn = timed(lib, eng, [rng.choice(si, 14, replace=False)], [rng.choice(oi, 14, replace=False)], sc.thr, False)
     print(f"{name}: one small fit (14+14): median {med:.1f} us, min {mn:.1f} us")
+    # one pass of the local optimisation's loop as gcr_lo_round issues it (labels, draws, 50 fits, scores, update)
+    import ctypes as C
+    start = np.array(sc.model) * (1.0 + 0.01 * np.random.default_rng(1).standard_normal(4))
+    ts = []
+    for _ in range(int(os.environ.get("REPS", "200"))):
+        t0 = time.perf_counter()
+        io, words = eng.lo_round(start, 0.0, 12345, sc.thr, 50, (14, 14), (2, 2))
+        ts.append((time.perf_counter() - t0) * 1e6)
+    ts = np.array(ts[min(10, len(ts) - 1):])
+    print(f"{name}: gcr_lo_round (labels + 50 trials of 14+14 + update; Python wrapper included): median {np.median(ts):.1f} us, min {ts.min():.1f} us")
     eng.close()
