@@ -120,6 +120,7 @@ struct gcr_engine_s
     bool have_masks = false, have_run = false, have_per_hyp = false;
     DevBuf<int> d_samples;
     const int* samples_view = nullptr; // where the samples of the last run live (own buffer or the caller's device array)
+    bool samples_u16 = false;          // ... as uint16 indices (GCR_RUN_SAMPLES_U16)
     DevBuf<Model4> d_models;
     DevBuf<unsigned char> d_flags;
     DevBuf<double> d_sums, d_score;
@@ -365,6 +366,7 @@ Buffers make_buffers(gcr_engine_s* h, unsigned long long seed, bool have_samples
     B.seed = seed;
     B.samples = const_cast<int*>(h->samples_view);
     B.have_samples = have_samples ? 1 : 0;
+    B.samples_u16 = have_samples && h->samples_u16 ? 1 : 0;
     B.models = h->d_models.p;
     B.flags = h->d_flags.p;
     B.sums = h->d_sums.p;
@@ -992,6 +994,10 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
 
     cudaStream_t s = h->stream;
     h->samples_view = h->d_samples.p;
+    h->samples_u16 = samples != nullptr && (flags & GCR_RUN_SAMPLES_U16) != 0;
+    if (h->samples_u16 && (h->ns > 65535 || h->no > 65535))
+        return h->fail(GCR_ERR_INVALID, "GCR_RUN_SAMPLES_U16: a class has more than 65 535 features");
+    const size_t sample_bytes = (h->samples_u16 ? sizeof(uint16_t) : sizeof(int)) * 4 * H;
     if (samples)
     {
         if (flags & GCR_RUN_SAMPLES_ON_DEVICE)
@@ -1005,14 +1011,14 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
             cudaPointerAttributes attr;
             static const bool no_zero_copy = std::getenv("GCR_NO_ZEROCOPY") != nullptr;
             if (!no_zero_copy && cudaPointerGetAttributes(&attr, samples) == cudaSuccess && attr.type == cudaMemoryTypeHost &&
-                attr.devicePointer != nullptr && reinterpret_cast<uintptr_t>(attr.devicePointer) % 16 == 0)
+                attr.devicePointer != nullptr && reinterpret_cast<uintptr_t>(attr.devicePointer) % (h->samples_u16 ? 8 : 16) == 0)
                 mapped = static_cast<const int*>(attr.devicePointer);
             else
                 cudaGetLastError(); // pageable memory: cudaPointerGetAttributes may leave an error state on old drivers
             if (mapped)
                 h->samples_view = mapped;
             else
-                GCR_CUDA(cudaMemcpyAsync(h->d_samples.p, samples, sizeof(int) * 4 * H, cudaMemcpyHostToDevice, s));
+                GCR_CUDA(cudaMemcpyAsync(h->d_samples.p, samples, sample_bytes, cudaMemcpyHostToDevice, s));
         }
     }
     const Thresholds T = make_thresholds(thr, h->problem);
@@ -1230,7 +1236,17 @@ int gcr_fetch(gcr_handle h, uint8_t* flags, double* models, double* score, uint3
     if (models) GCR_CUDA(cudaMemcpy(models, h->d_models.p, H * sizeof(Model4), cudaMemcpyDeviceToHost));
     if (score) GCR_CUDA(cudaMemcpy(score, h->d_score.p, H * sizeof(double), cudaMemcpyDeviceToHost));
     if (n_inl) GCR_CUDA(cudaMemcpy(n_inl, h->d_ninl.p, 2 * H * sizeof(unsigned int), cudaMemcpyDeviceToHost));
-    if (samples) GCR_CUDA(cudaMemcpy(samples, h->samples_view, 4 * H * sizeof(int), cudaMemcpyDeviceToHost));
+    if (samples)
+    {
+        if (h->samples_u16) // (replayed from a uint16 array: widened here, 0xFFFF = the unused index -1)
+        {
+            std::vector<uint16_t> narrow(4 * H);
+            GCR_CUDA(cudaMemcpy(narrow.data(), h->samples_view, 4 * H * sizeof(uint16_t), cudaMemcpyDeviceToHost));
+            for (size_t i = 0; i < 4 * H; ++i) samples[i] = (i % 4 == 3 && narrow[i] == 0xffffu) ? -1 : static_cast<int>(narrow[i]);
+        }
+        else
+            GCR_CUDA(cudaMemcpy(samples, h->samples_view, 4 * H * sizeof(int), cudaMemcpyDeviceToHost));
+    }
     if (masks)
     {
         if (!h->have_masks) return h->fail(GCR_ERR_STATE, "masks were not kept: run with GCR_RUN_EMIT_MASKS");

@@ -238,8 +238,16 @@ __global__ void __launch_bounds__(128) k_sample_solve(Buffers B, Thresholds T, i
     {
         if (B.have_samples)
         {
-            const int4 s = reinterpret_cast<const int4*>(B.samples)[h];
-            s0 = s.x; s1 = s.y; o0 = s.z; o1 = s.w;
+            if (B.samples_u16)
+            {
+                const ushort4 s = reinterpret_cast<const ushort4*>(B.samples)[h];
+                s0 = s.x; s1 = s.y; o0 = s.z; o1 = s.w == 0xffffu ? -1 : static_cast<int>(s.w);
+            }
+            else
+            {
+                const int4 s = reinterpret_cast<const int4*>(B.samples)[h];
+                s0 = s.x; s1 = s.y; o0 = s.z; o1 = s.w;
+            }
         }
         else
         {

@@ -137,6 +137,7 @@ struct Buffers
     unsigned long long first_hyp, seed;
     int* samples;       // [H,4]
     int have_samples;   // replay mode
+    int samples_u16;    // replay mode: the array holds uint16 indices (GCR_RUN_SAMPLES_U16)
     Model4* models;     // [H]
     unsigned char* flags; // [H]
     double* sums;       // [H,2]  sum of r^2 over inliers per class

@@ -15,7 +15,7 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("GCR_B200_LIB", os.path.join(PKG_DIR, "libgcr_b200.so"))  # override: kernel-variant sweeps
 
 FLAG_SAMPLE_VALID, FLAG_SOLVED, FLAG_MODEL_VALID, FLAG_EXACT = 1, 2, 4, 8
-RUN_EMIT_MASKS, RUN_SAMPLES_ON_DEVICE, RUN_KEEP_PER_HYP, RUN_ALL_EXACT, RUN_EXCHANGE, RUN_TIME_KERNELS = 1, 2, 4, 8, 16, 32
+RUN_EMIT_MASKS, RUN_SAMPLES_ON_DEVICE, RUN_KEEP_PER_HYP, RUN_ALL_EXACT, RUN_EXCHANGE, RUN_TIME_KERNELS, RUN_SAMPLES_U16 = 1, 2, 4, 8, 16, 32, 64
 FEATURES_ON_DEVICE, FEATURES_HOST_LIBM = 1, 2
 IPC_HANDLE_BYTES = 64
 PROBLEM_HYBRID, PROBLEM_SCALE_ONLY, PROBLEM_SCALE_ONLY_ORIGINAL = 0, 1, 2
@@ -210,9 +210,13 @@ class Engine:
         thr_c = (C.c_double * 2)(float(thr[0]), float(thr[1]))
         sp = None
         if samples is not None:
-            samples = np.ascontiguousarray(samples, np.int32)
+            if np.asarray(samples).dtype == np.uint16:  # GCR_RUN_SAMPLES_U16: half the bytes of a replayed host array
+                samples = np.ascontiguousarray(samples, np.uint16)
+                flags |= RUN_SAMPLES_U16
+            else:
+                samples = np.ascontiguousarray(samples, np.int32)
             if samples.shape != (n_hyp, 4):
-                raise ValueError("samples must be int32 [n_hyp,4]")
+                raise ValueError("samples must be int32 or uint16 [n_hyp,4]")
             self._samples_keep = samples
             sp = C.c_void_p(samples.ctypes.data)
         elif samples_ptr is not None:

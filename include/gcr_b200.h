@@ -56,6 +56,8 @@ enum gcr_status
 #define GCR_RUN_KEEP_PER_HYP 4u      /* keep per-hypothesis models/scores/counts for gcr_fetch (implied by EMIT_MASKS) */
 #define GCR_RUN_ALL_EXACT 8u         /* score every hypothesis with the FP64 reference-order kernel (validation) */
 #define GCR_RUN_EXCHANGE 16u         /* multi-GPU: exchange winner records with the attached peers inside the last kernel */
+#define GCR_RUN_SAMPLES_U16 64u      /* `samples` holds uint16_t[n_hyp,4] instead of int32_t[n_hyp,4] (both classes <= 65 535 features; the unused
+                                      * fourth index of the scale-only problems is 0xFFFF): half the bytes over PCIe for a replayed host array */
 #define GCR_RUN_TIME_KERNELS 32u     /* diagnostics: CUDA events around the whole stage and around the scoring kernel (gcr_result.device_ms,
                                       * score_kernel_ms; both 0 without it): four more in-stream operations, ~2.5 us each */
 

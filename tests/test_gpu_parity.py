@@ -506,6 +506,64 @@ def test_pinned_host_inputs_are_read_in_place_with_identical_results(eng, port):
     e.close()
 
 
+def test_uint16_replay_samples_equal_int32_replay_samples(eng):
+    """GCR_RUN_SAMPLES_U16: the replayed minimal samples as uint16[n_hyp,4] (half the bytes over PCIe) -- pageable, page-locked (read in
+    place) and device arrays -- give what the int32 array gives: flags, models, counts, masks bit for bit, the samples read back widened;
+    the scale-only problems' unused fourth index travels as 0xFFFF; a class of more than 65 535 features is refused."""
+    import ctypes as C
+    import torch
+    import gcr_capi
+    import gcr_scenes as gs
+    sc = gs.make_scene(1500, 400, 0.4, 21)
+    smp = gs.draw_samples(20000, 1500, 400, 22)
+    smp[7] = [3, 3, 5, 9]  # a degenerate sample and one out of range stay what they are
+    eng.set_features(sc.scale, sc.orient)
+    ref_res = eng.run(len(smp), sc.thr, samples=smp, flags=gcr_capi.RUN_EMIT_MASKS)
+    ref = eng.fetch(masks=True, samples=True)
+    narrow = smp.astype(np.uint16)
+    thr_c = (C.c_double * 2)(*sc.thr)
+    pinned, on_device = torch.from_numpy(narrow).pin_memory(), torch.from_numpy(narrow).cuda()
+    for how in ("pageable", "pinned", "device"):
+        if how == "pageable":
+            res = eng.run(len(smp), sc.thr, samples=narrow, flags=gcr_capi.RUN_EMIT_MASKS)
+        else:
+            res = gcr_capi.GcrResult()
+            ptr = pinned.data_ptr() if how == "pinned" else on_device.data_ptr()
+            fl = gcr_capi.RUN_EMIT_MASKS | gcr_capi.RUN_SAMPLES_U16 | (gcr_capi.RUN_SAMPLES_ON_DEVICE if how == "device" else 0)
+            assert eng.lib.gcr_run(eng.h, len(smp), 0, 0, C.c_void_p(ptr), thr_c, fl, None, C.byref(res)) == 0, how
+        got = eng.fetch(masks=True, samples=True)
+        for k in ("flags", "models", "n_inl", "masks", "samples"):
+            assert np.array_equal(got[k], ref[k]), (how, k)
+        assert (res.best_index, res.best_score) == (ref_res.best_index, ref_res.best_score), how
+    # winner-only run (no per-hypothesis outputs)
+    res = eng.run(len(smp), sc.thr, samples=narrow)
+    assert (res.best_index, res.best_score) == (ref_res.best_index, ref_res.best_score)
+    bad = narrow.copy()
+    bad[11, 2] = 400  # one past the orientation class
+    with pytest.raises(gcr_capi.GcrError):
+        eng.run(len(bad), sc.thr, samples=bad)
+    # scale-only: (s0, s1, s2, -1) <-> (s0, s1, s2, 0xFFFF)
+    e = gcr_capi.Engine(0)
+    e.set_problem(gcr_capi.PROBLEM_SCALE_ONLY)
+    e.set_features(sc.scale)
+    s3 = gs.draw_samples_scale3(5000, 1500, 23)
+    r32 = e.run(len(s3), [sc.thr[0], 0.0], samples=s3, flags=gcr_capi.RUN_KEEP_PER_HYP)
+    f32 = e.fetch(samples=True)
+    r16 = e.run(len(s3), [sc.thr[0], 0.0], samples=s3.astype(np.uint16), flags=gcr_capi.RUN_KEEP_PER_HYP)
+    f16 = e.fetch(samples=True)
+    assert (r16.best_index, r16.best_score) == (r32.best_index, r32.best_score) and r32.best_index >= 0
+    for k in ("flags", "models", "n_inl", "samples"):
+        assert np.array_equal(f16[k], f32[k]), k
+    e.close()
+    # more features than 16 bits index
+    big = gs.make_scene(66000, 300, 0.2, 24)
+    e = gcr_capi.Engine(0)
+    e.set_features(big.scale, big.orient)
+    with pytest.raises(gcr_capi.GcrError):
+        e.run(100, big.thr, samples=np.zeros((100, 4), np.uint16))
+    e.close()
+
+
 def test_ring_and_resident_scoring_kernels_agree(port):
     """Small feature sets are scored by k_score_resident (whole working set in shared memory, static cost partition over warps),
     large ones or big batches by k_score_fast (TMA ring).  Same arithmetic: masks, counts, flags and the winner are bit-identical,
