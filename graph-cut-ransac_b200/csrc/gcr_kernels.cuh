@@ -1468,20 +1468,38 @@ __device__ __forceinline__ void select_phase(const Buffers& B, const Thresholds&
         }
     }
     __syncthreads();
-    if (s_hyp != 0xfffffffeu)
+    // The winner's packed masks -> the result block on the device and its mirror in page-locked host memory (the caller needs no
+    // device-to-host copy after the run, only the stream synchronisation: [record 16 words][counters 16][phase stamps 16][winner masks]).
+    // Eight words per thread are requested before any is stored: a load-store pair per iteration is one L2 round trip each, which at
+    // C3's 2 189 mask words was 17 trips in a row through this one CTA (select 12.4 us against 7 us at C2's 79 words).
+    const bool keep = s_hyp == 0xfffffffeu, have = s_hyp != 0xffffffffu;
+    const bool mirror = final && B.host_block != nullptr;
+    const unsigned int* src_masks = keep ? B.best_masks : B.cand_masks + static_cast<size_t>(s_slot) * B.wmask;
+    if (!keep || mirror)
+        for (int base = 0; base < B.wmask; base += 8 * static_cast<int>(blockDim.x))
+        {
+            unsigned int v[8];
+#pragma unroll
+            for (int q = 0; q < 8; q++)
+            {
+                const int w = base + q * static_cast<int>(blockDim.x) + static_cast<int>(threadIdx.x);
+                v[q] = (have && w < B.wmask) ? __ldcg(src_masks + w) : 0u;
+            }
+#pragma unroll
+            for (int q = 0; q < 8; q++)
+            {
+                const int w = base + q * static_cast<int>(blockDim.x) + static_cast<int>(threadIdx.x);
+                if (w < B.wmask)
+                {
+                    if (!keep) B.best_masks[w] = v[q];
+                    if (mirror) B.host_block[kResultHeaderWords + w] = v[q];
+                }
+            }
+        }
+    if (mirror)
     {
-        const bool have = s_hyp != 0xffffffffu;
-        for (int w = threadIdx.x; w < B.wmask; w += blockDim.x)
-            B.best_masks[w] = have ? B.cand_masks[static_cast<size_t>(s_slot) * B.wmask + w] : 0u;
-    }
-    if (final && B.host_block)
-    {
-        // mirror of the result block in page-locked host memory: the caller needs no device-to-host copy after the run,
-        // only the stream synchronisation ([record 16 words][counters 16][phase stamps 16][winner masks])
-        __syncthreads();
-        const unsigned int* src = reinterpret_cast<const unsigned int*>(B.record);
+        const unsigned int* src = reinterpret_cast<const unsigned int*>(B.record); // (written by thread 0 before the barrier above)
         for (int w = threadIdx.x; w < 32; w += blockDim.x) B.host_block[w] = __ldcg(src + w);
-        for (int w = threadIdx.x; w < B.wmask; w += blockDim.x) B.host_block[kResultHeaderWords + w] = __ldcg(B.best_masks + w);
     }
 }
 
