@@ -15,7 +15,7 @@ KEYS = ["gpu__time_duration.sum", "sm__cycles_elapsed.avg", "sm__cycles_active.a
         "smsp__thread_inst_executed_pred_on_per_inst_executed.ratio"]
 TRAFFIC = {}
 for rep in sorted(glob.glob(f"gpurun_out/prof_*_{R}.ncu-rep")):
-    m = re.match(rf"gpurun_out/prof_(c\d)_(k_\w+?)_{R}\.ncu-rep", rep)
+    m = re.match(rf"gpurun_out/prof_(c\d|fit)_(k_\w+?)_{R}\.ncu-rep", rep)
     if not m:
         continue
     cfg, kern = m.group(1), m.group(2)
@@ -24,7 +24,8 @@ for rep in sorted(glob.glob(f"gpurun_out/prof_*_{R}.ncu-rep")):
     hdr, units = rows[0], rows[1]
     name = f"profiles/{OUT}_ncu_full_{kern}_{cfg}.txt"
     with open(name, "w") as f:
-        f.write(f"# ncu --set full --clock-control none --import-source on, kernel {kern}, bench.py config {cfg.upper()} (winner-only run, {rep})\n")
+        what = "tools/time_fit.py C1 (gcr_fit_score_models / gcr_lo_round calls)" if cfg == "fit" else f"bench.py config {cfg.upper()} (winner-only run)"
+        f.write(f"# ncu --set full --clock-control none --import-source on, kernel {kern}, {what}, {rep}\n")
         for r in rows[2:]:
             d = dict(zip(hdr, r))
             f.write(f"kernel: {d.get('Kernel Name')}  grid {d.get('Grid Size')} block {d.get('Block Size')}\n")
@@ -66,7 +67,7 @@ if TRAFFIC:
         old.setdefault(cfg, {}).update(d)
     json.dump(old, open("profiles/traffic.json", "w"), indent=1)
 for path in sorted(glob.glob(f"gpurun_out/launches_*_{R}.csv")):
-    cfg = re.match(rf"gpurun_out/launches_(c\d)_{R}\.csv", path).group(1)
+    cfg = re.match(rf"gpurun_out/launches_(c\d|fit)_{R}\.csv", path).group(1)
     rows = [r for r in csv.reader(open(path)) if len(r) > 10 and r[0].isdigit()]
     agg = collections.OrderedDict()
     for r in rows:
@@ -74,9 +75,13 @@ for path in sorted(glob.glob(f"gpurun_out/launches_*_{R}.csv")):
     tot = sum(sum(v) for k, v in agg.items() if "gcr::" in k[0])
     name = f"profiles/{OUT}_launch_list_{cfg}.txt"
     with open(name, "w") as f:
-        f.write(f"# ncu --metrics gpu__time_duration.sum --clock-control none  python bench.py {'--config C2 ' if cfg == 'c2' else ''}--steps .. --warmup 3 (config {cfg.upper()})\n")
-        f.write("# per-launch times are cold-cache and serialised: compare SHARES, not absolutes.  The list covers every loop of bench.py: device-resident\n")
-        f.write("# steps, the winner check, the kernel-timing pass and the host-buffer (e2e) steps.\n")
+        if cfg == "fit":
+            f.write("# ncu --metrics gpu__time_duration.sum --clock-control none  REPS=3 python tools/time_fit.py C1: gcr_fit_score_models (refit shape, 50-fit batch,\n")
+            f.write("# one small fit) and gcr_lo_round, three calls each.  Per-launch times are cold-cache and serialised.\n")
+        else:
+            f.write(f"# ncu --metrics gpu__time_duration.sum --clock-control none  python bench.py {'--config C2 ' if cfg == 'c2' else ''}--steps .. --warmup 3 (config {cfg.upper()})\n")
+            f.write("# per-launch times are cold-cache and serialised: compare SHARES, not absolutes.  The list covers every loop of bench.py: device-resident\n")
+            f.write("# steps, the winner check, the kernel-timing pass and the host-buffer (e2e) steps.\n")
         f.write(f"{'kernel':60s} {'grid':>16s} {'block':>14s} {'launches':>9s} {'mean_us':>10s} {'share_of_gcr':>12s}\n")
         for (n, g, b), v in agg.items():
             share = sum(v) / tot if "gcr::" in n else float("nan")
