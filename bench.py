@@ -823,13 +823,155 @@ def run_sweep(args):
         sys.exit(3)
 
 
+def front_keypoints(n: int, seed: int) -> np.ndarray:
+    """Synthetic cv2.KeyPoint rows (x, y, size, angle in degrees) as float32: a 4096 x 4096 image (about one keypoint in eight shares its
+    integer coordinate with an earlier one), one keypoint in five without an orientation (angle == -1)."""
+    rng = np.random.default_rng(seed)
+    kp = np.empty((n, 4), np.float32)
+    kp[:, 0] = rng.uniform(0.0, 4096.0, n)
+    kp[:, 1] = rng.uniform(0.0, 4096.0, n)
+    kp[:, 2] = rng.uniform(1.5, 40.0, n)
+    kp[:, 3] = np.where(rng.uniform(size=n) < 0.2, -1.0, rng.uniform(0.0, 360.0, n))
+    return kp
+
+
+def run_front(args):
+    """--config FRONT (not a BASELINE.json configuration): the feature front end gcr_set_keypoints on 4 Mi keypoints per
+    GPU -- de-duplication by integer coordinate, stable compaction, orientation rows, derived feature planes.  HBM-bound integer / copy
+    work: the roofline is the measured copy bandwidth of MEASURED_PEAKS.json."""
+    rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
+    n = 1 << 22
+    kp = front_keypoints(n, 77 + rank)
+    cpu = None
+    if rank == 0 and (not args.no_cpu or args.impl == "reference"):  # before torch: the numpy restatement of examples/utils.py:5-49 on a bounded sample, one core
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import frontend_oracle as fo
+        m = 1 << 19
+        t0 = time.perf_counter()
+        want_s = fo.scale_features_from_rows(kp[:m])
+        want_o, want_sz = fo.orientation_features_from_rows(kp[:m])
+        dt = time.perf_counter() - t0
+        cpu = {"value": m / dt, "unit": "keypoints/s", "cores": 1, "kind": "port",
+               "sample": f"first {m} of {n} keypoint rows, numpy restatement of examples/utils.py:5-49 (oracle/frontend_oracle.py), {dt:.2f} s"}
+    if args.impl == "reference":  # the reference's front end is host Python: its numpy restatement, one core, rank 0 only
+        if rank == 0:
+            print(json.dumps({"impl": "reference", "metric": "keypoints/s (feature front end, examples/utils.py:5-49)", "value": cpu["value"], "unit": "keypoints/s",
+                              "n_gpus": world, "steps": 1, "warmup": 0, "ms_per_step": 1e3 * (1 << 19) / cpu["value"], "higher_is_better": True, "scaling": "weak",
+                              "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": {"workload": f"FRONT: {n} float32 keypoint rows per GPU"},
+                              "cpu_baseline": cpu, "e2e": {"value": cpu["value"], "unit": "keypoints/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return
+    import torch
+    import torch.distributed as dist
+    import gcr_capi
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    C = gcr_capi.C
+    eng = gcr_capi.Engine(local)
+    stream = torch.cuda.Stream()
+    eng.set_stream(stream.cuda_stream)
+    d_kp = torch.from_numpy(kp).cuda()
+    h_kp = torch.from_numpy(kp).pin_memory()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    check = None
+    if cpu is not None:  # parity of this very input against the restatement (bit for bit), on the sample the CPU leg ran
+        ns_, no_, sz = eng.set_keypoints(device_ptr=d_kp.data_ptr(), n=1 << 19, is_f32=True)
+        got_s, got_o = eng.get_features()
+        check = "ok" if (np.array_equal(got_s, want_s) and np.array_equal(got_o, want_o) and np.array_equal(sz, want_sz)) else "MISMATCH"
+    n_s, n_o = C.c_int64(0), C.c_int64(0)
+
+    def step(host, rows=n):
+        rc = eng.lib.gcr_set_keypoints(eng.h, C.c_void_p(h_kp.data_ptr() if host else d_kp.data_ptr()), rows, 1, 0 if host else 1, C.byref(n_s), C.byref(n_o),
+                                       h_sizes.ctypes.data if host else None)
+        assert rc == 0, eng.lib.gcr_last_error(eng.h)
+    h_sizes = np.zeros(n)
+    # one image's worth of keypoints (65 536 rows): the call is six dependent launches and a synchronisation, not bandwidth
+    small = []
+    with torch.cuda.stream(stream):
+        for k in range(13):
+            flush.zero_()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            step(False, 1 << 16)
+            if k >= 3:
+                small.append((time.perf_counter() - t0) * 1e6)
+    small_us = float(np.median(small))
+    with torch.cuda.stream(stream):
+        for _ in range(max(args.warmup, 3)):
+            flush.zero_()
+            step(False)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        sampler = ClockSampler(local)
+        sampler.start()
+        sampler.active = rank == 0
+        evs = []
+        for _ in range(args.steps):
+            flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            step(False)
+            e1.record(stream)
+            evs.append((e0, e1))
+        torch.cuda.synchronize()
+        sampler.active = False
+        t = torch.tensor([sum(a.elapsed_time(b) for a, b in evs)], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.barrier()
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_per_step = float(t.item()) / args.steps
+        for _ in range(2):
+            step(True)
+        sampler.active = rank == 0
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            step(True)
+        e2e_s = (time.perf_counter() - t0) / args.steps
+        sampler.active = False
+        sampler.stop_flag = True
+        t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    if rank == 0:
+        peaks = _load_json(os.path.join(ROOT, "MEASURED_PEAKS.json")) or {}
+        peak = float(peaks.get("hbm_gbs", 0.0)) or 7700.0
+        ns_out, no_out = int(n_s.value), int(n_o.value)
+        # algorithmic bytes of one call: every keypoint row read once, every output row written once (scale rows, orientation rows, sizes)
+        alg = 16 * n + 24 * ns_out + 24 * no_out + 8 * no_out
+        achieved = alg / (ms_per_step * 1e-3) / 1e9
+        line = {"metric": "keypoints/s (feature front end, examples/utils.py:5-49)", "value": world * n / (ms_per_step * 1e-3), "unit": "keypoints/s",
+                "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f32 rows in, f64 rows out (integer keys)", "data": "synthetic",
+                "config": {"workload": f"FRONT: {n} float32 keypoint rows per GPU on a 4096 x 4096 image -> {ns_out} scale rows (unique integer "
+                                       f"coordinates, first wins, order of first appearance) + {no_out} orientation rows (angle != -1)",
+                           "l2": "flushed between timed steps (256 MiB write)", "note": "SURVEY 8f row 4; not a BASELINE.json configuration",
+                           "one_image_call_us": small_us, "one_image_what": "wall time of gcr_set_keypoints on 65 536 device-resident rows (L2 flushed): launch / "
+                           "synchronisation bound, six dependent kernels",
+                           "front_check": check, "front_check_what": "first 524288 rows: scale rows, orientation rows and sizes == the numpy restatement "
+                           "of the reference's functions, bit for bit"},
+                "clocks": sampler.summary(),
+                "e2e": {"value": world * n / e2e_s, "unit": "keypoints/s", "ms_per_step": e2e_s * 1e3, "h2d_bytes_per_step": 16 * n, "d2h_bytes_per_step": 8 * no_out + 16,
+                        "api": "gcr_set_keypoints on a page-locked host array (copied to the device inside the call), sizes copied back"},
+                "gpu_launches": 6 * args.steps,
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                             "note": "the whole call (memset of the hash table, insert, count, scan, compact, derived feature planes) against the measured "
+                                     "copy bandwidth of MEASURED_PEAKS.json" + ("" if peaks else " (absent: nominal 7.7 TB/s)") +
+                                     "; algorithmic bytes = 16 B per keypoint in + 24 B per scale row + 32 B per orientation row out"},
+                "cpu_baseline": cpu}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--config", default="C3", choices=sorted(gs.CONFIGS))
+    ap.add_argument("--config", default="C3", choices=sorted(gs.CONFIGS) + ["FRONT"])
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"], help="N>1: fused peer-memory exchange or NCCL all_gather")
     ap.add_argument("--engines", type=int, default=4, help="C4: engine handles / streams in flight per GPU")
     ap.add_argument("--images", type=int, default=None, help="C4: images per GPU (default 256 / world)")
@@ -837,7 +979,9 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the bounded CPU baseline leg (diagnostics)")
     ap.add_argument("--no-secondary", action="store_true", help="skip the C2 secondary block (diagnostics)")
     args = ap.parse_args()
-    if args.impl == "reference":
+    if args.config == "FRONT":
+        run_front(args)
+    elif args.impl == "reference":
         run_reference(args)
     elif "n_images" in gs.CONFIGS[args.config]:
         run_batched(args)

@@ -842,7 +842,7 @@ int gcr_set_keypoints(gcr_handle h, const void* keypoints, int64_t n, int is_f32
     while (cap < 2 * static_cast<size_t>(n)) cap <<= 1;
     const unsigned int nb = static_cast<unsigned int>((n + kFrontThreads - 1) / kFrontThreads);
     GCR_CUDA(h->d_front_table.ensure(cap));
-    GCR_CUDA(h->d_front_counts.ensure(2 * static_cast<size_t>(nb) + 2));
+    GCR_CUDA(h->d_front_counts.ensure(2 * static_cast<size_t>(nb) + 2 + 2 * ((static_cast<size_t>(n) + 31) / 32)));
     GCR_CUDA(h->d_scale.ensure(3 * static_cast<size_t>(n)));
     GCR_CUDA(h->d_orient.ensure(3 * static_cast<size_t>(n)));
     GCR_CUDA(h->d_front_sizes.ensure(static_cast<size_t>(n)));
@@ -858,9 +858,10 @@ int gcr_set_keypoints(gcr_handle h, const void* keypoints, int64_t n, int is_f32
     F.scale = h->d_scale.p;
     F.orient = h->d_orient.p;
     F.sizes = h->d_front_sizes.p;
+    F.votes = h->d_front_counts.p + 2 * static_cast<size_t>(nb) + 2;
     k_front_insert<<<nb, kFrontThreads, 0, s>>>(F);
     k_front_compact<false><<<nb, kFrontThreads, 0, s>>>(F);
-    k_front_scan<<<1, kFrontThreads, 0, s>>>(F);
+    k_front_scan<<<1, kFrontScanThreads, 0, s>>>(F);
     k_front_compact<true><<<nb, kFrontThreads, 0, s>>>(F);
     GCR_CUDA(cudaGetLastError());
     unsigned int totals[2] = {0, 0};

@@ -31,7 +31,10 @@ struct FrontBuffers
     double* scale;  // out f64[<= n, 3]
     double* orient; // out f64[<= n, 3]
     double* sizes;  // out f64[<= n]
+    unsigned int* votes; // [2, ceil(n / 32)]: per warp of 32 consecutive keypoints, who yields a scale row / an orientation row (written by the
+                         // counting pass, so that the emitting pass does not walk the table again)
 };
+constexpr int kFrontScanThreads = 1024;
 
 __device__ __forceinline__ void front_load(const FrontBuffers& F, unsigned int i, double v[4])
 {
@@ -117,13 +120,33 @@ __global__ void __launch_bounds__(kFrontThreads) k_front_compact(FrontBuffers F)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     double v[4] = {0, 0, 0, 0};
     bool is_scale = false, is_orient = false;
-    if (i < F.n)
+    const unsigned int n_warps = (F.n + 31u) / 32u, gw = i >> 5;
+    unsigned int bs, bo;
+    if (!EMIT)
     {
-        front_load(F, i, v);
-        is_scale = front_is_first(F, i, front_key(v[0], v[1]));
-        is_orient = v[3] != -1.0; // utils.py:45
+        if (i < F.n)
+        {
+            front_load(F, i, v);
+            is_scale = front_is_first(F, i, front_key(v[0], v[1]));
+            is_orient = v[3] != -1.0; // utils.py:45
+        }
+        __syncwarp();
+        bs = __ballot_sync(0xffffffffu, is_scale);
+        bo = __ballot_sync(0xffffffffu, is_orient);
+        if (lane == 0 && gw < n_warps)
+        {
+            F.votes[gw] = bs;
+            F.votes[n_warps + gw] = bo;
+        }
     }
-    const unsigned int bs = __ballot_sync(0xffffffffu, is_scale), bo = __ballot_sync(0xffffffffu, is_orient);
+    else
+    {
+        bs = gw < n_warps ? F.votes[gw] : 0u;
+        bo = gw < n_warps ? F.votes[n_warps + gw] : 0u;
+        is_scale = (bs >> lane) & 1u;
+        is_orient = (bo >> lane) & 1u;
+        if (is_scale || is_orient) front_load(F, i, v);
+    }
     if (lane == 0)
     {
         s_warp[0][warp] = __popc(bs);
@@ -165,40 +188,62 @@ __global__ void __launch_bounds__(kFrontThreads) k_front_compact(FrontBuffers F)
     }
 }
 
-// exclusive scan of the two count rows in place (one CTA), totals appended
-__global__ void __launch_bounds__(kFrontThreads) k_front_scan(FrontBuffers F)
+// exclusive scan of the two count rows in place (one CTA), totals appended: chunks of 1 024 counts per row, coalesced, a shuffle scan
+// per warp and one over the warp totals (the strided one-thread-per-segment form took 58 us for 16 384 blocks)
+__global__ void __launch_bounds__(kFrontScanThreads) k_front_scan(FrontBuffers F)
 {
-    __shared__ unsigned int s_part[kFrontThreads];
-    for (int row = 0; row < 2; row++)
+    __shared__ unsigned int s_warp[2][kFrontScanThreads / 32];
+    __shared__ unsigned int s_run[2];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid < 2) s_run[tid] = 0u;
+    __syncthreads();
+    for (unsigned int b0 = 0; b0 < F.n_blocks; b0 += kFrontScanThreads)
     {
-        unsigned int* c = F.block_counts + static_cast<size_t>(row) * F.n_blocks;
-        const unsigned int per = (F.n_blocks + kFrontThreads - 1) / kFrontThreads;
-        const unsigned int b0 = min(F.n_blocks, threadIdx.x * per), b1 = min(F.n_blocks, b0 + per);
-        unsigned int sum = 0;
-        for (unsigned int b = b0; b < b1; b++) sum += c[b];
-        s_part[threadIdx.x] = sum;
-        __syncthreads();
-        if (threadIdx.x == 0)
+        const unsigned int b = b0 + tid;
+        unsigned int c[2], incl[2];
+#pragma unroll
+        for (int row = 0; row < 2; row++)
         {
-            unsigned int run = 0;
-            for (int t = 0; t < kFrontThreads; t++)
+            c[row] = b < F.n_blocks ? F.block_counts[static_cast<size_t>(row) * F.n_blocks + b] : 0u;
+            incl[row] = c[row];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1)
             {
-                const unsigned int x = s_part[t];
-                s_part[t] = run;
-                run += x;
+                const unsigned int up = __shfl_up_sync(0xffffffffu, incl[row], o);
+                if (lane >= o) incl[row] += up;
             }
-            F.block_counts[2 * static_cast<size_t>(F.n_blocks) + row] = run;
+            if (lane == 31) s_warp[row][warp] = incl[row];
         }
         __syncthreads();
-        unsigned int run = s_part[threadIdx.x];
-        for (unsigned int b = b0; b < b1; b++)
+        if (warp < 2)
         {
-            const unsigned int x = c[b];
-            c[b] = run;
-            run += x;
+            const unsigned int v = s_warp[warp][lane];
+            unsigned int iv = v;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1)
+            {
+                const unsigned int up = __shfl_up_sync(0xffffffffu, iv, o);
+                if (lane >= o) iv += up;
+            }
+            s_warp[warp][lane] = iv - v; // exclusive prefix of the warp totals of row `warp`
+        }
+        __syncthreads();
+        unsigned int end[2];
+#pragma unroll
+        for (int row = 0; row < 2; row++)
+        {
+            end[row] = s_run[row] + s_warp[row][warp] + incl[row];
+            if (b < F.n_blocks) F.block_counts[static_cast<size_t>(row) * F.n_blocks + b] = end[row] - c[row];
+        }
+        __syncthreads();
+        if (tid == kFrontScanThreads - 1)
+        {
+            s_run[0] = end[0];
+            s_run[1] = end[1];
         }
         __syncthreads();
     }
+    if (tid < 2) F.block_counts[2 * static_cast<size_t>(F.n_blocks) + tid] = s_run[tid];
 }
 
 } // namespace gcr

@@ -75,14 +75,25 @@ __global__ void k_prep_features(const double* __restrict__ scale, int ns, const 
                 b = static_cast<float>(ya);
                 c = static_cast<float>(ia);
                 ad = xa; bd = ya; cd = ia;
-                atomicMax(reinterpret_cast<int*>(&scene->xq_max), __float_as_int(fabsf(a)));
-                atomicMax(reinterpret_cast<int*>(&scene->yq_max), __float_as_int(fabsf(b)));
-                atomicMax(reinterpret_cast<int*>(&scene->iq_max), __float_as_int(fabsf(c)));
             }
             else
             {
                 const unsigned int slot = atomicAdd(&scene->n_irr_s, 1u);
                 if (slot < kIrrCap) irr_s[slot] = i; else scene->irr_overflow = 1;
+            }
+        }
+        {
+            // scene maxima: one atomic per warp and quantity (the bit pattern of a non-negative float orders like the float; one atomic per
+            // FEATURE on the same four words was most of this kernel's time once a scene had millions of features)
+            const bool real = i < ns && pair_ok;
+            const int m0 = __reduce_max_sync(0xffffffffu, real ? __float_as_int(fabsf(a)) : 0);
+            const int m1 = __reduce_max_sync(0xffffffffu, real ? __float_as_int(fabsf(b)) : 0);
+            const int m2 = __reduce_max_sync(0xffffffffu, real ? __float_as_int(fabsf(c)) : 0);
+            if ((threadIdx.x & 31) == 0 && (m0 | m1 | m2) != 0)
+            {
+                atomicMax(reinterpret_cast<int*>(&scene->xq_max), m0);
+                atomicMax(reinterpret_cast<int*>(&scene->yq_max), m1);
+                atomicMax(reinterpret_cast<int*>(&scene->iq_max), m2);
             }
         }
         float* base = fs + (i / kChunk) * kChunkFloats + (i % kChunk);
@@ -128,13 +139,16 @@ __global__ void k_prep_features(const double* __restrict__ scale, int ns, const 
                 c = static_cast<float>(ct);
                 ad = k; bd = st; cd = ct;
                 pad = false;
-                atomicMax(reinterpret_cast<int*>(&scene->k_max), __float_as_int(fabsf(a)));
             }
             else
             {
                 const unsigned int slot = atomicAdd(&scene->n_irr_o, 1u);
                 if (slot < kIrrCap) irr_o[slot] = i; else scene->irr_overflow = 1;
             }
+        }
+        {
+            const int mk = __reduce_max_sync(0xffffffffu, pad ? 0 : __float_as_int(fabsf(a))); // (one atomic per warp, as for the scale class)
+            if ((threadIdx.x & 31) == 0 && mk != 0) atomicMax(reinterpret_cast<int*>(&scene->k_max), mk);
         }
         if (pad)
         {
