@@ -45,13 +45,19 @@ def test_ctypes_mirror_matches_the_header_as_compiled(tmp_path):
     src.write_text("#include <stdio.h>\n#include <stddef.h>\n#include \"gcr_b200.h\"\nint main(void) {\n"
                    "  printf(\"%zu\\n\", sizeof(gcr_result));\n"
                    + "".join(f"  printf(\"%zu\\n\", offsetof(gcr_result, {f}));\n" for f in fields)
-                   + "  printf(\"%zu\\n\", sizeof(gcr_record));\n  return 0;\n}\n")
+                   + "  printf(\"%zu\\n\", sizeof(gcr_record));\n"
+                   + "  printf(\"%zu\\n\", sizeof(gcr_lo_round_io));\n"
+                   + "".join(f"  printf(\"%zu\\n\", offsetof(gcr_lo_round_io, {f}));\n" for f, _ in gcr_capi.GcrLoRoundIo._fields_)
+                   + "  return 0;\n}\n")
     exe = tmp_path / "layout"
     subprocess.check_call(["gcc", "-std=c99", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
     out = [int(x) for x in subprocess.check_output([str(exe)]).split()]
+    nf = len(fields)
     assert out[0] == ctypes.sizeof(gcr_capi.GcrResult)
-    assert out[1:-1] == [getattr(gcr_capi.GcrResult, f).offset for f in fields]
-    assert out[-1] == gcr_capi.RECORD_DTYPE.itemsize
+    assert out[1:1 + nf] == [getattr(gcr_capi.GcrResult, f).offset for f in fields]
+    assert out[1 + nf] == gcr_capi.RECORD_DTYPE.itemsize
+    assert out[2 + nf] == ctypes.sizeof(gcr_capi.GcrLoRoundIo)  # gcr_lo_round_io and its ctypes mirror
+    assert out[3 + nf:] == [getattr(gcr_capi.GcrLoRoundIo, f).offset for f, _ in gcr_capi.GcrLoRoundIo._fields_]
 
 
 def test_null_handle_is_an_error_not_a_crash(lib):
