@@ -780,8 +780,11 @@ __global__ void __launch_bounds__(kScoreThreads, kRingMinB<MODE>) k_score_fast(c
     // Work decomposition, identical in every CTA: the chunk lists are cut so that there are ~8 items per resident
     // CTA; items are handed out dynamically (atomic counter), costliest first: precise tiles, then FP32 tiles from
     // the orientation end of the chunk list (an orientation evaluation costs about twice a scale evaluation).
-    const int target = kItemsPerCta * static_cast<int>(gridDim.x);
     const int tiles = tiles_a + 2 * tiles_b; // a precise tile has twice the chunks
+    // (twice the items where they stay >= 4 chunks long: C3's 1 M hypotheses 4.920 -> 4.865 ms; shorter items cost more in hand-out and
+    //  ring restarts than they level: a 125 000-hypothesis shard 0.640 -> 0.646 ms with 48 per CTA, same-box A/B)
+    const bool long_items = static_cast<long long>(tiles) * chunks_a >= 8ll * kItemsPerCta * static_cast<long long>(gridDim.x);
+    const int target = (long_items ? 2 : 1) * kItemsPerCta * static_cast<int>(gridDim.x);
     int splits_a = 1;
     if (tiles > 0 && tiles < target) splits_a = min(chunks_a, (target + tiles - 1) / tiles);
     const int cps_a = (chunks_a + splits_a - 1) / splits_a;
