@@ -573,6 +573,7 @@ def run_batched(args):
     engines = [gcr_capi.Engine(local) for _ in range(K)]
     for e, st in zip(engines, streams):
         e.set_stream(st.cuda_stream)
+        e.set_sm_share(max(1, args.sm_share))
     records = torch.zeros(n_img, 8, dtype=torch.float64, device="cuda")
     h_records = torch.zeros(n_img, 8, dtype=torch.float64).pin_memory()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
@@ -667,7 +668,8 @@ def run_batched(args):
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": DTYPE, "data": "synthetic",
                 "config": {"workload": workload_string(args.config),
-                           "sharding": f"{total_img} images, {n_img} per rank, {K} engines/streams in flight per GPU, no communication",
+                           "sharding": f"{total_img} images, {n_img} per rank, {K} engines/streams in flight per GPU, each sized for 1/{max(1, args.sm_share)} of the SMs "
+                                       "(gcr_set_sm_share), no communication",
                            "l2": "flushed between timed steps (256 MiB write)", "images_with_model": int((recs["index"] >= 0).sum()),
                            "median_vanishing_line_error": float(np.median(err)),
                            "winner_check": "ok" if same else "MISMATCH",
@@ -973,7 +975,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="C3", choices=sorted(gs.CONFIGS) + ["FRONT"])
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"], help="N>1: fused peer-memory exchange or NCCL all_gather")
-    ap.add_argument("--engines", type=int, default=4, help="C4: engine handles / streams in flight per GPU")
+    ap.add_argument("--engines", type=int, default=8, help="C4: engine handles / streams in flight per GPU")
+    ap.add_argument("--sm-share", type=int, default=8, help="C4: every engine sizes its launches for 1/share of the SMs (gcr_set_sm_share)")
     ap.add_argument("--images", type=int, default=None, help="C4: images per GPU (default 256 / world)")
     ap.add_argument("--hyp", type=int, default=None, help="override the configuration's total hypothesis count (diagnostics)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the bounded CPU baseline leg (diagnostics)")

@@ -77,7 +77,8 @@ struct PinnedBuf
 struct gcr_engine_s
 {
     int device = 0;
-    int n_sm = 148;
+    int n_sm = 148;        // SMs every grid of this engine is sized for (all of the device's, or a share of them: gcr_set_sm_share)
+    int n_sm_device = 148; // SMs of the device
     int problem = 0; // GCR_PROBLEM_*
     int score_grid[3] = {148, 148, 148}; // per scoring mode: winner-only, per-hypothesis counts, + masks
     bool pdl = true;            // programmatic dependent launch of the scoring kernel and the tail (GCR_PDL=0: plain launches)
@@ -585,6 +586,28 @@ extern "C"
 
 const char* gcr_version(void) { return "gcr_b200 0.1 sm_100a"; }
 
+// grids of the persistent scoring kernel (per mode) and of the cooperative tail for h->n_sm SMs
+static cudaError_t size_grids(gcr_engine_s* h)
+{
+    cudaError_t e = cudaSuccess;
+    for (int m = 0; m < 3 && e == cudaSuccess; m++)
+    {
+        int per_sm = 1;
+        e = m == 0 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_score_fast<0>, kScoreThreads, sizeof(ScoreSmem))
+                   : (m == 1 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_score_fast<1>, kScoreThreads, sizeof(ScoreSmem))
+                             : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_score_fast<2>, kScoreThreads, sizeof(ScoreSmem)));
+        h->score_grid[m] = h->n_sm * std::max(1, per_sm);
+    }
+    if (e == cudaSuccess)
+    {
+        int per_sm = 1;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_tail, kExactThreads, 0);
+        h->tail_grid = h->n_sm * std::max(1, std::min(per_sm, 2));
+        if (const char* v = std::getenv("GCR_TAIL_GRID")) h->tail_grid = std::max(1, std::min(std::atoi(v), h->n_sm * std::max(1, per_sm)));
+    }
+    return e;
+}
+
 int gcr_create(int device, gcr_handle* out)
 {
     if (!out) return GCR_ERR_INVALID;
@@ -602,6 +625,9 @@ int gcr_create(int device, gcr_handle* out)
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_wait, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_stage, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaDeviceGetAttribute(&h->n_sm, cudaDevAttrMultiProcessorCount, device);
+    h->n_sm_device = h->n_sm;
+    if (const char* v = std::getenv("GCR_SM_SHARE")) // (experiments: the default share of engines created from here on, see gcr_set_sm_share)
+        if (e == cudaSuccess && std::atoi(v) > 1) h->n_sm = std::max(1, h->n_sm_device / std::atoi(v));
     const int resident_smem = kResidentMaxChunks * kChunkBytes + 64;
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_score_fast<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ScoreSmem));
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_score_fast<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ScoreSmem));
@@ -618,21 +644,11 @@ int gcr_create(int device, gcr_handle* out)
     if (const char* v = std::getenv("GCR_RESIDENT_MAX_EVALS")) h->resident_max_evals = std::atoll(v);
     if (const char* v = std::getenv("GCR_COST_O")) h->resident_cost_o = std::max(1, std::atoi(v));
     if (const char* v = std::getenv("GCR_COST_P")) h->resident_cost_p = std::max(1, std::atoi(v));
-    for (int m = 0; m < 3 && e == cudaSuccess; m++)
-    {
-        int per_sm = 1;
-        e = m == 0 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_score_fast<0>, kScoreThreads, sizeof(ScoreSmem))
-                   : (m == 1 ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_score_fast<1>, kScoreThreads, sizeof(ScoreSmem))
-                             : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_score_fast<2>, kScoreThreads, sizeof(ScoreSmem)));
-        h->score_grid[m] = h->n_sm * std::max(1, per_sm);
-    }
+    if (e == cudaSuccess) e = size_grids(h);
     if (e == cudaSuccess)
     {
-        int per_sm = 1, coop = 0;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_tail, kExactThreads, 0);
-        if (e == cudaSuccess) e = cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device);
-        h->tail_grid = h->n_sm * std::max(1, std::min(per_sm, 2));
-        if (const char* v = std::getenv("GCR_TAIL_GRID")) h->tail_grid = std::max(1, std::min(std::atoi(v), h->n_sm * std::max(1, per_sm)));
+        int coop = 0;
+        e = cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device);
         if (e == cudaSuccess && !coop)
         {
             h->err = "device does not support cooperative launches";
@@ -885,6 +901,17 @@ int gcr_set_keypoints(gcr_handle h, const void* keypoints, int64_t n, int is_f32
     h->scale_ptr = h->d_scale.p;
     h->orient_ptr = hybrid ? h->d_orient.p : nullptr;
     return finish_features(h);
+}
+
+int gcr_set_sm_share(gcr_handle h, int share)
+{
+    if (!h) return GCR_ERR_INVALID;
+    if (!h->stream) return h->fail(GCR_ERR_STATE, "engine was not created successfully");
+    if (share < 1 || share > h->n_sm_device) return h->fail(GCR_ERR_INVALID, "gcr_set_sm_share: 1 <= share <= SMs of the device");
+    GCR_DEVICE(h);
+    h->n_sm = std::max(1, h->n_sm_device / share);
+    GCR_CUDA(size_grids(h));
+    return GCR_OK;
 }
 
 int gcr_set_problem(gcr_handle h, int problem)

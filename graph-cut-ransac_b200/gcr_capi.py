@@ -27,7 +27,7 @@ EXPORTS = [
     "gcr_best",
     "gcr_fetch", "gcr_score_model", "gcr_score_models", "gcr_fit_models", "gcr_set_keypoints", "gcr_debug_eval", "gcr_version", "gcr_peer_export",
     "gcr_peer_attach", "gcr_peer_buffer", "gcr_peer_attach_ptrs", "gcr_peer_detach", "gcr_score_models_static", "gcr_fit_score_models", "gcr_debug_phi_fallbacks",
-    "gcr_lo_round",
+    "gcr_lo_round", "gcr_set_sm_share",
 ]
 
 
@@ -77,6 +77,7 @@ def load_library() -> C.CDLL:
     lib.gcr_set_stream.argtypes = [vp, vp]
     lib.gcr_wait_stream.argtypes = [vp, vp]
     lib.gcr_set_problem.argtypes = [vp, C.c_int]
+    lib.gcr_set_sm_share.argtypes = [vp, C.c_int]
     lib.gcr_set_features.argtypes = [vp, vp, i64, vp, i64, C.c_int]
     lib.gcr_get_features.argtypes = [vp, vp, vp]
     lib.gcr_run.argtypes = [vp, i64, u64, u64, vp, C.POINTER(C.c_double), u32, vp, C.POINTER(GcrResult)]
@@ -146,6 +147,10 @@ class Engine:
     def wait_stream(self, cuda_stream: int):
         """The engine's stream waits for the work submitted so far to `cuda_stream` (0 = legacy default stream)."""
         self._check(self.lib.gcr_wait_stream(self.h, C.c_void_p(cuda_stream)))
+
+    def set_sm_share(self, share: int):
+        """Size every launch for 1/share of the SMs: `share` engines on `share` streams then run side by side (image batches)."""
+        self._check(self.lib.gcr_set_sm_share(self.h, int(share)))
 
     def set_problem(self, problem: int):
         """PROBLEM_HYBRID (default), PROBLEM_SCALE_ONLY or PROBLEM_SCALE_ONLY_ORIGINAL; call before set_features."""

@@ -564,6 +564,42 @@ def test_uint16_replay_samples_equal_int32_replay_samples(eng):
     e.close()
 
 
+def test_sm_share_does_not_change_results(eng):
+    """gcr_set_sm_share: an engine sized for 1/k of the SMs (k engines side by side on k streams: image batches) returns what the full-size
+    engine returns -- reporting mode: flags, models, counts, masks bit for bit, scores to FP32 summation accuracy (the partial sums are
+    grouped by the work cuts, which follow the grid); winner-only mode: the winner, its FP64 score, counts and masks bit for bit -- for the
+    resident kernel (small scene) and the ring kernel (larger scene), replayed and Philox samples."""
+    import gcr_capi
+    import gcr_scenes as gs
+    for sc, n_hyp in ((gs.make_scene(2000, 500, 0.3, 31), 30000), (gs.make_scene(9000, 4000, 0.2, 32), 40000)):
+        smp = gs.draw_samples(n_hyp, len(sc.scale), len(sc.orient), 33)
+        eng.set_sm_share(1)
+        eng.set_features(sc.scale, sc.orient)
+        eng.run(n_hyp, sc.thr, samples=smp, flags=gcr_capi.RUN_EMIT_MASKS)
+        ref = eng.fetch(masks=True)
+        ref_w = eng.run(n_hyp, sc.thr, seed=77)
+        ref_b = eng.best()
+        for share in (2, 8, 37):
+            e = gcr_capi.Engine(0)
+            e.set_sm_share(share)
+            e.set_features(sc.scale, sc.orient)
+            e.run(n_hyp, sc.thr, samples=smp, flags=gcr_capi.RUN_EMIT_MASKS)
+            got = e.fetch(masks=True)
+            for k in ("flags", "models", "n_inl", "masks"):
+                assert np.array_equal(got[k], ref[k]), (share, k)
+            assert np.allclose(got["score"], ref["score"], rtol=2e-6, atol=0.0), share
+            w = e.run(n_hyp, sc.thr, seed=77)
+            b = e.best()
+            assert (w.best_index, w.best_score, tuple(w.best_n_inl)) == (ref_w.best_index, ref_w.best_score, tuple(ref_w.best_n_inl)), share
+            assert np.array_equal(b["scale_words"], ref_b["scale_words"]) and np.array_equal(b["orient_words"], ref_b["orient_words"]), share
+            e.close()
+    with pytest.raises(gcr_capi.GcrError):
+        eng.set_sm_share(0)
+    with pytest.raises(gcr_capi.GcrError):
+        eng.set_sm_share(100000)
+    eng.set_sm_share(1)
+
+
 def test_ring_and_resident_scoring_kernels_agree(port):
     """Small feature sets are scored by k_score_resident (whole working set in shared memory, static cost partition over warps),
     large ones or big batches by k_score_fast (TMA ring).  Same arithmetic: masks, counts, flags and the winner are bit-identical,
