@@ -739,12 +739,75 @@ def run_sweep(args):
 
     for _ in range(max(args.warmup, 3)):
         sweep_pass(False)
+    per = np.array([sweep_pass(True) for _ in range(max(3, args.steps // 4))])  # [passes, 20] ms: per-setting stage times, one engine, one at a time
+    sequential_ms = float(per.sum(axis=1).mean())
+
+    # The timed step: the 20 settings are independent runs, spread over K engines / streams, each engine sized for 1/share of the SMs
+    # (gcr_set_sm_share) so that one setting's latency-bound kernels run under another's scoring; the L2 is flushed before every sweep.
+    K, share = max(1, min(args.sweep_engines, len(settings))), max(1, args.sweep_sm_share)
+    main_stream = torch.cuda.Stream()
+    streams = [torch.cuda.Stream() for _ in range(K)]
+    engines = [gcr_capi.Engine(local) for _ in range(K)]
+    for e, st in zip(engines, streams):
+        e.set_stream(st.cuda_stream)
+        e.set_sm_share(share)
+    records = torch.zeros(len(settings), 8, dtype=torch.float64, device="cuda")
+    h_records = torch.zeros(len(settings), 8, dtype=torch.float64).pin_memory()
+    hs = [(torch.from_numpy(sc.scale).pin_memory(), torch.from_numpy(sc.orient).pin_memory()) for _, _, sc, _ in settings]
+
+    def sweep_step(host):
+        start = torch.cuda.Event()
+        start.record(main_stream)
+        for st in streams:
+            st.wait_event(start)
+        for i, ((ratio, p, sc, seed), (ds, do), (ha, hb)) in enumerate(zip(settings, dev, hs)):
+            e = engines[i % K]
+            if host:
+                e._check(e.lib.gcr_set_features(e.h, ha.data_ptr(), len(sc.scale), hb.data_ptr(), len(sc.orient), 0))
+                e.ns, e.no = len(sc.scale), len(sc.orient)
+            else:
+                e.set_features_device(ds.data_ptr(), len(sc.scale), do.data_ptr(), len(sc.orient))
+            e.run(H, sc.thr, seed=seed, record_ptr=records[i].data_ptr(), sync=False)
+        for st in streams:
+            done = torch.cuda.Event()
+            done.record(st)
+            main_stream.wait_event(done)
+
     sampler = ClockSampler(local)
     sampler.start()
-    sampler.active = rank == 0
-    per = np.array([sweep_pass(True) for _ in range(args.steps)])  # [steps, 20] ms
-    sampler.active = False
-    ms_per_step = float(per.sum(axis=1).mean())
+    with torch.cuda.stream(main_stream):
+        for _ in range(max(args.warmup, 3)):
+            flush.zero_()
+            sweep_step(False)
+        torch.cuda.synchronize()
+        sampler.active = rank == 0
+        evs = []
+        for _ in range(args.steps):
+            flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(main_stream)
+            sweep_step(False)
+            e1.record(main_stream)
+            evs.append((e0, e1))
+        torch.cuda.synchronize()
+        sampler.active = False
+        ms_per_step = float(np.mean([a.elapsed_time(b) for a, b in evs]))
+        recs_dev = np.frombuffer(records.cpu().numpy().tobytes(), dtype=gcr_capi.RECORD_DTYPE).copy()
+        # e2e: pinned host features per setting in, all records out
+        for _ in range(2):
+            sweep_step(True)
+            h_records.copy_(records, non_blocking=True)
+            torch.cuda.synchronize()
+        sampler.active = rank == 0
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            sweep_step(True)
+            h_records.copy_(records, non_blocking=True)
+            main_stream.synchronize()
+        e2e_s = (time.perf_counter() - t0) / args.steps
+        sampler.active = False
+        sampler.stop_flag = True
+        recs_e2e = np.frombuffer(h_records.numpy().tobytes(), dtype=gcr_capi.RECORD_DTYPE).copy()
     value = len(settings) * H * nfeat / (ms_per_step * 1e-3)
 
     def one_setting(sc, seed, n_hyp):
@@ -764,6 +827,10 @@ def run_sweep(args):
     rows, all_ok, n_scored = [], True, 0
     for i, (ratio, p, sc, seed) in enumerate(settings):
         rf, good, res = one_setting(sc, seed, H)
+        # ... and the timed sweep's own record of this setting (concurrent engines of a share of the SMs, device and host inputs) == this
+        # full-size, one-at-a-time run == the oracle's scoring of the model
+        good = good and int(recs_dev[i]["index"]) == res.best_index and float(recs_dev[i]["score"]) == res.best_score and \
+            int(recs_e2e[i]["index"]) == res.best_index and float(recs_e2e[i]["score"]) == res.best_score
         all_ok &= good
         n_scored += res.n_scored
         rows.append({"inliers": ratio, "level": p, "stage_ms": float(per[:, i].mean()), "kernel_ms": rf["kernel_ms"], "frac": rf["frac"],
@@ -784,41 +851,22 @@ def run_sweep(args):
                      "frac_vs_feature_count": ladder, "per_setting": rows})
     roofline["note"] += "; C5: the block's kernel figures are the median setting's, frac_min/median/max over the 20 settings"
 
-    # e2e: the sweep through the C ABI with pinned host features per setting
-    C = gcr_capi.C
-    e2 = gcr_capi.Engine(local)
-    hs = [(torch.from_numpy(sc.scale).pin_memory(), torch.from_numpy(sc.orient).pin_memory()) for _, _, sc, _ in settings]
-    out = gcr_capi.GcrResult()
-    b_model, b_n = np.zeros(4), np.zeros(2, np.uint32)
-    b_sm, b_om = np.zeros((c["n_scale"] + 31) // 32, np.uint32), np.zeros((c["n_orient"] + 31) // 32, np.uint32)
-    b_score, b_idx = C.c_double(), C.c_int64()
-
-    def e2e_pass():
-        for (ratio, p, sc, seed), (a, b) in zip(settings, hs):
-            thr_c = (C.c_double * 2)(*sc.thr)
-            rc = e2.lib.gcr_set_features(e2.h, a.data_ptr(), len(sc.scale), b.data_ptr(), len(sc.orient), 0)
-            rc |= e2.lib.gcr_run(e2.h, H, seed, 0, None, thr_c, 0, None, C.byref(out))
-            rc |= e2.lib.gcr_best(e2.h, b_model.ctypes.data, C.byref(b_score), b_n.ctypes.data, b_sm.ctypes.data, b_om.ctypes.data, C.byref(b_idx))
-            assert rc == 0, e2.lib.gcr_last_error(e2.h)
-    e2e_pass()
-    sampler.active = rank == 0
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        e2e_pass()
-    e2e_s = (time.perf_counter() - t0) / args.steps
-    sampler.active = False
-    sampler.stop_flag = True
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": max(args.warmup, 3),
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": DTYPE, "data": "synthetic",
                 "value_scored": n_scored * nfeat / (ms_per_step * 1e-3),
-                "config": {"workload": workload_string("C5"), "l2": "flushed before every timed run (256 MiB write)",
+                "config": {"workload": workload_string("C5"), "l2": "flushed before every timed sweep (256 MiB write)",
+                           "sharding": f"the 20 settings are independent runs: {K} engines / streams in flight, each sized for 1/{share} of the SMs "
+                                       "(gcr_set_sm_share)",
+                           "sequential_ms_per_sweep": sequential_ms,
+                           "sequential_what": "the same 20 runs one at a time on one full-size engine, L2 flushed before every run (the per_setting stage_ms)",
                            "winner_check": "ok" if all_ok else "MISMATCH",
-                           "winner_check_what": "every winner of the 20 settings and the 5 ladder sizes == the CPU oracle's MSAC of the same model (masks identical, score equal)"},
+                           "winner_check_what": "every winner of the 20 settings and the 5 ladder sizes == the CPU oracle's MSAC of the same model (masks identical, "
+                                                "score equal); the timed sweep's records (device and host inputs) == the one-at-a-time runs"},
                 "clocks": sampler.summary(),
                 "e2e": {"value": len(settings) * H * nfeat / e2e_s, "unit": UNIT, "ms_per_step": 1e3 * e2e_s,
-                        "h2d_bytes_per_step": int(len(settings) * 24 * nfeat), "d2h_bytes_per_step": int(len(settings) * (128 + 4 * (len(b_sm) + len(b_om)))),
-                        "api": E2E_API},
+                        "h2d_bytes_per_step": int(len(settings) * 24 * nfeat), "d2h_bytes_per_step": int(len(settings) * 64),
+                        "api": "per setting gcr_set_features (pinned host rows, read in place) + asynchronous gcr_run with a device record; one copy of all records back"},
                 "gpu_launches": 3 * len(settings) * args.steps, "roofline": roofline, "cpu_baseline": cpu_leg}
         print(json.dumps(line))
     if not all_ok:
@@ -978,6 +1026,8 @@ def main():
     ap.add_argument("--engines", type=int, default=8, help="C4: engine handles / streams in flight per GPU")
     ap.add_argument("--sm-share", type=int, default=8, help="C4: every engine sizes its launches for 1/share of the SMs (gcr_set_sm_share)")
     ap.add_argument("--images", type=int, default=None, help="C4: images per GPU (default 256 / world)")
+    ap.add_argument("--sweep-engines", type=int, default=4, help="C5: engine handles / streams in flight")
+    ap.add_argument("--sweep-sm-share", type=int, default=4, help="C5: every engine sizes its launches for 1/share of the SMs")
     ap.add_argument("--hyp", type=int, default=None, help="override the configuration's total hypothesis count (diagnostics)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the bounded CPU baseline leg (diagnostics)")
     ap.add_argument("--no-secondary", action="store_true", help="skip the C2 secondary block (diagnostics)")
