@@ -103,7 +103,9 @@ int gcr_destroy(gcr_handle h);
  * reference's per-image entry point called in a loop, src/gcransac_python.cpp:256-406 -- with one engine per stream: a full-size engine's
  * kernels each fill the GPU, so streams only queue behind one another and an image costs the SUM of its kernels' latencies; `share`
  * engines of a 1/share size run their launch sequences side by side (256 images of 5 000 features x 100 000 hypotheses: 19.1 -> 11.4 ms
- * with 8 engines of share 8).  Results do not depend on the share.  Call between runs; it stays until changed. */
+ * with 8 engines of share 8).  Results do not depend on the share.  Call between runs; it stays until changed.  Keep the engines in flight
+ * at or below `share`: the last kernel of a run is a cooperative launch (two CTAs per SM of the engine's share), and the cooperative grids
+ * of all runs in flight should fit the device together. */
 int gcr_set_sm_share(gcr_handle h, int share);
 const char* gcr_last_error(gcr_handle h);
 
