@@ -1150,7 +1150,7 @@ int gcr_run(gcr_handle h, int64_t n_hyp, uint64_t seed, uint64_t first_hyp, cons
         if (resident)
         {
             cfg.gridDim = dim3(h->n_sm);
-            cfg.blockDim = dim3(kResidentThreads);
+            cfg.blockDim = dim3(mode == 0 ? kResThreads<0> : kResidentThreads);
             cfg.dynamicSmemBytes = rsmem;
             GCR_CUDA(cudaLaunchKernelEx(&cfg, mode == 2 ? k_score_resident<2> : (mode == 1 ? k_score_resident<1> : k_score_resident<0>), B, T,
                                         h->resident_cost_o, h->resident_cost_p));

@@ -834,6 +834,17 @@ __global__ void __launch_bounds__(kScoreThreads, kRingMinB<MODE>) k_score_fast(c
 // 10 us drain at C2 because its costliest items last 30 of the kernel's 40 us).  Arithmetic, verdicts, worklist and
 // mask emission are score_chunk's, i.e. bit-identical to the ring kernel.
 constexpr int kResidentThreads = 1024;
+// The winner-only form keeps two hypotheses per thread here too (every LDS.128 of the feature planes serves both, as in the ring kernel),
+// in a CTA of fewer threads so that the registers are there: GCR_RES_HB hypotheses per thread, GCR_RES_THREADS threads.  Same-box A/B of
+// (1, 1024) | (2, 768) | (2, 640) | (2, 512): C2 kernel 27.6 | 27.6 | 25.7 | 25.6 us, C4's image 50.2 us all four.
+#ifndef GCR_RES_HB
+#define GCR_RES_HB 2
+#endif
+#ifndef GCR_RES_THREADS
+#define GCR_RES_THREADS 512
+#endif
+template <int MODE> constexpr int kResHB = MODE == 0 ? GCR_RES_HB : 1;
+template <int MODE> constexpr int kResThreads = (MODE == 0 && GCR_RES_HB > 1) ? GCR_RES_THREADS : kResidentThreads;
 constexpr int kResidentMaxChunks = 75; // 75 x 3 KB + barriers <= 227 KB
 constexpr int kCostS = 10, kMinPieceCost = 40;
 
@@ -857,7 +868,7 @@ __device__ __forceinline__ void resident_task(const Buffers& B, const Thresholds
     constexpr int NF = PRECISE ? kChunk / 2 : kChunk; // features per chunk
     constexpr int G = PRECISE ? 2 : 4;
     constexpr int BPC = NF / 32, GPB = 32 / G;         // blocks per chunk, groups per block
-    constexpr int HB = 1; // (one hypothesis per thread: 1024-thread CTAs leave 64 registers)
+    constexpr int HB = kResHB<MODE>; // (the reporting forms: one hypothesis per thread, 1024-thread CTAs leave 64 registers)
     HypRegs H[HB];
     load_hyps<PRECISE, true, HB>(B, H, tile * 32 * HB, 32, threadIdx.x & 31, n_list, PRECISE);
     const int s1 = min(b1, P.nbs);
@@ -868,7 +879,7 @@ __device__ __forceinline__ void resident_task(const Buffers& B, const Thresholds
         {
             const int chunk = b / BPC, be = min(s1, (chunk + 1) * BPC);
             if constexpr (MODE == 0)
-                score_chunk_w<PRECISE, 0, true>(T, sm_s + chunk * kChunkFloats, H, (b - chunk * BPC) * GPB, (be - chunk * BPC) * GPB);
+                score_chunk_w<PRECISE, 0, true, HB>(T, sm_s + chunk * kChunkFloats, H, (b - chunk * BPC) * GPB, (be - chunk * BPC) * GPB);
             else
                 score_chunk<MODE == 2, PRECISE, 0, true>(B, T, sm_s + chunk * kChunkFloats, chunk * NF, H, (b - chunk * BPC) * GPB,
                                                          (be - chunk * BPC) * GPB);
@@ -883,7 +894,7 @@ __device__ __forceinline__ void resident_task(const Buffers& B, const Thresholds
         {
             const int chunk = b / BPC, be = min(o1, (chunk + 1) * BPC);
             if constexpr (MODE == 0)
-                score_chunk_w<PRECISE, 1, true>(T, sm_o + chunk * kChunkFloats, H, (b - chunk * BPC) * GPB, (be - chunk * BPC) * GPB);
+                score_chunk_w<PRECISE, 1, true, HB>(T, sm_o + chunk * kChunkFloats, H, (b - chunk * BPC) * GPB, (be - chunk * BPC) * GPB);
             else
                 score_chunk<MODE == 2, PRECISE, 1, true>(B, T, sm_o + chunk * kChunkFloats, chunk * NF, H, (b - chunk * BPC) * GPB,
                                                          (be - chunk * BPC) * GPB);
@@ -894,7 +905,7 @@ __device__ __forceinline__ void resident_task(const Buffers& B, const Thresholds
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(kResidentThreads, 1) k_score_resident(const __grid_constant__ Buffers B,
+__global__ void __launch_bounds__(kResThreads<MODE>, 1) k_score_resident(const __grid_constant__ Buffers B,
                                                                         const __grid_constant__ Thresholds T,
                                                                         const int cost_o, const int cost_p)
 {
@@ -931,11 +942,12 @@ __global__ void __launch_bounds__(kResidentThreads, 1) k_score_resident(const __
     P.nbo = (B.no + 31) / 32;
     P.cost_o = cost_o;
     P.total = kCostS * P.nbs + cost_o * P.nbo;
-    const int tiles_a = (n_fast + 31) / 32, tiles_b = (n_sens + 31) / 32;
+    constexpr int kTile = 32 * kResHB<MODE>; // hypotheses of a warp's tile
+    const int tiles_a = (n_fast + kTile - 1) / kTile, tiles_b = (n_sens + kTile - 1) / kTile;
     // the line of all tiles in units of 1/10 cost: a precise tile is cost_p * total long, an FP32 tile 10 * total
     const long long len_b = static_cast<long long>(cost_p) * P.total, len_a = 10ll * P.total;
     const long long end_b = len_b * tiles_b, end_all = end_b + len_a * tiles_a;
-    const int n_warps = static_cast<int>(gridDim.x) * (kResidentThreads / 32);
+    const int n_warps = static_cast<int>(gridDim.x) * (kResThreads<MODE> / 32);
     const long long piece = max((end_all + n_warps - 1) / n_warps, 10ll * kMinPieceCost);
     // consecutive pieces go to different SMs
     const int w = static_cast<int>(threadIdx.x >> 5) * static_cast<int>(gridDim.x) + static_cast<int>(blockIdx.x);
